@@ -1,0 +1,526 @@
+// rnnt_oracle.cpp — CPU ORACLE (TEST INFRASTRUCTURE, NOT PRODUCT CODE).
+//
+// A portable scalar C++ restatement of the arithmetic of the reference's int8/bf16 RNN-T hot path
+// (dbyoung18/rnnt-inference @ c9175d7).  Only tests/, __graft_entry__.smoke() and bench.py's
+// cpu_baseline / --impl reference legs may load this library; the product (rnnt_inference_b200)
+// never does.  Every function cites the reference file:line it follows.
+//
+// Parity status:
+//   * int8 GEMMs: exact int32, same as AMX tdpbssd (pinned: integer arithmetic).
+//   * fp16 gate math (encoder): every AVX512-FP16 op restated as one correctly-rounded binary16 op;
+//     VRCPPH restated by the table include/rnnt_rcp_ph_lut.h dumped from real hardware.  Pinned
+//     against vectors produced by real AVX512-FP16 hardware (tests/golden/postop_fp16_hw.npz,
+//     generator oracle/hwprobe/gen_postop_golden.cpp).
+//   * bf16 GEMMs (prediction/joint): AMX TDPBF16PS is NOT a sequence of IEEE FMAs (measured:
+//     oracle/hwprobe/amx_bf16_order.cpp); its internal accumulation is unspecified, so this oracle
+//     DEFINES the order as fp32 FMA sequential in k.  Parity with the real AMX build is therefore
+//     "unpinned" for bf16 accumulators; pinned only through exactly-representable KAT data.
+//   * fp32 gate math (prediction net): VRCP14PS replaced by RN(1/x) (declared deviation).
+//
+// Layout conventions: all weights are plain row-major [out_features][in_features] (PyTorch order),
+// activations time-major {T,N,C}.  bf16/fp16 travel as uint16_t bit patterns.
+#include <cstdint>
+#include <cstring>
+#include <cmath>
+#include <vector>
+#include <algorithm>
+#include "../include/rnnt_rcp_ph_lut.h"
+
+#define ORC_API extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+// ----------------------------------------------------------------------------------------------
+// binary16 / bfloat16 scalar arithmetic, one IEEE rounding per operation
+// ----------------------------------------------------------------------------------------------
+inline uint64_t dbits(double d) { uint64_t u; std::memcpy(&u, &d, 8); return u; }
+inline double bitsd(uint64_t u) { double d; std::memcpy(&d, &u, 8); return d; }
+inline uint32_t fbits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+inline float bitsf(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+
+inline float h2f(uint16_t h) {
+  uint32_t sign = (uint32_t)(h & 0x8000u) << 16;
+  uint32_t e = (h >> 10) & 31u, m = h & 1023u;
+  if (e == 0) {
+    if (m == 0) return bitsf(sign);
+    // subnormal: m * 2^-24
+    float v = (float)m * 5.9604644775390625e-08f;
+    return (h & 0x8000u) ? -v : v;
+  }
+  if (e == 31) return bitsf(sign | 0x7f800000u | (m << 13));
+  return bitsf(sign | ((e + 112u) << 23) | (m << 13));
+}
+
+// double -> binary16, round-to-nearest-even, correct for every double (incl. subnormal results).
+inline uint16_t d2h(double d) {
+  uint64_t u = dbits(d);
+  uint16_t sign = (uint16_t)((u >> 48) & 0x8000u);
+  int exp = (int)((u >> 52) & 0x7ff);
+  uint64_t mant = u & ((1ull << 52) - 1);
+  if (exp == 0x7ff) return (uint16_t)(sign | 0x7c00u | (mant ? 0x200u : 0u));
+  if (exp == 0) return sign;  // double subnormal: far below half of the smallest binary16 subnormal
+  int e = exp - 1023;
+  if (e > 15) return (uint16_t)(sign | 0x7c00u);
+  uint64_t full = (1ull << 52) | mant;
+  int ts;            // bits to drop
+  uint32_t base;     // exponent field contribution
+  if (e >= -14) { ts = 42; base = (uint32_t)(e + 15) << 10; full = mant; }
+  else { ts = 42 + (-14 - e); base = 0; }
+  if (ts >= 64) return sign;
+  uint64_t keep = full >> ts;
+  uint64_t rest = full & ((1ull << ts) - 1);
+  uint64_t half = 1ull << (ts - 1);
+  if (rest > half || (rest == half && (keep & 1))) keep++;
+  uint32_t r = base + (uint32_t)keep;  // mantissa carry bumps the exponent
+  if (r >= 0x7c00u) r = 0x7c00u;
+  return (uint16_t)(sign | r);
+}
+
+// float -> binary16 RNE (VCVTPS2PH imm=0, tpps/el_common_intrin.hpp:468-477)
+inline uint16_t f2h(float f) { return d2h((double)f); }
+
+inline uint16_t h_mul(uint16_t a, uint16_t b) { return d2h((double)h2f(a) * (double)h2f(b)); }  // product exact in double
+inline uint16_t h_add(uint16_t a, uint16_t b) { return d2h((double)h2f(a) + (double)h2f(b)); }  // sum exact in double
+
+// fused multiply-add with a single binary16 rounding.  a*b is exact in double; the sum may not be,
+// so it is rounded to odd (error-free TwoSum) before the final rounding: 53 >= 11 + 2 bits.
+inline uint16_t h_fma(uint16_t a, uint16_t b, uint16_t c) {
+  double p = (double)h2f(a) * (double)h2f(b);
+  double cc = (double)h2f(c);
+  double s = p + cc;
+  if (std::isfinite(s)) {
+    double bb = s - p;
+    double err = (p - (s - bb)) + (cc - bb);
+    if (err != 0.0) {
+      uint64_t u = dbits(s);
+      // truncated (toward zero) neighbour of the exact value
+      bool same_dir = (err > 0.0) == (s > 0.0);
+      if (s == 0.0) { s = err; u = dbits(s); }
+      else if (!same_dir) u -= 1;
+      u |= 1ull;
+      s = bitsd(u);
+    }
+  }
+  return d2h(s);
+}
+
+const uint16_t kRcpLut[1024] = {RNNT_RCP_PH_LUT_VALUES};
+
+// VRCPPH for normal inputs with normal results (the only ones reachable: denominators in
+// [495, 13000], el_common_intrin.hpp:104-152).
+inline uint16_t h_rcp(uint16_t x) {
+  uint16_t sign = x & 0x8000u;
+  int e = (x >> 10) & 31;
+  int m = x & 1023;
+  if (e == 31) return m ? (uint16_t)(x | 0x200u) : sign;   // NaN -> NaN, inf -> 0
+  if (e == 0) return (uint16_t)(sign | 0x7c00u);            // zero / subnormal -> inf (not reachable)
+  int r = (int)kRcpLut[m] + ((15 - e) << 10);
+  if (r <= 0x03ff) r = 0;                                   // would be subnormal (not reachable)
+  return (uint16_t)(sign | (uint16_t)r);
+}
+
+inline bool h_gt(uint16_t a, uint16_t b) { return h2f(a) > h2f(b); }   // ordered compare; NaN -> false
+inline bool h_lt(uint16_t a, uint16_t b) { return h2f(a) < h2f(b); }
+
+const uint16_t H_495 = 0x5fbc, H_60 = 0x5380, H_225 = 0x5b08, H_10 = 0x4900, H_ONE = 0x3c00,
+               H_NEG_ONE = 0xbc00, H_HALF = 0x3800;
+inline uint16_t H_1_21() { static const uint16_t v = f2h((float)(1.0 / 21.0)); return v; }
+inline uint16_t H_4_97() { static const uint16_t v = f2h(4.97f); return v; }
+inline uint16_t H_N4_97() { static const uint16_t v = f2h(-4.97f); return v; }
+
+// _mm512_tanh_ph, tpps/el_common_intrin.hpp:95-123
+inline uint16_t tanh_ph(uint16_t x) {
+  uint16_t x2 = h_mul(x, x);
+  uint16_t t1n = h_add(x2, H_60);
+  uint16_t t2n = h_fma(t1n, x2, H_495);
+  uint16_t nom = h_mul(t2n, x);
+  uint16_t t1d = h_fma(H_1_21(), x2, H_10);
+  uint16_t t2d = h_fma(t1d, x2, H_225);
+  uint16_t den = h_fma(t2d, x2, H_495);
+  uint16_t r = h_mul(nom, h_rcp(den));
+  if (h_gt(x, H_4_97())) r = H_ONE;
+  if (h_lt(x, H_N4_97())) r = H_NEG_ONE;
+  return r;
+}
+
+// _mm512_sigmoid_ph, tpps/el_common_intrin.hpp:126-152
+inline uint16_t sigmoid_ph(uint16_t x) {
+  uint16_t xh = h_mul(H_HALF, x);
+  uint16_t x2 = h_mul(xh, xh);
+  uint16_t t1n = h_add(x2, H_60);
+  uint16_t t2n = h_fma(t1n, x2, H_495);
+  uint16_t nom = h_mul(t2n, xh);
+  uint16_t t1d = h_fma(H_1_21(), x2, H_10);
+  uint16_t t2d = h_fma(t1d, x2, H_225);
+  uint16_t den = h_fma(t2d, x2, H_495);
+  uint16_t r = h_mul(nom, h_rcp(den));
+  if (h_gt(xh, H_4_97())) r = H_ONE;
+  if (h_lt(xh, H_N4_97())) r = H_NEG_ONE;
+  r = h_add(r, H_ONE);
+  return h_mul(r, H_HALF);
+}
+
+// _mm512_scale_min128max_i8_ph, tpps/el_common_intrin.hpp:295-303: fp16 multiply by the fp16-rounded
+// scale, VRNDSCALEPH to nearest-even integer, min(127) then max(-128), convert.
+inline int8_t quant_ph(uint16_t h, uint16_t scale_h) {
+  float v = h2f(h_mul(h, scale_h));       // binary16 value, exact in float
+  float r = std::nearbyintf(v);            // default rounding mode = nearest-even
+  r = std::fmin(r, 127.f);
+  r = std::fmax(r, -128.f);
+  return (int8_t)(int)r;
+}
+
+inline float bf2f(uint16_t b) { return bitsf((uint32_t)b << 16); }
+// VCVTNE2PS2BF16 (round-to-nearest-even).  Hardware additionally flushes fp32 denormals; not reachable.
+inline uint16_t f2bf(float f) {
+  uint32_t u = fbits(f);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40u);
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+// _mm512_scale_min128max_i8_ps, tpps/el_common_intrin.hpp:275-283 (+ quant_tpp.cpp:6-17)
+inline int8_t quant_ps(float x, float scale) {
+  float m = std::nearbyintf(x * scale);
+  m = std::fmin(m, 127.f);
+  m = std::fmax(m, -128.f);
+  return (int8_t)(int)m;
+}
+
+// _mm512_tanh_ps / _mm512_sigmoid_ps, tpps/el_common_intrin.hpp:66-93,154-185, with RN(1/x) in place
+// of VRCP14PS (declared deviation).  fmaf = one rounding, like VFMADD.
+inline float tanh_ps(float x) {
+  const float c0 = 4826.25f, c1 = 618.75f, c2 = 13.5f, c3 = (float)(1.0 / 28.0), c1d = 2227.5f, c2d = 112.5f;
+  float x2 = x * x;
+  float t1n = std::fmaf(c3, x2, c2);
+  float t2n = std::fmaf(t1n, x2, c1);
+  float t3n = std::fmaf(t2n, x2, c0);
+  float nom = t3n * x;
+  float t1d = x2 + c2d;
+  float t2d = std::fmaf(t1d, x2, c1d);
+  float den = std::fmaf(t2d, x2, c0);
+  float r = nom * (1.0f / den);
+  if (x > 4.97f) r = 1.0f;
+  if (x < -4.97f) r = -1.0f;
+  return r;
+}
+inline float sigmoid_ps(float x) {
+  const float c0 = 4826.25f, c1 = 618.75f, c2 = 13.5f, c3 = (float)(1.0 / 28.0), c1d = 2227.5f, c2d = 112.5f;
+  float xh = 0.5f * x;
+  float x2 = xh * xh;
+  float t1n = std::fmaf(c3, x2, c2);
+  float t2n = std::fmaf(t1n, x2, c1);
+  float t3n = std::fmaf(t2n, x2, c0);
+  float nom = t3n * xh;
+  float t1d = x2 + c2d;
+  float t2d = std::fmaf(t1d, x2, c1d);
+  float den = std::fmaf(t2d, x2, c0);
+  float r = nom * (1.0f / den);
+  if (xh > 4.97f) r = 1.0f;
+  if (xh < -4.97f) r = -1.0f;
+  r = r + 1.0f;
+  return r * 0.5f;
+}
+
+}  // namespace
+
+// ================================================================================================
+// Operator-level restatements (C ABI, host pointers)
+// ================================================================================================
+
+// quant_tpp::quant_ps_epi8 (tpps/quant_tpp.cpp:6-17) called from lstm_amx_int8 (lstm_amx.cpp:35-43),
+// followed by the zero pad of K to a multiple of 64 (lstm_amx.cpp:48-50).  in: [rows][k_in] fp32,
+// out: [rows][k_out] int8 with columns k_in..k_out-1 = 0.
+ORC_API void orc_quantize_pad(const float* in, int8_t* out, float scale, int64_t rows, int k_in, int k_out) {
+#pragma omp parallel for
+  for (int64_t r = 0; r < rows; ++r) {
+    for (int k = 0; k < k_in; ++k) out[r * k_out + k] = quant_ps(in[r * k_in + k], scale);
+    for (int k = k_in; k < k_out; ++k) out[r * k_out + k] = 0;
+  }
+}
+
+// i8o32b0: C_int32[M][N] = A[M][K] . W[N][K]^T, exact (tile_product_tpp.hpp:288-306,535-561;
+// call site lstm_amx.cpp:96-113).
+ORC_API void orc_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K) {
+#pragma omp parallel for
+  for (int64_t m = 0; m < M; ++m) {
+    const int8_t* a = A + m * K;
+    for (int n = 0; n < N; ++n) {
+      const int8_t* w = W + (int64_t)n * K;
+      int32_t acc = 0;
+      for (int k = 0; k < K; ++k) acc += (int32_t)a[k] * (int32_t)w[k];
+      C[m * N + n] = acc;
+    }
+  }
+}
+
+// lstm_postop_tpp::ref for one batch row (tpps/lstm_postop_tpp.cpp:12-98).  gates: 4*H fp32 in
+// order i,f,g,o.  c: H binary16, updated in place.  Writes hq (always, in_scale) and either
+// yq (out_scale) or ybf (last layer).
+static void postop_row_fp16(const float* gates, uint16_t* c, int8_t* hq, int8_t* yq, uint16_t* ybf,
+                            uint16_t in_scale_h, uint16_t out_scale_h, int H, bool last) {
+  for (int j = 0; j < H; ++j) {
+    uint16_t it = sigmoid_ph(f2h(gates[j]));
+    uint16_t ft = sigmoid_ph(f2h(gates[H + j]));
+    uint16_t gt = tanh_ph(f2h(gates[2 * H + j]));
+    uint16_t ot = sigmoid_ph(f2h(gates[3 * H + j]));
+    uint16_t a = h_mul(ft, c[j]);
+    uint16_t cn = h_fma(it, gt, a);
+    c[j] = cn;
+    uint16_t ht = h_mul(ot, tanh_ph(cn));
+    if (last) ybf[j] = f2bf(h2f(ht));
+    else yq[j] = quant_ph(ht, out_scale_h);
+    hq[j] = quant_ph(ht, in_scale_h);
+  }
+}
+
+// Exposed for the known-answer tests (reference op lstm_postop, lstm_postop.cpp; schema init.cpp:126-128).
+ORC_API void orc_lstm_postop_fp16(const float* gates, uint16_t* c, int8_t* hq, int8_t* yq, uint16_t* ybf,
+                                  float in_scale, float out_scale, int N, int H, int last) {
+  uint16_t is = f2h(in_scale), os = f2h(out_scale);
+#pragma omp parallel for
+  for (int n = 0; n < N; ++n)
+    postop_row_fp16(gates + (int64_t)n * 4 * H, c + (int64_t)n * H, hq + (int64_t)n * H,
+                    yq ? yq + (int64_t)n * H : nullptr, ybf ? ybf + (int64_t)n * H : nullptr, is, os, H, last != 0);
+}
+
+// Element-wise entry points for the hardware-golden test of the activations.
+ORC_API void orc_sigmoid_fp16(const float* in, uint16_t* out, int64_t n) { for (int64_t i = 0; i < n; ++i) out[i] = sigmoid_ph(f2h(in[i])); }
+ORC_API void orc_tanh_fp16(const float* in, uint16_t* out, int64_t n) { for (int64_t i = 0; i < n; ++i) out[i] = tanh_ph(f2h(in[i])); }
+ORC_API void orc_tanh_fp16_h(const uint16_t* in, uint16_t* out, int64_t n) { for (int64_t i = 0; i < n; ++i) out[i] = tanh_ph(in[i]); }
+ORC_API void orc_rcp_fp16(const uint16_t* in, uint16_t* out, int64_t n) { for (int64_t i = 0; i < n; ++i) out[i] = h_rcp(in[i]); }
+ORC_API void orc_fma_fp16(const uint16_t* a, const uint16_t* b, const uint16_t* c, uint16_t* out, int64_t n) { for (int64_t i = 0; i < n; ++i) out[i] = h_fma(a[i], b[i], c[i]); }
+ORC_API void orc_quant_fp16(const uint16_t* in, float scale, int8_t* out, int64_t n) { uint16_t s = f2h(scale); for (int64_t i = 0; i < n; ++i) out[i] = quant_ph(in[i], s); }
+ORC_API void orc_sigmoid_fp32(const float* in, float* out, int64_t n) { for (int64_t i = 0; i < n; ++i) out[i] = sigmoid_ps(in[i]); }
+ORC_API void orc_tanh_fp32(const float* in, float* out, int64_t n) { for (int64_t i = 0; i < n; ++i) out[i] = tanh_ps(in[i]); }
+
+// lstm_layer_amx_int8 (lstm_amx.cpp:59-158).
+//   x   [T][N][K] int8 (K already padded), w_ih [4H][K], w_hh [4H][H] int8 row-major,
+//   bias [4H] fp32 = (b_ih+b_hh)*in_scale*w_scale (quant_lstm.py:205-208), hx [N][H] int8 and
+//   cx [N][H] binary16 updated IN PLACE (lstm_amx.cpp:153-157).
+//   Phase A: G[t] = x_t.W_ih^T int32 (i8o32b0).  Phase B per t:
+//   gates = (float(h.W_hh^T + G[t]) + bias) * rb_scale  (dequant_float_out_accum,
+//   tile_product_tpp.hpp:308-345: int32 add first, then cvt, add bias, multiply), then postop.
+//   y: int8 [T][N][H] (skip_quant_y == 0) or bf16 [T][N][H].
+//   g_dump (optional): [T][N][4H] fp32 gates after dequant, for kernel debugging.
+ORC_API void orc_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* w_ih, const int8_t* w_hh,
+                               const float* bias, float rb_scale, float in_scale, float out_scale, int skip_quant_y,
+                               void* y, int T, int N, int K, int H, float* g_dump) {
+  const int G4 = 4 * H;
+  std::vector<int32_t> G((size_t)T * N * G4);
+  orc_gemm_i8_i32(x, w_ih, G.data(), (int64_t)T * N, G4, K);
+  uint16_t is = f2h(in_scale), os = f2h(out_scale);
+  std::vector<float> gates((size_t)N * G4);
+  std::vector<int8_t> hnew((size_t)N * H);
+  for (int t = 0; t < T; ++t) {
+#pragma omp parallel for
+    for (int n = 0; n < N; ++n) {
+      const int8_t* h = hx + (int64_t)n * H;
+      const int32_t* g = G.data() + ((size_t)t * N + n) * G4;
+      float* go = gates.data() + (size_t)n * G4;
+      for (int o = 0; o < G4; ++o) {
+        const int8_t* w = w_hh + (int64_t)o * H;
+        int32_t acc = 0;
+        for (int k = 0; k < H; ++k) acc += (int32_t)h[k] * (int32_t)w[k];
+        float v = (float)(acc + g[o]) + bias[o];
+        go[o] = v * rb_scale;
+      }
+      if (g_dump) std::memcpy(g_dump + ((size_t)t * N + n) * G4, go, sizeof(float) * G4);
+      int8_t* yq = skip_quant_y ? nullptr : (int8_t*)y + ((size_t)t * N + n) * H;
+      uint16_t* yb = skip_quant_y ? (uint16_t*)y + ((size_t)t * N + n) * H : nullptr;
+      postop_row_fp16(go, cx + (int64_t)n * H, hnew.data() + (size_t)n * H, yq, yb, is, os, H, skip_quant_y != 0);
+    }
+    std::memcpy(hx, hnew.data(), (size_t)N * H);
+  }
+}
+
+// stack_time (stack_time.cpp:27-59): int8 {T,N,C} -> {ceil(T/f),N,C*f}, zero from lens[n] on.
+ORC_API void orc_stack_time(const int8_t* in, const int32_t* lens, int factor, int8_t* out, int T, int N, int C) {
+  int T2 = (T + factor - 1) / factor;
+  for (int n = 0; n < N; ++n) {
+    int len = std::min(std::max(lens[n], 0), T);
+    for (int t = 0; t < len; ++t)
+      std::memcpy(out + ((size_t)(t / factor) * N + n) * C * factor + (size_t)(t % factor) * C, in + ((size_t)t * N + n) * C, C);
+    for (int t = len; t < T2 * factor; ++t)
+      std::memset(out + ((size_t)(t / factor) * N + n) * C * factor + (size_t)(t % factor) * C, 0, C);
+  }
+}
+
+// ================================================================================================
+// bf16 prediction / joint operators
+// ================================================================================================
+namespace {
+// fp32 dot of bf16 row vectors, FMA sequential in k from acc = 0 (the order this oracle defines for
+// _compute_impl_bf16, tile_product_tpp.hpp:563-581; AMX's own order is unspecified, see header).
+inline float dot_bf16(const uint16_t* a, const uint16_t* w, int K) {
+  float acc = 0.f;
+  for (int k = 0; k < K; ++k) acc = std::fmaf(bf2f(a[k]), bf2f(w[k]), acc);
+  return acc;
+}
+
+// lstm_postop_tpp::ref_bf16 for one row (tpps/lstm_postop_tpp.cpp:100-163)
+inline void postop_row_f32(const float* gates, const float* c_in, float* c_out, uint16_t* h_out, int H) {
+  for (int j = 0; j < H; ++j) {
+    float it = sigmoid_ps(gates[j]);
+    float ft = sigmoid_ps(gates[H + j]);
+    float gt = tanh_ps(gates[2 * H + j]);
+    float ot = sigmoid_ps(gates[3 * H + j]);
+    float a = ft * c_in[j];
+    float cn = std::fmaf(it, gt, a);
+    c_out[j] = cn;
+    float ht = ot * tanh_ps(cn);
+    h_out[j] = f2bf(ht);
+  }
+}
+}  // namespace
+
+// lstm_layer_amx_bf16 with seq_len == 1 (lstm_amx.cpp:187-264): G = x.W_ih^T (i16o32b0), then
+// G = (h.W_hh^T + G) + bias (float_out_accum, tile_product_tpp.hpp:387-408, bias = b_ih+b_hh,
+// modeling_rnnt.py:170-172), postop ref_bf16.  Returns NEW hy/cy (inputs untouched).
+ORC_API void orc_lstm_cell_bf16(const uint16_t* x, const uint16_t* h, const float* c, const uint16_t* w_ih,
+                                const uint16_t* w_hh, const float* bias, uint16_t* hy, float* cy, int N, int K, int H) {
+  const int G4 = 4 * H;
+#pragma omp parallel for
+  for (int n = 0; n < N; ++n) {
+    std::vector<float> g(G4);
+    for (int o = 0; o < G4; ++o) {
+      float gi = dot_bf16(x + (int64_t)n * K, w_ih + (int64_t)o * K, K);
+      float gh = dot_bf16(h + (int64_t)n * H, w_hh + (int64_t)o * H, H);
+      g[o] = (gh + gi) + bias[o];
+    }
+    postop_row_f32(g.data(), c + (int64_t)n * H, cy + (int64_t)n * H, hy + (int64_t)n * H, H);
+  }
+}
+
+// i16o16b0 (amx_linear.cpp:137-150; bf16_out_no_bias tile_product_tpp.hpp:410-424): y = bf16(x.W^T)
+ORC_API void orc_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t N, int K, int O) {
+#pragma omp parallel for
+  for (int64_t n = 0; n < N; ++n)
+    for (int o = 0; o < O; ++o) y[n * O + o] = f2bf(dot_bf16(x + n * K, w + (int64_t)o * K, K));
+}
+
+// amx_linear_bf16_accum_relu (amx_linear.cpp:119-170): y1 = bf16(x0.W0^T) rounded in memory, then
+// y = bf16(max((x1.W1^T + float(y1)) + bias, 0)) (bf16_out_accum_relu, tile_product_tpp.hpp:426-449).
+// If y1_pre != NULL it is used instead of computing x0.W0^T (hoisted transcription half).
+ORC_API void orc_linear_bf16_accum_relu(const uint16_t* x0, const uint16_t* w0, const uint16_t* y1_pre, const uint16_t* x1,
+                                        const uint16_t* w1, const float* bias, uint16_t* y, int N, int K0, int K1, int O) {
+#pragma omp parallel for
+  for (int n = 0; n < N; ++n)
+    for (int o = 0; o < O; ++o) {
+      uint16_t y1 = y1_pre ? y1_pre[(int64_t)n * O + o] : f2bf(dot_bf16(x0 + (int64_t)n * K0, w0 + (int64_t)o * K0, K0));
+      float acc = dot_bf16(x1 + (int64_t)n * K1, w1 + (int64_t)o * K1, K1);
+      float v = (acc + bf2f(y1)) + bias[o];
+      y[(int64_t)n * O + o] = f2bf(std::fmax(v, 0.f));
+    }
+}
+
+// amx_linear_i16o32 (amx_linear.cpp:113-117; float_out tile_product_tpp.hpp:347-367): y = x.W^T + b
+ORC_API void orc_linear_bf16_f32(const uint16_t* x, const uint16_t* w, const float* bias, float* y, int N, int K, int O) {
+#pragma omp parallel for
+  for (int n = 0; n < N; ++n)
+    for (int o = 0; o < O; ++o) y[(int64_t)n * O + o] = dot_bf16(x + (int64_t)n * K, w + (int64_t)o * K, K) + bias[o];
+}
+
+// greedy_decode_update (greedy_decode_update.cpp:13-96 + tpps/greedy_decode_update_tpp.cpp:9-51),
+// kBlank = 28, kMaxSymbolsPerStep = 30.  All state updated in place; returns 1 iff every lane has
+// time_idx >= f_lens.  f: [T2][N][C] bf16, fi: [N][C] bf16, hidden P per prediction layer (2 layers).
+ORC_API int orc_greedy_update(const int64_t* symbols, int32_t* symbols_added, int32_t* res, int32_t* res_idx,
+                              const uint16_t* f, const int32_t* f_lens, int32_t* time_idx, uint16_t* fi, int32_t* pre_g,
+                              uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, const uint16_t* hg0,
+                              const uint16_t* hg1, const float* cg0, const float* cg1, int N, int L, int C, int P) {
+  int all_finished = 1;
+  for (int n = 0; n < N; ++n) {
+    int32_t sym = (int32_t)symbols[n];
+    bool upd_g = (sym != 28) && (symbols_added[n] != 30) && (f_lens[n] != 0);
+    if (upd_g) {
+      res_idx[n] += 1;
+      res[(int64_t)n * L + res_idx[n]] = sym;
+      symbols_added[n] += 1;
+      pre_g[n] = sym;
+      std::memcpy(pre_hg0 + (int64_t)n * P, hg0 + (int64_t)n * P, 2 * P);
+      std::memcpy(pre_hg1 + (int64_t)n * P, hg1 + (int64_t)n * P, 2 * P);
+      std::memcpy(pre_cg0 + (int64_t)n * P, cg0 + (int64_t)n * P, 4 * P);
+      std::memcpy(pre_cg1 + (int64_t)n * P, cg1 + (int64_t)n * P, 4 * P);
+    } else {
+      symbols_added[n] = 0;
+      time_idx[n] += 1;
+    }
+    bool finish = time_idx[n] >= f_lens[n];
+    if (!finish) {
+      std::memcpy(fi + (int64_t)n * C, f + ((int64_t)time_idx[n] * N + n) * C, 2 * C);
+      all_finished = 0;
+    }
+  }
+  return all_finished;
+}
+
+// ================================================================================================
+// GreedyDecoder.greedy_decode_quant main loop (models/decoder.py:188-211) over an already-encoded
+// batch: prediction (modeling_rnnt.py:183-205) -> joint (:259-289) -> argmax over 32 columns
+// (decoder.py:193) -> update.  Batch-lockstep like the reference, including its quirk that lanes
+// which finished keep being updated until the whole batch has finished
+// (greedy_decode_update_tpp.cpp:22-29 masks only f_lens == 0).
+//   embed [28][P] bf16; pred layer l: w_ih[l] [4P][P], w_hh[l] [4P][P] bf16, bias[l] [4P] = b_ih+b_hh;
+//   w_trans [J][C], w_pred [J][P] bf16, b1 [J] = b_trans + b_pred; w2 [32][J] bf16 rows 29..31 zero,
+//   b2 [32] with 29..31 zero (modeling_rnnt.py:223-250).
+//   y1_pre: optional [T2][N][J] bf16 = bf16(f.W_trans^T) (hoisted; bit-identical to computing it per
+//   iteration because the reference rounds it to bf16 in memory, amx_linear.cpp:137-150).
+//   State (in/out): res [N][L] int32, res_idx, symbols_added, time_idx, pre_g [N] int32,
+//   pre_hg{0,1} [N][P] bf16, pre_cg{0,1} [N][P] fp32.  f_lens are STACKED lengths.
+//   Symbols >= 28 fed back as pre_g (only the 3 zero pad columns can produce 29..31, a case in which
+//   the reference's embedding lookup raises) use a zero embedding like SOS.
+// Returns the number of loop iterations executed.
+ORC_API int orc_greedy_decode(const uint16_t* f, const int32_t* f_lens, int T2, int N, int C, int P, int J,
+                              const uint16_t* embed, const uint16_t* const* w_ih, const uint16_t* const* w_hh,
+                              const float* const* bias, const uint16_t* w_trans, const uint16_t* w_pred, const float* b1,
+                              const uint16_t* w2, const float* b2, const uint16_t* y1_pre, int32_t* res, int L,
+                              int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
+                              uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int max_iters) {
+  std::vector<uint16_t> fi((size_t)N * C), x((size_t)N * P), hg0((size_t)N * P), hg1((size_t)N * P), y((size_t)N * J);
+  std::vector<uint16_t> y1((size_t)N * J);
+  std::vector<int32_t> cur_t(N, 0);   // frame index whose features are in fi
+  std::vector<float> cg0((size_t)N * P), cg1((size_t)N * P), logits((size_t)N * 32);
+  std::vector<int64_t> symbols(N);
+  // fi = f[0] (decoder.py:186); lanes whose time_idx was carried in are re-pointed by the first update.
+  std::memcpy(fi.data(), f, (size_t)N * C * 2);
+  int iters = 0;
+  if (T2 <= 0) return 0;
+  while (iters < max_iters) {
+    ++iters;
+    for (int n = 0; n < N; ++n) {
+      int g = pre_g[n];
+      if (g < 0 || g > 27) std::memset(&x[(size_t)n * P], 0, 2 * P);
+      else std::memcpy(&x[(size_t)n * P], embed + (size_t)g * P, 2 * P);
+    }
+    orc_lstm_cell_bf16(x.data(), pre_hg0, pre_cg0, w_ih[0], w_hh[0], bias[0], hg0.data(), cg0.data(), N, P, P);
+    orc_lstm_cell_bf16(hg0.data(), pre_hg1, pre_cg1, w_ih[1], w_hh[1], bias[1], hg1.data(), cg1.data(), N, P, P);
+    if (y1_pre) {
+      for (int n = 0; n < N; ++n)
+        std::memcpy(&y1[(size_t)n * J], y1_pre + ((size_t)cur_t[n] * N + n) * J, 2 * J);
+      orc_linear_bf16_accum_relu(nullptr, nullptr, y1.data(), hg1.data(), w_pred, b1, y.data(), N, C, P, J);
+    } else {
+      orc_linear_bf16_accum_relu(fi.data(), w_trans, nullptr, hg1.data(), w_pred, b1, y.data(), N, C, P, J);
+    }
+    orc_linear_bf16_f32(y.data(), w2, b2, logits.data(), N, J, 32);
+    for (int n = 0; n < N; ++n) {
+      const float* l = &logits[(size_t)n * 32];
+      int best = 0;
+      for (int k = 1; k < 32; ++k) if (l[k] > l[best]) best = k;   // first maximum, like torch.argmax
+      symbols[n] = best;
+    }
+    int done = orc_greedy_update(symbols.data(), symbols_added, res, res_idx, f, f_lens, time_idx, fi.data(), pre_g,
+                                 pre_hg0, pre_hg1, pre_cg0, pre_cg1, hg0.data(), hg1.data(), cg0.data(), cg1.data(), N, L, C, P);
+    for (int n = 0; n < N; ++n) if (time_idx[n] < f_lens[n]) cur_t[n] = time_idx[n];
+    if (done) break;
+  }
+  return iters;
+}
+
+// self-check of the binary16 constants used above; returns 0 when consistent.
+ORC_API int orc_selfcheck() {
+  int bad = 0;
+  bad |= (f2h(495.f) != H_495) | (f2h(60.f) != H_60) << 1 | (f2h(225.f) != H_225) << 2 | (f2h(10.f) != H_10) << 3;
+  bad |= (f2h(1.f) != H_ONE) << 4 | (f2h(-1.f) != H_NEG_ONE) << 5 | (f2h(0.5f) != H_HALF) << 6;
+  bad |= (h_rcp(0x4000) != 0x3800) << 7;  // 1/2
+  return bad;
+}
