@@ -1,0 +1,108 @@
+/* rnnt_b200.h — C ABI of librnnt_b200.so: the sm_100a CUDA implementation of the MLPerf RNN-T int8
+ * inference hot path of dbyoung18/rnnt-inference.
+ *
+ * Every entry point replaces one operator of the reference's plugin library
+ * (TORCH_LIBRARY(intel_mlperf), mlperf_plugins/csrc/init.cpp:20-144) or one fused stretch of its
+ * Python driver; the reference interface each one stands in for is cited beside it.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - the caller owns every buffer, including workspaces; nothing is allocated or freed here;
+ *   - return value 0 = success, otherwise a negative code; rnnt_last_error() gives the message
+ *     (thread-local).  No exception crosses this boundary (the reference throws std::runtime_error,
+ *     e.g. tpps/i_linear_tpp.cpp:23,104,109, stack_time.cpp:32 — the Python wrapper re-raises
+ *     RuntimeError from the code);
+ *   - weights are plain row-major [out_features][in_features] (torch layout); the x86 VNNI tiling
+ *     of models/quant_modules.py:177-208 is an AMX detail and is not part of this ABI;
+ *   - binary16 / bfloat16 buffers are typed uint16_t.
+ */
+#ifndef RNNT_B200_H_
+#define RNNT_B200_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RNNT_OK 0
+#define RNNT_ERR_INVALID (-1)   /* bad shape / alignment / null pointer                 */
+#define RNNT_ERR_CUDA (-2)      /* a CUDA runtime/driver call failed                    */
+#define RNNT_ERR_DEVICE (-3)    /* device-side watchdog or protocol error (see message) */
+
+const char* rnnt_last_error(void);
+/* library/ABI version, and the SM count / arch the library sees (-1 without a usable GPU) */
+int rnnt_abi_version(void);
+int rnnt_device_sm_count(void);
+/* Kernels run asynchronously on `stream`; their device-side watchdogs (a protocol error ends the kernel
+ * instead of hanging the GPU) record a code in a 4-byte status word owned by the library.  This call
+ * synchronises `stream`, returns RNNT_ERR_DEVICE if a code was recorded, and clears it. */
+int rnnt_check_device_status(void* stream);
+
+/* quant_tpp::quant_ps_epi8 + K zero-pad (mlperf_plugins/csrc/lstm_amx.cpp:35-50, tpps/quant_tpp.cpp:6-17)
+ * in [rows][k_in] fp32 -> out [rows][k_out] int8, out[:,k_in:] = 0.  q = clamp(rne(x*scale),-128,127) */
+int rnnt_quantize_pad_f32_i8(const float* in, int8_t* out, float scale, int64_t rows, int k_in, int k_out,
+                             void* stream);
+
+/* i8o32b0 input projection over all timesteps (lstm_amx.cpp:96-113; tile_product_tpp.hpp:288-306):
+ * C[M][N] int32 = A[M][K] int8 . W[N][K]^T int8, exact.  tcgen05 kind::i8, TMEM accumulators, TMA in/out.
+ * Requirements: K % 16 == 0, N % 64 == 0, pointers 16-byte aligned. */
+int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream);
+/* Same contract on CUDA cores (dp4a), M <= 65535.  TEST HELPER: lets the GPU tests cross-check the tcgen05
+ * kernel at sizes the CPU oracle cannot reach.  Never called by the product path. */
+int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream);
+
+/* Phase B of lstm_layer_amx_int8 (lstm_amx.cpp:122-152): for t in [0,T):
+ *   gates = (float(h.W_hh^T + G[t]) + bias) * rb_scale ; lstm_postop_tpp::ref (tpps/lstm_postop_tpp.cpp:12-98)
+ * as ONE persistent kernel.  G [T][N][4H] int32 (from rnnt_gemm_i8_i32), w_hh [4H][H], bias [4H] fp32,
+ * hx [N][H] int8 and cx [N][H] binary16 updated IN PLACE, y [T][N][H] int8 (skip_quant_y=0) or bf16.
+ * H must be 1024.
+ * workspace: rnnt_lstm_recurrent_workspace_bytes(N) bytes, 256-byte aligned, contents don't care. */
+int64_t rnnt_lstm_recurrent_workspace_bytes(int N);
+int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                           float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                           void* workspace, void* stream);
+
+/* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.
+ * x [T][N][K] int8 (K % 16 == 0).  g_ws: T*N*4H int32 scratch for the projection. */
+int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* w_ih, const int8_t* w_hh,
+                       const float* bias, float rb_scale, float in_scale, float out_scale, int skip_quant_y, void* y,
+                       int T, int N, int K, int H, int32_t* g_ws, void* workspace, void* stream);
+
+/* stack_time (mlperf_plugins/csrc/stack_time.cpp:27-59; schema init.cpp:96-98), int8 only:
+ * in {T,N,C} -> out {ceil(T/factor),N,C*factor}, zeros from lens[n] on. */
+int rnnt_stack_time_i8(const int8_t* in, const int32_t* lens, int factor, int8_t* out, int T, int N, int C,
+                       void* stream);
+
+/* Transcription half of Joint fc1, hoisted out of the decode loop (amx_linear.cpp:137-150, i16o16b0):
+ * y1[M][J] bf16 = bf16(f[M][C] . W_trans[J][C]^T), fp32 FMA sequential in k (the order the oracle defines). */
+int rnnt_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, void* stream);
+
+/* Prediction + Joint + argmax + greedy_decode_update fused into one device-resident kernel
+ * (models/decoder.py:171-212 loop; modeling_rnnt.py:183-205,259-289,335-365; greedy_decode_update.cpp:13-96).
+ * Runs the whole while-loop on the device; per-utterance symbol counters, max_symbols_per_step = 30.
+ * All model tensors bf16 row-major unless noted. */
+typedef struct {
+  const uint16_t* embed;      /* [28][P] bf16                                        */
+  const uint16_t* w_ih[2];    /* [4P][P]                                             */
+  const uint16_t* w_hh[2];    /* [4P][P]                                             */
+  const float* bias[2];       /* [4P] = b_ih + b_hh  (modeling_rnnt.py:170-172)      */
+  const uint16_t* w_pred;     /* [J][P]  joint.linear1_pred                          */
+  const float* b1;            /* [J] = b_trans + b_pred (modeling_rnnt.py:225-227)   */
+  const uint16_t* w2;         /* [32][J] rows 29..31 zero (modeling_rnnt.py:241-246) */
+  const float* b2;            /* [32] entries 29..31 zero                            */
+} rnnt_decode_weights;
+
+int64_t rnnt_greedy_decode_workspace_bytes(int N);
+/* y1 [T2][N][J] bf16 (from rnnt_linear_bf16_bf16), f_lens [N] STACKED lengths.
+ * In/out state: res [N][L] int32, res_idx/symbols_added/time_idx/pre_g [N] int32,
+ * pre_hg0/1 [N][P] bf16, pre_cg0/1 [N][P] fp32.  iters_out (device int32[1], may be NULL) receives
+ * the number of batch-lockstep iterations the reference loop would have run. */
+int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w_host,
+                       int32_t* res, int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
+                       uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int32_t* iters_out,
+                       void* workspace, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

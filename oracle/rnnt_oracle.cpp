@@ -350,12 +350,27 @@ ORC_API void orc_stack_time(const int8_t* in, const int32_t* lens, int factor, i
 // bf16 prediction / joint operators
 // ================================================================================================
 namespace {
-// fp32 dot of bf16 row vectors, FMA sequential in k from acc = 0 (the order this oracle defines for
-// _compute_impl_bf16, tile_product_tpp.hpp:563-581; AMX's own order is unspecified, see header).
-inline float dot_bf16(const uint16_t* a, const uint16_t* w, int K) {
-  float acc = 0.f;
-  for (int k = 0; k < K; ++k) acc = std::fmaf(bf2f(a[k]), bf2f(w[k]), acc);
-  return acc;
+// bf16 weight matrix [O][K] expanded once to fp32 and transposed to [K][O], so that the O independent
+// accumulation chains of one input row advance together (vectorisable) while EACH chain keeps the order this
+// oracle defines for _compute_impl_bf16 (tile_product_tpp.hpp:563-581): acc = fma(x[k], w[o][k], acc), k
+// ascending from acc = 0.  (AMX's own order is unspecified, see header.)
+struct WT {
+  std::vector<float> t;
+  int K = 0, O = 0;
+  WT(const uint16_t* w, int O_, int K_) : t((size_t)O_ * K_), K(K_), O(O_) {
+    for (int o = 0; o < O; ++o)
+      for (int k = 0; k < K; ++k) t[(size_t)k * O + o] = bf2f(w[(size_t)o * K + k]);
+  }
+};
+// acc[o] = sum_k x[k] * w[o][k]  (acc must hold O floats)
+inline void gemv_bf16(const uint16_t* x, const WT& w, float* acc) {
+  const int O = w.O;
+  for (int o = 0; o < O; ++o) acc[o] = 0.f;
+  for (int k = 0; k < w.K; ++k) {
+    const float xk = bf2f(x[k]);
+    const float* wr = w.t.data() + (size_t)k * O;
+    for (int o = 0; o < O; ++o) acc[o] = std::fmaf(xk, wr[o], acc[o]);
+  }
 }
 
 // lstm_postop_tpp::ref_bf16 for one row (tpps/lstm_postop_tpp.cpp:100-163)
@@ -377,48 +392,80 @@ inline void postop_row_f32(const float* gates, const float* c_in, float* c_out, 
 // lstm_layer_amx_bf16 with seq_len == 1 (lstm_amx.cpp:187-264): G = x.W_ih^T (i16o32b0), then
 // G = (h.W_hh^T + G) + bias (float_out_accum, tile_product_tpp.hpp:387-408, bias = b_ih+b_hh,
 // modeling_rnnt.py:170-172), postop ref_bf16.  Returns NEW hy/cy (inputs untouched).
+static void lstm_cell_bf16_wt(const uint16_t* x, const uint16_t* h, const float* c, const WT& wih, const WT& whh,
+                              const float* bias, uint16_t* hy, float* cy, int N, int K, int H) {
+  const int G4 = 4 * H;
+#pragma omp parallel
+  {
+    std::vector<float> gi(G4), gh(G4), g(G4);
+#pragma omp for
+    for (int n = 0; n < N; ++n) {
+      gemv_bf16(x + (int64_t)n * K, wih, gi.data());
+      gemv_bf16(h + (int64_t)n * H, whh, gh.data());
+      for (int o = 0; o < G4; ++o) g[o] = (gh[o] + gi[o]) + bias[o];
+      postop_row_f32(g.data(), c + (int64_t)n * H, cy + (int64_t)n * H, hy + (int64_t)n * H, H);
+    }
+  }
+}
 ORC_API void orc_lstm_cell_bf16(const uint16_t* x, const uint16_t* h, const float* c, const uint16_t* w_ih,
                                 const uint16_t* w_hh, const float* bias, uint16_t* hy, float* cy, int N, int K, int H) {
-  const int G4 = 4 * H;
-#pragma omp parallel for
-  for (int n = 0; n < N; ++n) {
-    std::vector<float> g(G4);
-    for (int o = 0; o < G4; ++o) {
-      float gi = dot_bf16(x + (int64_t)n * K, w_ih + (int64_t)o * K, K);
-      float gh = dot_bf16(h + (int64_t)n * H, w_hh + (int64_t)o * H, H);
-      g[o] = (gh + gi) + bias[o];
-    }
-    postop_row_f32(g.data(), c + (int64_t)n * H, cy + (int64_t)n * H, hy + (int64_t)n * H, H);
-  }
+  WT wih(w_ih, 4 * H, K), whh(w_hh, 4 * H, H);
+  lstm_cell_bf16_wt(x, h, c, wih, whh, bias, hy, cy, N, K, H);
 }
 
 // i16o16b0 (amx_linear.cpp:137-150; bf16_out_no_bias tile_product_tpp.hpp:410-424): y = bf16(x.W^T)
 ORC_API void orc_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t N, int K, int O) {
-#pragma omp parallel for
-  for (int64_t n = 0; n < N; ++n)
-    for (int o = 0; o < O; ++o) y[n * O + o] = f2bf(dot_bf16(x + n * K, w + (int64_t)o * K, K));
+  WT wt(w, O, K);
+#pragma omp parallel
+  {
+    std::vector<float> acc(O);
+#pragma omp for
+    for (int64_t n = 0; n < N; ++n) {
+      gemv_bf16(x + n * K, wt, acc.data());
+      for (int o = 0; o < O; ++o) y[n * O + o] = f2bf(acc[o]);
+    }
+  }
 }
 
 // amx_linear_bf16_accum_relu (amx_linear.cpp:119-170): y1 = bf16(x0.W0^T) rounded in memory, then
 // y = bf16(max((x1.W1^T + float(y1)) + bias, 0)) (bf16_out_accum_relu, tile_product_tpp.hpp:426-449).
 // If y1_pre != NULL it is used instead of computing x0.W0^T (hoisted transcription half).
+static void linear_accum_relu_wt(const uint16_t* x0, const WT* w0, const uint16_t* y1_pre, const uint16_t* x1, const WT& w1,
+                                 const float* bias, uint16_t* y, int N, int K0, int K1, int O) {
+#pragma omp parallel
+  {
+    std::vector<float> a0(O), a1(O);
+#pragma omp for
+    for (int n = 0; n < N; ++n) {
+      if (!y1_pre) gemv_bf16(x0 + (int64_t)n * K0, *w0, a0.data());
+      gemv_bf16(x1 + (int64_t)n * K1, w1, a1.data());
+      for (int o = 0; o < O; ++o) {
+        uint16_t y1 = y1_pre ? y1_pre[(int64_t)n * O + o] : f2bf(a0[o]);
+        float v = (a1[o] + bf2f(y1)) + bias[o];
+        y[(int64_t)n * O + o] = f2bf(std::fmax(v, 0.f));
+      }
+    }
+  }
+}
 ORC_API void orc_linear_bf16_accum_relu(const uint16_t* x0, const uint16_t* w0, const uint16_t* y1_pre, const uint16_t* x1,
                                         const uint16_t* w1, const float* bias, uint16_t* y, int N, int K0, int K1, int O) {
-#pragma omp parallel for
-  for (int n = 0; n < N; ++n)
-    for (int o = 0; o < O; ++o) {
-      uint16_t y1 = y1_pre ? y1_pre[(int64_t)n * O + o] : f2bf(dot_bf16(x0 + (int64_t)n * K0, w0 + (int64_t)o * K0, K0));
-      float acc = dot_bf16(x1 + (int64_t)n * K1, w1 + (int64_t)o * K1, K1);
-      float v = (acc + bf2f(y1)) + bias[o];
-      y[(int64_t)n * O + o] = f2bf(std::fmax(v, 0.f));
-    }
+  WT wt1(w1, O, K1);
+  if (y1_pre) { linear_accum_relu_wt(nullptr, nullptr, y1_pre, x1, wt1, bias, y, N, K0, K1, O); return; }
+  WT wt0(w0, O, K0);
+  linear_accum_relu_wt(x0, &wt0, nullptr, x1, wt1, bias, y, N, K0, K1, O);
 }
 
 // amx_linear_i16o32 (amx_linear.cpp:113-117; float_out tile_product_tpp.hpp:347-367): y = x.W^T + b
-ORC_API void orc_linear_bf16_f32(const uint16_t* x, const uint16_t* w, const float* bias, float* y, int N, int K, int O) {
+static void linear_f32_wt(const uint16_t* x, const WT& w, const float* bias, float* y, int N, int K, int O) {
 #pragma omp parallel for
-  for (int n = 0; n < N; ++n)
-    for (int o = 0; o < O; ++o) y[(int64_t)n * O + o] = dot_bf16(x + (int64_t)n * K, w + (int64_t)o * K, K) + bias[o];
+  for (int n = 0; n < N; ++n) {
+    gemv_bf16(x + (int64_t)n * K, w, y + (int64_t)n * O);
+    for (int o = 0; o < O; ++o) y[(int64_t)n * O + o] += bias[o];
+  }
+}
+ORC_API void orc_linear_bf16_f32(const uint16_t* x, const uint16_t* w, const float* bias, float* y, int N, int K, int O) {
+  WT wt(w, O, K);
+  linear_f32_wt(x, wt, bias, y, N, K, O);
 }
 
 // greedy_decode_update (greedy_decode_update.cpp:13-96 + tpps/greedy_decode_update_tpp.cpp:9-51),
@@ -485,6 +532,9 @@ ORC_API int orc_greedy_decode(const uint16_t* f, const int32_t* f_lens, int T2, 
   std::memcpy(fi.data(), f, (size_t)N * C * 2);
   int iters = 0;
   if (T2 <= 0) return 0;
+  const WT wih0(w_ih[0], 4 * P, P), whh0(w_hh[0], 4 * P, P), wih1(w_ih[1], 4 * P, P), whh1(w_hh[1], 4 * P, P);
+  const WT wpred(w_pred, J, P), wfc2(w2, 32, J);
+  const WT* wtrans = y1_pre ? nullptr : new WT(w_trans, J, C);
   while (iters < max_iters) {
     ++iters;
     for (int n = 0; n < N; ++n) {
@@ -492,16 +542,16 @@ ORC_API int orc_greedy_decode(const uint16_t* f, const int32_t* f_lens, int T2, 
       if (g < 0 || g > 27) std::memset(&x[(size_t)n * P], 0, 2 * P);
       else std::memcpy(&x[(size_t)n * P], embed + (size_t)g * P, 2 * P);
     }
-    orc_lstm_cell_bf16(x.data(), pre_hg0, pre_cg0, w_ih[0], w_hh[0], bias[0], hg0.data(), cg0.data(), N, P, P);
-    orc_lstm_cell_bf16(hg0.data(), pre_hg1, pre_cg1, w_ih[1], w_hh[1], bias[1], hg1.data(), cg1.data(), N, P, P);
+    lstm_cell_bf16_wt(x.data(), pre_hg0, pre_cg0, wih0, whh0, bias[0], hg0.data(), cg0.data(), N, P, P);
+    lstm_cell_bf16_wt(hg0.data(), pre_hg1, pre_cg1, wih1, whh1, bias[1], hg1.data(), cg1.data(), N, P, P);
     if (y1_pre) {
       for (int n = 0; n < N; ++n)
         std::memcpy(&y1[(size_t)n * J], y1_pre + ((size_t)cur_t[n] * N + n) * J, 2 * J);
-      orc_linear_bf16_accum_relu(nullptr, nullptr, y1.data(), hg1.data(), w_pred, b1, y.data(), N, C, P, J);
+      linear_accum_relu_wt(nullptr, nullptr, y1.data(), hg1.data(), wpred, b1, y.data(), N, C, P, J);
     } else {
-      orc_linear_bf16_accum_relu(fi.data(), w_trans, nullptr, hg1.data(), w_pred, b1, y.data(), N, C, P, J);
+      linear_accum_relu_wt(fi.data(), wtrans, nullptr, hg1.data(), wpred, b1, y.data(), N, C, P, J);
     }
-    orc_linear_bf16_f32(y.data(), w2, b2, logits.data(), N, J, 32);
+    linear_f32_wt(y.data(), wfc2, b2, logits.data(), N, J, 32);
     for (int n = 0; n < N; ++n) {
       const float* l = &logits[(size_t)n * 32];
       int best = 0;
@@ -513,6 +563,7 @@ ORC_API int orc_greedy_decode(const uint16_t* f, const int32_t* f_lens, int T2, 
     for (int n = 0; n < N; ++n) if (time_idx[n] < f_lens[n]) cur_t[n] = time_idx[n];
     if (done) break;
   }
+  delete wtrans;
   return iters;
 }
 

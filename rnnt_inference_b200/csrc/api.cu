@@ -1,0 +1,345 @@
+// api.cu — the C ABI of librnnt_b200.so (include/rnnt_b200.h): argument validation, TMA tensor-map
+// construction, workspace carving and kernel launches.  No torch types, no allocation of caller-visible
+// buffers, no exceptions; errors are codes + a thread-local message.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/rnnt_b200.h"
+#include "kernels.cuh"
+
+using namespace rnnt;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CUDA_TRY(expr)                                                                                  \
+  do {                                                                                                  \
+    cudaError_t e_ = (expr);                                                                            \
+    if (e_ != cudaSuccess) return fail(RNNT_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// rank <= 3 tiled tensor map with 128-byte swizzle; dims/box innermost first; strides in bytes for dims 1..rank-1
+int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
+              const uint64_t* strides, const uint32_t* box) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail(RNNT_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t d[3], s[2];
+  cuuint32_t b[3], es[3] = {1, 1, 1};
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; }
+  for (int i = 0; i + 1 < rank; ++i) s[i] = strides[i];
+  CUresult r = enc(m, dt, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(RNNT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return RNNT_OK;
+}
+
+// one int of device-side status per device, owned by the library (4 bytes; never handed to the caller)
+int* device_status() {
+  static int* ptr[64] = {nullptr};
+  static std::mutex mu;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    if (cudaMalloc(&ptr[dev], 256) != cudaSuccess) return nullptr;
+    cudaMemset(ptr[dev], 0, 256);
+  }
+  return ptr[dev];
+}
+
+int sm_count() {
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+  return n;
+}
+inline bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+inline int64_t round_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+// ================================================================================================
+extern "C" {
+
+const char* rnnt_last_error(void) { return g_err; }
+int rnnt_abi_version(void) { return 1; }
+int rnnt_device_sm_count(void) { return sm_count(); }
+
+// Synchronises `stream`, then reads and clears the device-side status word of kernels launched by this
+// library on the current device.  Returns RNNT_ERR_DEVICE if a device watchdog fired.
+int rnnt_check_device_status(void* stream) {
+  int* st = device_status();
+  if (!st) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+  cudaStream_t s = (cudaStream_t)stream;
+  int h = 0;
+  CUDA_TRY(cudaMemcpyAsync(&h, st, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  if (h != 0) {
+    cudaMemsetAsync(st, 0, sizeof(int), s);
+    return fail(RNNT_ERR_DEVICE, "device-side watchdog/protocol error %d (101 mbarrier timeout, 102 flag timeout)", h);
+  }
+  return RNNT_OK;
+}
+
+int rnnt_quantize_pad_f32_i8(const float* in, int8_t* out, float scale, int64_t rows, int k_in, int k_out, void* stream) {
+  if (!in || !out || rows < 0 || k_in <= 0 || k_out < k_in || (k_out & 3) || !aligned(out, 4))
+    return fail(RNNT_ERR_INVALID, "quantize_pad: need k_out >= k_in > 0, k_out %% 4 == 0 (got rows=%lld k_in=%d k_out=%d)",
+                (long long)rows, k_in, k_out);
+  if (rows == 0) return RNNT_OK;
+  const long long total = rows * (k_out / 4);
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 148ll * 16);
+  quantize_pad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, out, scale, rows, k_in, k_out);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+int rnnt_stack_time_i8(const int8_t* in, const int32_t* lens, int factor, int8_t* out, int T, int N, int C, void* stream) {
+  if (!in || !lens || !out || factor <= 0 || T < 0 || N <= 0 || C <= 0 || (C & 15) || !aligned(in, 16) || !aligned(out, 16))
+    return fail(RNNT_ERR_INVALID, "stack_time: need C %% 16 == 0 and 16-byte aligned buffers (T=%d N=%d C=%d factor=%d)", T, N,
+                C, factor);
+  if (T == 0) return RNNT_OK;
+  const int T2 = (T + factor - 1) / factor;
+  const long long total = (long long)T2 * factor * N * (C / 16);
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 148ll * 16);
+  stack_time_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, lens, factor, out, T, N, C);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+int rnnt_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, void* stream) {
+  if (!x || !w || !y || M < 0 || K <= 0 || O <= 0) return fail(RNNT_ERR_INVALID, "linear_bf16_bf16: bad arguments");
+  if (M == 0) return RNNT_OK;
+  dim3 grid((O + LB_TO - 1) / LB_TO, (unsigned)((M + LB_TM - 1) / LB_TM));
+  linear_bf16_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, w, y, M, K, O);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+// test-only CUDA-core GEMM (cross-checks the tcgen05 kernel on the device at sizes beyond the CPU oracle)
+int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream) {
+  if (!A || !W || !C || M <= 0 || N <= 0 || K <= 0 || (K & 3)) return fail(RNNT_ERR_INVALID, "gemm_simt: bad arguments");
+  if (M > 65535) return fail(RNNT_ERR_INVALID, "gemm_simt: M <= 65535 (test helper)");
+  dim3 grid((N + 127) / 128, (unsigned)M);
+  gemm_i8_i32_simt_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(A, W, C, M, N, K);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+}  // extern "C"
+template <int BN>
+static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, cudaStream_t st) {
+  CUtensorMap ta, tb, tc;
+  {
+    uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)K};
+    uint32_t box[2] = {GEMM_BK, GEMM_BM};
+    if (int r = make_tmap(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, A, dims, str, box)) return r;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)K, (uint64_t)N}, str[1] = {(uint64_t)K};
+    uint32_t box[2] = {GEMM_BK, BN};
+    if (int r = make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, W, dims, str, box)) return r;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[1] = {(uint64_t)N * 4};
+    uint32_t box[2] = {32, 32};
+    if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 2, C, dims, str, box)) return r;
+  }
+  int* status = device_status();
+  if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+  auto kern = gemm_i8_i32_kernel<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::TOTAL));
+    attr_set = true;
+  }
+  const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
+  const int sms = sm_count();
+  const int grid = std::max(1, std::min(sms > 0 ? sms : 148, num_m * num_n));
+  kern<<<grid, GEMM_THREADS, GemmSmem<BN>::TOTAL, st>>>(ta, tb, tc, num_m, num_n, num_k, status);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+extern "C" {
+int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream) {
+  if (!A || !W || !C || M < 0 || N <= 0 || K <= 0)
+    return fail(RNNT_ERR_INVALID, "gemm_i8_i32: null pointer or non-positive size");
+  if ((K & 15) || (N & 63) || !aligned(A, 16) || !aligned(W, 16) || !aligned(C, 16))
+    return fail(RNNT_ERR_INVALID, "gemm_i8_i32: need K %% 16 == 0, N %% 64 == 0, 16-byte aligned pointers (M=%lld N=%d K=%d)",
+                (long long)M, N, K);
+  if (M == 0) return RNNT_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (N % 256 == 0) return gemm_launch<256>(A, W, C, M, N, K, st);
+  if (N % 128 == 0) return gemm_launch<128>(A, W, C, M, N, K, st);
+  return gemm_launch<64>(A, W, C, M, N, K, st);
+}
+
+// ------------------------------------------------------------------------------------------------
+// recurrent kernel.  workspace: [0,256) reserved | flags [num_btiles][32] int | h ping-pong [2][N_pad][1024] int8
+static int64_t rec_flags_bytes(int N) { return round_up((int64_t)((N + REC_BM - 1) / REC_BM) * REC_FLAG_STRIDE * 4, 256); }
+int64_t rnnt_lstm_recurrent_workspace_bytes(int N) {
+  if (N <= 0) return 0;
+  const int64_t n_pad = round_up(N, REC_BM);
+  return 1024 + rec_flags_bytes(N) + 2 * n_pad * REC_H + 1024;
+}
+
+}  // extern "C"
+template <int HS>
+static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th, const RecParams& p, int num_slices, int grid_y,
+                      cudaStream_t st) {
+  auto kern = lstm_recurrent_kernel<HS>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, RecSmem<HS>::TOTAL));
+    attr_set = true;
+  }
+  void* args[3] = {(void*)&tw, (void*)&th, (void*)&p};
+  CUDA_TRY(cudaLaunchCooperativeKernel((const void*)kern, dim3(num_slices, grid_y), dim3(REC_THREADS), args,
+                                       RecSmem<HS>::TOTAL, st));
+  return RNNT_OK;
+}
+
+extern "C" {
+int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                           float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                           void* workspace, void* stream) {
+  if (!G || !w_hh || !bias || !hx || !cx || !y || !workspace) return fail(RNNT_ERR_INVALID, "lstm_recurrent: null pointer");
+  if (H != REC_H) return fail(RNNT_ERR_INVALID, "lstm_recurrent: hidden size must be 1024 (got %d)", H);
+  if (T < 0 || N <= 0) return fail(RNNT_ERR_INVALID, "lstm_recurrent: need T >= 0, N > 0 (T=%d N=%d)", T, N);
+  if (!aligned(G, 16) || !aligned(w_hh, 16) || !aligned(workspace, 256) || !aligned(y, 8) || !aligned(cx, 8) || !aligned(hx, 4))
+    return fail(RNNT_ERR_INVALID, "lstm_recurrent: misaligned buffer");
+  if (T == 0) return RNNT_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int num_btiles = (N + REC_BM - 1) / REC_BM;
+  const int64_t n_pad = (int64_t)num_btiles * REC_BM;
+  if (num_btiles > 8 * 2) return fail(RNNT_ERR_INVALID, "lstm_recurrent: N <= 2048 per call (got %d)", N);
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  int* flags = reinterpret_cast<int*>(ws + 1024);
+  int8_t* h_buf = reinterpret_cast<int8_t*>(ws + 1024 + rec_flags_bytes(N));
+  h_buf = reinterpret_cast<int8_t*>(round_up((int64_t)reinterpret_cast<uintptr_t>(h_buf), 1024));
+  int* status = device_status();
+  if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+
+  CUDA_TRY(cudaMemsetAsync(flags, 0, rec_flags_bytes(N), st));
+  CUDA_TRY(cudaMemsetAsync(h_buf, 0, 2 * n_pad * REC_H, st));
+  CUDA_TRY(cudaMemcpyAsync(h_buf, hx, (size_t)N * REC_H, cudaMemcpyDeviceToDevice, st));
+
+  // one slice of 8 units per CTA when a single batch tile exists (128 CTAs), else 16 units (64 slices x 2 tile groups)
+  const int HS = (num_btiles == 1) ? 8 : 16;
+  const int num_slices = REC_H / HS;
+  const int grid_y = (num_btiles == 1) ? 1 : 2;
+  CUtensorMap tw, th;
+  {
+    uint64_t dims[3] = {REC_H, REC_H, 4}, str[2] = {REC_H, (uint64_t)REC_H * REC_H};
+    uint32_t box[3] = {128, (uint32_t)HS, 4};
+    if (int r = make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, w_hh, dims, str, box)) return r;
+  }
+  {
+    uint64_t dims[3] = {REC_H, (uint64_t)n_pad, 2}, str[2] = {REC_H, (uint64_t)n_pad * REC_H};
+    uint32_t box[3] = {128, REC_BM, 1};
+    if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h_buf, dims, str, box)) return r;
+  }
+  RecParams p;
+  p.G = G; p.bias = bias; p.h_buf = h_buf; p.cx = cx; p.y = y; p.flags = flags; p.status = status;
+  p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
+  p.T = T; p.N = N; p.N_pad = (int)n_pad; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
+  int r = (HS == 8) ? rec_launch<8>(tw, th, p, num_slices, grid_y, st) : rec_launch<16>(tw, th, p, num_slices, grid_y, st);
+  if (r) return r;
+  CUDA_TRY(cudaMemcpyAsync(hx, h_buf + (size_t)(T & 1) * n_pad * REC_H, (size_t)N * REC_H, cudaMemcpyDeviceToDevice, st));
+  return RNNT_OK;
+}
+
+int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* w_ih, const int8_t* w_hh, const float* bias,
+                       float rb_scale, float in_scale, float out_scale, int skip_quant_y, void* y, int T, int N, int K, int H,
+                       int32_t* g_ws, void* workspace, void* stream) {
+  if (!g_ws) return fail(RNNT_ERR_INVALID, "lstm_layer: null projection workspace");
+  if (T == 0) return RNNT_OK;
+  if (int r = rnnt_gemm_i8_i32(x, w_ih, g_ws, (int64_t)T * N, 4 * H, K, stream)) return r;
+  return rnnt_lstm_recurrent_i8(g_ws, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, hx, cx, y, T, N, H, workspace,
+                                stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// greedy decode.  workspace: [0,256) global_sync | group_cnt [8][32] int | lane_state [N][8] int | z [N][512] f32 |
+//                            hg1 [2][N][320] bf16 | cg1 [2][N][320] f32
+int64_t rnnt_greedy_decode_workspace_bytes(int N) {
+  if (N <= 0) return 0;
+  return 256 + 1024 + round_up((int64_t)N * 32, 256) + round_up((int64_t)N * DEC_J * 4, 256) +
+         round_up((int64_t)2 * N * DEC_P * 2, 256) + round_up((int64_t)2 * N * DEC_P * 4, 256);
+}
+
+int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w, int32_t* res,
+                       int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g, uint16_t* pre_hg0,
+                       uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int32_t* iters_out, void* workspace, void* stream) {
+  if (!y1 || !f_lens || !w || !res || !res_idx || !symbols_added || !time_idx || !pre_g || !pre_hg0 || !pre_hg1 ||
+      !pre_cg0 || !pre_cg1 || !workspace)
+    return fail(RNNT_ERR_INVALID, "greedy_decode: null pointer");
+  if (!w->embed || !w->w_ih[0] || !w->w_ih[1] || !w->w_hh[0] || !w->w_hh[1] || !w->bias[0] || !w->bias[1] || !w->w_pred ||
+      !w->b1 || !w->w2 || !w->b2)
+    return fail(RNNT_ERR_INVALID, "greedy_decode: null weight pointer");
+  if (T2 <= 0 || N <= 0 || L <= 0) return fail(RNNT_ERR_INVALID, "greedy_decode: need T2, N, L > 0 (T2=%d N=%d L=%d)", T2, N, L);
+  if (!aligned(workspace, 256) || !aligned(w->w_pred, 8) || !aligned(w->w2, 16) || !aligned(w->w_ih[0], 4) ||
+      !aligned(w->w_hh[0], 4) || !aligned(w->w_ih[1], 4) || !aligned(w->w_hh[1], 4))
+    return fail(RNNT_ERR_INVALID, "greedy_decode: misaligned buffer");
+  const int NG = 7;
+  const int LG = (N + NG - 1) / NG;
+  if (LG > DEC_MAXLG) return fail(RNNT_ERR_INVALID, "greedy_decode: N <= %d per call (got %d)", NG * DEC_MAXLG, N);
+  cudaStream_t st = (cudaStream_t)stream;
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  int* status = device_status();
+  if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+  DecParams p;
+  p.embed = w->embed;
+  for (int l = 0; l < 2; ++l) { p.w_ih[l] = w->w_ih[l]; p.w_hh[l] = w->w_hh[l]; p.bias[l] = w->bias[l]; }
+  p.w_pred = w->w_pred; p.b1 = w->b1; p.w2 = w->w2; p.b2 = w->b2;
+  p.y1 = y1; p.f_lens = f_lens; p.T2 = T2; p.N = N;
+  p.res = res; p.L = L; p.res_idx = res_idx; p.symbols_added = symbols_added; p.time_idx = time_idx; p.pre_g = pre_g;
+  int64_t off = 0;
+  p.global_sync = reinterpret_cast<int32_t*>(ws + off); off += 256;
+  p.group_cnt = reinterpret_cast<int32_t*>(ws + off); off += 1024;
+  p.lane_state = reinterpret_cast<int32_t*>(ws + off); off += round_up((int64_t)N * 32, 256);
+  p.z = reinterpret_cast<float*>(ws + off); off += round_up((int64_t)N * DEC_J * 4, 256);
+  uint16_t* hg1 = reinterpret_cast<uint16_t*>(ws + off); off += round_up((int64_t)2 * N * DEC_P * 2, 256);
+  float* cg1 = reinterpret_cast<float*>(ws + off);
+  p.hg[0][0] = pre_hg0; p.hg[0][1] = pre_hg1; p.hg[1][0] = hg1; p.hg[1][1] = hg1 + (size_t)N * DEC_P;
+  p.cg[0][0] = pre_cg0; p.cg[0][1] = pre_cg1; p.cg[1][0] = cg1; p.cg[1][1] = cg1 + (size_t)N * DEC_P;
+  p.iters_out = iters_out; p.status = status; p.NG = NG; p.LG = LG;
+  CUDA_TRY(cudaMemsetAsync(ws, 0, 256 + 1024, st));
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(greedy_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DecSmem::TOTAL));
+    attr_set = true;
+  }
+  void* args[1] = {(void*)&p};
+  CUDA_TRY(cudaLaunchCooperativeKernel((const void*)greedy_decode_kernel, dim3(NG * DEC_S), dim3(DEC_THREADS), args,
+                                       DecSmem::TOTAL, st));
+  return RNNT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,362 @@
+// greedy_decode.cu — the whole greedy decode loop as ONE device-resident cooperative kernel.
+//
+// Replaces GreedyDecoder.greedy_decode_quant's while-loop (models/decoder.py:188-211), in which every iteration
+// dispatches Prediction (modeling_rnnt.py:183-205 -> lstm_amx_bf16, lstm_amx.cpp:160-266), Joint
+// (:259-289 -> amx_linear_bf16_accum_relu + amx_linear_i16o32, amx_linear.cpp:113-170), torch.argmax over 32
+// columns (decoder.py:193) and greedy_decode_update (greedy_decode_update.cpp:13-96) and returns a bool to Python.
+//
+// Arithmetic contract (matches oracle/rnnt_oracle.cpp): bf16 operands, fp32 FMA accumulation sequential in k
+// from 0 (one thread owns one output chain — no cross-thread reduction), epilogues in the reference's order:
+// G = (h.W_hh + x.W_ih) + bias; fp32 Pade sigmoid/tanh with RN reciprocal; y = bf16(relu((g.W_pred + y1) + b1));
+// logits = y.W2 + b2; first-maximum argmax over 32 columns.  Hence token sequences are bit-exact vs the oracle.
+//
+// Organisation: the batch is split into NG lane groups; a group is served by S=20 CTAs that keep the
+// prediction-LSTM weight columns of 16 hidden units (both layers, W_ih|W_hh, 162 KB) resident in shared memory.
+// Per iteration and group: (A) LSTM layer 0, (B) layer 1, (C) g.W_pred, (D) per lane: fc1 epilogue, fc2, argmax,
+// state update — with a group-local barrier (arrival counter in global memory) between phases.  Groups never
+// wait for each other inside the loop.  Ragged batch, per-utterance counters:
+//   * the prediction network is recomputed only for lanes whose previous symbol was accepted: the reference
+//     recomputes it every iteration, but with unchanged (pre_g, pre_hg, pre_cg) the result is bit-identical;
+//   * a finished lane whose last step was a blank is at a fixed point of the reference loop and is skipped; a
+//     lane that finished on the 30-symbol cap keeps emitting in the reference until the whole batch is done
+//     (greedy_decode_update_tpp.cpp:22-29 masks only f_lens == 0), which is reproduced exactly: phase 1 runs
+//     every group until its lanes finished, one grid-wide rendezvous yields the batch iteration count, phase 2
+//     replays the remaining iterations for the still-live lanes only.
+#include "kernels.cuh"
+#include "gate_math.cuh"
+
+namespace rnnt {
+
+
+__device__ __forceinline__ void group_barrier(const DecParams& p, int g, int& epoch, bool& ok) {
+  __syncthreads();
+  ++epoch;
+  if (threadIdx.x == 0 && ok) {
+    int* cnt = p.group_cnt + g * 32;
+    __threadfence();
+    asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(cnt) : "memory");
+    const int target = epoch * DEC_S;
+    long long t0 = clock64(); uint32_t spins = 0;
+    for (;;) {
+      int v;
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
+      if (v >= target) break;
+      if ((++spins & 63u) == 0) {
+        if (*(volatile int*)p.status != DEV_OK) break;
+        if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_FLAG); break; }
+      }
+    }
+  }
+  __syncthreads();
+  if (*(volatile int*)p.status != DEV_OK) ok = false;
+}
+
+// One LSTM layer for the `na` active lanes listed in `alist` (group-local lane ids), chunked by DEC_CHUNK.
+//   x source: layer 0 -> embedding of pre_g (zero for SOS / out-of-table), layer 1 -> candidate h of layer 0.
+//   h, c source: committed buffers (cur).  Results go to the candidate buffers (cur ^ 1).
+__device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g, int s, const int* alist, int na,
+                                           const uint16_t* wl, float* act, float* part) {
+  const int tid = threadIdx.x;
+  const int lane0 = g * p.LG;
+  for (int a0 = 0; a0 < na; a0 += DEC_CHUNK) {
+    const int nc = min(DEC_CHUNK, na - a0);
+    // ---- stage activations as fp32: act[a][0..319] = x, act[a][320..639] = h
+    for (int e = tid; e < nc * 2 * DEC_P; e += DEC_THREADS) {
+      const int a = e / (2 * DEC_P), k = e % (2 * DEC_P);
+      const int n = lane0 + alist[a0 + a];
+      const int cur = p.lane_state[n * 8 + 0];
+      uint32_t bits;
+      if (k < DEC_P) {
+        if (layer == 0) {
+          const int sym = p.pre_g[n];
+          bits = (sym < 0 || sym > 27) ? 0u : (uint32_t)p.embed[sym * DEC_P + k];
+        } else {
+          bits = p.hg[cur ^ 1][0][(size_t)n * DEC_P + k];
+        }
+      } else {
+        bits = p.hg[cur][layer][(size_t)n * DEC_P + (k - DEC_P)];
+      }
+      act[a * 2 * DEC_P + k] = bf16_bits_to_float(bits);
+    }
+    __syncthreads();
+    // ---- dot products: thread = (column c, matrix m, lane parity ls); chains sequential in k
+    {
+      const int c = tid & 63, m = (tid >> 6) & 1, ls = tid >> 7;
+      const uint16_t* wrow = wl + ((size_t)(layer * 2 + m) * DEC_COLS + c) * DEC_KSTR;
+      float acc[DEC_CHUNK / 2];
+#pragma unroll
+      for (int i = 0; i < DEC_CHUNK / 2; ++i) acc[i] = 0.f;
+      for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
+        const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
+        const float w0 = __uint_as_float(wb.x << 16), w1 = __uint_as_float(wb.x & 0xffff0000u);
+        const float w2 = __uint_as_float(wb.y << 16), w3 = __uint_as_float(wb.y & 0xffff0000u);
+#pragma unroll
+        for (int i = 0; i < DEC_CHUNK / 2; ++i) {
+          const int a = ls + 2 * i;
+          if (a < nc) {
+            const float4 xv = *reinterpret_cast<const float4*>(act + a * 2 * DEC_P + m * DEC_P + k4 * 4);
+            acc[i] = __fmaf_rn(xv.x, w0, acc[i]);
+            acc[i] = __fmaf_rn(xv.y, w1, acc[i]);
+            acc[i] = __fmaf_rn(xv.z, w2, acc[i]);
+            acc[i] = __fmaf_rn(xv.w, w3, acc[i]);
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < DEC_CHUNK / 2; ++i) {
+        const int a = ls + 2 * i;
+        if (a < nc) part[(m * DEC_CHUNK + a) * DEC_COLS + c] = acc[i];
+      }
+    }
+    __syncthreads();
+    // ---- cell update: thread = (unit u, lane a)
+    {
+      const int u = tid & 15, a = tid >> 4;
+      if (a < nc) {
+        const int n = lane0 + alist[a0 + a];
+        const int cur = p.lane_state[n * 8 + 0];
+        const int j = s * DEC_U + u;
+        float gate[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float gi = part[(0 * DEC_CHUNK + a) * DEC_COLS + q * DEC_U + u];
+          const float gh = part[(1 * DEC_CHUNK + a) * DEC_COLS + q * DEC_U + u];
+          gate[q] = __fadd_rn(__fadd_rn(gh, gi), p.bias[layer][q * DEC_P + j]);   // float_out_accum: (acc + prev) + bias
+        }
+        const float it = sigmoid_ps(gate[0]), ft = sigmoid_ps(gate[1]), gt = tanh_ps(gate[2]), ot = sigmoid_ps(gate[3]);
+        const float c_old = p.cg[cur][layer][(size_t)n * DEC_P + j];
+        const float c_new = __fmaf_rn(it, gt, __fmul_rn(ft, c_old));
+        const float ht = __fmul_rn(ot, tanh_ps(c_new));
+        p.cg[cur ^ 1][layer][(size_t)n * DEC_P + j] = c_new;
+        p.hg[cur ^ 1][layer][(size_t)n * DEC_P + j] = (uint16_t)float_to_bf16_bits(ht);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// z[n][col] = sum_k g[n][k] * W_pred[col][k] for the active lanes; this CTA's columns [s*26, s*26+26) ∩ [0,512).
+__device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, const int* alist, int na, float* act) {
+  const int tid = threadIdx.x;
+  const int lane0 = g * p.LG;
+  const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
+  for (int a0 = 0; a0 < na; a0 += 2 * DEC_CHUNK) {
+    const int nc = min(2 * DEC_CHUNK, na - a0);
+    for (int e = tid; e < nc * DEC_P; e += DEC_THREADS) {
+      const int a = e / DEC_P, k = e % DEC_P;
+      const int n = lane0 + alist[a0 + a];
+      const int cur = p.lane_state[n * 8 + 0];
+      act[a * DEC_P + k] = bf16_bits_to_float(p.hg[cur ^ 1][1][(size_t)n * DEC_P + k]);
+    }
+    __syncthreads();
+    for (int e = tid; e < nc * ncol; e += DEC_THREADS) {
+      const int a = e / ncol, col = col0 + e % ncol;
+      const uint2* wrow = reinterpret_cast<const uint2*>(p.w_pred + (size_t)col * DEC_P);
+      const float* xr = act + a * DEC_P;
+      float acc = 0.f;
+#pragma unroll 4
+      for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
+        const uint2 wb = __ldg(wrow + k4);
+        const float4 xv = *reinterpret_cast<const float4*>(xr + k4 * 4);
+        acc = __fmaf_rn(xv.x, __uint_as_float(wb.x << 16), acc);
+        acc = __fmaf_rn(xv.y, __uint_as_float(wb.x & 0xffff0000u), acc);
+        acc = __fmaf_rn(xv.z, __uint_as_float(wb.y << 16), acc);
+        acc = __fmaf_rn(xv.w, __uint_as_float(wb.y & 0xffff0000u), acc);
+      }
+      p.z[(size_t)(lane0 + alist[a0 + a]) * DEC_J + col] = acc;
+    }
+    __syncthreads();
+  }
+}
+
+// Phase D for one lane, executed by one warp: fc1 epilogue, fc2, argmax, greedy_decode_update state machine.
+__device__ __forceinline__ void joint_update_lane(const DecParams& p, int n, int iter, float* ybuf, int lane) {
+  int32_t* st = p.lane_state + n * 8;
+  const int cur_t = st[5];
+  const uint16_t* y1r = p.y1 + ((size_t)cur_t * p.N + n) * DEC_J;
+  const float* zr = p.z + (size_t)n * DEC_J;
+  for (int k = lane; k < DEC_J; k += 32) {
+    const float v = __fadd_rn(__fadd_rn(zr[k], bf16_bits_to_float(y1r[k])), p.b1[k]);   // (acc + y1) + bias
+    ybuf[k] = bf16_bits_to_float(float_to_bf16_bits(fmaxf(v, 0.f)));                    // relu, round to bf16
+  }
+  __syncwarp();
+  // logits[o], o = lane: sequential chain over k
+  const uint4* wrow = reinterpret_cast<const uint4*>(p.w2 + (size_t)lane * DEC_J);
+  float acc = 0.f;
+#pragma unroll 2
+  for (int k8 = 0; k8 < DEC_J / 8; ++k8) {
+    const uint4 wb = __ldg(wrow + k8);
+    const float4 ya = *reinterpret_cast<const float4*>(ybuf + k8 * 8);
+    const float4 yb = *reinterpret_cast<const float4*>(ybuf + k8 * 8 + 4);
+    acc = __fmaf_rn(ya.x, __uint_as_float(wb.x << 16), acc);
+    acc = __fmaf_rn(ya.y, __uint_as_float(wb.x & 0xffff0000u), acc);
+    acc = __fmaf_rn(ya.z, __uint_as_float(wb.y << 16), acc);
+    acc = __fmaf_rn(ya.w, __uint_as_float(wb.y & 0xffff0000u), acc);
+    acc = __fmaf_rn(yb.x, __uint_as_float(wb.z << 16), acc);
+    acc = __fmaf_rn(yb.y, __uint_as_float(wb.z & 0xffff0000u), acc);
+    acc = __fmaf_rn(yb.z, __uint_as_float(wb.w << 16), acc);
+    acc = __fmaf_rn(yb.w, __uint_as_float(wb.w & 0xffff0000u), acc);
+  }
+  float best = __fadd_rn(acc, p.b2[lane]);
+  int bidx = lane;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {   // first maximum wins ties (torch.argmax)
+    const float ov = __shfl_xor_sync(0xffffffffu, best, off);
+    const int oi = __shfl_xor_sync(0xffffffffu, bidx, off);
+    if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
+  }
+  __syncwarp();
+  if (lane == 0) {
+    const int sym = bidx;
+    const int flen = p.f_lens[n];
+    const bool upd_g = (sym != DEC_BLANK) && (p.symbols_added[n] != DEC_MAXSYM) && (flen != 0);
+    if (upd_g) {
+      const int ri = p.res_idx[n] + 1;
+      p.res_idx[n] = ri;
+      if (ri >= 0 && ri < p.L) p.res[(size_t)n * p.L + ri] = sym;
+      p.symbols_added[n] += 1;
+      p.pre_g[n] = sym;
+      st[0] ^= 1;        // candidate becomes the committed state
+      st[1] = 1;         // prediction network must be re-evaluated
+    } else {
+      p.symbols_added[n] = 0;
+      p.time_idx[n] += 1;
+      st[1] = 0;
+    }
+    const int ti = p.time_idx[n];
+    const bool finished = ti >= flen;
+    if (!finished) st[5] = ti;                 // fi = f[time_idx]
+    st[2] = finished ? 1 : 0;
+    if (finished && !upd_g && (sym == DEC_BLANK || flen == 0)) { st[3] = 1; st[4] = iter; }   // fixed point
+  }
+}
+
+__global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const DecParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint16_t* wl = reinterpret_cast<uint16_t*>(smem);
+  float* act = reinterpret_cast<float*>(smem + DecSmem::W_BYTES);
+  float* part = reinterpret_cast<float*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES);
+  float* ybuf = reinterpret_cast<float*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES + DecSmem::PART_BYTES);
+  __shared__ int alist[DEC_MAXLG];
+  __shared__ int s_na, s_unfinished, s_live;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = blockIdx.x / DEC_S, s = blockIdx.x % DEC_S;
+  const int lane0 = g * p.LG;
+  const int nl = max(0, min(p.LG, p.N - lane0));    // lanes of this group
+
+  // resident weights: wl[layer][m][c][k], c = gate*16 + u  <-  W[(gate*320 + s*16 + u)][k]
+  for (int e = tid; e < 2 * 2 * DEC_COLS * (DEC_P / 2); e += DEC_THREADS) {
+    const int k2 = e % (DEC_P / 2);
+    int r = e / (DEC_P / 2);
+    const int c = r % DEC_COLS; r /= DEC_COLS;
+    const int m = r & 1, layer = r >> 1;
+    const uint16_t* src = (m == 0 ? p.w_ih[layer] : p.w_hh[layer]) + (size_t)((c / DEC_U) * DEC_P + s * DEC_U + (c % DEC_U)) * DEC_P;
+    reinterpret_cast<uint32_t*>(wl + ((size_t)(layer * 2 + m) * DEC_COLS + c) * DEC_KSTR)[k2] =
+        reinterpret_cast<const uint32_t*>(src)[k2];
+  }
+  // lane state init (each lane by the CTA that owns it in phase D)
+  for (int li = s + tid * DEC_S; li < nl; li += DEC_S * DEC_THREADS) {
+    int32_t* st = p.lane_state + (lane0 + li) * 8;
+    st[0] = 0; st[1] = 1; st[2] = 0; st[3] = 0; st[4] = 0; st[5] = 0; st[6] = 0; st[7] = 0;
+  }
+  int epoch = 0; bool ok = true;
+  group_barrier(p, g, epoch, ok);
+
+  int iter = 0;
+  int total_iters = -1;   // unknown during phase 1
+  for (;;) {
+    // ---- build the active (need_lstm) list and the loop conditions from the lane states
+    if (tid == 0) { s_na = 0; s_unfinished = 0; s_live = 0; }
+    __syncthreads();
+    if (tid < 32) {
+      for (int base = 0; base < nl; base += 32) {
+        const int li = base + tid;
+        int need = 0, unfin = 0, live = 0;
+        if (li < nl) {
+          const int32_t* st = p.lane_state + (lane0 + li) * 8;
+          const int fixed = st[3];
+          need = st[1] && !fixed;
+          unfin = !st[2];
+          live = !fixed;
+        }
+        const unsigned mneed = __ballot_sync(0xffffffffu, need);
+        const unsigned munf = __ballot_sync(0xffffffffu, unfin);
+        const unsigned mlive = __ballot_sync(0xffffffffu, live);
+        if (need) alist[s_na + __popc(mneed & ((1u << tid) - 1))] = li;
+        __syncwarp();
+        if (tid == 0) { s_na += __popc(mneed); s_unfinished += __popc(munf); s_live += __popc(mlive); }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    const int na = s_na;
+    const bool phase1 = total_iters < 0;
+    if (!ok) break;
+    if (phase1 && s_unfinished == 0) {
+      // ---- every lane of the group has finished: rendezvous of all groups, learn the batch iteration count
+      if (tid == 0) {
+        if (s == 0) {
+          atomicMax(p.global_sync + 1, iter);
+          __threadfence();
+          atomicAdd(p.global_sync + 0, 1);
+        }
+        long long t0 = clock64(); uint32_t spins = 0;
+        for (;;) {
+          int v;
+          asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.global_sync) : "memory");
+          if (v >= p.NG) break;
+          if ((++spins & 63u) == 0) {
+            if (*(volatile int*)p.status != DEV_OK) break;
+            if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_FLAG); break; }
+          }
+        }
+        s_unfinished = *(volatile int*)(p.global_sync + 1);
+      }
+      __syncthreads();
+      total_iters = s_unfinished;
+      __syncthreads();
+      if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
+    }
+    if (total_iters >= 0 && (iter >= total_iters || s_live == 0)) break;
+    ++iter;
+
+    if (na > 0) {
+      lstm_phase(p, 0, g, s, alist, na, wl, act, part);
+      group_barrier(p, g, epoch, ok);
+      lstm_phase(p, 1, g, s, alist, na, wl, act, part);
+      group_barrier(p, g, epoch, ok);
+      fc1_phase(p, g, s, alist, na, act);
+      group_barrier(p, g, epoch, ok);
+    }
+    // ---- phase D: lanes li = s, s+S, ... ; one warp per lane
+    if (warp < DEC_DWARPS) {
+      for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_DWARPS) {
+        const int n = lane0 + li;
+        if (!p.lane_state[n * 8 + 3]) joint_update_lane(p, n, iter, ybuf + warp * DEC_J, lane);
+      }
+    }
+    group_barrier(p, g, epoch, ok);
+  }
+
+  // ---- epilogue: reference-visible state of lanes that were skipped at their fixed point, committed h/c back
+  // into the caller's arrays.
+  if (ok && total_iters >= 0) {
+    for (int li = s + warp * DEC_S; li < nl; li += DEC_S * 8) {
+      const int n = lane0 + li;
+      const int32_t* st = p.lane_state + n * 8;
+      if (lane == 0 && st[3]) p.time_idx[n] += total_iters - st[4];
+      if (st[0] == 1) {
+        for (int k = lane; k < DEC_P; k += 32) {
+          p.hg[0][0][(size_t)n * DEC_P + k] = p.hg[1][0][(size_t)n * DEC_P + k];
+          p.hg[0][1][(size_t)n * DEC_P + k] = p.hg[1][1][(size_t)n * DEC_P + k];
+          p.cg[0][0][(size_t)n * DEC_P + k] = p.cg[1][0][(size_t)n * DEC_P + k];
+          p.cg[0][1][(size_t)n * DEC_P + k] = p.cg[1][1][(size_t)n * DEC_P + k];
+        }
+      }
+    }
+    if (blockIdx.x == 0 && tid == 0 && p.iters_out) *p.iters_out = total_iters;
+  }
+}
+
+}  // namespace rnnt

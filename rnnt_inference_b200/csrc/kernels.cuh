@@ -1,0 +1,120 @@
+// kernels.cuh — tile constants, shared-memory plans, parameter blocks and kernel declarations shared between
+// the kernel translation units and api.cu.
+#pragma once
+#include "common.cuh"
+
+namespace rnnt {
+
+// ------------------------------------------------------------------ gemm_i8.cu
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 128;   // bytes of K per stage = one 128-byte swizzle row
+constexpr int GEMM_STAGES = 4;
+constexpr int GEMM_THREADS = 256;
+
+template <int BN>
+struct GemmSmem {
+  static constexpr int A_BYTES = GEMM_BM * GEMM_BK;           // 16 KB
+  static constexpr int B_BYTES = BN * GEMM_BK;                // 32 KB at BN=256
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int C_WARP_BYTES = 32 * 128;               // 32 rows x 32 int32
+  static constexpr int C_BYTES = 4 /*warps*/ * 2 /*buffers*/ * C_WARP_BYTES;  // 32 KB
+  static constexpr int BAR_OFFSET = GEMM_STAGES * STAGE_BYTES + C_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;       // barriers + alignment slack
+};
+
+template <int BN>
+__global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                                   const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
+                                   int num_k_blocks, int* __restrict__ status);
+__global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, int32_t* __restrict__ C,
+                                        long long M, int N, int K);
+
+// ------------------------------------------------------------------ lstm_recurrent.cu
+constexpr int REC_H = 1024;
+constexpr int REC_BM = 128;          // batch rows per tile (UMMA M)
+constexpr int REC_KC = 8;            // K chunks of 128 bytes
+constexpr int REC_CTRL_WARPS = 4;    // 0: TMA producer, 1: MMA issuer, 2: TMEM alloc, 3: idle
+constexpr int REC_EPI_WARPS = 16;
+constexpr int REC_THREADS = 32 * (REC_CTRL_WARPS + REC_EPI_WARPS);   // 640
+constexpr int REC_FLAG_STRIDE = 32;  // ints between per-tile counters (128 B)
+
+template <int HS>
+struct RecSmem {
+  static constexpr int UMMA_N = 4 * HS;
+  static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice
+  static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 64 KB at HS=16
+  static constexpr int H_CHUNK = REC_BM * 128;            // 16 KB
+  static constexpr int H_BYTES = REC_KC * H_CHUNK;        // 128 KB
+  static constexpr int LUT_OFFSET = W_BYTES + H_BYTES;
+  static constexpr int BAR_OFFSET = LUT_OFFSET + 2048;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;
+};
+
+struct RecParams {
+  const int32_t* G;        // [T][N][4H]
+  const float* bias;       // [4H]
+  int8_t* h_buf;           // [2][N_pad][H] ping-pong (workspace); buffer 0 holds h_0 on entry
+  uint16_t* cx;            // [N][H] binary16, in place
+  void* y;                 // [T][N][H] int8 or bf16
+  int* flags;              // [num_btiles][REC_FLAG_STRIDE] zeroed
+  int* status;
+  float rb_scale, in_scale, out_scale;
+  int T, N, N_pad, num_btiles, skip_quant_y;
+};
+
+template <int HS>
+__global__ void lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h,
+                                      const RecParams p);
+
+// ------------------------------------------------------------------ elementwise.cu
+constexpr int LB_TM = 64, LB_TO = 64, LB_TK = 32;
+__global__ void quantize_pad_kernel(const float* __restrict__ in, int8_t* __restrict__ out, float scale, long long rows,
+                                    int k_in, int k_out);
+__global__ void stack_time_kernel(const int8_t* __restrict__ in, const int32_t* __restrict__ lens, int factor,
+                                  int8_t* __restrict__ out, int T, int N, int C);
+__global__ void linear_bf16_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w,
+                                        uint16_t* __restrict__ y, long long M, int K, int O);
+
+// ------------------------------------------------------------------ greedy_decode.cu
+constexpr int DEC_P = 320, DEC_J = 512, DEC_V = 32;
+constexpr int DEC_S = 20;             // CTAs per lane group
+constexpr int DEC_U = DEC_P / DEC_S;  // 16 hidden units per CTA
+constexpr int DEC_COLS = 4 * DEC_U;   // 64 gate columns per CTA and matrix
+constexpr int DEC_KSTR = DEC_P + 4;   // padded bf16 row stride (648 B: conflict-free 8-byte reads)
+constexpr int DEC_THREADS = 256;
+constexpr int DEC_CHUNK = 16;         // active lanes processed per pass
+constexpr int DEC_JC = 26;            // fc1 columns per CTA (19*26 + 18 = 512)
+constexpr int DEC_MAXLG = 320;        // max lanes per group (N <= 7*320)
+constexpr int DEC_DWARPS = 4;         // warps used by phase D (one lane each per pass)
+constexpr int DEC_BLANK = 28, DEC_MAXSYM = 30;
+
+struct DecSmem {
+  static constexpr int W_BYTES = 2 * 2 * DEC_COLS * DEC_KSTR * 2;          // [layer][ih|hh][col][k] bf16 = 165,888
+  static constexpr int ACT_BYTES = DEC_CHUNK * 2 * DEC_P * 4;              // [lane][x|h] fp32 = 40,960
+  static constexpr int PART_BYTES = 2 * DEC_CHUNK * DEC_COLS * 4;          // [ih|hh][lane][col] fp32 = 8,192
+  static constexpr int Y_BYTES = DEC_DWARPS * DEC_J * 4;                   // per-warp y vector, 8,192
+  static constexpr int TOTAL = W_BYTES + ACT_BYTES + PART_BYTES + Y_BYTES;  // 223,232
+};
+
+struct DecParams {
+  // model
+  const uint16_t* embed; const uint16_t* w_ih[2]; const uint16_t* w_hh[2]; const float* bias[2];
+  const uint16_t* w_pred; const float* b1; const uint16_t* w2; const float* b2;
+  // inputs
+  const uint16_t* y1; const int32_t* f_lens; int T2, N;
+  // in/out state
+  int32_t* res; int L; int32_t* res_idx; int32_t* symbols_added; int32_t* time_idx; int32_t* pre_g;
+  uint16_t* hg[2][2];   // [buffer][layer] : buffer 0 = caller's pre_hg arrays, buffer 1 = workspace
+  float* cg[2][2];
+  // workspace
+  float* z;             // [N][J] fp32 : g.W_pred of the current candidate
+  int32_t* lane_state;  // [N][8]: 0 cur, 1 need_lstm, 2 finished, 3 fixed, 4 fix_iter, 5 cur_t
+  int32_t* group_cnt;   // [NG][32] barrier arrival counters
+  int32_t* global_sync; // [0] groups done, [1] max iterations
+  int32_t* iters_out; int* status;
+  int NG, LG;           // groups, lanes per group
+};
+
+__global__ void greedy_decode_kernel(const DecParams p);
+
+}  // namespace rnnt

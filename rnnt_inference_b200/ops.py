@@ -1,0 +1,151 @@
+"""Functional wrappers over the C ABI: torch CUDA tensors in, torch CUDA tensors out.
+
+Plain row-major weights ([out_features, in_features]).  The reference-named operator surface (`_C.py`) and the
+modules are built on these.  Every function runs on the current CUDA stream and does not synchronise.
+"""
+import ctypes
+
+import torch
+
+from . import _lib as L
+
+H = 1024          # trans_hidden_size (models/config.py:4)
+P = 320           # pred_hidden_size
+J = 512           # joint_hidden_size
+V_PAD = 32        # num_labels 29 padded to 32 (modeling_rnnt.py:241-250)
+
+
+class Workspace:
+    """Grow-only cache of device scratch buffers keyed by (name, device); the C ABI never allocates."""
+
+    def __init__(self):
+        self._bufs = {}
+
+    def get(self, name, nbytes, device):
+        key = (name, str(device))
+        buf = self._bufs.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(max(int(nbytes), 256) + 256, dtype=torch.uint8, device=device)
+            self._bufs[key] = buf
+        off = (-buf.data_ptr()) % 256
+        return buf[off:off + int(nbytes)]
+
+
+_ws = Workspace()
+
+
+def quantize_pad(x, scale, k_out=None):
+    """fp32 [..., k_in] -> int8 [..., k_out] (zero padded). quant_tpp.cpp:6-17 + lstm_amx.cpp:48-50."""
+    L.require_cuda(x)
+    if x.dtype != torch.float32:
+        raise RuntimeError("quantize_pad expects float32 input")
+    k_in = x.shape[-1]
+    k_out = k_in if k_out is None else k_out
+    out = torch.empty(x.shape[:-1] + (k_out,), dtype=torch.int8, device=x.device)
+    rows = x.numel() // k_in
+    L.check(L.lib.rnnt_quantize_pad_f32_i8(L.ptr(x), L.ptr(out), float(scale), rows, k_in, k_out, L.stream_ptr()))
+    return out
+
+
+def gemm_i8_i32(a, w, out=None, simt=False):
+    """int8 [..., K] x int8 [N, K]^T -> int32 [..., N], exact."""
+    L.require_cuda(a, w)
+    k = a.shape[-1]
+    m = a.numel() // k
+    n = w.shape[0]
+    if w.shape[1] != k:
+        raise RuntimeError(f"gemm_i8_i32: K mismatch {k} vs {w.shape[1]}")
+    if out is None:
+        out = torch.empty(a.shape[:-1] + (n,), dtype=torch.int32, device=a.device)
+    fn = L.lib.rnnt_gemm_i8_i32_simt if simt else L.lib.rnnt_gemm_i8_i32
+    L.check(fn(L.ptr(a), L.ptr(w), L.ptr(out), m, n, k, L.stream_ptr()))
+    return out
+
+
+def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y):
+    """lstm_layer_amx_int8 (lstm_amx.cpp:59-158). x int8 [T,N,K]; hx int8 [N,H], cx fp16 [N,H] updated IN PLACE.
+    Returns y: int8 [T,N,H] or bf16 [T,N,H] when skip_quant_y."""
+    L.require_cuda(x, hx, cx, w_ih, w_hh, bias)
+    t, n, k = x.shape
+    if hx.dtype != torch.int8 or cx.dtype != torch.float16 or x.dtype != torch.int8:
+        raise RuntimeError("lstm_layer_i8: x/hx must be int8 and cx float16")
+    y = torch.empty((t, n, H), dtype=torch.bfloat16 if skip_quant_y else torch.int8, device=x.device)
+    if t == 0:
+        return y
+    g_ws = _ws.get("lstm_g", t * n * 4 * H * 4, x.device)
+    ws = _ws.get("lstm_rec", L.lib.rnnt_lstm_recurrent_workspace_bytes(n), x.device)
+    L.check(L.lib.rnnt_lstm_layer_i8(L.ptr(x), L.ptr(hx), L.ptr(cx), L.ptr(w_ih), L.ptr(w_hh), L.ptr(bias), float(rb_scale),
+                                     float(in_scale), float(out_scale), int(bool(skip_quant_y)), L.ptr(y), t, n, k, H,
+                                     L.ptr(g_ws), L.ptr(ws), L.stream_ptr()))
+    return y
+
+
+def lstm_recurrent_i8(g, hx, cx, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y):
+    """Phase B only (lstm_amx.cpp:122-152) on a precomputed int32 projection g [T,N,4H]."""
+    L.require_cuda(g, hx, cx, w_hh, bias)
+    t, n, _ = g.shape
+    y = torch.empty((t, n, H), dtype=torch.bfloat16 if skip_quant_y else torch.int8, device=g.device)
+    ws = _ws.get("lstm_rec", L.lib.rnnt_lstm_recurrent_workspace_bytes(n), g.device)
+    L.check(L.lib.rnnt_lstm_recurrent_i8(L.ptr(g), L.ptr(w_hh), L.ptr(bias), float(rb_scale), float(in_scale),
+                                         float(out_scale), int(bool(skip_quant_y)), L.ptr(hx), L.ptr(cx), L.ptr(y), t, n, H,
+                                         L.ptr(ws), L.stream_ptr()))
+    return y
+
+
+def stack_time(x, lens, factor):
+    """stack_time.cpp:27-59 — int8 {T,N,C} -> {ceil(T/f),N,C*f} with the per-sample zero tail."""
+    L.require_cuda(x, lens)
+    if x.dtype != torch.int8:
+        raise RuntimeError("stack_time: int8 only")
+    if lens.dtype != torch.int32:
+        lens = lens.to(torch.int32)
+    t, n, c = x.shape
+    t2 = (t + factor - 1) // factor
+    out = torch.empty((t2, n, c * factor), dtype=torch.int8, device=x.device)
+    L.check(L.lib.rnnt_stack_time_i8(L.ptr(x), L.ptr(lens), int(factor), L.ptr(out), t, n, c, L.stream_ptr()))
+    return out
+
+
+def linear_bf16_bf16(x, w):
+    """y = bf16(x . w^T) with the oracle's accumulation order (amx_linear.cpp:137-150, i16o16b0)."""
+    L.require_cuda(x, w)
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
+        raise RuntimeError("linear_bf16_bf16 expects bfloat16")
+    k = x.shape[-1]
+    m = x.numel() // k
+    o = w.shape[0]
+    y = torch.empty(x.shape[:-1] + (o,), dtype=torch.bfloat16, device=x.device)
+    L.check(L.lib.rnnt_linear_bf16_bf16(L.ptr(x), L.ptr(w), L.ptr(y), m, k, o, L.stream_ptr()))
+    return y
+
+
+def make_decode_weights(embed, w_ih, w_hh, bias, w_pred, b1, w2, b2):
+    """Pack device pointers into rnnt_decode_weights; keeps the tensors alive on the returned object."""
+    tensors = [embed, *w_ih, *w_hh, *bias, w_pred, b1, w2, b2]
+    L.require_cuda(*tensors)
+    if tuple(w2.shape) != (V_PAD, J) or tuple(b2.shape) != (V_PAD,):
+        raise RuntimeError("decode weights: fc2 must be padded to 32 rows (modeling_rnnt.py:241-250)")
+    dw = L.DecodeWeights()
+    dw.embed = embed.data_ptr()
+    for i in range(2):
+        dw.w_ih[i] = w_ih[i].data_ptr()
+        dw.w_hh[i] = w_hh[i].data_ptr()
+        dw.bias[i] = bias[i].data_ptr()
+    dw.w_pred, dw.b1, dw.w2, dw.b2 = w_pred.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr()
+    dw._keep = tensors
+    return dw
+
+
+def greedy_decode(y1, f_lens, dw, res, res_idx, symbols_added, time_idx, pre_g, pre_hg, pre_cg, iters_out=None):
+    """Device-resident decode loop (decoder.py:188-211). State tensors are updated in place."""
+    L.require_cuda(y1, f_lens, res, res_idx, symbols_added, time_idx, pre_g, *pre_hg, *pre_cg)
+    t2, n, j = y1.shape
+    assert j == J and y1.dtype == torch.bfloat16
+    for t in (f_lens, res, res_idx, symbols_added, time_idx, pre_g):
+        if t.dtype != torch.int32:
+            raise RuntimeError("greedy_decode: integer state must be int32")
+    ws = _ws.get("decode", L.lib.rnnt_greedy_decode_workspace_bytes(n), y1.device)
+    L.check(L.lib.rnnt_greedy_decode(L.ptr(y1), L.ptr(f_lens), t2, n, ctypes.byref(dw), L.ptr(res), res.shape[1],
+                                     L.ptr(res_idx), L.ptr(symbols_added), L.ptr(time_idx), L.ptr(pre_g), L.ptr(pre_hg[0]),
+                                     L.ptr(pre_hg[1]), L.ptr(pre_cg[0]), L.ptr(pre_cg[1]), L.ptr(iters_out), L.ptr(ws),
+                                     L.stream_ptr()))
