@@ -43,6 +43,12 @@ int rnnt_check_device_status(void* stream);
 int rnnt_quantize_pad_f32_i8(const float* in, int8_t* out, float scale, int64_t rows, int k_in, int k_out,
                              void* stream);
 
+/* Same quantiser fed from the SUT's ragged batch (models/pytorch_sut.py:85-104 pad_sequence + batch pad, then
+ * lstm_amx.cpp:35-50): packed [sum T_i][k_in] fp32, utterance n = rows [offsets[n], offsets[n]+lens[n]);
+ * out {T,N,k_out} int8 time-major, zero beyond lens[n] and beyond k_in (lens[n] = 0 for batch-padding lanes). */
+int rnnt_quantize_ragged_f32_i8(const float* packed, const int64_t* offsets, const int32_t* lens, int8_t* out, float scale, int T,
+                                int N, int k_in, int k_out, void* stream);
+
 /* i8o32b0 input projection over all timesteps (lstm_amx.cpp:96-113; tile_product_tpp.hpp:288-306):
  * C[M][N] int32 = A[M][K] int8 . W[N][K]^T int8, exact.  tcgen05 kind::i8, TMEM accumulators, TMA in/out.
  * Requirements: K % 16 == 0, N % 64 == 0, pointers 16-byte aligned. */
@@ -76,6 +82,28 @@ int rnnt_stack_time_i8(const int8_t* in, const int32_t* lens, int factor, int8_t
 /* Transcription half of Joint fc1, hoisted out of the decode loop (amx_linear.cpp:137-150, i16o16b0):
  * y1[M][J] bf16 = bf16(f[M][C] . W_trans[J][C]^T), fp32 FMA sequential in k (the order the oracle defines). */
 int rnnt_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, void* stream);
+
+/* Per-iteration operators of the reference's decode loop, for callers that keep the Python loop of
+ * models/decoder.py:188-211 (the fused rnnt_greedy_decode below is the fast path; these share its arithmetic).
+ *   amx_linear_i16o32 (init.cpp:36-38; amx_linear.cpp:113-117): y[M][O] fp32 = x.W^T + bias (bias may be NULL). */
+int rnnt_linear_bf16_f32(const uint16_t* x, const uint16_t* w, const float* bias, float* y, int64_t M, int K, int O,
+                         void* stream);
+/*   second half of amx_linear_bf16_accum_relu (init.cpp:33-35; amx_linear.cpp:152-168):
+ *   y[M][O] bf16 = bf16(max((x1.W1^T + float(y1)) + bias, 0)), y1 = rnnt_linear_bf16_bf16(x0, W0). */
+int rnnt_linear_bf16_accum_relu(const uint16_t* y1, const uint16_t* x1, const uint16_t* w1, const float* bias, uint16_t* y,
+                                int64_t M, int K1, int O, void* stream);
+/*   i8o32b32 dequant (amx_linear_i8o32, init.cpp:30-32; amx_linear.cpp:18-92): out = (float(acc) + bias[o]) * scale */
+int rnnt_dequant_i32_f32(const int32_t* acc, const float* bias, float scale, float* out, int64_t M, int O, void* stream);
+/*   lstm_layer_amx_bf16 at seq_len 1 (init.cpp:135-140; lstm_amx.cpp:187-264 + lstm_postop_tpp.cpp:100-163):
+ *   x [N][K], h [N][P] bf16, c [N][P] fp32 -> NEW hy bf16, cy fp32.  bias = b_ih + b_hh.  gates_ws: 2*N*4P floats. */
+int rnnt_lstm_cell_bf16(const uint16_t* x, const uint16_t* h, const float* c, const uint16_t* w_ih, const uint16_t* w_hh,
+                        const float* bias, uint16_t* hy, float* cy, int N, int K, int P, float* gates_ws, void* stream);
+/*   greedy_decode_update (init.cpp:141-143; greedy_decode_update.cpp:13-96).  State updated in place;
+ *   *unfinished (device int32) receives the number of lanes with time_idx < f_lens (0 <=> the op's `true`). */
+int rnnt_greedy_decode_update(const int64_t* symbols, int32_t* symbols_added, int32_t* res, int32_t* res_idx, const uint16_t* f,
+                              const int32_t* f_lens, int32_t* time_idx, uint16_t* fi, int32_t* pre_g, uint16_t* pre_hg0,
+                              uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, const uint16_t* hg0, const uint16_t* hg1,
+                              const float* cg0, const float* cg1, int N, int L, int C, int P, int32_t* unfinished, void* stream);
 
 /* Prediction + Joint + argmax + greedy_decode_update fused into one device-resident kernel
  * (models/decoder.py:171-212 loop; modeling_rnnt.py:183-205,259-289,335-365; greedy_decode_update.cpp:13-96).

@@ -34,6 +34,7 @@ _SIGS = {
     "rnnt_device_sm_count": (_i, []),
     "rnnt_check_device_status": (_i, [_vp]),
     "rnnt_quantize_pad_f32_i8": (_i, [_vp, _vp, _f, _i64, _i, _i, _vp]),
+    "rnnt_quantize_ragged_f32_i8": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),
     "rnnt_gemm_i8_i32": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "rnnt_gemm_i8_i32_simt": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "rnnt_lstm_recurrent_workspace_bytes": (_i64, [_i]),
@@ -41,6 +42,11 @@ _SIGS = {
     "rnnt_lstm_layer_i8": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_stack_time_i8": (_i, [_vp, _vp, _i, _vp, _i, _i, _i, _vp]),
     "rnnt_linear_bf16_bf16": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
+    "rnnt_linear_bf16_f32": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _vp]),
+    "rnnt_linear_bf16_accum_relu": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp]),
+    "rnnt_dequant_i32_f32": (_i, [_vp, _vp, _f, _vp, _i64, _i, _vp]),
+    "rnnt_lstm_cell_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "rnnt_greedy_decode_update": (_i, [_vp] * 17 + [_i, _i, _i, _i, _vp, _vp]),
     "rnnt_greedy_decode_workspace_bytes": (_i64, [_i]),
     "rnnt_greedy_decode": (_i, [_vp, _vp, _i, _i, ctypes.POINTER(DecodeWeights), _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp,
                                 _vp, _vp, _vp, _vp, _vp]),

@@ -84,6 +84,15 @@ inline int64_t round_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
 }  // namespace
 
+template <int MODE>
+static int linear_launch(const uint16_t* x, const uint16_t* w, const float* bias, const uint16_t* prev, void* y, int64_t M, int K,
+                         int O, cudaStream_t st) {
+  dim3 grid((O + LB_TO - 1) / LB_TO, (unsigned)((M + LB_TM - 1) / LB_TM));
+  linear_bf16_kernel<MODE><<<grid, 256, 0, st>>>(x, w, bias, prev, y, M, K, O);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
 // ================================================================================================
 extern "C" {
 
@@ -119,6 +128,21 @@ int rnnt_quantize_pad_f32_i8(const float* in, int8_t* out, float scale, int64_t 
   return RNNT_OK;
 }
 
+int rnnt_quantize_ragged_f32_i8(const float* packed, const int64_t* offsets, const int32_t* lens, int8_t* out, float scale, int T,
+                                int N, int k_in, int k_out, void* stream) {
+  if (!packed || !offsets || !lens || !out || T < 0 || N <= 0 || k_in <= 0 || k_out < k_in || (k_out & 3) || (k_in & 3) ||
+      !aligned(out, 4) || !aligned(packed, 16))
+    return fail(RNNT_ERR_INVALID, "quantize_ragged: need k_out >= k_in > 0, both %% 4 == 0, 16-byte aligned input (T=%d N=%d k_in=%d k_out=%d)",
+                T, N, k_in, k_out);
+  if (T == 0) return RNNT_OK;
+  const long long total = (long long)T * N * (k_out / 4);
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 148ll * 16);
+  quantize_ragged_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(packed, reinterpret_cast<const long long*>(offsets), lens, out,
+                                                                   scale, T, N, k_in, k_out);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
 int rnnt_stack_time_i8(const int8_t* in, const int32_t* lens, int factor, int8_t* out, int T, int N, int C, void* stream) {
   if (!in || !lens || !out || factor <= 0 || T < 0 || N <= 0 || C <= 0 || (C & 15) || !aligned(in, 16) || !aligned(out, 16))
     return fail(RNNT_ERR_INVALID, "stack_time: need C %% 16 == 0 and 16-byte aligned buffers (T=%d N=%d C=%d factor=%d)", T, N,
@@ -135,8 +159,63 @@ int rnnt_stack_time_i8(const int8_t* in, const int32_t* lens, int factor, int8_t
 int rnnt_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, void* stream) {
   if (!x || !w || !y || M < 0 || K <= 0 || O <= 0) return fail(RNNT_ERR_INVALID, "linear_bf16_bf16: bad arguments");
   if (M == 0) return RNNT_OK;
-  dim3 grid((O + LB_TO - 1) / LB_TO, (unsigned)((M + LB_TM - 1) / LB_TM));
-  linear_bf16_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, w, y, M, K, O);
+  return linear_launch<LIN_BF16>(x, w, nullptr, nullptr, y, M, K, O, (cudaStream_t)stream);
+}
+
+int rnnt_linear_bf16_f32(const uint16_t* x, const uint16_t* w, const float* bias, float* y, int64_t M, int K, int O,
+                         void* stream) {
+  if (!x || !w || !y || M < 0 || K <= 0 || O <= 0) return fail(RNNT_ERR_INVALID, "linear_bf16_f32: bad arguments");
+  if (M == 0) return RNNT_OK;
+  if (bias) return linear_launch<LIN_F32_BIAS>(x, w, bias, nullptr, y, M, K, O, (cudaStream_t)stream);
+  return linear_launch<LIN_F32>(x, w, nullptr, nullptr, y, M, K, O, (cudaStream_t)stream);
+}
+
+int rnnt_linear_bf16_accum_relu(const uint16_t* y1, const uint16_t* x1, const uint16_t* w1, const float* bias, uint16_t* y,
+                                int64_t M, int K1, int O, void* stream) {
+  if (!y1 || !x1 || !w1 || !bias || !y || M < 0 || K1 <= 0 || O <= 0)
+    return fail(RNNT_ERR_INVALID, "linear_bf16_accum_relu: bad arguments");
+  if (M == 0) return RNNT_OK;
+  return linear_launch<LIN_ACCUM_RELU>(x1, w1, bias, y1, y, M, K1, O, (cudaStream_t)stream);
+}
+
+int rnnt_dequant_i32_f32(const int32_t* acc, const float* bias, float scale, float* out, int64_t M, int O, void* stream) {
+  if (!acc || !out || M < 0 || O <= 0) return fail(RNNT_ERR_INVALID, "dequant_i32_f32: bad arguments");
+  if (M == 0) return RNNT_OK;
+  const long long total = M * O;
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 148ll * 16);
+  dequant_i32_f32_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(acc, bias, scale, out, total, O);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+int rnnt_lstm_cell_bf16(const uint16_t* x, const uint16_t* h, const float* c, const uint16_t* w_ih, const uint16_t* w_hh,
+                        const float* bias, uint16_t* hy, float* cy, int N, int K, int P, float* gates_ws, void* stream) {
+  if (!x || !h || !c || !w_ih || !w_hh || !bias || !hy || !cy || !gates_ws || N <= 0 || K <= 0 || P <= 0)
+    return fail(RNNT_ERR_INVALID, "lstm_cell_bf16: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* gi = gates_ws;
+  float* gh = gates_ws + (size_t)N * 4 * P;
+  if (int r = linear_launch<LIN_F32>(x, w_ih, nullptr, nullptr, gi, N, K, 4 * P, st)) return r;
+  if (int r = linear_launch<LIN_F32>(h, w_hh, nullptr, nullptr, gh, N, P, 4 * P, st)) return r;
+  const long long total = (long long)N * P;
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 148ll * 16);
+  lstm_postop_f32_kernel<<<blocks, 256, 0, st>>>(gi, gh, bias, c, hy, cy, N, P);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+int rnnt_greedy_decode_update(const int64_t* symbols, int32_t* symbols_added, int32_t* res, int32_t* res_idx, const uint16_t* f,
+                              const int32_t* f_lens, int32_t* time_idx, uint16_t* fi, int32_t* pre_g, uint16_t* pre_hg0,
+                              uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, const uint16_t* hg0, const uint16_t* hg1,
+                              const float* cg0, const float* cg1, int N, int L, int C, int P, int32_t* unfinished, void* stream) {
+  if (!symbols || !symbols_added || !res || !res_idx || !f || !f_lens || !time_idx || !fi || !pre_g || !pre_hg0 || !pre_hg1 ||
+      !pre_cg0 || !pre_cg1 || !hg0 || !hg1 || !cg0 || !cg1 || !unfinished || N <= 0 || L <= 0 || C <= 0 || P <= 0)
+    return fail(RNNT_ERR_INVALID, "greedy_decode_update: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemsetAsync(unfinished, 0, sizeof(int32_t), st));
+  greedy_update_kernel<<<(N + 7) / 8, 256, 0, st>>>(reinterpret_cast<const long long*>(symbols), symbols_added, res, res_idx, f,
+                                                    f_lens, time_idx, fi, pre_g, pre_hg0, pre_hg1, pre_cg0, pre_cg1, hg0, hg1,
+                                                    cg0, cg1, N, L, C, P, unfinished);
   CUDA_TRY(cudaGetLastError());
   return RNNT_OK;
 }

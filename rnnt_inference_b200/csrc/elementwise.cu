@@ -31,6 +31,44 @@ __global__ void quantize_pad_kernel(const float* __restrict__ in, int8_t* __rest
   }
 }
 
+// Ragged variant for the SUT: the batch arrives as the unpadded concatenation of its utterances (packed [sum T_i][k_in]
+// fp32, utterance n starting at row offsets[n]); this writes the time-major padded int8 tensor {T, N, k_out} that
+// pad_sequence + lstm_amx_int8's quantiser would have produced (models/pytorch_sut.py:85-104, lstm_amx.cpp:35-50):
+// out[t][n][k] = t < lens[n] && k < k_in ? q(packed[offsets[n] + t][k]) : 0.  Rows n >= n_valid are all zero (batch pad).
+__global__ void quantize_ragged_kernel(const float* __restrict__ packed, const long long* __restrict__ offsets,
+                                       const int32_t* __restrict__ lens, int8_t* __restrict__ out, float scale, int T, int N,
+                                       int k_in, int k_out) {
+  const int words_per_row = k_out >> 2;
+  const long long total = (long long)T * N * words_per_row;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int wi = (int)(i % words_per_row);
+    const long long r = i / words_per_row;
+    const int n = (int)(r % N), t = (int)(r / N);
+    const int k0 = wi << 2;
+    uint32_t packed_q = 0;
+    if (t < lens[n] && k0 < k_in) {
+      const float* src = packed + (offsets[n] + t) * k_in + k0;
+      if (k0 + 3 < k_in) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(src));
+        const float xs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float m = rintf(__fmul_rn(xs[j], scale));
+          m = fmaxf(fminf(m, 127.f), -128.f);
+          packed_q |= ((uint32_t)(int)m & 0xffu) << (8 * j);
+        }
+      } else {
+        for (int j = 0; j < 4 && k0 + j < k_in; ++j) {
+          float m = rintf(__fmul_rn(src[j], scale));
+          m = fmaxf(fminf(m, 127.f), -128.f);
+          packed_q |= ((uint32_t)(int)m & 0xffu) << (8 * j);
+        }
+      }
+    }
+    reinterpret_cast<uint32_t*>(out)[i] = packed_q;
+  }
+}
+
 // stack_time (stack_time.cpp:27-59), 16 bytes per thread.  out[t2][n][(t%f)*C + c] = in[t][n][c] if t < lens[n] else 0.
 __global__ void stack_time_kernel(const int8_t* __restrict__ in, const int32_t* __restrict__ lens, int factor,
                                   int8_t* __restrict__ out, int T, int N, int C) {
@@ -49,12 +87,18 @@ __global__ void stack_time_kernel(const int8_t* __restrict__ in, const int32_t* 
   }
 }
 
-// y[m][o] = bf16( sum_k x[m][k] * w[o][k] ), fp32 FMA sequential in k from 0 (oracle order; i16o16b0,
-// amx_linear.cpp:137-150).  CTA tile 64 rows x 64 outputs; one thread owns a 4x4 block of outputs (16 independent
-// chains), operands staged in shared memory as fp32 in k-chunks of 32.
+// Order-defined bf16 linear: acc[m][o] = sum_k x[m][k] * w[o][k], fp32 FMA sequential in k from 0 (the order the oracle
+// defines for the AMX bf16 kernels, tile_product_tpp.hpp:563-581).  CTA tile 64 rows x 64 outputs; one thread owns a
+// 4x4 block of outputs (16 independent chains), operands staged in shared memory as fp32 in k-chunks of 32.
+// Epilogues (tile_product_tpp.hpp:347-449):
+//   LIN_BF16        y_bf16 = bf16(acc)                                        i16o16b0       (amx_linear.cpp:137-150)
+//   LIN_F32_BIAS    y_f32  = acc + bias                                       i16o32b32      (amx_linear.cpp:113-117)
+//   LIN_F32         y_f32  = acc                                              i16o32b0       (lstm_amx.cpp:218-232)
+//   LIN_ACCUM_RELU  y_bf16 = bf16(max((acc + float(prev_bf16)) + bias, 0))    i16o16b32_accum_relu (amx_linear.cpp:152-168)
+template <int MODE>
 __global__ void __launch_bounds__(256)
-linear_bf16_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w, uint16_t* __restrict__ y,
-                        long long M, int K, int O) {
+linear_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w, const float* __restrict__ bias,
+                   const uint16_t* __restrict__ prev, void* __restrict__ yout, long long M, int K, int O) {
   __shared__ float xs[LB_TK][LB_TM + 4];
   __shared__ float ws[LB_TK][LB_TO + 4];
   const long long m0 = (long long)blockIdx.y * LB_TM;
@@ -67,7 +111,6 @@ linear_bf16_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restri
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
   for (int k0 = 0; k0 < K; k0 += LB_TK) {
-    // stage: 64 rows x 32 k of x and of w (each thread 8 elements of each)
     for (int e = threadIdx.x; e < LB_TM * LB_TK; e += 256) {
       const int r = e / LB_TK, kk = e % LB_TK;
       const long long m = m0 + r;
@@ -97,8 +140,95 @@ linear_bf16_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restri
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int o = o0 + to + j;
-      if (o < O) y[m * O + o] = (uint16_t)float_to_bf16_bits(acc[i][j]);
+      if (o >= O) continue;
+      const long long idx = m * O + o;
+      if constexpr (MODE == LIN_BF16) {
+        reinterpret_cast<uint16_t*>(yout)[idx] = (uint16_t)float_to_bf16_bits(acc[i][j]);
+      } else if constexpr (MODE == LIN_F32_BIAS) {
+        reinterpret_cast<float*>(yout)[idx] = __fadd_rn(acc[i][j], bias[o]);
+      } else if constexpr (MODE == LIN_F32) {
+        reinterpret_cast<float*>(yout)[idx] = acc[i][j];
+      } else {
+        const float v = __fadd_rn(__fadd_rn(acc[i][j], bf16_bits_to_float(prev[idx])), bias[o]);
+        reinterpret_cast<uint16_t*>(yout)[idx] = (uint16_t)float_to_bf16_bits(fmaxf(v, 0.f));
+      }
     }
+  }
+}
+template __global__ void linear_bf16_kernel<LIN_BF16>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
+template __global__ void linear_bf16_kernel<LIN_F32_BIAS>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
+template __global__ void linear_bf16_kernel<LIN_F32>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
+template __global__ void linear_bf16_kernel<LIN_ACCUM_RELU>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
+
+// dequant of an int32 accumulator (i8o32b32, tile_product_tpp.hpp:347-367 for int8): (float(acc) + bias[o]) * scale,
+// two separately rounded fp32 operations.
+__global__ void dequant_i32_f32_kernel(const int32_t* __restrict__ acc, const float* __restrict__ bias, float scale,
+                                       float* __restrict__ out, long long total, int O) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const float b = bias ? bias[i % O] : 0.f;
+    out[i] = __fmul_rn(__fadd_rn(__int2float_rn(acc[i]), b), scale);
+  }
+}
+
+// lstm_postop_tpp::ref_bf16 (tpps/lstm_postop_tpp.cpp:100-163) preceded by the float_out_accum epilogue
+// (tile_product_tpp.hpp:387-408): gate = (gh + gi) + bias.  gi, gh [N][4P] fp32; c_in [N][P]; writes hy bf16, cy fp32.
+__global__ void lstm_postop_f32_kernel(const float* __restrict__ gi, const float* __restrict__ gh, const float* __restrict__ bias,
+                                       const float* __restrict__ c_in, uint16_t* __restrict__ hy, float* __restrict__ cy,
+                                       int N, int P) {
+  const long long total = (long long)N * P;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / P), j = (int)(i % P);
+    float gate[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const long long gidx = (long long)n * 4 * P + q * P + j;
+      gate[q] = __fadd_rn(__fadd_rn(gh[gidx], gi[gidx]), bias[q * P + j]);
+    }
+    const float it = sigmoid_ps(gate[0]), ft = sigmoid_ps(gate[1]), gt = tanh_ps(gate[2]), ot = sigmoid_ps(gate[3]);
+    const float c_new = __fmaf_rn(it, gt, __fmul_rn(ft, c_in[i]));
+    cy[i] = c_new;
+    hy[i] = (uint16_t)float_to_bf16_bits(__fmul_rn(ot, tanh_ps(c_new)));
+  }
+}
+
+// greedy_decode_update (greedy_decode_update.cpp:13-96 + tpps/greedy_decode_update_tpp.cpp:9-51): one warp per lane.
+// unfinished: device int, incremented once per lane that has not finished (caller zeroes it first).
+__global__ void greedy_update_kernel(const long long* __restrict__ symbols, int32_t* symbols_added, int32_t* res, int32_t* res_idx,
+                                     const uint16_t* __restrict__ f, const int32_t* __restrict__ f_lens, int32_t* time_idx,
+                                     uint16_t* fi, int32_t* pre_g, uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0,
+                                     float* pre_cg1, const uint16_t* __restrict__ hg0, const uint16_t* __restrict__ hg1,
+                                     const float* __restrict__ cg0, const float* __restrict__ cg1, int N, int L, int C, int P,
+                                     int* unfinished) {
+  const int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  const int sym = (int)symbols[n];
+  const int flen = f_lens[n];
+  const bool upd_g = (sym != 28) && (symbols_added[n] != 30) && (flen != 0);
+  int ti = time_idx[n];
+  __syncwarp();
+  if (upd_g) {
+    if (lane == 0) {
+      const int ri = res_idx[n] + 1;
+      res_idx[n] = ri;
+      if (ri >= 0 && ri < L) res[(long long)n * L + ri] = sym;
+      symbols_added[n] += 1;
+      pre_g[n] = sym;
+    }
+    for (int k = lane; k < P; k += 32) {
+      pre_hg0[(long long)n * P + k] = hg0[(long long)n * P + k];
+      pre_hg1[(long long)n * P + k] = hg1[(long long)n * P + k];
+      pre_cg0[(long long)n * P + k] = cg0[(long long)n * P + k];
+      pre_cg1[(long long)n * P + k] = cg1[(long long)n * P + k];
+    }
+  } else {
+    ti += 1;
+    if (lane == 0) { symbols_added[n] = 0; time_idx[n] = ti; }
+  }
+  if (ti < flen) {
+    const uint16_t* src = f + ((long long)ti * N + n) * C;
+    for (int k = lane; k < C; k += 32) fi[(long long)n * C + k] = src[k];
+    if (lane == 0) atomicAdd(unfinished, 1);
   }
 }
 

@@ -70,10 +70,27 @@ __global__ void lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w
 constexpr int LB_TM = 64, LB_TO = 64, LB_TK = 32;
 __global__ void quantize_pad_kernel(const float* __restrict__ in, int8_t* __restrict__ out, float scale, long long rows,
                                     int k_in, int k_out);
+__global__ void quantize_ragged_kernel(const float* __restrict__ packed, const long long* __restrict__ offsets,
+                                       const int32_t* __restrict__ lens, int8_t* __restrict__ out, float scale, int T, int N,
+                                       int k_in, int k_out);
 __global__ void stack_time_kernel(const int8_t* __restrict__ in, const int32_t* __restrict__ lens, int factor,
                                   int8_t* __restrict__ out, int T, int N, int C);
-__global__ void linear_bf16_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w,
-                                        uint16_t* __restrict__ y, long long M, int K, int O);
+enum : int { LIN_BF16 = 0, LIN_F32_BIAS = 1, LIN_F32 = 2, LIN_ACCUM_RELU = 3 };
+template <int MODE>
+__global__ void linear_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w,
+                                   const float* __restrict__ bias, const uint16_t* __restrict__ prev, void* __restrict__ y,
+                                   long long M, int K, int O);
+__global__ void dequant_i32_f32_kernel(const int32_t* __restrict__ acc, const float* __restrict__ bias, float scale,
+                                       float* __restrict__ out, long long total, int O);
+__global__ void lstm_postop_f32_kernel(const float* __restrict__ gi, const float* __restrict__ gh, const float* __restrict__ bias,
+                                       const float* __restrict__ c_in, uint16_t* __restrict__ hy, float* __restrict__ cy,
+                                       int N, int P);
+__global__ void greedy_update_kernel(const long long* __restrict__ symbols, int32_t* symbols_added, int32_t* res, int32_t* res_idx,
+                                     const uint16_t* __restrict__ f, const int32_t* __restrict__ f_lens, int32_t* time_idx,
+                                     uint16_t* fi, int32_t* pre_g, uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0,
+                                     float* pre_cg1, const uint16_t* __restrict__ hg0, const uint16_t* __restrict__ hg1,
+                                     const float* __restrict__ cg0, const float* __restrict__ cg1, int N, int L, int C, int P,
+                                     int* unfinished);
 
 // ------------------------------------------------------------------ greedy_decode.cu
 constexpr int DEC_P = 320, DEC_J = 512, DEC_V = 32;

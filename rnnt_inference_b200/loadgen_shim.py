@@ -1,0 +1,168 @@
+"""Minimal in-process stand-in for the `mlperf_loadgen` Python binding (absent offline).
+
+Only what models/pytorch_sut.py, models/rnnt_qsl.py and models/main.py touch: QuerySample / QuerySampleResponse,
+ConstructSUT / ConstructQSL / Destroy*, QuerySamplesComplete, TestSettings / TestScenario / TestMode and StartTest
+for the Offline scenario (one query holding every sample; result = samples / (last completion - issue)) and the
+Server scenario (Poisson arrivals at target_qps; per-sample latency percentiles).  pytorch_sut.py imports the real
+`mlperf_loadgen` when it is installed and falls back to this module otherwise.
+"""
+import ctypes
+import enum
+import threading
+import time
+
+import numpy as np
+
+
+class TestScenario(enum.Enum):
+    SingleStream = 0
+    Offline = 1
+    Server = 2
+
+
+class TestMode(enum.Enum):
+    PerformanceOnly = 0
+    AccuracyOnly = 1
+
+
+class TestSettings:
+    def __init__(self):
+        self.scenario = TestScenario.Offline
+        self.mode = TestMode.PerformanceOnly
+        self.min_query_count = 0           # Offline: samples in the single query (0 = the QSL's performance count)
+        self.server_target_qps = 100.0
+        self.server_duration_s = 5.0
+        self.server_seed = 20240607
+
+    def FromConfig(self, path, model, scenario):   # mlperf.conf / user.conf parsing is not needed offline
+        return 0
+
+
+class QuerySample:
+    __slots__ = ("id", "index")
+
+    def __init__(self, id, index):
+        self.id = id
+        self.index = index
+
+
+class QuerySampleResponse:
+    __slots__ = ("id", "data", "size")
+
+    def __init__(self, id, data, size):
+        self.id = id
+        self.data = data
+        self.size = size
+
+
+class _SUT:
+    def __init__(self, issue, flush):
+        self.issue, self.flush = issue, flush
+
+
+class _QSL:
+    def __init__(self, count, perf_count, load, unload):
+        self.count, self.perf_count, self.load, self.unload = count, perf_count, load, unload
+
+
+def ConstructSUT(issue_queries, flush_queries):
+    return _SUT(issue_queries, flush_queries)
+
+
+def ConstructQSL(count, perf_count, load_cb, unload_cb):
+    return _QSL(count, perf_count, load_cb, unload_cb)
+
+
+def DestroySUT(sut):
+    pass
+
+
+def DestroyQSL(qsl):
+    pass
+
+
+class _Run:
+    """Bookkeeping of the test in flight (the shim runs one test at a time, like LoadGen)."""
+
+    def __init__(self, mode):
+        self.mode = mode
+        self.lock = threading.Lock()
+        self.issue_time = {}
+        self.done_time = {}
+        self.accuracy = {}
+
+
+_run = None
+
+
+def QuerySamplesComplete(responses):
+    now = time.perf_counter()
+    run = _run
+    if run is None:
+        return
+    with run.lock:
+        for r in responses:
+            run.done_time[r.id] = now
+            if run.mode == TestMode.AccuracyOnly:
+                run.accuracy[r.id] = ctypes.string_at(r.data, int(r.size)) if r.size else b""
+
+
+def StartTest(sut, qsl, settings):
+    """Runs one test; returns a dict with the result (the real LoadGen writes mlperf_log_summary.txt instead)."""
+    global _run
+    _run = run = _Run(settings.mode)
+    count = settings.min_query_count or qsl.perf_count
+    indices = [i % qsl.count for i in range(count)]
+    qsl.load(sorted(set(indices)))
+    samples = [QuerySample(i + 1, idx) for i, idx in enumerate(indices)]
+    result = {"scenario": settings.scenario.name, "mode": settings.mode.name, "samples": count}
+    if settings.scenario == TestScenario.Offline:
+        t0 = time.perf_counter()
+        for s in samples:
+            run.issue_time[s.id] = t0
+        sut.issue(samples)
+        sut.flush()
+        t1 = max(run.done_time.values()) if run.done_time else time.perf_counter()
+        result.update(seconds=t1 - t0, samples_per_second=len(run.done_time) / max(t1 - t0, 1e-9),
+                      completed=len(run.done_time))
+    else:
+        rng = np.random.default_rng(settings.server_seed)
+        n = min(count, max(1, int(settings.server_target_qps * settings.server_duration_s)))
+        gaps = rng.exponential(1.0 / settings.server_target_qps, size=n)
+        t0 = time.perf_counter()
+        due = t0
+        for i in range(n):
+            due += gaps[i]
+            delay = due - time.perf_counter()
+            if delay > 0:
+                time.sleep(delay)
+            run.issue_time[samples[i].id] = time.perf_counter()
+            sut.issue([samples[i]])
+        sut.flush()
+        deadline = time.perf_counter() + 60.0
+        while len(run.done_time) < n and time.perf_counter() < deadline:
+            time.sleep(0.001)
+        lat = np.array([run.done_time[k] - run.issue_time[k] for k in run.done_time])
+        t1 = max(run.done_time.values()) if run.done_time else time.perf_counter()
+        result.update(seconds=t1 - t0, completed=len(lat), samples_per_second=len(lat) / max(t1 - t0, 1e-9),
+                      latency_p50_ms=float(np.percentile(lat, 50) * 1e3) if len(lat) else None,
+                      latency_p99_ms=float(np.percentile(lat, 99) * 1e3) if len(lat) else None)
+    if settings.mode == TestMode.AccuracyOnly:
+        # same content as mlperf_log_accuracy.json entries: qsl_idx + hex of the int32 token bytes (eval_accuracy.py:85-101)
+        result["accuracy_log"] = [{"qsl_idx": s.index, "data": run.accuracy.get(s.id, b"").hex()} for s in samples
+                                  if s.id in run.accuracy]
+    _run = None
+    return result
+
+
+def StartTestWithLogSettings(sut, qsl, settings, log_settings=None):
+    return StartTest(sut, qsl, settings)
+
+
+class LogOutputSettings:
+    outdir = "."
+    copy_summary_to_stdout = False
+
+
+class LogSettings:
+    log_output = None

@@ -47,6 +47,19 @@ def quantize_pad(x, scale, k_out=None):
     return out
 
 
+def quantize_ragged(packed, offsets, lens, scale, t_max, k_out):
+    """Ragged batch -> padded time-major int8 {t_max, N, k_out} (pad_sequence + quantise + K pad in one pass)."""
+    L.require_cuda(packed, offsets, lens)
+    if packed.dtype != torch.float32 or offsets.dtype != torch.int64 or lens.dtype != torch.int32:
+        raise RuntimeError("quantize_ragged expects float32 features, int64 offsets, int32 lens")
+    n = lens.numel()
+    k_in = packed.shape[-1]
+    out = torch.empty((t_max, n, k_out), dtype=torch.int8, device=packed.device)
+    L.check(L.lib.rnnt_quantize_ragged_f32_i8(L.ptr(packed), L.ptr(offsets), L.ptr(lens), L.ptr(out), float(scale), int(t_max), n,
+                                              k_in, int(k_out), L.stream_ptr()))
+    return out
+
+
 def gemm_i8_i32(a, w, out=None, simt=False):
     """int8 [..., K] x int8 [N, K]^T -> int32 [..., N], exact."""
     L.require_cuda(a, w)
@@ -149,3 +162,75 @@ def greedy_decode(y1, f_lens, dw, res, res_idx, symbols_added, time_idx, pre_g, 
                                      L.ptr(res_idx), L.ptr(symbols_added), L.ptr(time_idx), L.ptr(pre_g), L.ptr(pre_hg[0]),
                                      L.ptr(pre_hg[1]), L.ptr(pre_cg[0]), L.ptr(pre_cg[1]), L.ptr(iters_out), L.ptr(ws),
                                      L.stream_ptr()))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# per-iteration operators of the reference decode loop (same arithmetic as the fused kernel)
+def linear_bf16_f32(x, w, bias=None):
+    """amx_linear_i16o32 (amx_linear.cpp:113-117): fp32 [..., O] = x . w^T + bias."""
+    L.require_cuda(x, w, bias)
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
+        raise RuntimeError("linear_bf16_f32 expects bfloat16 x / w")
+    k = x.shape[-1]
+    m = x.numel() // k
+    o = w.shape[0]
+    y = torch.empty(x.shape[:-1] + (o,), dtype=torch.float32, device=x.device)
+    L.check(L.lib.rnnt_linear_bf16_f32(L.ptr(x), L.ptr(w), L.ptr(bias), L.ptr(y), m, k, o, L.stream_ptr()))
+    return y
+
+
+def linear_bf16_accum_relu(y1, x1, w1, bias):
+    """second half of amx_linear_bf16_accum_relu (amx_linear.cpp:152-168); y1 = linear_bf16_bf16(x0, w0)."""
+    L.require_cuda(y1, x1, w1, bias)
+    for t in (y1, x1, w1):
+        if t.dtype != torch.bfloat16:
+            raise RuntimeError("linear_bf16_accum_relu expects bfloat16")
+    k = x1.shape[-1]
+    m = x1.numel() // k
+    o = w1.shape[0]
+    if y1.numel() != m * o:
+        raise RuntimeError("linear_bf16_accum_relu: y1 shape mismatch")
+    y = torch.empty(x1.shape[:-1] + (o,), dtype=torch.bfloat16, device=x1.device)
+    L.check(L.lib.rnnt_linear_bf16_accum_relu(L.ptr(y1), L.ptr(x1), L.ptr(w1), L.ptr(bias), L.ptr(y), m, k, o, L.stream_ptr()))
+    return y
+
+
+def dequant_i32_f32(acc, bias, scale):
+    """(float(acc) + bias) * scale — the i8o32b32 epilogue (amx_linear.cpp:18-92)."""
+    L.require_cuda(acc, bias)
+    o = acc.shape[-1]
+    out = torch.empty(acc.shape, dtype=torch.float32, device=acc.device)
+    L.check(L.lib.rnnt_dequant_i32_f32(L.ptr(acc), L.ptr(bias), float(scale), L.ptr(out), acc.numel() // o, o, L.stream_ptr()))
+    return out
+
+
+def lstm_cell_bf16(x, h, c, w_ih, w_hh, bias):
+    """lstm_layer_amx_bf16 at seq_len 1 (lstm_amx.cpp:187-264). Returns NEW (hy bf16, cy fp32)."""
+    L.require_cuda(x, h, c, w_ih, w_hh, bias)
+    n, k = x.shape
+    p = h.shape[1]
+    hy = torch.empty((n, p), dtype=torch.bfloat16, device=x.device)
+    cy = torch.empty((n, p), dtype=torch.float32, device=x.device)
+    ws = _ws.get("cell_gates", 2 * n * 4 * p * 4, x.device)
+    L.check(L.lib.rnnt_lstm_cell_bf16(L.ptr(x), L.ptr(h), L.ptr(c), L.ptr(w_ih), L.ptr(w_hh), L.ptr(bias), L.ptr(hy), L.ptr(cy),
+                                      n, k, p, L.ptr(ws), L.stream_ptr()))
+    return hy, cy
+
+
+def greedy_decode_update(symbols, symbols_added, res, res_idx, f, f_lens, time_idx, fi, pre_g, pre_hg, pre_cg, hg, cg):
+    """greedy_decode_update.cpp:13-96; in place; returns True when all lanes finished."""
+    L.require_cuda(symbols, symbols_added, res, res_idx, f, f_lens, time_idx, fi, pre_g, *pre_hg, *pre_cg, *hg, *cg)
+    if symbols.dtype != torch.int64:
+        raise RuntimeError("greedy_decode_update: symbols must be int64 (greedy_decode_update.cpp:25)")
+    for t in (symbols_added, res, res_idx, f_lens, time_idx, pre_g):
+        if t.dtype != torch.int32:
+            raise RuntimeError("greedy_decode_update: counters must be int32 (greedy_decode_update.cpp:26-43)")
+    n, l = res.shape
+    c = f.shape[2]
+    p = hg[0].shape[1]
+    flag = _ws.get("update_flag", 256, res.device)
+    L.check(L.lib.rnnt_greedy_decode_update(L.ptr(symbols), L.ptr(symbols_added), L.ptr(res), L.ptr(res_idx), L.ptr(f),
+                                            L.ptr(f_lens), L.ptr(time_idx), L.ptr(fi), L.ptr(pre_g), L.ptr(pre_hg[0]),
+                                            L.ptr(pre_hg[1]), L.ptr(pre_cg[0]), L.ptr(pre_cg[1]), L.ptr(hg[0]), L.ptr(hg[1]),
+                                            L.ptr(cg[0]), L.ptr(cg[1]), n, l, c, p, L.ptr(flag), L.stream_ptr()))
+    return int(flag[:4].view(torch.int32).item()) == 0

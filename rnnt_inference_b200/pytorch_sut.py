@@ -1,0 +1,208 @@
+"""System under test (reference: models/pytorch_sut.py:20-125).
+
+PytorchSUT(model_path, dataset_dir, batch_size, run_mode, args) with the reference's issue/complete contract:
+  issue_queries(samples)      Offline: sort by feature length descending, cut into batch_size chunks, run each,
+                              respond per chunk (pytorch_sut.py:58-65)
+  inference(batch_idx)        pad T to the batch maximum, pad N up to a multiple of 32 with zero-length lanes
+                              (:85-104), run the greedy decoder, return (res, res_len)
+  query_samples_complete(...) one QuerySampleResponse(id, ptr, n_tokens * 4) + one QuerySamplesComplete per sample
+                              (:107-118); tokens are int32
+What changes underneath on the B200: the batch travels as the UNPADDED concatenation of its utterances (one async
+copy per pinned sample on a copy stream), padding/quantisation happen in one device kernel, and the Offline loop is
+software-pipelined — batch i+1 is staged while batch i computes and batch i-1 is answered — so the GPU never waits
+for the host.  Results are identical to the synchronous order.
+"""
+import math
+import os
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+try:
+    import mlperf_loadgen as lg
+except ImportError:   # not installed offline
+    from . import loadgen_shim as lg
+
+from .decoder import GreedyDecoder
+from .modeling_rnnt import RNNT
+from .rnnt_qsl import RNNTQSL
+from .utils import logger, seq_to_sen
+
+_DEFAULT_ARGS = dict(enable_bf16=False, split_len=-1, scenario="Offline", load_jit=False, save_jit=False,
+                     enable_process=False, toml_path="", processor_path="")
+
+
+class _Batch:
+    """One staged / in-flight batch of the pipelined Offline loop."""
+    __slots__ = ("samples", "n_actual", "n_padded", "max_len", "packed", "meta", "ready", "done", "res", "res_len", "tok_host",
+                 "len_host", "cap", "h2d_bytes", "keep")
+
+
+class PytorchSUT:
+    def __init__(self, model_path, dataset_dir, batch_size=1, run_mode=None, args=None, **kwargs):
+        merged = dict(_DEFAULT_ARGS)
+        if args is not None:
+            merged.update({k: v for k, v in vars(args).items()})
+        merged.update(kwargs)
+        args = SimpleNamespace(**merged)
+        if args.enable_process:
+            raise RuntimeError("the audio front-end (--enable_process) is outside this package's scope: feed pre-extracted "
+                               "240-dim stacked filterbank features, as launch_sut.sh does without --processor")
+        self.processor = None
+        self.enable_process = False
+        self.batch_size = batch_size
+        self.run_mode = run_mode
+        self.device = kwargs.get("device")
+        rnnt = RNNT(model_path, run_mode, args.enable_bf16, args.load_jit, device=self.device).eval()
+        self.model = GreedyDecoder(rnnt, run_mode, args.enable_bf16, args.split_len, self.batch_size)
+        self.scenario = args.scenario if run_mode != "calib" else None
+        self.batch_sort = self.scenario == "Offline"
+        self.pipelined = run_mode == "quant" and args.split_len == -1
+        self.qsl = RNNTQSL(dataset_dir)
+        self.sut = lg.ConstructSUT(self.issue_queries, self.flush_queries)
+        self.h2d_bytes = 0          # running totals, read by bench.py
+        self.d2h_bytes = 0
+        self.batches_run = 0
+        if self.pipelined:
+            dev = self.model.device
+            self._copy_stream = torch.cuda.Stream(dev)
+            self._compute_stream = torch.cuda.Stream(dev)
+            self._packed = [None, None]         # double-buffered device staging of the ragged batch
+            self._slot = 0
+            self._prev_done = [None, None]
+
+    # --------------------------------------------------------------------------------------------- LoadGen entry
+    def issue_queries(self, samples):
+        if self.batch_sort:
+            samples.sort(key=lambda s: int(self.qsl[s.index][1]), reverse=True)
+        chunks = [samples[i:i + self.batch_size] for i in range(0, len(samples), self.batch_size)]
+        if not self.pipelined:
+            for chunk in chunks:
+                results, results_idx = self.inference([s.index for s in chunk])
+                self.query_samples_complete(chunk, results, results_idx)
+            return
+        staged = self._stage(chunks[0]) if chunks else None
+        in_flight = None
+        for i in range(len(chunks)):
+            current = staged
+            self._launch(current)
+            staged = self._stage(chunks[i + 1]) if i + 1 < len(chunks) else None
+            if in_flight is not None:
+                self._finish(in_flight)
+            in_flight = current
+        if in_flight is not None:
+            self._finish(in_flight)
+
+    def flush_queries(self):
+        pass
+
+    # --------------------------------------------------------------------------------------------- pipelined path
+    def _stage(self, chunk):
+        """Host->device copy of one batch on the copy stream: every pinned sample goes straight into its slice of a
+        packed [sum T_i, 240] device buffer; offsets and lengths travel as one small tensor."""
+        dev = self.model.device
+        b = _Batch()
+        b.samples = chunk
+        b.n_actual = len(chunk)
+        b.n_padded = math.ceil(b.n_actual / 32) * 32          # pytorch_sut.py:90-104: pad N to a multiple of 32
+        feats = [self.qsl[s.index][0] for s in chunk]
+        lens = [int(f.shape[0]) for f in feats]
+        b.max_len = max(lens)
+        meta = torch.zeros((2, b.n_padded), dtype=torch.int64)
+        meta[0, :b.n_actual] = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]), dtype=torch.int64)
+        meta[1, :b.n_actual] = torch.tensor(lens, dtype=torch.int64)
+        total = int(sum(lens))
+        slot = self._slot
+        self._slot ^= 1
+        with torch.cuda.stream(self._copy_stream):
+            if self._prev_done[slot] is not None:
+                self._copy_stream.wait_event(self._prev_done[slot])   # the buffer's previous batch must have been consumed
+            buf = self._packed[slot]
+            if buf is None or buf.shape[0] < total:
+                grow = max(total, self.batch_size * 512)
+                buf = torch.empty((grow, feats[0].shape[1]), dtype=torch.float32, device=dev)
+                self._packed[slot] = buf
+            off = 0
+            for f, n in zip(feats, lens):
+                buf[off:off + n].copy_(f, non_blocking=True)
+                off += n
+            meta_host = meta.pin_memory()
+            b.meta = meta_host.to(dev, non_blocking=True)
+            b.packed = buf
+            b.ready = torch.cuda.Event()
+            b.ready.record(self._copy_stream)
+        b.keep = (meta_host, slot)
+        b.h2d_bytes = total * feats[0].shape[1] * 4 + meta.numel() * 8
+        return b
+
+    def _launch(self, b):
+        """Encoder + fused decode of a staged batch on the compute stream, then the (small) result copy back."""
+        with torch.cuda.stream(self._compute_stream), torch.no_grad():
+            self._compute_stream.wait_event(b.ready)
+            offsets = b.meta[0]
+            lens = b.meta[1].to(torch.int32)
+            b.res, b.res_len = self.model.forward_ragged(b.packed, offsets, lens, b.max_len)
+            # tokens: almost always fewer than one per stacked frame; the rare longer row is fetched in _finish
+            b.cap = min(b.res.shape[1], max(32, (b.max_len + 1) // 2))
+            b.tok_host = torch.empty((b.n_padded, b.cap), dtype=torch.int32, pin_memory=True)
+            b.len_host = torch.empty((b.n_padded,), dtype=torch.int32, pin_memory=True)
+            b.tok_host.copy_(b.res[:, :b.cap], non_blocking=True)
+            b.len_host.copy_(b.res_len, non_blocking=True)
+            b.done = torch.cuda.Event()
+            b.done.record(self._compute_stream)
+        self._prev_done[b.keep[1]] = b.done
+
+    def _finish(self, b):
+        b.done.synchronize()
+        lens = b.len_host.numpy()
+        tokens = b.tok_host.numpy()
+        self.h2d_bytes += b.h2d_bytes
+        self.d2h_bytes += tokens.nbytes + lens.nbytes
+        self.batches_run += 1
+        if int(lens[:b.n_actual].max(initial=0)) > b.cap:
+            with torch.cuda.stream(self._compute_stream):
+                full = b.res[:b.n_actual].cpu()
+            tokens = full.numpy()
+            self.d2h_bytes += tokens.nbytes
+        self._respond(b.samples, tokens, lens)
+
+    def _respond(self, samples, tokens, lens):
+        """query_samples_complete (pytorch_sut.py:107-118) on host arrays: pointer into the row, n_tokens * 4 bytes."""
+        base, stride = tokens.ctypes.data, tokens.strides[0]
+        debug = logger.isEnabledFor(10)
+        for i, s in enumerate(samples):
+            n = int(lens[i])
+            lg.QuerySamplesComplete([lg.QuerySampleResponse(s.id, base + i * stride, n * 4)])
+            if debug:
+                logger.debug(f"{s.index}::{seq_to_sen(tokens[i], n)}")
+
+    # --------------------------------------------------------------------------------------------- synchronous path
+    def inference(self, batch_idx):
+        """pytorch_sut.py:67-105: returns (res {N_padded, L}, res_len {N_padded}) for the given sample indices."""
+        batch_idx = list(batch_idx)
+        self.actual_batch_size = len(batch_idx)
+        with torch.no_grad():
+            feas = torch.nn.utils.rnn.pad_sequence([self.qsl[i][0] for i in batch_idx])          # {T, N, 240}
+            fea_lens = torch.tensor([int(self.qsl[i][1]) for i in batch_idx], dtype=torch.int64)
+            if self.actual_batch_size % 32 != 0:
+                pad_n = math.ceil(self.actual_batch_size / 32) * 32 - self.actual_batch_size
+                feas = torch.nn.functional.pad(feas, (0, 0, 0, pad_n, 0, 0), "constant", 0.0)
+                fea_lens = torch.nn.functional.pad(fea_lens, (0, pad_n), "constant", 0)
+            self.h2d_bytes += feas.numel() * 4 + fea_lens.numel() * 8
+            results = self.model(feas, fea_lens)
+        self.batches_run += 1
+        return results
+
+    def query_samples_complete(self, samples, results, results_idx):
+        lens = results_idx[:len(samples)].to(torch.int32).cpu().numpy()
+        width = max(1, int(lens.max(initial=0)))
+        tokens = np.ascontiguousarray(results[:len(samples), :width].to(torch.int32).cpu().numpy())
+        self.d2h_bytes += tokens.nbytes + lens.nbytes
+        self._respond(samples, tokens, lens)
+
+    def __del__(self):
+        try:
+            lg.DestroySUT(self.sut)
+        except Exception:
+            pass
