@@ -1,0 +1,448 @@
+#!/usr/bin/env python
+"""bench.py — Offline utterances/s of the int8 RNN-T hot path on N B200s (+ encoder LSTM-step us).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json config 3, per-GPU share): one STEP = one Offline query of 2513 synthetic utterances per GPU
+(dev-clean-like length distribution, 240-dim stacked filterbank features, random-init weights with synthetic
+calibration ranges), sorted by length and cut into ragged batches of <= 256 like PytorchSUT.issue_queries.  Weak
+scaling: every rank decodes its own query; the only collective is the gather of transcripts at the end of a query.
+
+  value  utterances/s with the query's features already in HBM (device-timed, CUDA events, max over ranks)
+  e2e    the same metric through PytorchSUT + the LoadGen shim with HOST (pinned) features: host->device copies and
+         the device->host token read are inside the timed region
+  roofline      the persistent recurrent LSTM kernel (the dominant kernel), timed live with CUDA events
+  cpu_baseline  the CPU oracle (a restatement of the reference's AMX path) on the host cores, bounded sample
+`--impl reference` prints the reference arm: the same CPU path timed on the host cores on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+UTTS_PER_GPU = 2513       # configs/mlperf.conf:13 performance_sample_count of the reference
+BATCH = 256               # run.sh:71 Offline BS=256
+METRIC = "offline_utterances_per_second"
+UNIT = "utterances/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--utts", type=int, default=UTTS_PER_GPU, help="utterances per GPU and step")
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--microbench", action="store_true", help="also run config 2: encoder only, 256 x 500 frames")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu_index)], stdout=open(self.path, "w"),
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, reasons, smax = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                parts = [p.strip() for p in line.split(",")]
+                if len(parts) < 9:
+                    continue
+                try:
+                    sm.append(float(parts[1]))
+                    smax = float(parts[2])
+                except ValueError:
+                    continue
+                for name, val in zip(names, parts[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=smax, reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ workload
+def build_query(world, rank, utts_per_gpu, batch):
+    """Global query = world * utts_per_gpu utterances (lengths: fixed-seed gamma fit of dev-clean), sorted by length
+    descending and cut into batches of `batch` (PytorchSUT.issue_queries); batch j belongs to rank j % world
+    (SURVEY.md 8(e)).  Returns this rank's list of batches, each a list of (utt_id, length)."""
+    from rnnt_inference_b200 import synthetic as S
+    total = world * utts_per_gpu
+    lens = S.utterance_lengths(UTTS_PER_GPU)            # 2513 distinct utterances, replicated beyond (like MLPerf)
+    ids = np.arange(total)
+    ulen = lens[ids % UTTS_PER_GPU]
+    order = np.argsort(-ulen, kind="stable")
+    batches = [order[i:i + batch] for i in range(0, total, batch)]
+    mine = batches[rank::world]
+    return [[(int(u), int(ulen[u])) for u in b] for b in mine], int(ulen.sum())
+
+
+def make_model(device):
+    from rnnt_inference_b200 import synthetic as S
+    from rnnt_inference_b200.decoder import GreedyDecoder
+    from rnnt_inference_b200.modeling_rnnt import RNNT
+    sd = S.make_checkpoint()
+    rnnt = RNNT(sd, "quant", True, device=device).eval()
+    return sd, GreedyDecoder(rnnt, "quant", True, -1, BATCH)
+
+
+def features_for(batches):
+    """Host features of every distinct utterance this rank touches (replicas share one tensor)."""
+    from rnnt_inference_b200 import synthetic as S
+    feats = {}
+    for b in batches:
+        for u, n in b:
+            key = u % UTTS_PER_GPU
+            if key not in feats:
+                feats[key] = S.make_features(n, key)
+    return feats
+
+
+def stage_on_device(batches, feats, device):
+    """Device-resident form of each batch: packed ragged fp32 [sum T_i, 240], offsets, lens (N padded to 32)."""
+    staged = []
+    for b in batches:
+        n_pad = (len(b) + 31) // 32 * 32
+        lens = [n for _, n in b]
+        packed = torch.cat([feats[u % UTTS_PER_GPU] for u, _ in b], 0).to(device)
+        offsets = torch.zeros(n_pad, dtype=torch.int64)
+        offsets[:len(b)] = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]))
+        lens_t = torch.zeros(n_pad, dtype=torch.int32)
+        lens_t[:len(b)] = torch.tensor(lens, dtype=torch.int32)
+        staged.append((packed, offsets.to(device), lens_t.to(device), max(lens), len(b)))
+    return staged
+
+
+def run_step_device(decoder, staged):
+    """One step = one pass over this rank's query, inputs already in HBM.  Returns emitted-token count tensor."""
+    total = None
+    for packed, offsets, lens, max_len, n_actual in staged:
+        _res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len)
+        s = res_len[:n_actual].sum()
+        total = s if total is None else total + s
+    return total
+
+
+# ------------------------------------------------------------------------------------------------ roofline
+def recurrent_roofline(events, peaks):
+    """Algorithmic HBM bytes of the recurrent kernel per launch (DESIGN.md / SURVEY.md 8(d)): per (timestep, utterance)
+    G int32 16384 + h_in 1024 + c read+write 4096 + h_out 1024 + y 1024 (int8) or 2048 (bf16) = 23552 / 24576 bytes."""
+    recs = events.get("lstm_recurrent", [])
+    if not recs:
+        return None, None
+    tot_ms, tot_bytes, tot_ops, steps = 0.0, 0.0, 0.0, 0
+    for start, end, (t, n, last) in recs:
+        tot_ms += start.elapsed_time(end)
+        tot_bytes += float(t) * n * (24576 if last else 23552)
+        tot_ops += float(t) * n * 2 * 1024 * 4096
+        steps += t
+    launches = len(recs)
+    achieved = tot_bytes / (tot_ms * 1e-3) / 1e9
+    peak = peaks.get("hbm_gbs", 6650.0)
+    roof = {"kernel": "lstm_recurrent_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peaks.get("_source", "fallback"),
+            "launches": launches, "avg_launch_ms": round(tot_ms / launches, 4),
+            "algorithmic_bytes_per_launch": round(tot_bytes / launches), "tensor_top_s": round(tot_ops / (tot_ms * 1e-3) / 1e12, 1)}
+    return roof, tot_ms * 1e3 / steps     # second value: mean us per (layer, timestep)
+
+
+def kernel_shares(events):
+    out = {}
+    for name, recs in events.items():
+        out[name] = round(sum(s.elapsed_time(e) for s, e, _ in recs), 3)
+    return out
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            p = json.load(open(path))
+            p["_source"] = "MEASURED_PEAKS.json (burst copy bandwidth)"
+            return p
+        except Exception:
+            pass
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "_source": "fallback (B200_PROFILING.md)"}
+
+
+# ------------------------------------------------------------------------------------------------ CPU baseline
+def cpu_baseline(sd, world_batches, mean_frames, budget_s):
+    """The CPU oracle (restatement of the reference's int8/bf16 path, OpenMP over the batch) on the host cores, on
+    contiguous chunks of the length-sorted query taken at spread quantiles.  Throughput is frames-weighted:
+    (frames processed / seconds) / mean frames per utterance of the query, so a short sample is not biased by the
+    lengths it happened to contain."""
+    from oracle import pipeline as OP
+    from rnnt_inference_b200 import synthetic as S
+    cores = os.cpu_count() or 1
+    chunk = int(min(256, max(32, cores)))
+    flat = [u for b in world_batches for u in b]          # (utt_id, length), sorted by length descending
+    params = OP.prepare_params(sd)
+    frames, utts, elapsed, used = 0, 0, 0.0, []
+    for q in (0.5, 0.25, 0.75, 0.125, 0.625, 0.375, 0.875):
+        start = int(q * max(0, len(flat) - chunk))
+        part = flat[start:start + chunk]
+        feats = [S.make_features(n, u % UTTS_PER_GPU) for u, n in part]
+        x, xl = OP.pad_batch(feats, pad_to=32)
+        t0 = time.perf_counter()
+        OP.greedy_decode_batch(params, x, xl)
+        elapsed += time.perf_counter() - t0
+        frames += int(sum(n for _, n in part))
+        utts += len(part)
+        used.append(q)
+        if elapsed >= budget_s:
+            break
+    value = (frames / elapsed) / mean_frames
+    return {"value": round(value, 3), "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{utts} utterances ({frames} frames) in {len(used)} length-sorted chunks of {chunk} at quantiles {used}, "
+                      f"{elapsed:.1f} s; frames-weighted to the query's mean of {mean_frames:.1f} frames/utterance"}
+
+
+def reference_arm(args):
+    """`--impl reference`: the reference's CPU path (restated: its AMX/oneDNN plugin cannot be built offline, see
+    DESIGN.md) timed on the host cores with all threads; every step is a bounded sample of the same workload."""
+    rank, _local, world = dist_env()
+    if rank != 0:
+        return
+    from rnnt_inference_b200 import synthetic as S
+    batches, total_frames = build_query(1, 0, args.utts, args.batch)
+    mean_frames = total_frames / args.utts
+    sd = S.make_checkpoint()
+    per_step = max(3.0, min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(min(args.warmup, 1)):
+        cpu_baseline(sd, batches, mean_frames, 0.0)
+    vals, last = [], None
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        last = cpu_baseline(sd, batches, mean_frames, per_step)
+        vals.append(last["value"])
+    ms = (time.perf_counter() - t0) * 1e3 / max(1, args.steps)
+    value = float(np.mean(vals))
+    last["value"] = round(value, 3)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int8", "data": "synthetic",
+        "config": {"workload": "C3 Offline: 2513 synthetic dev-clean-length utterances per GPU, batch 256, full int8 RNN-T greedy decode",
+                   "note": "CPU restatement of the reference path (oracle/), bounded sample per step"},
+        "cpu_baseline": last,
+        "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ------------------------------------------------------------------------------------------------ e2e through the SUT
+def make_sut(sd, batches, feats, device, batch):
+    from rnnt_inference_b200.pytorch_sut import PytorchSUT
+    xs, xl = [], []
+    for b in batches:
+        for u, n in b:
+            xs.append(feats[u % UTTS_PER_GPU])
+            xl.append(torch.tensor(n, dtype=torch.int64))
+    sut = PytorchSUT(sd, {"x": xs, "x_lens": xl}, batch, "quant", None, enable_bf16=True, scenario="Offline", device=device)
+    return sut, len(xs)
+
+
+def run_e2e_query(sut, count):
+    """One Offline query through the LoadGen shim: host features -> transcripts on the host."""
+    from rnnt_inference_b200 import loadgen_shim as lg
+    settings = lg.TestSettings()
+    settings.scenario = lg.TestScenario.Offline
+    settings.min_query_count = count
+    return lg.StartTest(sut.sut, sut.qsl.qsl, settings)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    rank, local, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_scalar(v, op):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    from rnnt_inference_b200 import ops
+    sd, decoder = make_model(device)
+    batches, _ = build_query(world, rank, args.utts, args.batch)
+    feats = features_for(batches)
+    staged = stage_on_device(batches, feats, device)
+    my_utts = sum(len(b) for b in batches)
+    my_frames = sum(n for b in batches for _, n in b)
+
+    # ---- device-resident leg: W warm-up steps, then exactly K timed steps
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            run_step_device(decoder, staged)
+        ops.telemetry.events = {}
+        launches0 = ops.telemetry.launches
+        sampler = ClockSampler(local)
+        barrier()
+        sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        tokens = None
+        for _ in range(args.steps):
+            tokens = run_step_device(decoder, staged)
+        ev1.record()
+        barrier()
+        clocks = sampler.stop()
+        events = ops.telemetry.events
+        ops.telemetry.events = None
+        launches = ops.telemetry.launches - launches0
+    from rnnt_inference_b200 import _lib
+    _lib.check_device_status()
+    ms_total = reduce_scalar(ev0.elapsed_time(ev1), dist.ReduceOp.MAX if world > 1 else None)
+    utts_total = reduce_scalar(float(my_utts), dist.ReduceOp.SUM if world > 1 else None)
+    ms_per_step = ms_total / args.steps
+    value = utts_total * args.steps / (ms_total * 1e-3)
+    roof, step_us = recurrent_roofline(events, load_peaks())
+    shares = kernel_shares(events)
+    tokens_per_step = int(tokens.item()) if tokens is not None else 0
+
+    # ---- e2e leg: PytorchSUT + LoadGen shim, host features
+    e2e = None
+    if not args.no_e2e:
+        sut, count = make_sut(sd, batches, feats, device, args.batch)
+        for _ in range(2):
+            run_e2e_query(sut, count)
+        k_e2e = max(1, min(args.steps, 5))
+        h0, d0 = sut.h2d_bytes, sut.d2h_bytes
+        barrier()
+        t0 = time.perf_counter()
+        done = 0
+        for _ in range(k_e2e):
+            r = run_e2e_query(sut, count)
+            done += r["completed"]
+        torch.cuda.synchronize()
+        sec = time.perf_counter() - t0
+        sec = reduce_scalar(sec, dist.ReduceOp.MAX if world > 1 else None)
+        done_all = reduce_scalar(float(done), dist.ReduceOp.SUM if world > 1 else None)
+        h2d = reduce_scalar(float(sut.h2d_bytes - h0), dist.ReduceOp.SUM if world > 1 else None)
+        d2h = reduce_scalar(float(sut.d2h_bytes - d0), dist.ReduceOp.SUM if world > 1 else None)
+        e2e = {"value": round(done_all / sec, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d / k_e2e),
+               "d2h_bytes_per_step": int(d2h / k_e2e), "steps": k_e2e, "api": "PytorchSUT.issue_queries via loadgen_shim.StartTest"}
+
+    micro = encoder_microbench(decoder, device) if (args.microbench and rank == 0) else None
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        full, total_frames = build_query(1, 0, args.utts, args.batch)
+        cpu = cpu_baseline(sd, full, total_frames / args.utts, args.cpu_seconds)
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_per_step, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int8", "data": "synthetic",
+            "config": {"workload": "C3 Offline: 2513 synthetic dev-clean-length utterances per GPU, batch 256, full int8 RNN-T greedy decode",
+                       "utterances_per_gpu_per_step": my_utts, "frames_per_gpu_per_step": my_frames, "batch": args.batch,
+                       "batches_per_step": len(batches), "tokens_per_step_rank0": tokens_per_step,
+                       "l2": "inputs and per-layer int32 projections (up to 2 GB) exceed the 126 MB L2; no explicit flush",
+                       "parallelism": f"dp{world}: sorted batches dealt round-robin to ranks"},
+            "lstm_step_us": round(step_us, 3) if step_us else None,
+            "kernel_ms": shares, "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": roof, "cpu_baseline": cpu}
+        if micro:
+            line["encoder_microbench"] = micro
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def encoder_microbench(decoder, device, n=256, t=500, reps=3):
+    """BASELINE config 2: int8 encoder only, batch 256 x 500 frames; mean us per (layer, timestep) of the recurrent kernel."""
+    from rnnt_inference_b200 import ops
+    trans = decoder.rnnt.transcription
+    x = torch.randn((t, n, 240), device=device).clamp_(-5.8, 5.8)
+    lens = torch.full((n,), t, dtype=torch.int32, device=device)
+
+    def run():
+        hid = 1024
+        z = lambda dt: [torch.zeros((n, hid), dtype=dt, device=device) for _ in range(5)]
+        hx, cx = z(torch.int8), z(torch.float16)
+        return trans(x, lens, hx[:2], cx[:2], hx[2:], cx[2:])
+
+    with torch.no_grad():
+        for _ in range(2):
+            run()
+        ops.telemetry.events = {}
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        ev0.record()
+        for _ in range(reps):
+            run()
+        ev1.record()
+        torch.cuda.synchronize()
+        events = ops.telemetry.events
+        ops.telemetry.events = None
+    roof, step_us = recurrent_roofline(events, load_peaks())
+    shares = kernel_shares(events)
+    gemm_ms = shares.get("gemm_i8", 0.0) / reps
+    gemm_ops = 2.0 * n * (t * (4096 * 256 + 4096 * 1024) + (t // 2) * (4096 * 2048 + 2 * 4096 * 1024))
+    return {"workload": f"C2 encoder only, {n} x {t} frames", "encoder_ms": round(ev0.elapsed_time(ev1) / reps, 3),
+            "lstm_step_us": round(step_us, 3), "recurrent_roofline": roof, "gemm_ms": round(gemm_ms, 3),
+            "gemm_top_s": round(gemm_ops / (gemm_ms * 1e-3) / 1e12, 1) if gemm_ms else None,
+            "kernel_ms": {k: round(v / reps, 3) for k, v in shares.items()}}
+
+
+if __name__ == "__main__":
+    main()

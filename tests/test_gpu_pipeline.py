@@ -1,0 +1,120 @@
+"""GPU parity of the whole path (checkpoint -> RNNT modules -> GreedyDecoder / PytorchSUT) against the CPU oracle pipeline.
+Token sequences and lengths must be bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import pipeline as OP
+from rnnt_inference_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+LENS = [37, 30, 30, 22, 9, 4, 1]
+
+
+@pytest.fixture(scope="module")
+def setup():
+    from rnnt_inference_b200.modeling_rnnt import RNNT
+    sd = S.make_checkpoint(seed=11)
+    rnnt = RNNT(sd, "quant", True).eval()
+    params = OP.prepare_params(sd)
+    feats = [S.make_features(n, 100 + i) for i, n in enumerate(LENS)]
+    return sd, rnnt, params, feats
+
+
+def _oracle(params, feats, split_len=-1, pad_to=0):
+    x, xl = OP.pad_batch(feats, pad_to=pad_to)
+    return OP.greedy_decode_batch(params, x, xl, split_len)
+
+
+def _check(res, res_len, o_res, o_len, n):
+    res, res_len = res.cpu().numpy(), res_len.cpu().numpy()
+    np.testing.assert_array_equal(res_len[:n], o_len[:n])
+    assert o_len[:n].sum() > 0, "degenerate case: the oracle emitted nothing"
+    for i in range(n):
+        np.testing.assert_array_equal(res[i, :o_len[i]], o_res[i, :o_len[i]])
+
+
+def test_quantised_parameters_match_oracle(setup):
+    """Scale algebra / weight quantisation of the modules (quant_lstm.py:193-215) == the oracle's restatement."""
+    _sd, rnnt, params, _ = setup
+    stacks = [rnnt.transcription.pre_rnn, rnnt.transcription.post_rnn]
+    i = 0
+    for rnn in stacks:
+        for layer in range(rnn.num_layers):
+            w_ih, w_hh, _b, bias = rnn.weights[layer]
+            p = params["enc"][i]
+            np.testing.assert_array_equal(w_ih.cpu().numpy(), p["w_ih"])
+            np.testing.assert_array_equal(w_hh.cpu().numpy(), p["w_hh"])
+            np.testing.assert_array_equal(bias.cpu().numpy().view(np.uint32), p["bias"].view(np.uint32))
+            assert float(rnn.rb_scale[layer]) == p["rb_scale"] and float(rnn.in_scale[layer]) == p["in_scale"]
+            if i != 4:
+                assert float(rnn.out_scale[layer]) == p["out_scale"]
+            i += 1
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_decoder_forward_vs_oracle(setup, fused):
+    from rnnt_inference_b200.decoder import GreedyDecoder
+    _sd, rnnt, params, feats = setup
+    dec = GreedyDecoder(rnnt, "quant", True, -1, len(feats), fused=fused)
+    x, xl = OP.pad_batch(feats, pad_to=0)
+    with torch.no_grad():
+        res, res_len = dec(torch.from_numpy(x), torch.from_numpy(xl))
+    o_res, o_len, o_iters = _oracle(params, feats)
+    _check(res, res_len, o_res, o_len, len(feats))
+    if fused:
+        assert int(dec.last_iters.item()) == o_iters
+
+
+def test_decoder_split_len_vs_oracle(setup):
+    """Chunked encoder with carried state (decoder.py:80-91, split_len = 8)."""
+    from rnnt_inference_b200.decoder import GreedyDecoder
+    _sd, rnnt, params, feats = setup
+    dec = GreedyDecoder(rnnt, "quant", True, 8, len(feats))
+    x, xl = OP.pad_batch(feats, pad_to=0)
+    with torch.no_grad():
+        res, res_len = dec(torch.from_numpy(x), torch.from_numpy(xl))
+    o_res, o_len, _ = _oracle(params, feats, split_len=8)
+    _check(res, res_len, o_res, o_len, len(feats))
+
+
+def test_forward_ragged_equals_forward(setup):
+    from rnnt_inference_b200.decoder import GreedyDecoder
+    _sd, rnnt, _params, feats = setup
+    dec = GreedyDecoder(rnnt, "quant", True, -1, len(feats))
+    x, xl = OP.pad_batch(feats, pad_to=32)
+    with torch.no_grad():
+        res, res_len = dec(torch.from_numpy(x), torch.from_numpy(xl))
+        res, res_len = res.clone(), res_len.clone()
+        packed = torch.cat(feats, 0).cuda()
+        offsets = torch.zeros(32, dtype=torch.int64)
+        offsets[:len(feats)] = torch.tensor(np.concatenate([[0], np.cumsum(LENS[:-1])]))
+        lens = torch.zeros(32, dtype=torch.int32)
+        lens[:len(feats)] = torch.tensor(LENS, dtype=torch.int32)
+        res2, len2 = dec.forward_ragged(packed, offsets.cuda(), lens.cuda(), max(LENS))
+    assert torch.equal(res_len, len2) and torch.equal(res, res2)
+
+
+def test_sut_offline_query_vs_oracle(setup):
+    """PytorchSUT issue/complete contract through the LoadGen shim (Offline, accuracy mode): every sample's int32 token
+    bytes equal the oracle's transcript of that utterance decoded in the same sorted batches."""
+    from rnnt_inference_b200 import loadgen_shim as lg
+    from rnnt_inference_b200.pytorch_sut import PytorchSUT
+    sd, _rnnt, params, _ = setup
+    lens = [25, 7, 31, 18, 12, 31, 3, 22, 9, 16]
+    feats = [S.make_features(n, 300 + i) for i, n in enumerate(lens)]
+    data = {"x": feats, "x_lens": [torch.tensor(n) for n in lens]}
+    sut = PytorchSUT(sd, data, 4, "quant", None, enable_bf16=True, scenario="Offline")
+    settings = lg.TestSettings()
+    settings.scenario = lg.TestScenario.Offline
+    settings.mode = lg.TestMode.AccuracyOnly
+    out = lg.StartTest(sut.sut, sut.qsl.qsl, settings)
+    assert out["completed"] == len(lens)
+    got = {e["qsl_idx"]: np.frombuffer(bytes.fromhex(e["data"]), np.int32) for e in out["accuracy_log"]}
+    order = sorted(range(len(lens)), key=lambda i: -lens[i])          # stable, like list.sort(reverse=True)
+    for c in range(0, len(order), 4):
+        idx = order[c:c + 4]
+        o_res, o_len, _ = _oracle(params, [feats[i] for i in idx], pad_to=32)
+        for j, i in enumerate(idx):
+            np.testing.assert_array_equal(got[i], o_res[j, :o_len[j]])
