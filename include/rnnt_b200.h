@@ -68,6 +68,11 @@ int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bi
                            float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
                            void* workspace, void* stream);
 
+/* DEBUG: when set to a device buffer of T*8 int64, the next recurrent launches record clock64() stamps of CTA (0,0)
+ * per timestep (h ready, first operand chunk landed, MMAs issued, accumulator ready, TMEM read, gate math done,
+ * proxy fence done, published).  NULL switches it off.  Used by profiles/trace_recurrent.py only. */
+int rnnt_debug_set_recurrent_trace(void* device_buffer);
+
 /* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.
  * x [T][N][K] int8 (K % 16 == 0).  g_ws: T*N*4H int32 scratch for the projection. */
 int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* w_ih, const int8_t* w_hh,

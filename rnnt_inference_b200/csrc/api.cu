@@ -279,6 +279,10 @@ int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, in
   return gemm_launch<64>(A, W, C, M, N, K, st);
 }
 
+// debug hook: device buffer [T][8] int64 receiving clock64 stamps of CTA (0,0) of the next recurrent launches (NULL = off)
+static long long* g_rec_trace = nullptr;
+int rnnt_debug_set_recurrent_trace(void* device_buffer) { g_rec_trace = reinterpret_cast<long long*>(device_buffer); return RNNT_OK; }
+
 // ------------------------------------------------------------------------------------------------
 // recurrent kernel.  workspace: [0,256) reserved | flags [num_btiles][32] int | h ping-pong [2][N_pad][1024] int8
 static int64_t rec_flags_bytes(int N) { return round_up((int64_t)((N + REC_BM - 1) / REC_BM) * REC_FLAG_STRIDE * 4, 256); }
@@ -348,6 +352,7 @@ int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bi
   p.G = G; p.bias = bias; p.h_buf = h_buf; p.cx = cx; p.y = y; p.flags = flags; p.status = status;
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
   p.T = T; p.N = N; p.N_pad = (int)n_pad; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
+  p.trace = g_rec_trace;
   int r = (HS == 8) ? rec_launch<8>(tw, th, p, num_slices, grid_y, st) : rec_launch<16>(tw, th, p, num_slices, grid_y, st);
   if (r) return r;
   CUDA_TRY(cudaMemcpyAsync(hx, h_buf + (size_t)(T & 1) * n_pad * REC_H, (size_t)N * REC_H, cudaMemcpyDeviceToDevice, st));

@@ -60,6 +60,7 @@ struct RecParams {
   int* status;
   float rb_scale, in_scale, out_scale;
   int T, N, N_pad, num_btiles, skip_quant_y;
+  long long* trace;        // optional [T][8] clock64 stamps of CTA (0,0) (debug builds of the bench only; NULL otherwise)
 };
 
 template <int HS>

@@ -98,6 +98,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           if (!ok) break;
           fence_proxy_async_all();   // generic-proxy writes of h_t (other CTAs) -> async-proxy (TMA) reads
         }
+        if (p.trace && blockIdx.x == 0 && blockIdx.y == 0) p.trace[t * 8 + 0] = clock64();
         for (int kc = 0; kc < REC_KC; ++kc) {
           if (!mbar_wait(empty_bar + 8 * kc, phase ^ 1, p.status)) { ok = false; break; }
           mbar_expect_tx(full_bar + 8 * kc, S::H_CHUNK);
@@ -118,6 +119,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         const uint32_t d_tmem = tmem_base + acc * S::UMMA_N;
         for (int kc = 0; kc < REC_KC; ++kc) {
           if (!mbar_wait(full_bar + 8 * kc, phase, p.status)) { ok = false; break; }
+          if (kc == 0 && p.trace && blockIdx.x == 0 && blockIdx.y == 0) p.trace[(it / my_tiles) * 8 + 1] = clock64();
           tc_fence_after();
           const uint64_t adesc = umma_desc_sw128(smem_h + kc * S::H_CHUNK);
           const uint64_t bdesc = umma_desc_sw128(smem_w + kc * S::W_CHUNK);
@@ -128,6 +130,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         }
         if (!ok) break;
         umma_commit(tfull_bar + 8 * acc);
+        if (p.trace && blockIdx.x == 0 && blockIdx.y == 0) p.trace[(it / my_tiles) * 8 + 2] = clock64();
         phase ^= 1;
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
@@ -181,6 +184,8 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       }
 
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
+      const bool tr = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && e == 0 && lane == 0;
+      if (tr) p.trace[t * 8 + 3] = clock64();
       tc_fence_after();
       uint32_t a[4][UPT];
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * UPT);
@@ -201,6 +206,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       if (lane == 0) mbar_arrive(tempty_bar + 8 * acc);   // accumulator stage may be overwritten
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
 
+      if (tr) p.trace[t * 8 + 4] = clock64();
       uint32_t hq_pack = 0, yq_pack = 0;
       uint32_t ybf[UPT / 2];
 #pragma unroll
@@ -247,13 +253,16 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       // publish h_{t+1}[tile bt][this slice]: generic -> async proxy fence for the TMA readers, every
       // epilogue warp arrives on epi_bar (release.cta), the publisher thread waits for all 16 (bounded, so a
       // protocol error cannot hang a bar.sync), then does one release increment of the tile counter.
+      if (tr) p.trace[t * 8 + 5] = clock64();
       fence_proxy_async_all();
       __syncwarp();
+      if (tr) p.trace[t * 8 + 6] = clock64();
       if (lane == 0) mbar_arrive(epi_bar);
       if (e == 0 && lane == 0) {
         if (mbar_wait(epi_bar, epi_phase, p.status)) {
           __threadfence();
           asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+          if (tr) p.trace[t * 8 + 7] = clock64();
         }
       }
       epi_phase ^= 1;
