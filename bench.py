@@ -126,13 +126,13 @@ def build_query(world, rank, utts_per_gpu, batch):
     return [[(int(u), int(ulen[u])) for u in b] for b in mine], int(ulen.sum())
 
 
-def make_model(device):
+def make_model(device, batch=BATCH):
     from rnnt_inference_b200 import synthetic as S
     from rnnt_inference_b200.decoder import GreedyDecoder
     from rnnt_inference_b200.modeling_rnnt import RNNT
     sd = S.make_checkpoint()
     rnnt = RNNT(sd, "quant", True, device=device).eval()
-    return sd, GreedyDecoder(rnnt, "quant", True, -1, BATCH)
+    return sd, GreedyDecoder(rnnt, "quant", True, -1, batch)
 
 
 def features_for(batches):
@@ -158,15 +158,15 @@ def stage_on_device(batches, feats, device):
         offsets[:len(b)] = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]))
         lens_t = torch.zeros(n_pad, dtype=torch.int32)
         lens_t[:len(b)] = torch.tensor(lens, dtype=torch.int32)
-        staged.append((packed, offsets.to(device), lens_t.to(device), max(lens), len(b)))
+        staged.append((packed, offsets.to(device), lens_t.to(device), max(lens), len(b), lens))
     return staged
 
 
 def run_step_device(decoder, staged):
     """One step = one pass over this rank's query, inputs already in HBM.  Returns emitted-token count tensor."""
     total = None
-    for packed, offsets, lens, max_len, n_actual in staged:
-        _res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len)
+    for packed, offsets, lens, max_len, n_actual, lens_host in staged:
+        _res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len, lens_host)
         s = res_len[:n_actual].sum()
         total = s if total is None else total + s
     return total
@@ -324,7 +324,7 @@ def main():
         return float(t.item())
 
     from rnnt_inference_b200 import ops
-    sd, decoder = make_model(device)
+    sd, decoder = make_model(device, args.batch)
     batches, _ = build_query(world, rank, args.utts, args.batch)
     feats = features_for(batches)
     staged = stage_on_device(batches, feats, device)

@@ -67,11 +67,23 @@ int64_t rnnt_lstm_recurrent_workspace_bytes(int N);
 int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
                            float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
                            void* workspace, void* stream);
+/* Same kernel for a ragged batch whose rows are sorted by length (PytorchSUT.issue_queries sorts descending,
+ * models/pytorch_sut.py:58-65): tile_steps_host[b] (HOST array, ceil(N/128) entries, each in [0,T]) is the number of
+ * timesteps batch tile b (rows [128b, 128b+128)) runs.  Steps t >= tile_steps[b] of that tile are skipped entirely:
+ * y[t] is not written there and hx/cx hold the state after tile_steps[b] steps.  The reference runs every lane for all
+ * T steps and discards the tail (stack_time.cpp:42-57 zeroes it, greedy_decode_update reads t < f_lens only), so
+ * transcripts are unchanged as long as tile_steps[b] >= max length in the tile.  NULL = every tile runs T steps. */
+int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                                  float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                                  const int32_t* tile_steps_host, void* workspace, void* stream);
 
 /* DEBUG: when set to a device buffer of T*8 int64, the next recurrent launches record clock64() stamps of CTA (0,0)
  * per timestep (h ready, first operand chunk landed, MMAs issued, accumulator ready, TMEM read, gate math done,
  * proxy fence done, published).  NULL switches it off.  Used by profiles/trace_recurrent.py only. */
 int rnnt_debug_set_recurrent_trace(void* device_buffer);
+/* TUNING/DEBUG: slice-CTAs per thread-block cluster of the recurrent kernel (1, 2 or 4; default 4, or the environment
+ * variable RNNT_REC_CLUSTER).  The h tile of a batch tile is TMA-multicast inside a cluster.  Results do not depend on it. */
+int rnnt_debug_set_recurrent_cluster(int ctas);
 
 /* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.
  * x [T][N][K] int8 (K % 16 == 0).  g_ws: T*N*4H int32 scratch for the projection. */

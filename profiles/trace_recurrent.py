@@ -13,13 +13,15 @@ from rnnt_inference_b200.modeling_rnnt import RNNT
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 60
+if len(sys.argv) > 3:
+    _lib.check(_lib.lib.rnnt_debug_set_recurrent_cluster(int(sys.argv[3])))
 torch.cuda.set_device(0)
 rnnt = RNNT(S.make_checkpoint(), "quant", True).eval()
 post = rnnt.transcription.post_rnn
 w_ih, w_hh, _b, bias = post.weights[1]
 x = torch.randint(-60, 61, (T, n, 1024), dtype=torch.int8, device="cuda")
 trace = torch.zeros((T, 8), dtype=torch.int64, device="cuda")
-names = ["h_ready", "chunk0_landed", "mma_issued", "acc_ready", "tmem_read", "math_done", "fence_done", "published"]
+names = ["h_ready", "chunk0_landed", "mma_issued", "acc_ready", "tmem_read", "math_stores_done", "publisher_saw_done", "published"]
 for rep in range(3):
     hx = torch.zeros((n, 1024), dtype=torch.int8, device="cuda")
     cx = torch.zeros((n, 1024), dtype=torch.float16, device="cuda")

@@ -4,6 +4,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/rnnt_b200.h"
@@ -46,7 +47,7 @@ EncodeTiledFn get_encode() {
 
 // rank <= 3 tiled tensor map with 128-byte swizzle; dims/box innermost first; strides in bytes for dims 1..rank-1
 int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
-              const uint64_t* strides, const uint32_t* box) {
+              const uint64_t* strides, const uint32_t* box, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return fail(RNNT_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
   cuuint64_t d[3], s[2];
@@ -54,7 +55,7 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int rank, const void* base
   for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; }
   for (int i = 0; i + 1 < rank; ++i) s[i] = strides[i];
   CUresult r = enc(m, dt, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(RNNT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return RNNT_OK;
 }
@@ -284,44 +285,85 @@ static long long* g_rec_trace = nullptr;
 int rnnt_debug_set_recurrent_trace(void* device_buffer) { g_rec_trace = reinterpret_cast<long long*>(device_buffer); return RNNT_OK; }
 
 // ------------------------------------------------------------------------------------------------
-// recurrent kernel.  workspace: [0,256) reserved | flags [num_btiles][32] int | h ping-pong [2][N_pad][1024] int8
+// recurrent kernel.  workspace: [0,1024) reserved | flags [num_btiles][32] int | h ping-pong [2][N_pad][1024] int8 (K-chunk-major)
+//                             | c scratch [N_pad][1024] binary16 (blocked)
 static int64_t rec_flags_bytes(int N) { return round_up((int64_t)((N + REC_BM - 1) / REC_BM) * REC_FLAG_STRIDE * 4, 256); }
 int64_t rnnt_lstm_recurrent_workspace_bytes(int N) {
   if (N <= 0) return 0;
   const int64_t n_pad = round_up(N, REC_BM);
-  return 1024 + rec_flags_bytes(N) + 2 * n_pad * REC_H + 1024;
+  return 1024 + rec_flags_bytes(N) + 2 * n_pad * REC_H + 1024 + n_pad * REC_H * 2;
 }
 
 }  // extern "C"
-template <int HS>
-static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th, const RecParams& p, int num_slices, int grid_y,
-                      cudaStream_t st) {
-  auto kern = lstm_recurrent_kernel<HS>;
+
+// Launch with `cs` slice-CTAs per thread-block cluster (h tiles are TMA-multicast inside a cluster).  Cooperative so that
+// all CTAs are co-resident (they exchange h through per-tile counters).  Returns cudaErrorCooperativeLaunchTooLarge /
+// cluster errors to the caller, which falls back to a smaller cluster.
+template <int CS>
+static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th, const CUtensorMap& tg,
+                                 const RecParams& p, int num_slices, int grid_y, cudaStream_t st) {
+  auto kern = lstm_recurrent_kernel<CS>;
   static bool attr_set = false;
   if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, RecSmem<HS>::TOTAL));
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, RecSmem::TOTAL);
+    if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  void* args[3] = {(void*)&tw, (void*)&th, (void*)&p};
-  CUDA_TRY(cudaLaunchCooperativeKernel((const void*)kern, dim3(num_slices, grid_y), dim3(REC_THREADS), args,
-                                       RecSmem<HS>::TOTAL, st));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_slices, grid_y);
+  cfg.blockDim = dim3(REC_THREADS);
+  cfg.dynamicSmemBytes = RecSmem::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  int na = 0;
+  attrs[na].id = cudaLaunchAttributeCooperative; attrs[na].val.cooperative = 1; ++na;
+  if (CS > 1) {
+    attrs[na].id = cudaLaunchAttributeClusterDimension;
+    attrs[na].val.clusterDim.x = CS; attrs[na].val.clusterDim.y = 1; attrs[na].val.clusterDim.z = 1; ++na;
+  }
+  cfg.attrs = attrs; cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, kern, tw, th0, th, tg, p);
+}
+static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th, const CUtensorMap& tg,
+                      const RecParams& p, int num_slices, int grid_y, int cs_max, cudaStream_t st) {
+  cudaError_t e = cudaErrorUnknown;
+  if (cs_max >= 4) { e = rec_launch_cs<4>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  if (cs_max >= 2) { e = rec_launch_cs<2>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  e = rec_launch_cs<1>(tw, th0, th, tg, p, num_slices, grid_y, st);
+  if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "lstm_recurrent launch failed: %s", cudaGetErrorString(e));
   return RNNT_OK;
 }
 
+static int g_rec_cluster = -1;
+static int rec_cluster_pref() {
+  int& v = g_rec_cluster;
+  if (v < 0) {
+    const char* s = getenv("RNNT_REC_CLUSTER");   // 1, 2 or 4 slice-CTAs per cluster (tuning knob; default 1: L2 already
+    v = s ? atoi(s) : 1;                          // de-duplicates <= 4 concurrent readers of a line, measured no gain)
+    if (v != 1 && v != 2 && v != 4) v = 1;
+  }
+  return v;
+}
+
 extern "C" {
-int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
-                           float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
-                           void* workspace, void* stream) {
+int rnnt_debug_set_recurrent_cluster(int ctas) {
+  if (ctas != 1 && ctas != 2 && ctas != 4) return fail(RNNT_ERR_INVALID, "recurrent cluster size must be 1, 2 or 4");
+  g_rec_cluster = ctas;
+  return RNNT_OK;
+}
+int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                                  float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                                  const int32_t* tile_steps_host, void* workspace, void* stream) {
   if (!G || !w_hh || !bias || !hx || !cx || !y || !workspace) return fail(RNNT_ERR_INVALID, "lstm_recurrent: null pointer");
   if (H != REC_H) return fail(RNNT_ERR_INVALID, "lstm_recurrent: hidden size must be 1024 (got %d)", H);
   if (T < 0 || N <= 0) return fail(RNNT_ERR_INVALID, "lstm_recurrent: need T >= 0, N > 0 (T=%d N=%d)", T, N);
-  if (!aligned(G, 16) || !aligned(w_hh, 16) || !aligned(workspace, 256) || !aligned(y, 8) || !aligned(cx, 8) || !aligned(hx, 4))
+  if (!aligned(G, 16) || !aligned(w_hh, 16) || !aligned(workspace, 256) || !aligned(y, 8) || !aligned(cx, 16) || !aligned(hx, 16))
     return fail(RNNT_ERR_INVALID, "lstm_recurrent: misaligned buffer");
   if (T == 0) return RNNT_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const int num_btiles = (N + REC_BM - 1) / REC_BM;
   const int64_t n_pad = (int64_t)num_btiles * REC_BM;
-  if (num_btiles > 8 * 2) return fail(RNNT_ERR_INVALID, "lstm_recurrent: N <= 2048 per call (got %d)", N);
+  if (num_btiles > REC_MAX_TILES) return fail(RNNT_ERR_INVALID, "lstm_recurrent: N <= %d per call (got %d)", REC_MAX_TILES * REC_BM, N);
   uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
   int* flags = reinterpret_cast<int*>(ws + 1024);
   int8_t* h_buf = reinterpret_cast<int8_t*>(ws + 1024 + rec_flags_bytes(N));
@@ -329,34 +371,57 @@ int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bi
   int* status = device_status();
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
 
-  CUDA_TRY(cudaMemsetAsync(flags, 0, rec_flags_bytes(N), st));
-  CUDA_TRY(cudaMemsetAsync(h_buf, 0, 2 * n_pad * REC_H, st));
-  CUDA_TRY(cudaMemcpyAsync(h_buf, hx, (size_t)N * REC_H, cudaMemcpyDeviceToDevice, st));
+  RecParams p;
+  bool any = false;
+  for (int b = 0; b < REC_MAX_TILES; ++b) {
+    int s = 0;
+    if (b < num_btiles) {
+      s = tile_steps_host ? tile_steps_host[b] : T;
+      if (s < 0 || s > T) return fail(RNNT_ERR_INVALID, "lstm_recurrent: tile_steps[%d] = %d outside [0, T=%d]", b, s, T);
+    }
+    p.tile_steps[b] = s;
+    any |= s > 0;
+  }
+  if (!any) return RNNT_OK;
 
-  // one slice of 8 units per CTA when a single batch tile exists (128 CTAs), else 16 units (64 slices x 2 tile groups)
-  const int HS = (num_btiles == 1) ? 8 : 16;
-  const int num_slices = REC_H / HS;
+  CUDA_TRY(cudaMemsetAsync(flags, 0, rec_flags_bytes(N), st));
+  uint16_t* c_ws = reinterpret_cast<uint16_t*>(h_buf + 2 * n_pad * REC_H);
+
+  const int num_slices = REC_H / REC_HS;
   const int grid_y = (num_btiles == 1) ? 1 : 2;
-  CUtensorMap tw, th;
-  {
+  CUtensorMap tw, th0, th, tg;
+  {   // W_hh [4 gates][1024 units][1024 k]: box = 128 B of k x 16 units x 4 gates
     uint64_t dims[3] = {REC_H, REC_H, 4}, str[2] = {REC_H, (uint64_t)REC_H * REC_H};
-    uint32_t box[3] = {128, (uint32_t)HS, 4};
+    uint32_t box[3] = {128, (uint32_t)REC_HS, 4};
     if (int r = make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, w_hh, dims, str, box)) return r;
   }
-  {
-    uint64_t dims[3] = {REC_H, (uint64_t)n_pad, 2}, str[2] = {REC_H, (uint64_t)n_pad * REC_H};
-    uint32_t box[3] = {128, REC_BM, 1};
-    if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h_buf, dims, str, box)) return r;
+  {   // h_0 = the caller's hx [N][1024] (rows >= N read as zero)
+    uint64_t dims[2] = {REC_H, (uint64_t)N}, str[1] = {REC_H};
+    uint32_t box[2] = {128, REC_BM};
+    if (int r = make_tmap(&th0, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, hx, dims, str, box)) return r;
   }
-  RecParams p;
-  p.G = G; p.bias = bias; p.h_buf = h_buf; p.cx = cx; p.y = y; p.flags = flags; p.status = status;
+  {   // h ping-pong, K-chunk-major: rows of 128 B, one 128-row chunk = 16 KB contiguous
+    uint64_t dims[2] = {128, (uint64_t)(2 * n_pad * REC_KC)}, str[1] = {128};
+    uint32_t box[2] = {128, REC_BM};
+    if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, h_buf, dims, str, box)) return r;
+  }
+  {   // G [T][N][4096] int32: box = 16 columns (64 B) x 128 rows, 64-byte swizzle; rows >= N read as zero
+    uint64_t dims[3] = {4 * REC_H, (uint64_t)N, (uint64_t)T}, str[2] = {16 * REC_H, (uint64_t)N * 16 * REC_H};
+    uint32_t box[3] = {REC_HS, REC_BM, 1};
+    if (int r = make_tmap(&tg, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, G, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B)) return r;
+  }
+  p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
-  p.T = T; p.N = N; p.N_pad = (int)n_pad; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
+  p.T = T; p.N = N; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
   p.trace = g_rec_trace;
-  int r = (HS == 8) ? rec_launch<8>(tw, th, p, num_slices, grid_y, st) : rec_launch<16>(tw, th, p, num_slices, grid_y, st);
-  if (r) return r;
-  CUDA_TRY(cudaMemcpyAsync(hx, h_buf + (size_t)(T & 1) * n_pad * REC_H, (size_t)N * REC_H, cudaMemcpyDeviceToDevice, st));
-  return RNNT_OK;
+  return rec_launch(tw, th0, th, tg, p, num_slices, grid_y, rec_cluster_pref(), st);
+}
+
+int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                           float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                           void* workspace, void* stream) {
+  return rnnt_lstm_recurrent_i8_ragged(G, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, hx, cx, y, T, N, H, nullptr,
+                                       workspace, stream);
 }
 
 int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* w_ih, const int8_t* w_hh, const float* bias,

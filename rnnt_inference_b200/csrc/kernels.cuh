@@ -32,39 +32,53 @@ __global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8
 // ------------------------------------------------------------------ lstm_recurrent.cu
 constexpr int REC_H = 1024;
 constexpr int REC_BM = 128;          // batch rows per tile (UMMA M)
-constexpr int REC_KC = 8;            // K chunks of 128 bytes
-constexpr int REC_CTRL_WARPS = 4;    // 0: TMA producer, 1: MMA issuer, 2: TMEM alloc, 3: idle
+constexpr int REC_HS = 16;           // hidden units per slice CTA (all four gates: UMMA N = 64)
+constexpr int REC_KC = 8;            // K chunks of 128 bytes per tile
+constexpr int REC_NS = 4;            // stages of the h operand ring (16 KB each)
+constexpr int REC_GS = 2;            // stages of the input-projection (G) tile ring (32 KB each)
+constexpr int REC_CTRL_WARPS = 4;    // 0: TMA producer, 1: MMA issuer, 2: TMEM alloc, 3: publisher
 constexpr int REC_EPI_WARPS = 16;
+constexpr int REC_STORE_WARPS = 4;   // epilogue warps 0..3 also write the staged h / y rows to global memory
 constexpr int REC_THREADS = 32 * (REC_CTRL_WARPS + REC_EPI_WARPS);   // 640
 constexpr int REC_FLAG_STRIDE = 32;  // ints between per-tile counters (128 B)
+constexpr int REC_MAX_TILES = 32;    // batch tiles per launch (N <= 4096)
 
-template <int HS>
 struct RecSmem {
-  static constexpr int UMMA_N = 4 * HS;
-  static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice
-  static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 64 KB at HS=16
+  static constexpr int UMMA_N = 4 * REC_HS;
+  static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice (8 KB)
+  static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 64 KB
   static constexpr int H_CHUNK = REC_BM * 128;            // 16 KB
-  static constexpr int H_BYTES = REC_KC * H_CHUNK;        // 128 KB
-  static constexpr int LUT_OFFSET = W_BYTES + H_BYTES;
+  static constexpr int H_BYTES = REC_NS * H_CHUNK;        // 64 KB
+  static constexpr int G_GATE = REC_BM * REC_HS * 4;      // one gate of a G tile: 128 rows x 64 B = 8 KB
+  static constexpr int G_STAGE = 4 * G_GATE;              // 32 KB
+  static constexpr int G_OFFSET = W_BYTES + H_BYTES;
+  static constexpr int OUT_OFFSET = G_OFFSET + REC_GS * G_STAGE;   // staging of h (int8) and y (int8 | bf16) rows
+  static constexpr int OUT_H = 4 * REC_BM * 4;            // [ug][row] 4 B  = 2 KB
+  static constexpr int OUT_Y = 4 * REC_BM * 8;            // [ug][row] 8 B  = 4 KB
+  static constexpr int OUT_STAGE = OUT_H + OUT_Y;
+  static constexpr int LUT_OFFSET = OUT_OFFSET + 2 * OUT_STAGE;
   static constexpr int BAR_OFFSET = LUT_OFFSET + 2048;
-  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;
+  static constexpr int TOTAL = BAR_OFFSET + 512 + 1024;   // barriers/counters + alignment slack
 };
 
 struct RecParams {
-  const int32_t* G;        // [T][N][4H]
   const float* bias;       // [4H]
-  int8_t* h_buf;           // [2][N_pad][H] ping-pong (workspace); buffer 0 holds h_0 on entry
-  uint16_t* cx;            // [N][H] binary16, in place
+  int8_t* h_buf;           // [2][tiles][8 chunks][128 rows][128 B] ping-pong (workspace), K-chunk-major
+  int8_t* hx;              // [N][H] caller's state: h_0 on entry (read by TMA), receives h after the last step of each tile
+  uint16_t* cx;            // [N][H] binary16: c_0 on entry, final c on exit
+  uint16_t* c_ws;          // [tiles][64 slices][4][128 rows][4] binary16: c between steps, CTA-private blocked layout
   void* y;                 // [T][N][H] int8 or bf16
   int* flags;              // [num_btiles][REC_FLAG_STRIDE] zeroed
   int* status;
   float rb_scale, in_scale, out_scale;
-  int T, N, N_pad, num_btiles, skip_quant_y;
-  long long* trace;        // optional [T][8] clock64 stamps of CTA (0,0) (debug builds of the bench only; NULL otherwise)
+  int T, N, num_btiles, skip_quant_y;
+  int tile_steps[REC_MAX_TILES];   // timesteps to run for each batch tile (<= T); ragged batches sorted by length
+  long long* trace;        // optional [T][8] clock64 stamps of CTA (0,0) (profiles/trace_recurrent.py; NULL otherwise)
 };
 
-template <int HS>
-__global__ void lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h,
+template <int CS>
+__global__ void lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h0,
+                                      const __grid_constant__ CUtensorMap tmap_h, const __grid_constant__ CUtensorMap tmap_g,
                                       const RecParams p);
 
 // ------------------------------------------------------------------ elementwise.cu

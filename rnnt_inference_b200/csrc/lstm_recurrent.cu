@@ -5,82 +5,163 @@
 // lstm_postop_tpp::ref per row (tpps/lstm_postop_tpp.cpp:12-98) — two OpenMP regions and a round trip of the
 // fp32 gates through memory per step.  Here all T steps run inside ONE cooperative launch:
 //
-//   grid = (1024/HS hidden slices) x (batch-tile groups); CTA (s, y) owns hidden units [s*HS, s*HS+HS) of all
-//   four gates and walks the batch tiles y, y+gridDim.y, ... of 128 rows each.
-//   * W_hh rows of the slice ([4*HS] x 1024 int8, 32/64 KB) are loaded ONCE by TMA and stay in shared memory.
-//   * per (t, batch tile): TMA streams the 128x1024 int8 h tile through an 8-stage ring (one 128-byte
-//     K-chunk per stage), one elected thread issues tcgen05.mma.kind::i8 (M=128, N=4*HS, K=32) into a
-//     double-buffered TMEM accumulator, 16 epilogue warps read it back (tcgen05.ld), add the precomputed
-//     input projection G[t] (int32, exact), dequantise, evaluate the fp16 gates, update c, and write
-//     h_{t+1} (int8) to the ping-pong h buffer in L2 plus y[t].
-//   * the only cross-CTA dependency is "h_t of batch tile b is complete": a per-tile arrival counter in
-//     global memory (release by every slice CTA, acquire by the TMA producer).  No grid-wide barrier.
-// Bounded by: SMEM reads of the two MMA operands (192 KB per tile-step at 128 B/clk), the fp16 gate math
-// (~100 instructions per cell), and the L2 hand-off latency; see DESIGN.md.
+//   grid = 64 hidden slices x 2 batch-tile groups (optionally clusters of CS slice-CTAs); CTA (s, y) owns hidden
+//   units [16 s, 16 s + 16) of all four gates and walks the batch tiles y, y + 2, ... of 128 rows each.
+//   * its 64 rows of W_hh (64 KB int8) are loaded ONCE by TMA and stay in shared memory for the whole sequence.
+//   * per work item (t, batch tile):
+//       - warp 0 (producer): TMA-loads the 128x1024 int8 h_t tile as eight 16 KB K-chunks through a 4-stage ring
+//         (h lives in a K-chunk-major ping-pong buffer, so a chunk is one contiguous 16 KB read), and — as early as
+//         two items ahead, it does not depend on h — the tile's input projection G[t] (4 gates x 128 rows x 16
+//         int32, 64-byte swizzle) into a 2-stage ring;
+//       - warp 1: one thread issues tcgen05.mma.kind::i8 (M=128, N=64, K=32) x 32 into a double-buffered TMEM
+//         accumulator;
+//       - 16 epilogue warps: tcgen05.ld the accumulator, add G (int32, exact), dequantise, evaluate the fp16 gates,
+//         update c (kept between steps in a CTA-private blocked scratch, so its traffic is fully coalesced), stage
+//         h_{t+1} (int8) and y[t] in shared memory; 4 of them then write whole 16/32-byte row segments out;
+//       - warp 3 (publisher): when the item's stores are issued, one release increment of the tile's counter.
+//   * the only cross-CTA dependency is "h_t of batch tile b is complete": that per-tile counter (acquire by the
+//     producers).  No grid-wide barrier.  Several batch tiles per CTA are in flight, so the publish -> poll -> load
+//     latency of one tile is covered by the work of the others.
+//   * ragged batches: tile b runs tile_steps[b] timesteps only (the SUT sorts utterances by length, so a tile's
+//     rows have similar lengths); dead (t, tile) items are skipped by every role.
+// See DESIGN.md for the byte/instruction budget and the measured timeline.
 #include "kernels.cuh"
 #include "gate_math.cuh"
 #include "../../include/rnnt_rcp_ph_lut.h"
 
 namespace rnnt {
 
-
 __constant__ uint16_t c_rcp_lut[1024] = {RNNT_RCP_PH_LUT_VALUES};
 
+__device__ __forceinline__ uint32_t ld_acquire_cta_shared(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_cta_shared_inc(uint32_t addr) {
+  asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts64(uint32_t addr, uint32_t a, uint32_t b) {
+  asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
 
-template <int HS>
+// Work items of a CTA in issue order: for t, for its tiles, skipping tiles that have finished.  Start with (t=0, i=-1).
+struct ItemCursor {
+  int t, i;
+  __device__ __forceinline__ bool next(int T, int my_tiles, int by, int gy, const int* steps) {
+    for (;;) {
+      if (++i >= my_tiles) { i = 0; if (++t >= T) return false; }
+      if (t < steps[by + i * gy]) return true;
+    }
+  }
+};
+
+template <int CS>
 __global__ void __launch_bounds__(REC_THREADS, 1)
-lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h,
+lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h0,
+                      const __grid_constant__ CUtensorMap tmap_h, const __grid_constant__ CUtensorMap tmap_g,
                       const RecParams p) {
-  using S = RecSmem<HS>;
-  constexpr int UPT = HS / (REC_EPI_WARPS / 4);   // hidden units per epilogue thread (4 or 2)
-  static_assert(UPT == 2 || UPT == 4, "HS must be 8 or 16");
+  using S = RecSmem;
+  constexpr int HS = REC_HS;
+  constexpr uint16_t MC_MASK = (uint16_t)((1u << CS) - 1u);
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const uint32_t smem_w = smem_base;
   const uint32_t smem_h = smem_base + S::W_BYTES;
+  const uint32_t smem_g = smem_base + S::G_OFFSET;
+  const uint32_t smem_out = smem_base + S::OUT_OFFSET;
   uint16_t* lut = reinterpret_cast<uint16_t*>(smem_gen + S::LUT_OFFSET);
   const uint32_t bar_base = smem_base + S::BAR_OFFSET;
-  const uint32_t full_bar = bar_base;                  // [8]
-  const uint32_t empty_bar = bar_base + 64;            // [8]
-  const uint32_t tfull_bar = bar_base + 128;           // [2]
-  const uint32_t tempty_bar = bar_base + 144;          // [2]
-  const uint32_t wfull_bar = bar_base + 160;
-  const uint32_t epi_bar = bar_base + 168;             // epilogue warps -> publisher
-  const uint32_t tmem_slot = bar_base + 176;
+  const uint32_t full_bar = bar_base;                  // [REC_NS] h chunk landed (TMA complete_tx)
+  const uint32_t empty_bar = bar_base + 32;            // [REC_NS] h chunk consumed by the MMAs of all CS CTAs
+  const uint32_t gfull_bar = bar_base + 64;            // [REC_GS] G tile landed
+  const uint32_t gempty_bar = bar_base + 80;           // [REC_GS] G tile read by all epilogue warps
+  const uint32_t tfull_bar = bar_base + 96;            // [2] accumulator complete
+  const uint32_t done_bar = bar_base + 112;            // [2] item finished by all epilogue warps (frees the accumulator)
+  const uint32_t staged_bar = bar_base + 128;          // [2] h / y rows of the item staged in shared memory
+  const uint32_t wfull_bar = bar_base + 144;
+  const uint32_t tmem_slot = bar_base + 152;
+  const uint32_t done_cnt = bar_base + 160;            // [2] u32: monotonic "stores issued" counters for the publisher
+  int* s_steps = reinterpret_cast<int*>(smem_gen + S::BAR_OFFSET + 192);   // [REC_MAX_TILES]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x;
   const int num_slices = gridDim.x;
-  const int my_tiles = (p.num_btiles - (int)blockIdx.y + (int)gridDim.y - 1) / (int)gridDim.y;
-  const int num_items = p.T * my_tiles;
+  const int by = blockIdx.y, gy = gridDim.y;
+  const int my_tiles = (p.num_btiles - by + gy - 1) / gy;
+  const uint32_t cta_rank = (CS > 1) ? cluster_ctarank() : 0u;
+  const bool tracer = p.trace && blockIdx.x == 0 && blockIdx.y == 0;
 
   for (int i = threadIdx.x; i < 1024; i += REC_THREADS) lut[i] = c_rcp_lut[i];
-  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_h); }
+  if (threadIdx.x < REC_MAX_TILES) s_steps[threadIdx.x] = (threadIdx.x < p.num_btiles) ? p.tile_steps[threadIdx.x] : 0;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_h0); tma_prefetch_desc(&tmap_h); tma_prefetch_desc(&tmap_g);
+  }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < REC_KC; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(tfull_bar + 8 * i, 1); mbar_init(tempty_bar + 8 * i, REC_EPI_WARPS); }
+    for (int i = 0; i < REC_NS; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CS); }
+    for (int i = 0; i < REC_GS; ++i) { mbar_init(gfull_bar + 8 * i, 1); mbar_init(gempty_bar + 8 * i, REC_EPI_WARPS); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tfull_bar + 8 * i, 1);
+      mbar_init(done_bar + 8 * i, REC_EPI_WARPS);
+      mbar_init(staged_bar + 8 * i, REC_EPI_WARPS);
+    }
     mbar_init(wfull_bar, 1);
-    mbar_init(epi_bar, REC_EPI_WARPS);
+    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 160) = 0u;
+    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 164) = 0u;
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<(2 * S::UMMA_N < 32 ? 32 : 2 * S::UMMA_N)>(tmem_slot);
+  if (warp == 2) tmem_alloc<2 * S::UMMA_N>(tmem_slot);
   tc_fence_before();
   __syncthreads();
+  if (CS > 1) cluster_sync_all();     // peers' barriers are initialised before any multicast / remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *(volatile uint32_t*)(smem_gen + (tmem_slot - smem_base));
 
   if (warp == 0) {
     // ---------------------------------------------------------------- TMA producer
     if (lane == 0) {
-      // resident weight slice: 8 chunks of [4 gates][HS units][128 B]
       mbar_expect_tx(wfull_bar, S::W_BYTES);
       for (int kc = 0; kc < REC_KC; ++kc)
         tma_load_3d(smem_w + kc * S::W_CHUNK, &tmap_w, wfull_bar, kc * 128, slice * HS, 0);
-      uint32_t phase = 0; bool ok = true;
-      for (int it = 0; it < num_items && ok; ++it) {
-        const int t = it / my_tiles;
-        const int bt = (int)blockIdx.y + (it % my_tiles) * (int)gridDim.y;
+      bool ok = true;
+      uint32_t chunk = 0, gk = 0;
+      ItemCursor cur{0, -1}, gcur{0, -1};
+      bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
+      bool ghave = gcur.next(p.T, my_tiles, by, gy, s_steps);
+      auto issue_g = [&]() {
+        const uint32_t st = gk % REC_GS, ph = (gk / REC_GS) & 1u;
+        if (!mbar_wait(gempty_bar + 8 * st, ph ^ 1u, p.status)) { ok = false; return; }
+        const int bt = by + gcur.i * gy;
+        mbar_expect_tx(gfull_bar + 8 * st, S::G_STAGE);
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          tma_load_3d(smem_g + st * S::G_STAGE + g * S::G_GATE, &tmap_g, gfull_bar + 8 * st, g * REC_H + slice * HS, bt * REC_BM,
+                      gcur.t);
+        ++gk;
+        ghave = gcur.next(p.T, my_tiles, by, gy, s_steps);
+      };
+      if (ghave) issue_g();
+      while (have && ok) {
+        if (ghave) issue_g();          // projection tile of the NEXT item (independent of h)
+        if (!ok) break;
+        const int t = cur.t, bt = by + cur.i * gy;
         if (t > 0) {
           // wait until every slice CTA has published its part of h_t for this batch tile
           const int* flag = p.flags + bt * REC_FLAG_STRIDE;
@@ -98,13 +179,24 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           if (!ok) break;
           fence_proxy_async_all();   // generic-proxy writes of h_t (other CTAs) -> async-proxy (TMA) reads
         }
-        if (p.trace && blockIdx.x == 0 && blockIdx.y == 0) p.trace[t * 8 + 0] = clock64();
-        for (int kc = 0; kc < REC_KC; ++kc) {
-          if (!mbar_wait(empty_bar + 8 * kc, phase ^ 1, p.status)) { ok = false; break; }
-          mbar_expect_tx(full_bar + 8 * kc, S::H_CHUNK);
-          tma_load_3d(smem_h + kc * S::H_CHUNK, &tmap_h, full_bar + 8 * kc, kc * 128, bt * REC_BM, t & 1);
+        if (tracer && cur.i == 0) p.trace[t * 8 + 0] = clock64();
+        const int hrow0 = (((t & 1) * p.num_btiles + bt) * REC_KC) * REC_BM;   // row of chunk 0 in the chunk-major h buffer
+        for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
+          const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
+          // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
+          if (!mbar_wait(empty_bar + 8 * st, ph ^ 1u, p.status)) { ok = false; break; }
+          mbar_expect_tx(full_bar + 8 * st, S::H_CHUNK);
+          if (CS > 1 && (uint32_t)(kc % CS) != cta_rank) continue;
+          const uint32_t dst = smem_h + st * S::H_CHUNK, bar = full_bar + 8 * st;
+          if (t == 0) {              // h_0 straight from the caller's [N][1024] array (rows >= N read as zero)
+            if (CS == 1) tma_load_2d(dst, &tmap_h0, bar, kc * 128, bt * REC_BM);
+            else tma_load_2d_mc(dst, &tmap_h0, bar, kc * 128, bt * REC_BM, MC_MASK);
+          } else {
+            if (CS == 1) tma_load_2d(dst, &tmap_h, bar, 0, hrow0 + kc * REC_BM);
+            else tma_load_2d_mc(dst, &tmap_h, bar, 0, hrow0 + kc * REC_BM, MC_MASK);
+          }
         }
-        phase ^= 1;
+        have = cur.next(p.T, my_tiles, by, gy, s_steps);
       }
     }
   } else if (warp == 1) {
@@ -112,105 +204,125 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_i8(REC_BM, S::UMMA_N);
       bool ok = mbar_wait(wfull_bar, 0, p.status);
-      uint32_t phase = 0; int acc = 0; uint32_t acc_phase = 0;
-      for (int it = 0; it < num_items && ok; ++it) {
-        if (!mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, p.status)) break;
+      uint32_t chunk = 0; int acc = 0; uint32_t acc_phase = 0;
+      ItemCursor cur{0, -1};
+      while (ok && cur.next(p.T, my_tiles, by, gy, s_steps)) {
+        if (!mbar_wait(done_bar + 8 * acc, acc_phase ^ 1u, p.status)) break;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * S::UMMA_N;
-        for (int kc = 0; kc < REC_KC; ++kc) {
-          if (!mbar_wait(full_bar + 8 * kc, phase, p.status)) { ok = false; break; }
-          if (kc == 0 && p.trace && blockIdx.x == 0 && blockIdx.y == 0) p.trace[(it / my_tiles) * 8 + 1] = clock64();
+        for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
+          const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
+          if (!mbar_wait(full_bar + 8 * st, ph, p.status)) { ok = false; break; }
+          if (kc == 0 && tracer && cur.i == 0) p.trace[cur.t * 8 + 1] = clock64();
           tc_fence_after();
-          const uint64_t adesc = umma_desc_sw128(smem_h + kc * S::H_CHUNK);
+          const uint64_t adesc = umma_desc_sw128(smem_h + st * S::H_CHUNK);
           const uint64_t bdesc = umma_desc_sw128(smem_w + kc * S::W_CHUNK);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) != 0);
-          umma_commit(empty_bar + 8 * kc);
+          if (CS == 1) umma_commit(empty_bar + 8 * st);
+          else umma_commit_mc(empty_bar + 8 * st, MC_MASK);
         }
         if (!ok) break;
         umma_commit(tfull_bar + 8 * acc);
-        if (p.trace && blockIdx.x == 0 && blockIdx.y == 0) p.trace[(it / my_tiles) * 8 + 2] = clock64();
-        phase ^= 1;
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        if (tracer && cur.i == 0) p.trace[cur.t * 8 + 2] = clock64();
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else if (warp == 3) {
+    // ---------------------------------------------------------------- publisher
+    if (lane == 0) {
+      uint32_t item = 0; bool ok = true;
+      ItemCursor cur{0, -1};
+      while (ok && cur.next(p.T, my_tiles, by, gy, s_steps)) {
+        const int t = cur.t, bt = by + cur.i * gy;
+        const uint32_t target = REC_STORE_WARPS * (item / 2 + 1);
+        const uint32_t cnt = done_cnt + 4 * (item & 1u);
+        long long t0 = clock64(); uint32_t spins = 0;
+        while (ld_acquire_cta_shared(cnt) < target) {
+          if ((++spins & 255u) == 0) {
+            if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
+            if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_MBAR); ok = false; break; }
+          }
+        }
+        if (!ok) break;
+        if (tracer && cur.i == 0) p.trace[t * 8 + 6] = clock64();
+        // h_{t+1}[tile bt][this slice] is written: one release increment of the tile counter (cumulative over the
+        // storing warps' global stores through the shared-memory counter they released)
+        if (t + 1 < s_steps[bt])
+          asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+        if (tracer && cur.i == 0) p.trace[t * 8 + 7] = clock64();
+        ++item;
       }
     }
   } else if (warp >= REC_CTRL_WARPS) {
     // ---------------------------------------------------------------- epilogue: gates, cell update, outputs
     const int e = warp - REC_CTRL_WARPS;
     const int q = warp & 3;                 // TMEM lane quarter accessible to this warp (warp id % 4)
-    const int ug = e >> 2;                  // unit group within the slice
+    const int ug = e >> 2;                  // unit group within the slice (4 units each)
     const int row = q * 32 + lane;          // batch row within the tile
-    const int j0 = slice * HS + ug * UPT;   // first hidden unit of this thread
+    const int j0 = slice * HS + ug * 4;     // first hidden unit of this thread
+    const bool storer = e < REC_STORE_WARPS;
     const HalfConsts k = make_half_consts();
     const __half2 in_s = __float2half2_rn(p.in_scale), out_s = __float2half2_rn(p.out_scale);
-    float bias[4][UPT];
+    const bool same_scale = h2_bits(in_s) == h2_bits(out_s);
+    float bias[4][4];
 #pragma unroll
     for (int g = 0; g < 4; ++g)
 #pragma unroll
-      for (int u = 0; u < UPT; ++u) bias[g][u] = p.bias[g * REC_H + j0 + u];
+      for (int u = 0; u < 4; ++u) bias[g][u] = p.bias[g * REC_H + j0 + u];
+    const uint32_t g_off = (uint32_t)(row * 64 + ((ug ^ ((row >> 1) & 3)) << 4));   // SWIZZLE_64B position of this thread's 16 B
 
-    int acc = 0; uint32_t acc_phase = 0, epi_phase = 0;
-    for (int it = 0; it < num_items; ++it) {
-      const int t = it / my_tiles;
-      const int bt = (int)blockIdx.y + (it % my_tiles) * (int)gridDim.y;
+    int acc = 0; uint32_t acc_phase = 0;
+    ItemCursor cur{0, -1};
+    while (cur.next(p.T, my_tiles, by, gy, s_steps)) {
+      const int t = cur.t, bt = by + cur.i * gy;
+      const int steps = s_steps[bt];
       const int n = bt * REC_BM + row;
       const bool valid = n < p.N;
-      // operands that do not depend on the recurrent product: fetch them before waiting on the MMA
-      int gi[4][UPT];
-      uint32_t cbits[UPT / 2];
-      if (valid) {
-        const int32_t* gp = p.G + ((size_t)t * p.N + n) * (4 * REC_H) + j0;
+      const bool tr = tracer && cur.i == 0 && e == 0 && lane == 0;
+      // ---- operands that do not depend on the recurrent product
+      if (!mbar_wait(gfull_bar + 8 * acc, acc_phase, p.status)) break;      // G ring stage == accumulator parity
+      int gi[4][4];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          if constexpr (UPT == 4) {
-            const int4 v = __ldg(reinterpret_cast<const int4*>(gp + g * REC_H));
-            gi[g][0] = v.x; gi[g][1] = v.y; gi[g][2] = v.z; gi[g][3] = v.w;
-          } else {
-            const int2 v = __ldg(reinterpret_cast<const int2*>(gp + g * REC_H));
-            gi[g][0] = v.x; gi[g][1] = v.y;
-          }
+      for (int g = 0; g < 4; ++g) {
+        const uint4 v = lds128(smem_g + acc * S::G_STAGE + g * S::G_GATE + g_off);
+        gi[g][0] = (int)v.x; gi[g][1] = (int)v.y; gi[g][2] = (int)v.z; gi[g][3] = (int)v.w;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(gempty_bar + 8 * acc);
+      uint32_t cbits[2];
+      uint16_t* c_blk = p.c_ws + ((((size_t)bt * 64 + slice) * 4 + ug) * REC_BM + row) * 4;
+      if (t == 0) {
+        if (valid) {
+          const uint2 v = *reinterpret_cast<const uint2*>(p.cx + (size_t)n * REC_H + j0);
+          cbits[0] = v.x; cbits[1] = v.y;
+        } else {
+          cbits[0] = 0u; cbits[1] = 0u;
         }
-        const uint32_t* cp = reinterpret_cast<const uint32_t*>(p.cx + (size_t)n * REC_H + j0);
-#pragma unroll
-        for (int u = 0; u < UPT / 2; ++u) cbits[u] = cp[u];
       } else {
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-#pragma unroll
-          for (int u = 0; u < UPT; ++u) gi[g][u] = 0;
-#pragma unroll
-        for (int u = 0; u < UPT / 2; ++u) cbits[u] = 0;
+        const uint2 v = *reinterpret_cast<const uint2*>(c_blk);
+        cbits[0] = v.x; cbits[1] = v.y;
       }
 
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
-      const bool tr = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && e == 0 && lane == 0;
       if (tr) p.trace[t * 8 + 3] = clock64();
       tc_fence_after();
-      uint32_t a[4][UPT];
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * UPT);
+      uint32_t a[4][4];
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * 4);
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        if constexpr (UPT == 4) {
-          asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
-                       : "=r"(a[g][0]), "=r"(a[g][1]), "=r"(a[g][2]), "=r"(a[g][3])
-                       : "r"(t_row + g * HS) : "memory");
-        } else {
-          asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];"
-                       : "=r"(a[g][0]), "=r"(a[g][1]) : "r"(t_row + g * HS) : "memory");
-        }
-      }
+      for (int g = 0; g < 4; ++g)
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(a[g][0]), "=r"(a[g][1]), "=r"(a[g][2]), "=r"(a[g][3])
+                     : "r"(t_row + g * HS) : "memory");
       tmem_ld_wait();
       tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar + 8 * acc);   // accumulator stage may be overwritten
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-
       if (tr) p.trace[t * 8 + 4] = clock64();
+
       uint32_t hq_pack = 0, yq_pack = 0;
-      uint32_t ybf[UPT / 2];
+      uint32_t ybf[2];
 #pragma unroll
-      for (int u = 0; u < UPT; u += 2) {
+      for (int u = 0; u < 4; u += 2) {
         __half2 gate[4];
 #pragma unroll
         for (int g = 0; g < 4; ++g)
@@ -224,57 +336,78 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         const __half2 c_new = __hfma2(it_, gt_, __hmul2_rn(ft_, c_old));     // c = fma(i, g, f*c)
         cbits[u / 2] = h2_bits(c_new);
         const __half2 ht = __hmul2_rn(ot_, tanh_ph2(c_new, k, lut));
-        hq_pack |= quant_ph2(ht, in_s) << (8 * u);
+        const uint32_t hq = quant_ph2(ht, in_s);
+        hq_pack |= hq << (8 * u);
         if (p.skip_quant_y) {
           const float2 hf = __half22float2(ht);
           ybf[u / 2] = float_to_bf16_bits(hf.x) | (float_to_bf16_bits(hf.y) << 16);
         } else {
-          yq_pack |= quant_ph2(ht, out_s) << (8 * u);
+          yq_pack |= (same_scale ? hq : quant_ph2(ht, out_s)) << (8 * u);
         }
       }
-      if (valid) {
-        int8_t* hn = p.h_buf + ((size_t)((t + 1) & 1) * p.N_pad + n) * REC_H + j0;
-        if constexpr (UPT == 4) *reinterpret_cast<uint32_t*>(hn) = hq_pack;
-        else *reinterpret_cast<uint16_t*>(hn) = (uint16_t)hq_pack;
-        uint32_t* cp = reinterpret_cast<uint32_t*>(p.cx + (size_t)n * REC_H + j0);
-#pragma unroll
-        for (int u = 0; u < UPT / 2; ++u) cp[u] = cbits[u];
-        const size_t yoff = ((size_t)t * p.N + n) * REC_H + j0;
-        if (p.skip_quant_y) {
-          uint32_t* yp = reinterpret_cast<uint32_t*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
-#pragma unroll
-          for (int u = 0; u < UPT / 2; ++u) yp[u] = ybf[u];
-        } else {
-          int8_t* yp = reinterpret_cast<int8_t*>(p.y) + yoff;
-          if constexpr (UPT == 4) *reinterpret_cast<uint32_t*>(yp) = yq_pack;
-          else *reinterpret_cast<uint16_t*>(yp) = (uint16_t)yq_pack;
-        }
+      // ---- c: final value to the caller's array, otherwise to the CTA-private blocked scratch (coalesced 256 B per warp)
+      const bool last = t + 1 == steps;
+      if (last) {
+        if (valid) *reinterpret_cast<uint2*>(p.cx + (size_t)n * REC_H + j0) = make_uint2(cbits[0], cbits[1]);
+      } else {
+        *reinterpret_cast<uint2*>(c_blk) = make_uint2(cbits[0], cbits[1]);
       }
-      // publish h_{t+1}[tile bt][this slice]: generic -> async proxy fence for the TMA readers, every
-      // epilogue warp arrives on epi_bar (release.cta), the publisher thread waits for all 16 (bounded, so a
-      // protocol error cannot hang a bar.sync), then does one release increment of the tile counter.
-      if (tr) p.trace[t * 8 + 5] = clock64();
-      fence_proxy_async_all();
+      // ---- stage h_{t+1} and y[t] as [ug][row] so that four warps can write whole 16 / 32-byte row segments
+      const uint32_t out_h = smem_out + acc * S::OUT_STAGE, out_y = out_h + S::OUT_H;
+      sts32(out_h + (uint32_t)(ug * REC_BM + row) * 4u, hq_pack);
+      if (p.skip_quant_y) sts64(out_y + (uint32_t)(ug * REC_BM + row) * 8u, ybf[0], ybf[1]);
+      else sts32(out_y + (uint32_t)(ug * REC_BM + row) * 4u, yq_pack);
       __syncwarp();
-      if (tr) p.trace[t * 8 + 6] = clock64();
-      if (lane == 0) mbar_arrive(epi_bar);
-      if (e == 0 && lane == 0) {
-        if (mbar_wait(epi_bar, epi_phase, p.status)) {
-          __threadfence();
-          asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
-          if (tr) p.trace[t * 8 + 7] = clock64();
+      if (lane == 0) mbar_arrive(staged_bar + 8 * acc);
+      if (storer) {
+        if (!mbar_wait(staged_bar + 8 * acc, acc_phase, p.status)) break;
+        uint4 hv;
+        hv.x = lds32(out_h + (uint32_t)(0 * REC_BM + row) * 4u); hv.y = lds32(out_h + (uint32_t)(1 * REC_BM + row) * 4u);
+        hv.z = lds32(out_h + (uint32_t)(2 * REC_BM + row) * 4u); hv.w = lds32(out_h + (uint32_t)(3 * REC_BM + row) * 4u);
+        if (!last) {
+          int8_t* hn = p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 3)) * REC_BM + row) * 128 +
+                       (slice & 7) * 16;
+          *reinterpret_cast<uint4*>(hn) = hv;
+        } else if (valid) {   // last step of this tile: hand the state back to the caller's hx
+          *reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS) = hv;
         }
+        if (valid) {
+          const size_t yoff = ((size_t)t * p.N + n) * REC_H + slice * HS;
+          if (p.skip_quant_y) {
+            uint2 y0 = lds64(out_y + (uint32_t)(0 * REC_BM + row) * 8u), y1 = lds64(out_y + (uint32_t)(1 * REC_BM + row) * 8u);
+            uint2 y2 = lds64(out_y + (uint32_t)(2 * REC_BM + row) * 8u), y3 = lds64(out_y + (uint32_t)(3 * REC_BM + row) * 8u);
+            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
+            yp[0] = make_uint4(y0.x, y0.y, y1.x, y1.y);
+            yp[1] = make_uint4(y2.x, y2.y, y3.x, y3.y);
+          } else {
+            uint4 yv;
+            yv.x = lds32(out_y + (uint32_t)(0 * REC_BM + row) * 4u); yv.y = lds32(out_y + (uint32_t)(1 * REC_BM + row) * 4u);
+            yv.z = lds32(out_y + (uint32_t)(2 * REC_BM + row) * 4u); yv.w = lds32(out_y + (uint32_t)(3 * REC_BM + row) * 4u);
+            *reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff) = yv;
+          }
+        }
+        if (tr) p.trace[t * 8 + 5] = clock64();
+        __syncwarp();
+        if (lane == 0) red_release_cta_shared_inc(done_cnt + 4 * acc);   // publisher: this warp's rows are written
       }
-      epi_phase ^= 1;
+      // item finished by this warp.  A warp can be at most one item ahead of the slowest one (the next-but-one MMA waits
+      // on done_bar), so barriers / counters / staging buffers indexed by item parity suffice.
+      __syncwarp();
+      if (lane == 0) mbar_arrive(done_bar + 8 * acc);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) { tc_fence_after(); tmem_dealloc<(2 * S::UMMA_N < 32 ? 32 : 2 * S::UMMA_N)>(tmem_base); }
+  if (CS > 1) cluster_sync_all();     // no CTA leaves while peers may still multicast into it / arrive on its barriers
+  if (warp == 2) { tc_fence_after(); tmem_dealloc<2 * S::UMMA_N>(tmem_base); }
 }
 
-template __global__ void lstm_recurrent_kernel<16>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const RecParams);
-template __global__ void lstm_recurrent_kernel<8>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const RecParams);
+#define RNNT_REC_INST(CS)                                                                                            \
+  template __global__ void lstm_recurrent_kernel<CS>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
+                                                     const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
+                                                     const RecParams);
+RNNT_REC_INST(1) RNNT_REC_INST(2) RNNT_REC_INST(4)
 
 }  // namespace rnnt

@@ -64,10 +64,12 @@ class GreedyDecoder(torch.nn.Module):
             self.greedy_decode(x, x_lens)
         return self.res, self.res_idx + 1
 
-    def forward_ragged(self, packed: Tensor, offsets: Tensor, lens: Tensor, max_len: int):
+    def forward_ragged(self, packed: Tensor, offsets: Tensor, lens: Tensor, max_len: int, lens_host=None):
         """SUT fast path (quant mode): the batch as the unpadded concatenation of its utterances, all on the device.
         packed {sum T_i, 240} fp32, offsets {N} int64, lens {N} int32 (0 for batch-padding lanes).  Produces the same
-        int8 {T, N, 256} tensor that forward() derives from the padded fp32 batch, without materialising that batch."""
+        int8 {T, N, 256} tensor that forward() derives from the padded fp32 batch, without materialising that batch.
+        lens_host (host copy of lens, rows sorted by length as PytorchSUT.issue_queries does) lets the encoder skip the
+        (timestep, 128-row tile) items past a tile's longest utterance; transcripts are unchanged."""
         if self.run_mode != "quant" or self.split_len != -1:
             raise RuntimeError("forward_ragged serves run_mode='quant' without split_len")
         dev = packed.device
@@ -76,7 +78,7 @@ class GreedyDecoder(torch.nn.Module):
         pre = self.rnnt.transcription.pre_rnn
         k = packed.shape[-1]
         x = P.quantize_ragged(packed, offsets, lens, float(pre.in_scale[0].item()), max_len, (k + 63) // 64 * 64)
-        self.greedy_decode_quant(x, lens)
+        self.greedy_decode_quant(x, lens, lens_host)
         return self.res, self.res_idx + 1
 
     def greedy_decode(self, f: Tensor, f_lens: Tensor):
@@ -87,14 +89,14 @@ class GreedyDecoder(torch.nn.Module):
         return self.greedy_decode_f32(f, f_lens)     # fake_quant: torch modules, fp32 state
 
     # ------------------------------------------------------------------------------------------- int8 / bf16
-    def greedy_decode_quant(self, f: Tensor, f_lens: Tensor):
+    def greedy_decode_quant(self, f: Tensor, f_lens: Tensor, lens_host=None):
         n = self.batch_size
         dev = f.device
         self.symbols_added = torch.zeros(n, dtype=torch.int32, device=dev)
         self.time_idx = torch.zeros(n, dtype=torch.int32, device=dev)
         f_lens = f_lens.to(torch.int32)
         f, self.pre_hx, self.pre_cx, self.post_hx, self.post_cx = self.rnnt.transcription(
-            f, f_lens, self.pre_hx, self.pre_cx, self.post_hx, self.post_cx)
+            f, f_lens, self.pre_hx, self.pre_cx, self.post_hx, self.post_cx, lens_host)
         fac = RNNTParam.stack_time_factor
         f_lens = torch.div(f_lens + (fac - 1), fac, rounding_mode="floor").to(torch.int32)
         if self.fused:

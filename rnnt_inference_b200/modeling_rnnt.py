@@ -105,9 +105,20 @@ class Transcription(torch.nn.Module):
         self.run_mode = run_mode
 
     def forward(self, x: Tensor, x_lens: Tensor, pre_hx: List[Tensor], pre_cx: List[Tensor], post_hx: List[Tensor],
-                post_cx: List[Tensor]) -> Tuple[Tensor, List[Tensor], List[Tensor], List[Tensor], List[Tensor]]:
+                post_cx: List[Tensor], lens_host=None
+                ) -> Tuple[Tensor, List[Tensor], List[Tensor], List[Tensor], List[Tensor]]:
         """x {T, N, 240} fp32 (or int8 already quantised), x_lens {N} -> x {ceil(T/2), N, 1024} (bf16 in quant mode);
         the four state lists are updated in place and returned (modeling_rnnt.py:116-144)."""
+        if lens_host is not None and self.run_mode == "quant":
+            # ragged batch sorted by length: per-128-row-tile step counts for the recurrent kernels (pre: frames,
+            # post: stacked frames); the skipped tail is exactly what stack_time / the decode loop never read
+            from . import ops
+            n = x.size(1)
+            x, pre_hx, pre_cx = self.pre_rnn(x, pre_hx, pre_cx, tile_steps=ops.tile_steps_for(lens_host, n))
+            x = self.stack_time(x, x_lens)
+            x, post_hx, post_cx = self.post_rnn(
+                x, post_hx, post_cx, tile_steps=ops.tile_steps_for(lens_host, n, RNNTParam.stack_time_factor))
+            return x, pre_hx, pre_cx, post_hx, post_cx
         x, pre_hx, pre_cx = self.pre_rnn(x, pre_hx, pre_cx)
         x = self.stack_time(x, x_lens)
         x, post_hx, post_cx = self.post_rnn(x, post_hx, post_cx)

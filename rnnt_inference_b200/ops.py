@@ -100,26 +100,45 @@ def gemm_i8_i32(a, w, out=None, simt=False):
     return out
 
 
-def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y):
+def tile_steps_for(lens_host, n, divisor=1):
+    """Host int32 array for rnnt_lstm_recurrent_i8_ragged: per 128-row batch tile, max(ceil(len / divisor)) of its rows."""
+    import numpy as np
+    lens = np.zeros((n + 127) // 128 * 128, dtype=np.int64)
+    lens[:len(lens_host)] = np.asarray(lens_host, dtype=np.int64)
+    steps = (lens.reshape(-1, 128).max(axis=1) + divisor - 1) // divisor
+    return np.ascontiguousarray(steps.astype(np.int32))
+
+
+def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, tile_steps=None):
     """lstm_layer_amx_int8 (lstm_amx.cpp:59-158). x int8 [T,N,K]; hx int8 [N,H], cx fp16 [N,H] updated IN PLACE.
-    Returns y: int8 [T,N,H] or bf16 [T,N,H] when skip_quant_y."""
+    Returns y: int8 [T,N,H] or bf16 [T,N,H] when skip_quant_y.  tile_steps (host int32 per 128-row tile, see
+    tile_steps_for): ragged batch sorted by length — (t, tile) items past a tile's last step are skipped and y is zero
+    there."""
     L.require_cuda(x, hx, cx, w_ih, w_hh, bias)
     t, n, k = x.shape
     if hx.dtype != torch.int8 or cx.dtype != torch.float16 or x.dtype != torch.int8:
         raise RuntimeError("lstm_layer_i8: x/hx must be int8 and cx float16")
-    y = torch.empty((t, n, H), dtype=torch.bfloat16 if skip_quant_y else torch.int8, device=x.device)
+    alloc = torch.empty if tile_steps is None else torch.zeros
+    y = alloc((t, n, H), dtype=torch.bfloat16 if skip_quant_y else torch.int8, device=x.device)
     if t == 0:
         return y
     g_ws = _ws.get("lstm_g", t * n * 4 * H * 4, x.device)
     ws = _ws.get("lstm_rec", L.lib.rnnt_lstm_recurrent_workspace_bytes(n), x.device)
     st = L.stream_ptr()
+    ts_ptr = None
+    if tile_steps is not None:
+        if tile_steps.dtype.name != "int32" or len(tile_steps) != (n + 127) // 128:
+            raise RuntimeError("lstm_layer_i8: tile_steps must be int32 with ceil(N/128) entries")
+        ts_ptr = ctypes.c_void_p(tile_steps.ctypes.data)
     # phase A: one projection GEMM over all timesteps; phase B: one persistent recurrent kernel (rnnt_lstm_layer_i8 is
     # exactly these two calls; they are issued separately so that bench.py can time each kernel with CUDA events)
     telemetry.bracket("gemm_i8", (t * n, k), lambda: L.check(
         L.lib.rnnt_gemm_i8_i32(L.ptr(x), L.ptr(w_ih), L.ptr(g_ws), t * n, 4 * H, k, st)))
-    telemetry.bracket("lstm_recurrent", (t, n, bool(skip_quant_y)), lambda: L.check(
-        L.lib.rnnt_lstm_recurrent_i8(L.ptr(g_ws), L.ptr(w_hh), L.ptr(bias), float(rb_scale), float(in_scale), float(out_scale),
-                                     int(bool(skip_quant_y)), L.ptr(hx), L.ptr(cx), L.ptr(y), t, n, H, L.ptr(ws), st)))
+    units = (t, n, bool(skip_quant_y)) if tile_steps is None else (int(tile_steps.sum()), 128, bool(skip_quant_y))
+    telemetry.bracket("lstm_recurrent", units, lambda: L.check(
+        L.lib.rnnt_lstm_recurrent_i8_ragged(L.ptr(g_ws), L.ptr(w_hh), L.ptr(bias), float(rb_scale), float(in_scale),
+                                            float(out_scale), int(bool(skip_quant_y)), L.ptr(hx), L.ptr(cx), L.ptr(y), t, n, H,
+                                            ts_ptr, L.ptr(ws), st)))
     telemetry.launches += 2
     return y
 

@@ -36,7 +36,7 @@ _DEFAULT_ARGS = dict(enable_bf16=False, split_len=-1, scenario="Offline", load_j
 class _Batch:
     """One staged / in-flight batch of the pipelined Offline loop."""
     __slots__ = ("samples", "n_actual", "n_padded", "max_len", "packed", "meta", "ready", "done", "res", "res_len", "tok_host",
-                 "len_host", "cap", "h2d_bytes", "keep")
+                 "len_host", "cap", "h2d_bytes", "keep", "lens_host")
 
 
 class PytorchSUT:
@@ -109,6 +109,7 @@ class PytorchSUT:
         feats = [self.qsl[s.index][0] for s in chunk]
         lens = [int(f.shape[0]) for f in feats]
         b.max_len = max(lens)
+        b.lens_host = lens
         meta = torch.zeros((2, b.n_padded), dtype=torch.int64)
         meta[0, :b.n_actual] = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]), dtype=torch.int64)
         meta[1, :b.n_actual] = torch.tensor(lens, dtype=torch.int64)
@@ -142,7 +143,7 @@ class PytorchSUT:
             self._compute_stream.wait_event(b.ready)
             offsets = b.meta[0]
             lens = b.meta[1].to(torch.int32)
-            b.res, b.res_len = self.model.forward_ragged(b.packed, offsets, lens, b.max_len)
+            b.res, b.res_len = self.model.forward_ragged(b.packed, offsets, lens, b.max_len, b.lens_host)
             # tokens: almost always fewer than one per stacked frame; the rare longer row is fetched in _finish
             b.cap = min(b.res.shape[1], max(32, (b.max_len + 1) // 2))
             b.tok_host = torch.empty((b.n_padded, b.cap), dtype=torch.int32, pin_memory=True)

@@ -71,7 +71,8 @@ def test_stack_time(ops, t, n, c):
 
 
 @pytest.mark.parametrize("t,n,k,last", [(3, 32, 256, False), (4, 17, 1024, False), (3, 160, 1024, True), (2, 300, 2048, False),
-                                        (5, 128, 1024, True)])
+                                        (5, 128, 1024, True), (6, 640, 256, False), (5, 1000, 256, True),
+                                        (40, 256, 256, False)])
 def test_lstm_layer_i8(ops, t, n, k, last):
     """The hot-path pin restated from test_amx_linear.py:214-295 (fused layer vs composed ops), here GPU vs oracle:
     y / hx / cx must be bit-identical."""
@@ -89,6 +90,39 @@ def test_lstm_layer_i8(ops, t, n, k, last):
     _lib.check_device_status()
     y_np = bits(y) if last else y.cpu().numpy()
     np.testing.assert_array_equal(y_np, y_o)
+    np.testing.assert_array_equal(hx.cpu().numpy(), hx_o)
+    np.testing.assert_array_equal(cx.cpu().numpy().view(np.uint16), cx_o)
+
+
+@pytest.mark.parametrize("cluster", [1, 2, 4])
+def test_lstm_layer_i8_ragged_tiles(ops, cluster):
+    """Ragged batch sorted by length: tile b runs tile_steps[b] steps.  Each 128-row tile must equal the oracle run on that
+    tile alone for its own number of steps (y beyond it stays zero), for every cluster size of the recurrent kernel."""
+    from rnnt_inference_b200 import _lib
+    t, n, k = 7, 520, 256
+    steps = np.array([7, 6, 4, 4, 1], np.int32)
+    lp = Hh.make_lstm_layer(seed=77, k_in=k)
+    rng = np.random.default_rng(cluster + 5)
+    x = rng.integers(-100, 101, (t, n, k), dtype=np.int8)
+    hx0 = rng.integers(-127, 128, (n, 1024), dtype=np.int8)
+    cx0 = rng.normal(0, 0.5, (n, 1024)).astype(np.float16)
+    y_o = np.zeros((t, n, 1024), np.int8)
+    hx_o, cx_o = hx0.copy(), cx0.view(np.uint16).copy()
+    for b, s in enumerate(steps):
+        r = slice(128 * b, min(n, 128 * b + 128))
+        h_t, c_t = np.ascontiguousarray(hx_o[r]), np.ascontiguousarray(cx_o[r])
+        y_o[:s, r] = O.lstm_layer_i8(np.ascontiguousarray(x[:s, r]), h_t, c_t, lp["w_ih"], lp["w_hh"], lp["bias"], lp["rb_scale"],
+                                     lp["in_scale"], lp["out_scale"], False)
+        hx_o[r], cx_o[r] = h_t, c_t
+    _lib.check(_lib.lib.rnnt_debug_set_recurrent_cluster(cluster))
+    try:
+        hx, cx = dev(hx0), dev(cx0)
+        y = ops.lstm_layer_i8(dev(x), hx, cx, dev(lp["w_ih"]), dev(lp["w_hh"]), dev(lp["bias"]), lp["rb_scale"], lp["in_scale"],
+                              lp["out_scale"], False, tile_steps=steps)
+        _lib.check_device_status()
+    finally:
+        _lib.lib.rnnt_debug_set_recurrent_cluster(4)
+    np.testing.assert_array_equal(y.cpu().numpy(), y_o)
     np.testing.assert_array_equal(hx.cpu().numpy(), hx_o)
     np.testing.assert_array_equal(cx.cpu().numpy().view(np.uint16), cx_o)
 

@@ -93,7 +93,10 @@ def test_forward_ragged_equals_forward(setup):
         lens = torch.zeros(32, dtype=torch.int32)
         lens[:len(feats)] = torch.tensor(LENS, dtype=torch.int32)
         res2, len2 = dec.forward_ragged(packed, offsets.cuda(), lens.cuda(), max(LENS))
+        res2, len2 = res2.clone(), len2.clone()
+        res3, len3 = dec.forward_ragged(packed, offsets.cuda(), lens.cuda(), max(LENS), list(LENS))   # tile-skipping encoder
     assert torch.equal(res_len, len2) and torch.equal(res, res2)
+    assert torch.equal(res_len, len3) and torch.equal(res, res3)
 
 
 def test_sut_offline_query_vs_oracle(setup):
