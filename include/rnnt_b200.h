@@ -84,6 +84,9 @@ int rnnt_debug_set_recurrent_trace(void* device_buffer);
 /* TUNING/DEBUG: slice-CTAs per thread-block cluster of the recurrent kernel (1, 2 or 4; default 4, or the environment
  * variable RNNT_REC_CLUSTER).  The h tile of a batch tile is TMA-multicast inside a cluster.  Results do not depend on it. */
 int rnnt_debug_set_recurrent_cluster(int ctas);
+/* PROFILING ONLY (results become garbage): bit 0 skip the MMAs, bit 1 skip the gate math, bit 2 skip the h loads.
+ * Used by profiles/trace_recurrent.py to attribute the step time; 0 = normal operation. */
+int rnnt_debug_set_recurrent_flags(int flags);
 
 /* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.
  * x [T][N][K] int8 (K % 16 == 0).  g_ws: T*N*4H int32 scratch for the projection. */

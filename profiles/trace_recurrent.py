@@ -13,6 +13,8 @@ from rnnt_inference_b200.modeling_rnnt import RNNT
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 60
+if len(sys.argv) > 4:
+    _lib.check(_lib.lib.rnnt_debug_set_recurrent_flags(int(sys.argv[4])))
 if len(sys.argv) > 3:
     _lib.check(_lib.lib.rnnt_debug_set_recurrent_cluster(int(sys.argv[3])))
 torch.cuda.set_device(0)

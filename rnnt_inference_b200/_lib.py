@@ -42,6 +42,7 @@ _SIGS = {
     "rnnt_lstm_recurrent_i8_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_debug_set_recurrent_trace": (_i, [_vp]),
     "rnnt_debug_set_recurrent_cluster": (_i, [_i]),
+    "rnnt_debug_set_recurrent_flags": (_i, [_i]),
     "rnnt_lstm_layer_i8": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_stack_time_i8": (_i, [_vp, _vp, _i, _vp, _i, _i, _i, _vp]),
     "rnnt_linear_bf16_bf16": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),

@@ -327,6 +327,7 @@ static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, 
 static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th, const CUtensorMap& tg,
                       const RecParams& p, int num_slices, int grid_y, int cs_max, cudaStream_t st) {
   cudaError_t e = cudaErrorUnknown;
+  if (cs_max >= 8) { e = rec_launch_cs<8>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
   if (cs_max >= 4) { e = rec_launch_cs<4>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
   if (cs_max >= 2) { e = rec_launch_cs<2>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
   e = rec_launch_cs<1>(tw, th0, th, tg, p, num_slices, grid_y, st);
@@ -340,14 +341,16 @@ static int rec_cluster_pref() {
   if (v < 0) {
     const char* s = getenv("RNNT_REC_CLUSTER");   // 1, 2 or 4 slice-CTAs per cluster (tuning knob; default 1: L2 already
     v = s ? atoi(s) : 1;                          // de-duplicates <= 4 concurrent readers of a line, measured no gain)
-    if (v != 1 && v != 2 && v != 4) v = 1;
+    if (v != 1 && v != 2 && v != 4 && v != 8) v = 1;
   }
   return v;
 }
 
 extern "C" {
+static int g_rec_debug = 0;
+int rnnt_debug_set_recurrent_flags(int flags) { g_rec_debug = flags; return RNNT_OK; }
 int rnnt_debug_set_recurrent_cluster(int ctas) {
-  if (ctas != 1 && ctas != 2 && ctas != 4) return fail(RNNT_ERR_INVALID, "recurrent cluster size must be 1, 2 or 4");
+  if (ctas != 1 && ctas != 2 && ctas != 4 && ctas != 8) return fail(RNNT_ERR_INVALID, "recurrent cluster size must be 1, 2, 4 or 8");
   g_rec_cluster = ctas;
   return RNNT_OK;
 }
@@ -414,6 +417,7 @@ int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const fl
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
   p.T = T; p.N = N; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
   p.trace = g_rec_trace;
+  p.debug = g_rec_debug;
   return rec_launch(tw, th0, th, tg, p, num_slices, grid_y, rec_cluster_pref(), st);
 }
 

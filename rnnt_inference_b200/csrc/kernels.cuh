@@ -73,6 +73,7 @@ struct RecParams {
   float rb_scale, in_scale, out_scale;
   int T, N, num_btiles, skip_quant_y;
   int tile_steps[REC_MAX_TILES];   // timesteps to run for each batch tile (<= T); ragged batches sorted by length
+  int debug;               // profiling only (rnnt_debug_set_recurrent_flags): 1 skip MMAs, 2 skip gate math, 4 skip h loads
   long long* trace;        // optional [T][8] clock64 stamps of CTA (0,0) (profiles/trace_recurrent.py; NULL otherwise)
 };
 

@@ -112,8 +112,9 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   for (int i = threadIdx.x; i < 1024; i += REC_THREADS) lut[i] = c_rcp_lut[i];
   if (threadIdx.x < REC_MAX_TILES) s_steps[threadIdx.x] = (threadIdx.x < p.num_btiles) ? p.tile_steps[threadIdx.x] : 0;
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_h0); tma_prefetch_desc(&tmap_h); tma_prefetch_desc(&tmap_g);
+    tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_h0); tma_prefetch_desc(&tmap_h);
   }
+  if (warp == 2 && lane == 0) tma_prefetch_desc(&tmap_g);
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < REC_NS; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CS); }
     for (int i = 0; i < REC_GS; ++i) { mbar_init(gfull_bar + 8 * i, 1); mbar_init(gempty_bar + 8 * i, REC_EPI_WARPS); }
@@ -141,26 +142,10 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       for (int kc = 0; kc < REC_KC; ++kc)
         tma_load_3d(smem_w + kc * S::W_CHUNK, &tmap_w, wfull_bar, kc * 128, slice * HS, 0);
       bool ok = true;
-      uint32_t chunk = 0, gk = 0;
-      ItemCursor cur{0, -1}, gcur{0, -1};
+      uint32_t chunk = 0;
+      ItemCursor cur{0, -1};
       bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
-      bool ghave = gcur.next(p.T, my_tiles, by, gy, s_steps);
-      auto issue_g = [&]() {
-        const uint32_t st = gk % REC_GS, ph = (gk / REC_GS) & 1u;
-        if (!mbar_wait(gempty_bar + 8 * st, ph ^ 1u, p.status)) { ok = false; return; }
-        const int bt = by + gcur.i * gy;
-        mbar_expect_tx(gfull_bar + 8 * st, S::G_STAGE);
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          tma_load_3d(smem_g + st * S::G_STAGE + g * S::G_GATE, &tmap_g, gfull_bar + 8 * st, g * REC_H + slice * HS, bt * REC_BM,
-                      gcur.t);
-        ++gk;
-        ghave = gcur.next(p.T, my_tiles, by, gy, s_steps);
-      };
-      if (ghave) issue_g();
       while (have && ok) {
-        if (ghave) issue_g();          // projection tile of the NEXT item (independent of h)
-        if (!ok) break;
         const int t = cur.t, bt = by + cur.i * gy;
         if (t > 0) {
           // wait until every slice CTA has published its part of h_t for this batch tile
@@ -169,7 +154,8 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           long long t0 = clock64(); uint32_t spins = 0;
           for (;;) {
             int v;
-            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+            // relaxed polls (an acquire load costs an L1 invalidation per poll); one acquire fence after the loop
+            asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
             if (v >= target) break;
             if ((++spins & 63u) == 0) {
               if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
@@ -177,7 +163,8 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
             }
           }
           if (!ok) break;
-          fence_proxy_async_all();   // generic-proxy writes of h_t (other CTAs) -> async-proxy (TMA) reads
+          asm volatile("fence.acquire.gpu;" ::: "memory");
+          if (!(p.debug & 32)) fence_proxy_async_all();   // generic-proxy writes of h_t (other CTAs) -> async-proxy (TMA) reads
         }
         if (tracer && cur.i == 0) p.trace[t * 8 + 0] = clock64();
         const int hrow0 = (((t & 1) * p.num_btiles + bt) * REC_KC) * REC_BM;   // row of chunk 0 in the chunk-major h buffer
@@ -185,6 +172,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
           // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
           if (!mbar_wait(empty_bar + 8 * st, ph ^ 1u, p.status)) { ok = false; break; }
+          if (p.debug & 4) { mbar_arrive(full_bar + 8 * st); continue; }
           mbar_expect_tx(full_bar + 8 * st, S::H_CHUNK);
           if (CS > 1 && (uint32_t)(kc % CS) != cta_rank) continue;
           const uint32_t dst = smem_h + st * S::H_CHUNK, bar = full_bar + 8 * st;
@@ -219,7 +207,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           const uint64_t bdesc = umma_desc_sw128(smem_w + kc * S::W_CHUNK);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) != 0);
+            if (!(p.debug & 1)) umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) != 0);
           if (CS == 1) umma_commit(empty_bar + 8 * st);
           else umma_commit_mc(empty_bar + 8 * st, MC_MASK);
         }
@@ -227,6 +215,24 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         umma_commit(tfull_bar + 8 * acc);
         if (tracer && cur.i == 0) p.trace[cur.t * 8 + 2] = clock64();
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else if (warp == 2) {
+    // ---------------------------------------------------------------- G producer: the tile's input projection does not
+    // depend on h, so it runs ahead of everything else by the depth of its ring (as soon as the epilogue has read a stage)
+    if (lane == 0) {
+      uint32_t gk = 0;
+      ItemCursor cur{0, -1};
+      while (!(p.debug & 64) && cur.next(p.T, my_tiles, by, gy, s_steps)) {
+        const uint32_t st = gk % REC_GS, ph = (gk / REC_GS) & 1u;
+        if (!mbar_wait(gempty_bar + 8 * st, ph ^ 1u, p.status)) break;
+        const int bt = by + cur.i * gy;
+        mbar_expect_tx(gfull_bar + 8 * st, S::G_STAGE);
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          tma_load_3d(smem_g + st * S::G_STAGE + g * S::G_GATE, &tmap_g, gfull_bar + 8 * st, g * REC_H + slice * HS, bt * REC_BM,
+                      cur.t);
+        ++gk;
       }
     }
   } else if (warp == 3) {
@@ -249,8 +255,10 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (tracer && cur.i == 0) p.trace[t * 8 + 6] = clock64();
         // h_{t+1}[tile bt][this slice] is written: one release increment of the tile counter (cumulative over the
         // storing warps' global stores through the shared-memory counter they released)
-        if (t + 1 < s_steps[bt])
-          asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+        if (t + 1 < s_steps[bt]) {
+          if (p.debug & 16) asm volatile("red.relaxed.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+          else asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+        }
         if (tracer && cur.i == 0) p.trace[t * 8 + 7] = clock64();
         ++item;
       }
@@ -273,37 +281,55 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       for (int u = 0; u < 4; ++u) bias[g][u] = p.bias[g * REC_H + j0 + u];
     const uint32_t g_off = (uint32_t)(row * 64 + ((ug ^ ((row >> 1) & 3)) << 4));   // SWIZZLE_64B position of this thread's 16 B
 
+    // c of an item: t == 0 from the caller's cx, else from the blocked scratch this same thread wrote one step earlier.
+    // It is fetched one item ahead (cn) so that its L2 latency hides behind the previous item's gate math; when the next
+    // item is the same tile (a CTA with one live tile) the freshly computed value is carried in registers instead.
+    auto load_c = [&](int t_, int bt_, uint32_t (&c)[2]) {
+      if (t_ == 0) {
+        const int n_ = bt_ * REC_BM + row;
+        if (n_ < p.N) {
+          const uint2 v = *reinterpret_cast<const uint2*>(p.cx + (size_t)n_ * REC_H + j0);
+          c[0] = v.x; c[1] = v.y;
+        } else {
+          c[0] = 0u; c[1] = 0u;
+        }
+      } else {
+        const uint2 v = *reinterpret_cast<const uint2*>(p.c_ws + ((((size_t)bt_ * 64 + slice) * 4 + ug) * REC_BM + row) * 4);
+        c[0] = v.x; c[1] = v.y;
+      }
+    };
     int acc = 0; uint32_t acc_phase = 0;
-    ItemCursor cur{0, -1};
-    while (cur.next(p.T, my_tiles, by, gy, s_steps)) {
+    ItemCursor cur{0, -1}, nxt{0, -1};
+    bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
+    bool have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);     // nxt runs one item ahead of cur
+    if (have_next) have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);
+    uint32_t cn[2] = {0u, 0u};
+    if (have) load_c(cur.t, by + cur.i * gy, cn);
+    for (; have; have = cur.next(p.T, my_tiles, by, gy, s_steps)) {
       const int t = cur.t, bt = by + cur.i * gy;
       const int steps = s_steps[bt];
       const int n = bt * REC_BM + row;
       const bool valid = n < p.N;
+      uint32_t cbits[2] = {cn[0], cn[1]};
+      const bool carry = have_next && (by + nxt.i * gy) == bt;       // next item = next step of this very tile
+      if (have_next && !carry && !(p.debug & 128)) load_c(nxt.t, by + nxt.i * gy, cn);
       const bool tr = tracer && cur.i == 0 && e == 0 && lane == 0;
       // ---- operands that do not depend on the recurrent product
-      if (!mbar_wait(gfull_bar + 8 * acc, acc_phase, p.status)) break;      // G ring stage == accumulator parity
       int gi[4][4];
+      if (!(p.debug & 64)) {
+        if (!mbar_wait(gfull_bar + 8 * acc, acc_phase, p.status)) break;      // G ring stage == accumulator parity
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const uint4 v = lds128(smem_g + acc * S::G_STAGE + g * S::G_GATE + g_off);
-        gi[g][0] = (int)v.x; gi[g][1] = (int)v.y; gi[g][2] = (int)v.z; gi[g][3] = (int)v.w;
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(gempty_bar + 8 * acc);
-      uint32_t cbits[2];
-      uint16_t* c_blk = p.c_ws + ((((size_t)bt * 64 + slice) * 4 + ug) * REC_BM + row) * 4;
-      if (t == 0) {
-        if (valid) {
-          const uint2 v = *reinterpret_cast<const uint2*>(p.cx + (size_t)n * REC_H + j0);
-          cbits[0] = v.x; cbits[1] = v.y;
-        } else {
-          cbits[0] = 0u; cbits[1] = 0u;
+        for (int g = 0; g < 4; ++g) {
+          const uint4 v = lds128(smem_g + acc * S::G_STAGE + g * S::G_GATE + g_off);
+          gi[g][0] = (int)v.x; gi[g][1] = (int)v.y; gi[g][2] = (int)v.z; gi[g][3] = (int)v.w;
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(gempty_bar + 8 * acc);
       } else {
-        const uint2 v = *reinterpret_cast<const uint2*>(c_blk);
-        cbits[0] = v.x; cbits[1] = v.y;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) { gi[g][0] = t; gi[g][1] = n; gi[g][2] = g; gi[g][3] = lane; }
       }
+      uint16_t* c_blk = p.c_ws + ((((size_t)bt * 64 + slice) * 4 + ug) * REC_BM + row) * 4;
 
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
       if (tr) p.trace[t * 8 + 3] = clock64();
@@ -323,6 +349,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       uint32_t ybf[2];
 #pragma unroll
       for (int u = 0; u < 4; u += 2) {
+        if (p.debug & 2) { hq_pack ^= a[0][u] + gi[1][u]; yq_pack = hq_pack; ybf[u / 2] = hq_pack; continue; }
         __half2 gate[4];
 #pragma unroll
         for (int g = 0; g < 4; ++g)
@@ -349,7 +376,9 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       const bool last = t + 1 == steps;
       if (last) {
         if (valid) *reinterpret_cast<uint2*>(p.cx + (size_t)n * REC_H + j0) = make_uint2(cbits[0], cbits[1]);
-      } else {
+      } else if (carry) {
+        cn[0] = cbits[0]; cn[1] = cbits[1];
+      } else if (!(p.debug & 8)) {
         *reinterpret_cast<uint2*>(c_blk) = make_uint2(cbits[0], cbits[1]);
       }
       // ---- stage h_{t+1} and y[t] as [ug][row] so that four warps can write whole 16 / 32-byte row segments
@@ -371,7 +400,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         } else if (valid) {   // last step of this tile: hand the state back to the caller's hx
           *reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS) = hv;
         }
-        if (valid) {
+        if (valid && !(p.debug & 8)) {
           const size_t yoff = ((size_t)t * p.N + n) * REC_H + slice * HS;
           if (p.skip_quant_y) {
             uint2 y0 = lds64(out_y + (uint32_t)(0 * REC_BM + row) * 8u), y1 = lds64(out_y + (uint32_t)(1 * REC_BM + row) * 8u);
@@ -395,6 +424,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       __syncwarp();
       if (lane == 0) mbar_arrive(done_bar + 8 * acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      if (have_next) have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);
     }
   }
 
@@ -408,6 +438,6 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   template __global__ void lstm_recurrent_kernel<CS>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
                                                      const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
                                                      const RecParams);
-RNNT_REC_INST(1) RNNT_REC_INST(2) RNNT_REC_INST(4)
+RNNT_REC_INST(1) RNNT_REC_INST(2) RNNT_REC_INST(4) RNNT_REC_INST(8)
 
 }  // namespace rnnt

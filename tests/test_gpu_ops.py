@@ -94,7 +94,7 @@ def test_lstm_layer_i8(ops, t, n, k, last):
     np.testing.assert_array_equal(cx.cpu().numpy().view(np.uint16), cx_o)
 
 
-@pytest.mark.parametrize("cluster", [1, 2, 4])
+@pytest.mark.parametrize("cluster", [1, 2, 4, 8])
 def test_lstm_layer_i8_ragged_tiles(ops, cluster):
     """Ragged batch sorted by length: tile b runs tile_steps[b] steps.  Each 128-row tile must equal the oracle run on that
     tile alone for its own number of steps (y beyond it stays zero), for every cluster size of the recurrent kernel."""
@@ -121,7 +121,7 @@ def test_lstm_layer_i8_ragged_tiles(ops, cluster):
                               lp["out_scale"], False, tile_steps=steps)
         _lib.check_device_status()
     finally:
-        _lib.lib.rnnt_debug_set_recurrent_cluster(4)
+        _lib.lib.rnnt_debug_set_recurrent_cluster(1)
     np.testing.assert_array_equal(y.cpu().numpy(), y_o)
     np.testing.assert_array_equal(hx.cpu().numpy(), hx_o)
     np.testing.assert_array_equal(cx.cpu().numpy().view(np.uint16), cx_o)
