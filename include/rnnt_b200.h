@@ -141,6 +141,9 @@ typedef struct {
 } rnnt_decode_weights;
 
 int64_t rnnt_greedy_decode_workspace_bytes(int N);
+/* DEBUG: device buffer of max_iters*8 int64 receiving clock64 stamps of CTA 0 per decode iteration (iteration start, LSTM
+ * layer 0 done, after barrier, layer 1 + barrier, fc1 + barrier, joint/update done, after barrier, active lanes). NULL = off. */
+int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);
 /* y1 [T2][N][J] bf16 (from rnnt_linear_bf16_bf16), f_lens [N] STACKED lengths.
  * In/out state: res [N][L] int32, res_idx/symbols_added/time_idx/pre_g [N] int32,
  * pre_hg0/1 [N][P] bf16, pre_cg0/1 [N][P] fp32.  iters_out (device int32[1], may be NULL) receives

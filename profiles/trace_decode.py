@@ -1,0 +1,49 @@
+"""Per-iteration timeline of CTA 0 of the fused greedy-decode kernel (clock64 stamps via rnnt_debug_set_decode_trace).
+Usage: python profiles/trace_decode.py [N] [max_frames]"""
+import ctypes
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+from rnnt_inference_b200 import _lib, synthetic as S
+from rnnt_inference_b200.decoder import GreedyDecoder
+from rnnt_inference_b200.modeling_rnnt import RNNT
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
+cap_frames = int(sys.argv[2]) if len(sys.argv) > 2 else 500
+torch.cuda.set_device(0)
+rnnt = RNNT(S.make_checkpoint(), "quant", True).eval()
+dec = GreedyDecoder(rnnt, "quant", True, -1, n)
+lens = np.sort(S.utterance_lengths(2513))[::-1][:n]
+lens = np.minimum(lens, cap_frames)
+feats = [S.make_features(int(l), i) for i, l in enumerate(lens)]
+packed = torch.cat(feats, 0).cuda()
+offsets = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]), dtype=torch.int64).cuda()
+lens_t = torch.tensor(lens.copy(), dtype=torch.int32).cuda()
+CAP = 2000
+trace = torch.zeros((CAP, 8), dtype=torch.int64, device="cuda")
+from rnnt_inference_b200 import ops
+with torch.no_grad():
+    for rep in range(3):
+        if rep == 2:
+            _lib.lib.rnnt_debug_set_decode_trace(ctypes.c_void_p(trace.data_ptr()), CAP)
+            ops.telemetry.events = {}
+        res, res_len = dec.forward_ragged(packed, offsets, lens_t, int(lens.max()), [int(x) for x in lens])
+        torch.cuda.synchronize()
+_lib.lib.rnnt_debug_set_decode_trace(None, 0)
+ev = ops.telemetry.events
+for k, v in ev.items():
+    print(k, "ms", round(sum(s.elapsed_time(e) for s, e, _ in v), 3))
+iters = int(dec.last_iters.item())
+print("N", n, "T2", (int(lens.max()) + 1) // 2, "iters", iters, "tokens", int(res_len.sum()))
+tr = trace.cpu().numpy()[:min(iters, CAP)].astype(np.float64)
+full = tr[tr[:, 7] > 0]
+d = lambda a, b: np.median(full[:, a] - full[:, b])
+print("iterations with LSTM work:", len(full), "median active lanes in group 0:", np.median(full[:, 7]))
+print("cycles (median): lstm0 %.0f  barrier %.0f  lstm1+barrier %.0f  fc1+barrier %.0f  joint/update %.0f  barrier %.0f" %
+      (d(1, 0), d(2, 1), d(3, 2), d(4, 3), d(5, 4), d(6, 5)))
+per = np.diff(tr[:, 0])
+print("iteration period (cycles): median %.0f mean %.0f" % (np.median(per), per.mean()))

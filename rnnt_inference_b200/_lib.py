@@ -52,6 +52,7 @@ _SIGS = {
     "rnnt_lstm_cell_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "rnnt_greedy_decode_update": (_i, [_vp] * 17 + [_i, _i, _i, _i, _vp, _vp]),
     "rnnt_greedy_decode_workspace_bytes": (_i64, [_i]),
+    "rnnt_debug_set_decode_trace": (_i, [_vp, _i]),
     "rnnt_greedy_decode": (_i, [_vp, _vp, _i, _i, ctypes.POINTER(DecodeWeights), _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp,
                                 _vp, _vp, _vp, _vp, _vp]),
 }

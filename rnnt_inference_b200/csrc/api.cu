@@ -441,6 +441,11 @@ int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* 
 // ------------------------------------------------------------------------------------------------
 // greedy decode.  workspace: [0,256) global_sync | group_cnt [8][32] int | lane_state [N][8] int | z [N][512] f32 |
 //                            hg1 [2][N][320] bf16 | cg1 [2][N][320] f32
+static long long* g_dec_trace = nullptr;
+static int g_dec_trace_cap = 0;
+int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters) {
+  g_dec_trace = reinterpret_cast<long long*>(device_buffer); g_dec_trace_cap = max_iters; return RNNT_OK;
+}
 int64_t rnnt_greedy_decode_workspace_bytes(int N) {
   if (N <= 0) return 0;
   return 256 + 1024 + round_up((int64_t)N * 32, 256) + round_up((int64_t)N * DEC_J * 4, 256) +
@@ -483,6 +488,7 @@ int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N,
   p.hg[0][0] = pre_hg0; p.hg[0][1] = pre_hg1; p.hg[1][0] = hg1; p.hg[1][1] = hg1 + (size_t)N * DEC_P;
   p.cg[0][0] = pre_cg0; p.cg[0][1] = pre_cg1; p.cg[1][0] = cg1; p.cg[1][1] = cg1 + (size_t)N * DEC_P;
   p.iters_out = iters_out; p.status = status; p.NG = NG; p.LG = LG;
+  p.trace = g_dec_trace; p.trace_cap = g_dec_trace_cap;
   CUDA_TRY(cudaMemsetAsync(ws, 0, 256 + 1024, st));
   static bool attr_set = false;
   if (!attr_set) {

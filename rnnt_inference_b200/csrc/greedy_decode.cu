@@ -320,14 +320,21 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     }
     if (total_iters >= 0 && (iter >= total_iters || s_live == 0)) break;
     ++iter;
+    const bool tr = p.trace && blockIdx.x == 0 && tid == 0 && iter <= p.trace_cap;
+    long long* trow = p.trace + (size_t)(iter - 1) * 8;
+    if (tr) { trow[0] = clock64(); trow[7] = na; }
 
     if (na > 0) {
       lstm_phase(p, 0, g, s, alist, na, wl, act, part);
+      if (tr) trow[1] = clock64();
       group_barrier(p, g, epoch, ok);
+      if (tr) trow[2] = clock64();
       lstm_phase(p, 1, g, s, alist, na, wl, act, part);
       group_barrier(p, g, epoch, ok);
+      if (tr) trow[3] = clock64();
       fc1_phase(p, g, s, alist, na, act);
       group_barrier(p, g, epoch, ok);
+      if (tr) trow[4] = clock64();
     }
     // ---- phase D: lanes li = s, s+S, ... ; one warp per lane
     if (warp < DEC_DWARPS) {
@@ -336,7 +343,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         if (!p.lane_state[n * 8 + 3]) joint_update_lane(p, n, iter, ybuf + warp * DEC_J, lane);
       }
     }
+    if (tr) trow[5] = clock64();
     group_barrier(p, g, epoch, ok);
+    if (tr) trow[6] = clock64();
   }
 
   // ---- epilogue: reference-visible state of lanes that were skipped at their fixed point, committed h/c back

@@ -146,6 +146,8 @@ struct DecParams {
   int32_t* global_sync; // [0] groups done, [1] max iterations
   int32_t* iters_out; int* status;
   int NG, LG;           // groups, lanes per group
+  long long* trace;     // optional [iters][8] clock64 stamps of CTA 0 (profiles/trace_decode.py; NULL otherwise)
+  int trace_cap;
 };
 
 __global__ void greedy_decode_kernel(const DecParams p);
