@@ -11,10 +11,13 @@
 // logits = y.W2 + b2; first-maximum argmax over 32 columns.  Hence token sequences are bit-exact vs the oracle.
 //
 // Organisation: the batch is split into NG lane groups; a group is served by S=20 CTAs that keep the
-// prediction-LSTM weight columns of 16 hidden units (both layers, W_ih|W_hh, 162 KB) resident in shared memory.
-// Per iteration and group: (A) LSTM layer 0, (B) layer 1, (C) g.W_pred, (D) per lane: fc1 epilogue, fc2, argmax,
-// state update — with a group-local barrier (arrival counter in global memory) between phases.  Groups never
-// wait for each other inside the loop.  Ragged batch, per-utterance counters:
+// prediction-LSTM weight columns of 16 hidden units (both layers, W_ih|W_hh, 162 KB) and their 26 rows of W_pred
+// resident in shared memory.  Per iteration and group: (A) LSTM layer 0, (B) layer 1, (C) g.W_pred, (D) per lane:
+// fc1 epilogue, fc2, argmax, state update — with a group-local barrier (arrival counter in global memory) between
+// phases.  Groups never wait for each other inside the loop.  The loop is latency-bound (a handful of active lanes
+// per group and iteration), so every phase issues all of its global loads up front (one L2 round trip), per-lane
+// state travels as one 16-byte word, and inter-CTA data is read with ld.global.cg.  Ragged batch, per-utterance
+// counters:
 //   * the prediction network is recomputed only for lanes whose previous symbol was accepted: the reference
 //     recomputes it every iteration, but with unchanged (pre_g, pre_hg, pre_cg) the result is bit-identical;
 //   * a finished lane whose last step was a blank is at a fixed point of the reference loop and is skipped; a
@@ -27,56 +30,91 @@
 
 namespace rnnt {
 
+enum : int { LS_CUR = 1, LS_NEED = 2, LS_FINISHED = 4, LS_FIXED = 8 };
 
 __device__ __forceinline__ void group_barrier(const DecParams& p, int g, int& epoch, bool& ok) {
   __syncthreads();
   ++epoch;
   if (threadIdx.x == 0 && ok) {
     int* cnt = p.group_cnt + g * 32;
-    __threadfence();
     asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(cnt) : "memory");
     const int target = epoch * DEC_S;
     long long t0 = clock64(); uint32_t spins = 0;
     for (;;) {
       int v;
-      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
+      asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
       if (v >= target) break;
       if ((++spins & 63u) == 0) {
         if (*(volatile int*)p.status != DEV_OK) break;
         if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_FLAG); break; }
       }
     }
+    asm volatile("fence.acquire.gpu;" ::: "memory");
   }
   __syncthreads();
   if (*(volatile int*)p.status != DEV_OK) ok = false;
 }
 
+__device__ __forceinline__ void bf16x8_to_smem(float* dst, uint4 v) {
+  float4 a, b;
+  a.x = __uint_as_float(v.x << 16); a.y = __uint_as_float(v.x & 0xffff0000u);
+  a.z = __uint_as_float(v.y << 16); a.w = __uint_as_float(v.y & 0xffff0000u);
+  b.x = __uint_as_float(v.z << 16); b.y = __uint_as_float(v.z & 0xffff0000u);
+  b.z = __uint_as_float(v.w << 16); b.w = __uint_as_float(v.w & 0xffff0000u);
+  reinterpret_cast<float4*>(dst)[0] = a;
+  reinterpret_cast<float4*>(dst)[1] = b;
+}
+
 // One LSTM layer for the `na` active lanes listed in `alist` (group-local lane ids), chunked by DEC_CHUNK.
 //   x source: layer 0 -> embedding of pre_g (zero for SOS / out-of-table), layer 1 -> candidate h of layer 0.
 //   h, c source: committed buffers (cur).  Results go to the candidate buffers (cur ^ 1).
+// s_state[li] = {flags, cur_t, pre_g, fix_iter} of the group's lanes (shared-memory copy made by the list builder).
 __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g, int s, const int* alist, int na,
-                                           const uint16_t* wl, float* act, float* part) {
+                                           const int4* s_state, const uint16_t* wl, const float* s_bias, float* act,
+                                           float* part) {
   const int tid = threadIdx.x;
   const int lane0 = g * p.LG;
+  constexpr int VPL = 2 * DEC_P / 8;      // 16-byte vectors per lane: 40 of x, 40 of h
   for (int a0 = 0; a0 < na; a0 += DEC_CHUNK) {
     const int nc = min(DEC_CHUNK, na - a0);
-    // ---- stage activations as fp32: act[a][0..319] = x, act[a][320..639] = h
-    for (int e = tid; e < nc * 2 * DEC_P; e += DEC_THREADS) {
-      const int a = e / (2 * DEC_P), k = e % (2 * DEC_P);
-      const int n = lane0 + alist[a0 + a];
-      const int cur = p.lane_state[n * 8 + 0];
-      uint32_t bits;
-      if (k < DEC_P) {
-        if (layer == 0) {
-          const int sym = p.pre_g[n];
-          bits = (sym < 0 || sym > 27) ? 0u : (uint32_t)p.embed[sym * DEC_P + k];
-        } else {
-          bits = p.hg[cur ^ 1][0][(size_t)n * DEC_P + k];
+    // ---- cell-update operand prefetch: thread = (unit u, lane a); its c_old is needed only after the dot products
+    const int uu = tid & 15, ua = tid >> 4;
+    float c_old = 0.f; int un = 0, ucur = 0;
+    if (ua < nc) {
+      const int li = alist[a0 + ua];
+      un = lane0 + li;
+      ucur = s_state[li].x & LS_CUR;
+      c_old = p.cg[ucur][layer][(size_t)un * DEC_P + s * DEC_U + uu];
+    }
+    // ---- stage activations as fp32: act[a][0..319] = x, act[a][320..639] = h; all loads issued before any use
+    {
+      uint4 v[4]; int dsti[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int e = tid + r * DEC_THREADS;
+        dsti[r] = -1;
+        v[r] = make_uint4(0u, 0u, 0u, 0u);
+        if (e < nc * VPL) {
+          const int a = e / VPL, q = e % VPL;
+          const int li = alist[a0 + a];
+          const int4 st = s_state[li];
+          const int n = lane0 + li, cur = st.x & LS_CUR;
+          dsti[r] = a * 2 * DEC_P + q * 8;
+          if (q < VPL / 2) {
+            if (layer == 0) {
+              const int sym = st.z;
+              if (sym >= 0 && sym <= 27) v[r] = __ldg(reinterpret_cast<const uint4*>(p.embed + sym * DEC_P) + q);
+            } else {
+              v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][0] + (size_t)n * DEC_P) + q);
+            }
+          } else {
+            v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur][layer] + (size_t)n * DEC_P) + (q - VPL / 2));
+          }
         }
-      } else {
-        bits = p.hg[cur][layer][(size_t)n * DEC_P + (k - DEC_P)];
       }
-      act[a * 2 * DEC_P + k] = bf16_bits_to_float(bits);
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (dsti[r] >= 0) bf16x8_to_smem(act + dsti[r], v[r]);
     }
     __syncthreads();
     // ---- dot products: thread = (column c, matrix m, lane parity ls); chains sequential in k
@@ -110,94 +148,128 @@ __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g,
     }
     __syncthreads();
     // ---- cell update: thread = (unit u, lane a)
-    {
-      const int u = tid & 15, a = tid >> 4;
-      if (a < nc) {
-        const int n = lane0 + alist[a0 + a];
-        const int cur = p.lane_state[n * 8 + 0];
-        const int j = s * DEC_U + u;
-        float gate[4];
+    if (ua < nc) {
+      const int j = s * DEC_U + uu;
+      float gate[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float gi = part[(0 * DEC_CHUNK + a) * DEC_COLS + q * DEC_U + u];
-          const float gh = part[(1 * DEC_CHUNK + a) * DEC_COLS + q * DEC_U + u];
-          gate[q] = __fadd_rn(__fadd_rn(gh, gi), p.bias[layer][q * DEC_P + j]);   // float_out_accum: (acc + prev) + bias
-        }
-        const float it = sigmoid_ps(gate[0]), ft = sigmoid_ps(gate[1]), gt = tanh_ps(gate[2]), ot = sigmoid_ps(gate[3]);
-        const float c_old = p.cg[cur][layer][(size_t)n * DEC_P + j];
-        const float c_new = __fmaf_rn(it, gt, __fmul_rn(ft, c_old));
-        const float ht = __fmul_rn(ot, tanh_ps(c_new));
-        p.cg[cur ^ 1][layer][(size_t)n * DEC_P + j] = c_new;
-        p.hg[cur ^ 1][layer][(size_t)n * DEC_P + j] = (uint16_t)float_to_bf16_bits(ht);
+      for (int q = 0; q < 4; ++q) {
+        const float gi = part[(0 * DEC_CHUNK + ua) * DEC_COLS + q * DEC_U + uu];
+        const float gh = part[(1 * DEC_CHUNK + ua) * DEC_COLS + q * DEC_U + uu];
+        gate[q] = __fadd_rn(__fadd_rn(gh, gi), s_bias[layer * DEC_COLS + q * DEC_U + uu]);   // float_out_accum: (acc + prev) + bias
       }
+      const float it = sigmoid_ps(gate[0]), ft = sigmoid_ps(gate[1]), gt = tanh_ps(gate[2]), ot = sigmoid_ps(gate[3]);
+      const float c_new = __fmaf_rn(it, gt, __fmul_rn(ft, c_old));
+      const float ht = __fmul_rn(ot, tanh_ps(c_new));
+      p.cg[ucur ^ 1][layer][(size_t)un * DEC_P + j] = c_new;
+      p.hg[ucur ^ 1][layer][(size_t)un * DEC_P + j] = (uint16_t)float_to_bf16_bits(ht);
     }
     __syncthreads();
   }
 }
 
-// z[n][col] = sum_k g[n][k] * W_pred[col][k] for the active lanes; this CTA's columns [s*26, s*26+26) ∩ [0,512).
-__device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, const int* alist, int na, float* act) {
+// z[n][col] = sum_k g[n][k] * W_pred[col][k] for the active lanes; this CTA's columns [s*26, s*26+26) ∩ [0,512),
+// whose W_pred rows live in shared memory (wp, row stride DEC_KSTR).
+__device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, const int* alist, int na, const int4* s_state,
+                                          const uint16_t* wp, float* act) {
   const int tid = threadIdx.x;
   const int lane0 = g * p.LG;
   const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
+  constexpr int VPL = DEC_P / 8;     // 40 vectors of 8 bf16 per lane
   for (int a0 = 0; a0 < na; a0 += 2 * DEC_CHUNK) {
     const int nc = min(2 * DEC_CHUNK, na - a0);
-    for (int e = tid; e < nc * DEC_P; e += DEC_THREADS) {
-      const int a = e / DEC_P, k = e % DEC_P;
-      const int n = lane0 + alist[a0 + a];
-      const int cur = p.lane_state[n * 8 + 0];
-      act[a * DEC_P + k] = bf16_bits_to_float(p.hg[cur ^ 1][1][(size_t)n * DEC_P + k]);
+    {
+      uint4 v[4]; int dsti[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int e = tid + r * DEC_THREADS;
+        dsti[r] = -1;
+        v[r] = make_uint4(0u, 0u, 0u, 0u);
+        if (e < nc * VPL) {
+          const int a = e / VPL, q = e % VPL;
+          const int li = alist[a0 + a];
+          const int cur = s_state[li].x & LS_CUR;
+          dsti[r] = a * DEC_P + q * 8;
+          v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li) * DEC_P) + q);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (dsti[r] >= 0) bf16x8_to_smem(act + dsti[r], v[r]);
     }
     __syncthreads();
     for (int e = tid; e < nc * ncol; e += DEC_THREADS) {
-      const int a = e / ncol, col = col0 + e % ncol;
-      const uint2* wrow = reinterpret_cast<const uint2*>(p.w_pred + (size_t)col * DEC_P);
+      const int a = e / ncol, cl = e % ncol;
+      const uint16_t* wrow = wp + (size_t)cl * DEC_KSTR;
       const float* xr = act + a * DEC_P;
       float acc = 0.f;
 #pragma unroll 4
       for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
-        const uint2 wb = __ldg(wrow + k4);
+        const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
         const float4 xv = *reinterpret_cast<const float4*>(xr + k4 * 4);
         acc = __fmaf_rn(xv.x, __uint_as_float(wb.x << 16), acc);
         acc = __fmaf_rn(xv.y, __uint_as_float(wb.x & 0xffff0000u), acc);
         acc = __fmaf_rn(xv.z, __uint_as_float(wb.y << 16), acc);
         acc = __fmaf_rn(xv.w, __uint_as_float(wb.y & 0xffff0000u), acc);
       }
-      p.z[(size_t)(lane0 + alist[a0 + a]) * DEC_J + col] = acc;
+      p.z[(size_t)(lane0 + alist[a0 + a]) * DEC_J + col0 + cl] = acc;
     }
     __syncthreads();
   }
 }
 
 // Phase D for one lane, executed by one warp: fc1 epilogue, fc2, argmax, greedy_decode_update state machine.
-__device__ __forceinline__ void joint_update_lane(const DecParams& p, int n, int iter, float* ybuf, int lane) {
-  int32_t* st = p.lane_state + n * 8;
-  const int cur_t = st[5];
+// st = the lane's state word at the start of the iteration; the new word is written back to global memory.
+__device__ __forceinline__ void joint_update_lane(const DecParams& p, int n, int iter, int4 st, float* ybuf, const float* s_b1,
+                                                  const float* s_b2, int lane) {
+  const int cur_t = st.y;
   const uint16_t* y1r = p.y1 + ((size_t)cur_t * p.N + n) * DEC_J;
   const float* zr = p.z + (size_t)n * DEC_J;
-  for (int k = lane; k < DEC_J; k += 32) {
-    const float v = __fadd_rn(__fadd_rn(zr[k], bf16_bits_to_float(y1r[k])), p.b1[k]);   // (acc + y1) + bias
-    ybuf[k] = bf16_bits_to_float(float_to_bf16_bits(fmaxf(v, 0.f)));                    // relu, round to bf16
+  // ---- every global operand of this lane is requested before the first use (one memory round trip)
+  float zv[DEC_J / 32]; uint16_t yb[DEC_J / 32];
+#pragma unroll
+  for (int i = 0; i < DEC_J / 32; ++i) { zv[i] = __ldcg(zr + lane + 32 * i); yb[i] = __ldg(y1r + lane + 32 * i); }
+  int sa = 0, ri = 0, ti = 0, flen = 0;
+  if (lane == 0) { sa = p.symbols_added[n]; ri = p.res_idx[n]; ti = p.time_idx[n]; flen = p.f_lens[n]; }
+  const uint4* wrow = reinterpret_cast<const uint4*>(p.w2 + (size_t)lane * DEC_J);
+  uint4 wq[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) wq[j] = __ldg(wrow + j);
+#pragma unroll
+  for (int i = 0; i < DEC_J / 32; ++i) {
+    const int k = lane + 32 * i;
+    const float v = __fadd_rn(__fadd_rn(zv[i], bf16_bits_to_float(yb[i])), s_b1[k]);   // (acc + y1) + bias
+    ybuf[k] = bf16_bits_to_float(float_to_bf16_bits(fmaxf(v, 0.f)));                   // relu, round to bf16
   }
   __syncwarp();
-  // logits[o], o = lane: sequential chain over k
-  const uint4* wrow = reinterpret_cast<const uint4*>(p.w2 + (size_t)lane * DEC_J);
+  // logits[o], o = lane: sequential chain over k; W2 row streamed 8 x 16 bytes ahead
   float acc = 0.f;
-#pragma unroll 2
-  for (int k8 = 0; k8 < DEC_J / 8; ++k8) {
-    const uint4 wb = __ldg(wrow + k8);
-    const float4 ya = *reinterpret_cast<const float4*>(ybuf + k8 * 8);
-    const float4 yb = *reinterpret_cast<const float4*>(ybuf + k8 * 8 + 4);
-    acc = __fmaf_rn(ya.x, __uint_as_float(wb.x << 16), acc);
-    acc = __fmaf_rn(ya.y, __uint_as_float(wb.x & 0xffff0000u), acc);
-    acc = __fmaf_rn(ya.z, __uint_as_float(wb.y << 16), acc);
-    acc = __fmaf_rn(ya.w, __uint_as_float(wb.y & 0xffff0000u), acc);
-    acc = __fmaf_rn(yb.x, __uint_as_float(wb.z << 16), acc);
-    acc = __fmaf_rn(yb.y, __uint_as_float(wb.z & 0xffff0000u), acc);
-    acc = __fmaf_rn(yb.z, __uint_as_float(wb.w << 16), acc);
-    acc = __fmaf_rn(yb.w, __uint_as_float(wb.w & 0xffff0000u), acc);
+#pragma unroll 1
+  for (int k64 = 0; k64 < DEC_J / 64; ++k64) {
+    uint4 wn[8];
+    if (k64 + 1 < DEC_J / 64) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) wn[j] = __ldg(wrow + (k64 + 1) * 8 + j);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint4 wb = wq[j];
+      const float4 ya = *reinterpret_cast<const float4*>(ybuf + k64 * 64 + j * 8);
+      const float4 yc = *reinterpret_cast<const float4*>(ybuf + k64 * 64 + j * 8 + 4);
+      acc = __fmaf_rn(ya.x, __uint_as_float(wb.x << 16), acc);
+      acc = __fmaf_rn(ya.y, __uint_as_float(wb.x & 0xffff0000u), acc);
+      acc = __fmaf_rn(ya.z, __uint_as_float(wb.y << 16), acc);
+      acc = __fmaf_rn(ya.w, __uint_as_float(wb.y & 0xffff0000u), acc);
+      acc = __fmaf_rn(yc.x, __uint_as_float(wb.z << 16), acc);
+      acc = __fmaf_rn(yc.y, __uint_as_float(wb.z & 0xffff0000u), acc);
+      acc = __fmaf_rn(yc.z, __uint_as_float(wb.w << 16), acc);
+      acc = __fmaf_rn(yc.w, __uint_as_float(wb.w & 0xffff0000u), acc);
+    }
+    if (k64 + 1 < DEC_J / 64) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) wq[j] = wn[j];
+    }
   }
-  float best = __fadd_rn(acc, p.b2[lane]);
+  float best = __fadd_rn(acc, s_b2[lane]);
   int bidx = lane;
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) {   // first maximum wins ties (torch.argmax)
@@ -206,28 +278,37 @@ __device__ __forceinline__ void joint_update_lane(const DecParams& p, int n, int
     if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
   }
   __syncwarp();
+  int next_t = cur_t;
   if (lane == 0) {
     const int sym = bidx;
-    const int flen = p.f_lens[n];
-    const bool upd_g = (sym != DEC_BLANK) && (p.symbols_added[n] != DEC_MAXSYM) && (flen != 0);
+    int flags = st.x, pre_g = st.z, fix_iter = st.w;
+    const bool upd_g = (sym != DEC_BLANK) && (sa != DEC_MAXSYM) && (flen != 0);
     if (upd_g) {
-      const int ri = p.res_idx[n] + 1;
+      ri += 1;
       p.res_idx[n] = ri;
       if (ri >= 0 && ri < p.L) p.res[(size_t)n * p.L + ri] = sym;
-      p.symbols_added[n] += 1;
+      p.symbols_added[n] = sa + 1;
       p.pre_g[n] = sym;
-      st[0] ^= 1;        // candidate becomes the committed state
-      st[1] = 1;         // prediction network must be re-evaluated
+      pre_g = sym;
+      flags ^= LS_CUR;       // candidate becomes the committed state
+      flags |= LS_NEED;      // prediction network must be re-evaluated
     } else {
       p.symbols_added[n] = 0;
-      p.time_idx[n] += 1;
-      st[1] = 0;
+      ti += 1;
+      p.time_idx[n] = ti;
+      flags &= ~LS_NEED;
     }
-    const int ti = p.time_idx[n];
     const bool finished = ti >= flen;
-    if (!finished) st[5] = ti;                 // fi = f[time_idx]
-    st[2] = finished ? 1 : 0;
-    if (finished && !upd_g && (sym == DEC_BLANK || flen == 0)) { st[3] = 1; st[4] = iter; }   // fixed point
+    if (!finished) next_t = ti;                 // fi = f[time_idx]
+    flags = finished ? (flags | LS_FINISHED) : (flags & ~LS_FINISHED);
+    if (finished && !upd_g && (sym == DEC_BLANK || flen == 0)) { flags |= LS_FIXED; fix_iter = iter; }   // fixed point
+    *reinterpret_cast<int4*>(p.lane_state + (size_t)n * 4) = make_int4(flags, next_t, pre_g, fix_iter);
+  }
+  // warm the L2 with the transcription row the next iteration of this lane will read
+  next_t = __shfl_sync(0xffffffffu, next_t, 0);
+  if (next_t != cur_t) {
+    const uint16_t* nr = p.y1 + ((size_t)next_t * p.N + n) * DEC_J + lane * 16;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(nr));
   }
 }
 
@@ -236,14 +317,17 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   uint16_t* wl = reinterpret_cast<uint16_t*>(smem);
   float* act = reinterpret_cast<float*>(smem + DecSmem::W_BYTES);
   float* part = reinterpret_cast<float*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES);
-  float* ybuf = reinterpret_cast<float*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES + DecSmem::PART_BYTES);
+  uint16_t* wp = reinterpret_cast<uint16_t*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES + DecSmem::PART_BYTES);
+  __shared__ int4 s_state[DEC_MAXLG];
   __shared__ int alist[DEC_MAXLG];
+  __shared__ float s_bias[2 * DEC_COLS], s_b1[DEC_J], s_b2[DEC_V];
   __shared__ int s_na, s_unfinished, s_live;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = blockIdx.x / DEC_S, s = blockIdx.x % DEC_S;
   const int lane0 = g * p.LG;
   const int nl = max(0, min(p.LG, p.N - lane0));    // lanes of this group
+  const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
 
   // resident weights: wl[layer][m][c][k], c = gate*16 + u  <-  W[(gate*320 + s*16 + u)][k]
   for (int e = tid; e < 2 * 2 * DEC_COLS * (DEC_P / 2); e += DEC_THREADS) {
@@ -255,30 +339,40 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     reinterpret_cast<uint32_t*>(wl + ((size_t)(layer * 2 + m) * DEC_COLS + c) * DEC_KSTR)[k2] =
         reinterpret_cast<const uint32_t*>(src)[k2];
   }
-  // lane state init (each lane by the CTA that owns it in phase D)
-  for (int li = s + tid * DEC_S; li < nl; li += DEC_S * DEC_THREADS) {
-    int32_t* st = p.lane_state + (lane0 + li) * 8;
-    st[0] = 0; st[1] = 1; st[2] = 0; st[3] = 0; st[4] = 0; st[5] = 0; st[6] = 0; st[7] = 0;
+  for (int e = tid; e < ncol * (DEC_P / 2); e += DEC_THREADS) {
+    const int k2 = e % (DEC_P / 2), cl = e / (DEC_P / 2);
+    reinterpret_cast<uint32_t*>(wp + (size_t)cl * DEC_KSTR)[k2] =
+        reinterpret_cast<const uint32_t*>(p.w_pred + (size_t)(col0 + cl) * DEC_P)[k2];
   }
+  for (int e = tid; e < 2 * DEC_COLS; e += DEC_THREADS) {
+    const int layer = e / DEC_COLS, c = e % DEC_COLS;
+    s_bias[e] = p.bias[layer][(c / DEC_U) * DEC_P + s * DEC_U + (c % DEC_U)];
+  }
+  for (int e = tid; e < DEC_J; e += DEC_THREADS) s_b1[e] = p.b1[e];
+  if (tid < DEC_V) s_b2[tid] = p.b2[tid];
+  // lane state init (each lane by the CTA that owns it in phase D)
+  for (int li = s + tid * DEC_S; li < nl; li += DEC_S * DEC_THREADS)
+    *reinterpret_cast<int4*>(p.lane_state + (size_t)(lane0 + li) * 4) = make_int4(LS_NEED, 0, p.pre_g[lane0 + li], 0);
   int epoch = 0; bool ok = true;
   group_barrier(p, g, epoch, ok);
 
   int iter = 0;
   int total_iters = -1;   // unknown during phase 1
   for (;;) {
-    // ---- build the active (need_lstm) list and the loop conditions from the lane states
+    // ---- snapshot the group's lane states (one 16-byte load per lane), build the active (need_lstm) list
     if (tid == 0) { s_na = 0; s_unfinished = 0; s_live = 0; }
+    for (int li = tid; li < nl; li += DEC_THREADS)
+      s_state[li] = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li) * 4));
     __syncthreads();
     if (tid < 32) {
       for (int base = 0; base < nl; base += 32) {
         const int li = base + tid;
         int need = 0, unfin = 0, live = 0;
         if (li < nl) {
-          const int32_t* st = p.lane_state + (lane0 + li) * 8;
-          const int fixed = st[3];
-          need = st[1] && !fixed;
-          unfin = !st[2];
-          live = !fixed;
+          const int f = s_state[li].x;
+          need = (f & LS_NEED) && !(f & LS_FIXED);
+          unfin = !(f & LS_FINISHED);
+          live = !(f & LS_FIXED);
         }
         const unsigned mneed = __ballot_sync(0xffffffffu, need);
         const unsigned munf = __ballot_sync(0xffffffffu, unfin);
@@ -325,23 +419,21 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     if (tr) { trow[0] = clock64(); trow[7] = na; }
 
     if (na > 0) {
-      lstm_phase(p, 0, g, s, alist, na, wl, act, part);
+      lstm_phase(p, 0, g, s, alist, na, s_state, wl, s_bias, act, part);
       if (tr) trow[1] = clock64();
       group_barrier(p, g, epoch, ok);
       if (tr) trow[2] = clock64();
-      lstm_phase(p, 1, g, s, alist, na, wl, act, part);
+      lstm_phase(p, 1, g, s, alist, na, s_state, wl, s_bias, act, part);
       group_barrier(p, g, epoch, ok);
       if (tr) trow[3] = clock64();
-      fc1_phase(p, g, s, alist, na, act);
+      fc1_phase(p, g, s, alist, na, s_state, wp, act);
       group_barrier(p, g, epoch, ok);
       if (tr) trow[4] = clock64();
     }
     // ---- phase D: lanes li = s, s+S, ... ; one warp per lane
-    if (warp < DEC_DWARPS) {
-      for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_DWARPS) {
-        const int n = lane0 + li;
-        if (!p.lane_state[n * 8 + 3]) joint_update_lane(p, n, iter, ybuf + warp * DEC_J, lane);
-      }
+    for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
+      const int4 st = s_state[li];
+      if (!(st.x & LS_FIXED)) joint_update_lane(p, lane0 + li, iter, st, act + warp * DEC_J, s_b1, s_b2, lane);
     }
     if (tr) trow[5] = clock64();
     group_barrier(p, g, epoch, ok);
@@ -349,18 +441,18 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   }
 
   // ---- epilogue: reference-visible state of lanes that were skipped at their fixed point, committed h/c back
-  // into the caller's arrays.
+  // into the caller's arrays (s_state holds the final states: it was refreshed after the last barrier).
   if (ok && total_iters >= 0) {
-    for (int li = s + warp * DEC_S; li < nl; li += DEC_S * 8) {
+    for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
       const int n = lane0 + li;
-      const int32_t* st = p.lane_state + n * 8;
-      if (lane == 0 && st[3]) p.time_idx[n] += total_iters - st[4];
-      if (st[0] == 1) {
+      const int4 st = s_state[li];
+      if (lane == 0 && (st.x & LS_FIXED)) p.time_idx[n] += total_iters - st.w;
+      if (st.x & LS_CUR) {
         for (int k = lane; k < DEC_P; k += 32) {
-          p.hg[0][0][(size_t)n * DEC_P + k] = p.hg[1][0][(size_t)n * DEC_P + k];
-          p.hg[0][1][(size_t)n * DEC_P + k] = p.hg[1][1][(size_t)n * DEC_P + k];
-          p.cg[0][0][(size_t)n * DEC_P + k] = p.cg[1][0][(size_t)n * DEC_P + k];
-          p.cg[0][1][(size_t)n * DEC_P + k] = p.cg[1][1][(size_t)n * DEC_P + k];
+          p.hg[0][0][(size_t)n * DEC_P + k] = __ldcg(p.hg[1][0] + (size_t)n * DEC_P + k);
+          p.hg[0][1][(size_t)n * DEC_P + k] = __ldcg(p.hg[1][1] + (size_t)n * DEC_P + k);
+          p.cg[0][0][(size_t)n * DEC_P + k] = __ldcg(p.cg[1][0] + (size_t)n * DEC_P + k);
+          p.cg[0][1][(size_t)n * DEC_P + k] = __ldcg(p.cg[1][1] + (size_t)n * DEC_P + k);
         }
       }
     }

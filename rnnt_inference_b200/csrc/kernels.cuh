@@ -115,18 +115,18 @@ constexpr int DEC_U = DEC_P / DEC_S;  // 16 hidden units per CTA
 constexpr int DEC_COLS = 4 * DEC_U;   // 64 gate columns per CTA and matrix
 constexpr int DEC_KSTR = DEC_P + 4;   // padded bf16 row stride (648 B: conflict-free 8-byte reads)
 constexpr int DEC_THREADS = 256;
-constexpr int DEC_CHUNK = 16;         // active lanes processed per pass
+constexpr int DEC_WARPS = DEC_THREADS / 32;
+constexpr int DEC_CHUNK = 12;         // active lanes per LSTM pass (the fc1 pass takes 2 * DEC_CHUNK)
 constexpr int DEC_JC = 26;            // fc1 columns per CTA (19*26 + 18 = 512)
 constexpr int DEC_MAXLG = 320;        // max lanes per group (N <= 7*320)
-constexpr int DEC_DWARPS = 4;         // warps used by phase D (one lane each per pass)
 constexpr int DEC_BLANK = 28, DEC_MAXSYM = 30;
 
 struct DecSmem {
   static constexpr int W_BYTES = 2 * 2 * DEC_COLS * DEC_KSTR * 2;          // [layer][ih|hh][col][k] bf16 = 165,888
-  static constexpr int ACT_BYTES = DEC_CHUNK * 2 * DEC_P * 4;              // [lane][x|h] fp32 = 40,960
-  static constexpr int PART_BYTES = 2 * DEC_CHUNK * DEC_COLS * 4;          // [ih|hh][lane][col] fp32 = 8,192
-  static constexpr int Y_BYTES = DEC_DWARPS * DEC_J * 4;                   // per-warp y vector, 8,192
-  static constexpr int TOTAL = W_BYTES + ACT_BYTES + PART_BYTES + Y_BYTES;  // 223,232
+  static constexpr int ACT_BYTES = DEC_CHUNK * 2 * DEC_P * 4;              // [lane][x|h] fp32 = 30,720 (joint: per-warp y)
+  static constexpr int PART_BYTES = 2 * DEC_CHUNK * DEC_COLS * 4;          // [ih|hh][lane][col] fp32 = 6,144
+  static constexpr int WP_BYTES = DEC_JC * DEC_KSTR * 2;                   // this CTA's W_pred rows, bf16 = 16,848
+  static constexpr int TOTAL = W_BYTES + ACT_BYTES + PART_BYTES + WP_BYTES;  // 219,600 (+ ~7 KB static)
 };
 
 struct DecParams {
@@ -141,7 +141,7 @@ struct DecParams {
   float* cg[2][2];
   // workspace
   float* z;             // [N][J] fp32 : g.W_pred of the current candidate
-  int32_t* lane_state;  // [N][8]: 0 cur, 1 need_lstm, 2 finished, 3 fixed, 4 fix_iter, 5 cur_t
+  int32_t* lane_state;  // [N][4]: flags (1 cur, 2 need_lstm, 4 finished, 8 fixed), cur_t, pre_g, fix_iter
   int32_t* group_cnt;   // [NG][32] barrier arrival counters
   int32_t* global_sync; // [0] groups done, [1] max iterations
   int32_t* iters_out; int* status;
