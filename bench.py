@@ -271,7 +271,7 @@ def reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int8", "data": "synthetic",
-        "config": {"workload": "C3 Offline: 2513 synthetic dev-clean-length utterances per GPU, batch 256, full int8 RNN-T greedy decode",
+        "config": {"workload": f"C3 Offline: {args.utts} synthetic dev-clean-length utterances per GPU, sorted, batch {args.batch}, full int8 RNN-T greedy decode",
                    "note": "CPU restatement of the reference path (oracle/), bounded sample per step"},
         "cpu_baseline": last,
         "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
@@ -394,7 +394,7 @@ def main():
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_per_step, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int8", "data": "synthetic",
-            "config": {"workload": "C3 Offline: 2513 synthetic dev-clean-length utterances per GPU, batch 256, full int8 RNN-T greedy decode",
+            "config": {"workload": f"C3 Offline: {args.utts} synthetic dev-clean-length utterances per GPU, sorted, batch {args.batch}, full int8 RNN-T greedy decode",
                        "utterances_per_gpu_per_step": my_utts, "frames_per_gpu_per_step": my_frames, "batch": args.batch,
                        "batches_per_step": len(batches), "tokens_per_step_rank0": tokens_per_step,
                        "l2": "inputs and per-layer int32 projections (up to 2 GB) exceed the 126 MB L2; no explicit flush",

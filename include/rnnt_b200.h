@@ -53,6 +53,11 @@ int rnnt_quantize_ragged_f32_i8(const float* packed, const int64_t* offsets, con
  * C[M][N] int32 = A[M][K] int8 . W[N][K]^T int8, exact.  tcgen05 kind::i8, TMEM accumulators, TMA in/out.
  * Requirements: K % 16 == 0, N % 64 == 0, pointers 16-byte aligned. */
 int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream);
+/* Same GEMM over a ragged time-major batch sorted by length: M = T * rows_per_step rows, rows_per_step % 128 == 0;
+ * 128-row tile b of timestep t is computed only if t < tile_steps_host[b] (HOST array, rows_per_step/128 entries);
+ * the other rows of C are left untouched (the recurrent kernel never reads them).  tile_steps_host NULL = all rows. */
+int rnnt_gemm_i8_i32_ragged(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, int rows_per_step,
+                            const int32_t* tile_steps_host, void* stream);
 /* Same contract on CUDA cores (dp4a), M <= 65535.  TEST HELPER: lets the GPU tests cross-check the tcgen05
  * kernel at sizes the CPU oracle cannot reach.  Never called by the product path. */
 int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream);
@@ -102,6 +107,9 @@ int rnnt_stack_time_i8(const int8_t* in, const int32_t* lens, int factor, int8_t
 /* Transcription half of Joint fc1, hoisted out of the decode loop (amx_linear.cpp:137-150, i16o16b0):
  * y1[M][J] bf16 = bf16(f[M][C] . W_trans[J][C]^T), fp32 FMA sequential in k (the order the oracle defines). */
 int rnnt_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, void* stream);
+/* Ragged variant (see rnnt_gemm_i8_i32_ragged; rows_per_step % 64 == 0): dead rows of y are left untouched. */
+int rnnt_linear_bf16_bf16_ragged(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, int rows_per_step,
+                                 const int32_t* tile_steps_host, void* stream);
 
 /* Per-iteration operators of the reference's decode loop, for callers that keep the Python loop of
  * models/decoder.py:188-211 (the fused rnnt_greedy_decode below is the fast path; these share its arithmetic).
@@ -141,7 +149,7 @@ typedef struct {
 } rnnt_decode_weights;
 
 int64_t rnnt_greedy_decode_workspace_bytes(int N);
-/* DEBUG: device buffer of max_iters*8 int64 receiving clock64 stamps of CTA 0 per decode iteration (iteration start, LSTM
+/* DEBUG: device buffer of max_iters*16 int64 receiving clock64 stamps of CTA 0 per decode iteration (iteration start, LSTM
  * layer 0 done, after barrier, layer 1 + barrier, fc1 + barrier, joint/update done, after barrier, active lanes). NULL = off. */
 int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);
 /* y1 [T2][N][J] bf16 (from rnnt_linear_bf16_bf16), f_lens [N] STACKED lengths.

@@ -15,8 +15,8 @@ what = sys.argv[1] if len(sys.argv) > 1 else "all"
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 100
 torch.cuda.set_device(0)
 rnnt = RNNT(S.make_checkpoint(), "quant", True).eval()
-dec = GreedyDecoder(rnnt, "quant", True, -1, 256)
-n = 256
+dec = GreedyDecoder(rnnt, "quant", True, -1, 1024)
+n = int(sys.argv[3]) if len(sys.argv) > 3 else 1024
 with torch.no_grad():
     if what in ("lstm", "all"):
         post = rnnt.transcription.post_rnn

@@ -24,7 +24,7 @@ packed = torch.cat(feats, 0).cuda()
 offsets = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]), dtype=torch.int64).cuda()
 lens_t = torch.tensor(lens.copy(), dtype=torch.int32).cuda()
 CAP = 2000
-trace = torch.zeros((CAP, 8), dtype=torch.int64, device="cuda")
+trace = torch.zeros((CAP, 16), dtype=torch.int64, device="cuda")
 from rnnt_inference_b200 import ops
 with torch.no_grad():
     for rep in range(3):
@@ -45,5 +45,13 @@ d = lambda a, b: np.median(full[:, a] - full[:, b])
 print("iterations with LSTM work:", len(full), "median active lanes in group 0:", np.median(full[:, 7]))
 print("cycles (median): lstm0 %.0f  barrier %.0f  lstm1+barrier %.0f  fc1+barrier %.0f  joint/update %.0f  barrier %.0f" %
       (d(1, 0), d(2, 1), d(3, 2), d(4, 3), d(5, 4), d(6, 5)))
+j = tr[tr[:, 8] > 0]
+if len(j):
+    print("joint of lane 0 (cycles, median): loads+fc1-epilogue %.0f  fc2 %.0f  argmax+update %.0f" %
+          (np.median(j[:, 9] - j[:, 8]), np.median(j[:, 10] - j[:, 9]), np.median(j[:, 11] - j[:, 10])))
+l0 = tr[(tr[:, 12] > 0) & (tr[:, 7] <= 12)]
+if len(l0):
+    print("lstm layer 0, single chunk (cycles, median): staging %.0f  dot %.0f  cell update %.0f" %
+          (np.median(l0[:, 12] - l0[:, 0]), np.median(l0[:, 13] - l0[:, 12]), np.median(l0[:, 1] - l0[:, 13])))
 per = np.diff(tr[:, 0])
 print("iteration period (cycles): median %.0f mean %.0f" % (np.median(per), per.mean()))

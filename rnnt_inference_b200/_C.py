@@ -140,3 +140,4 @@ def lstm(x: Tensor, hx: List[Tensor], cx: List[Tensor], all_weights: List[List[T
         cy.append(c)
     return x, hy, cy
 quantize_ragged = ops.quantize_ragged
+tile_steps_for = ops.tile_steps_for

@@ -85,11 +85,25 @@ inline int64_t round_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
 }  // namespace
 
+// RowSkip for a ragged batch: rows_per_step rows per timestep, tile_steps_host[b] live steps of 128-row tile b (NULL = all live)
+static int make_skip(RowSkip* skip, int64_t M, int rows_per_step, const int32_t* tile_steps_host, int block_rows) {
+  memset(skip, 0, sizeof *skip);
+  if (!tile_steps_host) return RNNT_OK;
+  if (rows_per_step <= 0 || rows_per_step % block_rows != 0 || M % rows_per_step != 0 || rows_per_step > 32 * 128)
+    return fail(RNNT_ERR_INVALID, "ragged row skipping needs rows_per_step %% %d == 0, <= 4096 and M %% rows_per_step == 0 (M=%lld, rows_per_step=%d)",
+                block_rows, (long long)M, rows_per_step);
+  skip->rows_per_t = rows_per_step;
+  for (int b = 0; b < (rows_per_step + 127) / 128; ++b) skip->steps[b] = tile_steps_host[b];
+  return RNNT_OK;
+}
+
 template <int MODE>
 static int linear_launch(const uint16_t* x, const uint16_t* w, const float* bias, const uint16_t* prev, void* y, int64_t M, int K,
-                         int O, cudaStream_t st) {
+                         int O, cudaStream_t st, const RowSkip* skip_in = nullptr) {
+  RowSkip skip;
+  if (skip_in) skip = *skip_in; else memset(&skip, 0, sizeof skip);
   dim3 grid((O + LB_TO - 1) / LB_TO, (unsigned)((M + LB_TM - 1) / LB_TM));
-  linear_bf16_kernel<MODE><<<grid, 256, 0, st>>>(x, w, bias, prev, y, M, K, O);
+  linear_bf16_kernel<MODE><<<grid, 256, 0, st>>>(x, w, bias, prev, y, M, K, O, skip);
   CUDA_TRY(cudaGetLastError());
   return RNNT_OK;
 }
@@ -157,10 +171,18 @@ int rnnt_stack_time_i8(const int8_t* in, const int32_t* lens, int factor, int8_t
   return RNNT_OK;
 }
 
+int rnnt_linear_bf16_bf16_ragged(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, int rows_per_step,
+                                 const int32_t* tile_steps_host, void* stream) {
+  if (!x || !w || !y || M < 0 || K <= 0 || O <= 0) return fail(RNNT_ERR_INVALID, "linear_bf16_bf16: null pointer or bad size");
+  if (M == 0) return RNNT_OK;
+  RowSkip skip;
+  if (int r = make_skip(&skip, M, rows_per_step, tile_steps_host, LB_TM)) return r;
+  return linear_launch<LIN_BF16>(x, w, nullptr, nullptr, y, M, K, O, (cudaStream_t)stream, &skip);
+}
 int rnnt_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, void* stream) {
   if (!x || !w || !y || M < 0 || K <= 0 || O <= 0) return fail(RNNT_ERR_INVALID, "linear_bf16_bf16: bad arguments");
   if (M == 0) return RNNT_OK;
-  return linear_launch<LIN_BF16>(x, w, nullptr, nullptr, y, M, K, O, (cudaStream_t)stream);
+  return rnnt_linear_bf16_bf16_ragged(x, w, y, M, K, O, 0, nullptr, stream);
 }
 
 int rnnt_linear_bf16_f32(const uint16_t* x, const uint16_t* w, const float* bias, float* y, int64_t M, int K, int O,
@@ -233,7 +255,7 @@ int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t 
 
 }  // extern "C"
 template <int BN>
-static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, cudaStream_t st) {
+static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, const RowSkip& skip, cudaStream_t st) {
   CUtensorMap ta, tb, tc;
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)K};
@@ -261,13 +283,17 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
   const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
   const int sms = sm_count();
   const int grid = std::max(1, std::min(sms > 0 ? sms : 148, num_m * num_n));
-  kern<<<grid, GEMM_THREADS, GemmSmem<BN>::TOTAL, st>>>(ta, tb, tc, num_m, num_n, num_k, status);
+  kern<<<grid, GEMM_THREADS, GemmSmem<BN>::TOTAL, st>>>(ta, tb, tc, num_m, num_n, num_k, status, skip);
   CUDA_TRY(cudaGetLastError());
   return RNNT_OK;
 }
 
 extern "C" {
 int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream) {
+  return rnnt_gemm_i8_i32_ragged(A, W, C, M, N, K, 0, nullptr, stream);
+}
+int rnnt_gemm_i8_i32_ragged(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, int rows_per_step,
+                            const int32_t* tile_steps_host, void* stream) {
   if (!A || !W || !C || M < 0 || N <= 0 || K <= 0)
     return fail(RNNT_ERR_INVALID, "gemm_i8_i32: null pointer or non-positive size");
   if ((K & 15) || (N & 63) || !aligned(A, 16) || !aligned(W, 16) || !aligned(C, 16))
@@ -275,9 +301,11 @@ int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, in
                 (long long)M, N, K);
   if (M == 0) return RNNT_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  if (N % 256 == 0) return gemm_launch<256>(A, W, C, M, N, K, st);
-  if (N % 128 == 0) return gemm_launch<128>(A, W, C, M, N, K, st);
-  return gemm_launch<64>(A, W, C, M, N, K, st);
+  RowSkip skip;
+  if (int r = make_skip(&skip, M, rows_per_step, tile_steps_host, GEMM_BM)) return r;
+  if (N % 256 == 0) return gemm_launch<256>(A, W, C, M, N, K, skip, st);
+  if (N % 128 == 0) return gemm_launch<128>(A, W, C, M, N, K, skip, st);
+  return gemm_launch<64>(A, W, C, M, N, K, skip, st);
 }
 
 // debug hook: device buffer [T][8] int64 receiving clock64 stamps of CTA (0,0) of the next recurrent launches (NULL = off)

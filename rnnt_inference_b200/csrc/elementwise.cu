@@ -98,11 +98,12 @@ __global__ void stack_time_kernel(const int8_t* __restrict__ in, const int32_t* 
 template <int MODE>
 __global__ void __launch_bounds__(256)
 linear_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w, const float* __restrict__ bias,
-                   const uint16_t* __restrict__ prev, void* __restrict__ yout, long long M, int K, int O) {
+                   const uint16_t* __restrict__ prev, void* __restrict__ yout, long long M, int K, int O, const RowSkip skip) {
   __shared__ float xs[LB_TK][LB_TM + 4];
   __shared__ float ws[LB_TK][LB_TO + 4];
   const long long m0 = (long long)blockIdx.y * LB_TM;
   const int o0 = blockIdx.x * LB_TO;
+  if (skip.dead(m0)) return;
   const int tm = (threadIdx.x >> 4) << 2;   // 0..60
   const int to = (threadIdx.x & 15) << 2;   // 0..60
   float acc[4][4];
@@ -155,10 +156,10 @@ linear_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ 
     }
   }
 }
-template __global__ void linear_bf16_kernel<LIN_BF16>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
-template __global__ void linear_bf16_kernel<LIN_F32_BIAS>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
-template __global__ void linear_bf16_kernel<LIN_F32>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
-template __global__ void linear_bf16_kernel<LIN_ACCUM_RELU>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int);
+template __global__ void linear_bf16_kernel<LIN_BF16>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
+template __global__ void linear_bf16_kernel<LIN_F32_BIAS>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
+template __global__ void linear_bf16_kernel<LIN_F32>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
+template __global__ void linear_bf16_kernel<LIN_ACCUM_RELU>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
 
 // dequant of an int32 accumulator (i8o32b32, tile_product_tpp.hpp:347-367 for int8): (float(acc) + bias[o]) * scale,
 // two separately rounded fp32 operations.

@@ -24,7 +24,7 @@ template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles, int num_k_blocks,
-                   int* __restrict__ status) {
+                   int* __restrict__ status, const RowSkip skip) {
   using S = GemmSmem<BN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -65,6 +65,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       int stage = 0; uint32_t phase = 0; bool ok = true;
       for (int tile = blockIdx.x; tile < num_tiles && ok; tile += gridDim.x) {
         const int m_blk = tile / num_n_tiles, n_blk = tile % num_n_tiles;
+        if (skip.dead((long long)m_blk * GEMM_BM)) continue;
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           if (!mbar_wait(empty_bar + 8 * stage, phase ^ 1, status)) { ok = false; break; }
           mbar_expect_tx(full_bar + 8 * stage, S::STAGE_BYTES);
@@ -80,6 +81,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       constexpr uint32_t idesc = umma_idesc_i8(GEMM_BM, BN);
       int stage = 0; uint32_t phase = 0; int acc = 0; uint32_t acc_phase = 0; bool ok = true;
       for (int tile = blockIdx.x; tile < num_tiles && ok; tile += gridDim.x) {
+        if (skip.dead((long long)(tile / num_n_tiles) * GEMM_BM)) continue;
         if (!mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, status)) break;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -106,6 +108,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     int acc = 0; uint32_t acc_phase = 0; int buf = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile / num_n_tiles, n_blk = tile % num_n_tiles;
+      if (skip.dead((long long)m_blk * GEMM_BM)) continue;
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, status)) break;
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
@@ -148,9 +151,9 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 }
 
 // explicit instantiations used by api.cu
-template __global__ void gemm_i8_i32_kernel<256>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__);
-template __global__ void gemm_i8_i32_kernel<128>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__);
-template __global__ void gemm_i8_i32_kernel<64>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__);
+template __global__ void gemm_i8_i32_kernel<256>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip);
+template __global__ void gemm_i8_i32_kernel<128>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip);
+template __global__ void gemm_i8_i32_kernel<64>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip);
 
 // ---------------------------------------------------------------------------------------------
 // Plain CUDA-core int8 GEMM.  NOT a fallback: used by tests (device-side cross-check of the tcgen05 kernel at

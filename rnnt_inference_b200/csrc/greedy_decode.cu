@@ -32,7 +32,7 @@ namespace rnnt {
 
 enum : int { LS_CUR = 1, LS_NEED = 2, LS_FINISHED = 4, LS_FIXED = 8 };
 
-__device__ __forceinline__ void group_barrier(const DecParams& p, int g, int& epoch, bool& ok) {
+__device__ __forceinline__ void group_barrier(const DecParams& p, int g, int& epoch, bool& ok, int* s_fail) {
   __syncthreads();
   ++epoch;
   if (threadIdx.x == 0 && ok) {
@@ -45,14 +45,14 @@ __device__ __forceinline__ void group_barrier(const DecParams& p, int g, int& ep
       asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
       if (v >= target) break;
       if ((++spins & 63u) == 0) {
-        if (*(volatile int*)p.status != DEV_OK) break;
-        if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_FLAG); break; }
+        if (*(volatile int*)p.status != DEV_OK) { *s_fail = 1; break; }
+        if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_FLAG); *s_fail = 1; break; }
       }
     }
     asm volatile("fence.acquire.gpu;" ::: "memory");
   }
   __syncthreads();
-  if (*(volatile int*)p.status != DEV_OK) ok = false;
+  if (*s_fail) ok = false;     // shared-memory flag: no global status read on the fast path
 }
 
 __device__ __forceinline__ void bf16x8_to_smem(float* dst, uint4 v) {
@@ -65,13 +65,38 @@ __device__ __forceinline__ void bf16x8_to_smem(float* dst, uint4 v) {
   reinterpret_cast<float4*>(dst)[1] = b;
 }
 
+// NL independent dot-product chains of one weight row against the activations of lanes ls, ls + 2, ... (stride 2 lanes =
+// 4 * DEC_P floats); every chain is sequential in k from 0 (the oracle's order).  Results to part[...][lane][col].
+template <int NL>
+__device__ __forceinline__ void dot_chains(const uint16_t* wrow, const float* xbase, float* pout) {
+  float acc[NL];
+#pragma unroll
+  for (int i = 0; i < NL; ++i) acc[i] = 0.f;
+#pragma unroll 4
+  for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
+    const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
+    const float w0 = __uint_as_float(wb.x << 16), w1 = __uint_as_float(wb.x & 0xffff0000u);
+    const float w2 = __uint_as_float(wb.y << 16), w3 = __uint_as_float(wb.y & 0xffff0000u);
+#pragma unroll
+    for (int i = 0; i < NL; ++i) {
+      const float4 xv = *reinterpret_cast<const float4*>(xbase + i * 4 * DEC_P + k4 * 4);
+      acc[i] = __fmaf_rn(xv.x, w0, acc[i]);
+      acc[i] = __fmaf_rn(xv.y, w1, acc[i]);
+      acc[i] = __fmaf_rn(xv.z, w2, acc[i]);
+      acc[i] = __fmaf_rn(xv.w, w3, acc[i]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NL; ++i) pout[2 * i * DEC_COLS] = acc[i];
+}
+
 // One LSTM layer for the `na` active lanes listed in `alist` (group-local lane ids), chunked by DEC_CHUNK.
 //   x source: layer 0 -> embedding of pre_g (zero for SOS / out-of-table), layer 1 -> candidate h of layer 0.
 //   h, c source: committed buffers (cur).  Results go to the candidate buffers (cur ^ 1).
 // s_state[li] = {flags, cur_t, pre_g, fix_iter} of the group's lanes (shared-memory copy made by the list builder).
 __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g, int s, const int* alist, int na,
                                            const int4* s_state, const uint16_t* wl, const float* s_bias, float* act,
-                                           float* part) {
+                                           float* part, long long* lt = nullptr) {
   const int tid = threadIdx.x;
   const int lane0 = g * p.LG;
   constexpr int VPL = 2 * DEC_P / 8;      // 16-byte vectors per lane: 40 of x, 40 of h
@@ -117,36 +142,26 @@ __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g,
         if (dsti[r] >= 0) bf16x8_to_smem(act + dsti[r], v[r]);
     }
     __syncthreads();
-    // ---- dot products: thread = (column c, matrix m, lane parity ls); chains sequential in k
+    if (lt && tid == 0 && a0 == 0) lt[0] = clock64();
+    // ---- dot products: thread = (column c, matrix m, lane parity ls) owns the chains of lanes ls, ls + 2, ...;
+    // specialised by the number of lanes so that a sparse chunk issues no predicated-off instructions
     {
       const int c = tid & 63, m = (tid >> 6) & 1, ls = tid >> 7;
       const uint16_t* wrow = wl + ((size_t)(layer * 2 + m) * DEC_COLS + c) * DEC_KSTR;
-      float acc[DEC_CHUNK / 2];
-#pragma unroll
-      for (int i = 0; i < DEC_CHUNK / 2; ++i) acc[i] = 0.f;
-      for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
-        const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
-        const float w0 = __uint_as_float(wb.x << 16), w1 = __uint_as_float(wb.x & 0xffff0000u);
-        const float w2 = __uint_as_float(wb.y << 16), w3 = __uint_as_float(wb.y & 0xffff0000u);
-#pragma unroll
-        for (int i = 0; i < DEC_CHUNK / 2; ++i) {
-          const int a = ls + 2 * i;
-          if (a < nc) {
-            const float4 xv = *reinterpret_cast<const float4*>(act + a * 2 * DEC_P + m * DEC_P + k4 * 4);
-            acc[i] = __fmaf_rn(xv.x, w0, acc[i]);
-            acc[i] = __fmaf_rn(xv.y, w1, acc[i]);
-            acc[i] = __fmaf_rn(xv.z, w2, acc[i]);
-            acc[i] = __fmaf_rn(xv.w, w3, acc[i]);
-          }
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < DEC_CHUNK / 2; ++i) {
-        const int a = ls + 2 * i;
-        if (a < nc) part[(m * DEC_CHUNK + a) * DEC_COLS + c] = acc[i];
+      const float* xbase = act + ls * 2 * DEC_P + m * DEC_P;
+      float* pout = part + (m * DEC_CHUNK + ls) * DEC_COLS + c;
+      switch ((nc - ls + 1) / 2) {
+        case 1: dot_chains<1>(wrow, xbase, pout); break;
+        case 2: dot_chains<2>(wrow, xbase, pout); break;
+        case 3: dot_chains<3>(wrow, xbase, pout); break;
+        case 4: dot_chains<4>(wrow, xbase, pout); break;
+        case 5: dot_chains<5>(wrow, xbase, pout); break;
+        case 6: dot_chains<6>(wrow, xbase, pout); break;
+        default: break;
       }
     }
     __syncthreads();
+    if (lt && tid == 0 && a0 == 0) lt[1] = clock64();
     // ---- cell update: thread = (unit u, lane a)
     if (ua < nc) {
       const int j = s * DEC_U + uu;
@@ -217,56 +232,51 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
   }
 }
 
-// Phase D for one lane, executed by one warp: fc1 epilogue, fc2, argmax, greedy_decode_update state machine.
-// st = the lane's state word at the start of the iteration; the new word is written back to global memory.
-__device__ __forceinline__ void joint_update_lane(const DecParams& p, int n, int iter, int4 st, float* ybuf, const float* s_b1,
-                                                  const float* s_b2, int lane) {
+// Phase D for one lane, executed by one warp, in two halves so that the block-wide staging of the fc2 weights into
+// shared memory overlaps the first half's global loads.
+//   joint_stage : fc1 epilogue  y = bf16(relu((z + y1[cur_t]) + b1))  -> per-warp bf16 vector in shared memory
+//   joint_finish: fc2 from shared memory (rows 29..31 of W2 are zero by contract, modeling_rnnt.py:241-246), argmax,
+//                 greedy_decode_update state machine; the lane's new state word goes back to global memory.
+struct JointRegs { int sa, ri, ti, flen; };
+
+__device__ __forceinline__ JointRegs joint_stage(const DecParams& p, int n, int4 st, uint16_t* ybuf, const float* s_b1, int lane) {
   const int cur_t = st.y;
   const uint16_t* y1r = p.y1 + ((size_t)cur_t * p.N + n) * DEC_J;
   const float* zr = p.z + (size_t)n * DEC_J;
-  // ---- every global operand of this lane is requested before the first use (one memory round trip)
   float zv[DEC_J / 32]; uint16_t yb[DEC_J / 32];
 #pragma unroll
   for (int i = 0; i < DEC_J / 32; ++i) { zv[i] = __ldcg(zr + lane + 32 * i); yb[i] = __ldg(y1r + lane + 32 * i); }
-  int sa = 0, ri = 0, ti = 0, flen = 0;
-  if (lane == 0) { sa = p.symbols_added[n]; ri = p.res_idx[n]; ti = p.time_idx[n]; flen = p.f_lens[n]; }
-  const uint4* wrow = reinterpret_cast<const uint4*>(p.w2 + (size_t)lane * DEC_J);
-  uint4 wq[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) wq[j] = __ldg(wrow + j);
+  JointRegs r = {0, 0, 0, 0};
+  if (lane == 0) { r.sa = p.symbols_added[n]; r.ri = p.res_idx[n]; r.ti = p.time_idx[n]; r.flen = p.f_lens[n]; }
 #pragma unroll
   for (int i = 0; i < DEC_J / 32; ++i) {
     const int k = lane + 32 * i;
     const float v = __fadd_rn(__fadd_rn(zv[i], bf16_bits_to_float(yb[i])), s_b1[k]);   // (acc + y1) + bias
-    ybuf[k] = bf16_bits_to_float(float_to_bf16_bits(fmaxf(v, 0.f)));                   // relu, round to bf16
+    ybuf[k] = (uint16_t)float_to_bf16_bits(fmaxf(v, 0.f));                             // relu, round to bf16
   }
   __syncwarp();
-  // logits[o], o = lane: sequential chain over k; W2 row streamed 8 x 16 bytes ahead
+  return r;
+}
+
+__device__ __forceinline__ void joint_finish(const DecParams& p, int n, int iter, int4 st, JointRegs r, const uint8_t* w2s,
+                                             const uint16_t* ybuf, const float* s_b2, int lane) {
+  const int cur_t = st.y;
   float acc = 0.f;
-#pragma unroll 1
-  for (int k64 = 0; k64 < DEC_J / 64; ++k64) {
-    uint4 wn[8];
-    if (k64 + 1 < DEC_J / 64) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) wn[j] = __ldg(wrow + (k64 + 1) * 8 + j);
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const uint4 wb = wq[j];
-      const float4 ya = *reinterpret_cast<const float4*>(ybuf + k64 * 64 + j * 8);
-      const float4 yc = *reinterpret_cast<const float4*>(ybuf + k64 * 64 + j * 8 + 4);
-      acc = __fmaf_rn(ya.x, __uint_as_float(wb.x << 16), acc);
-      acc = __fmaf_rn(ya.y, __uint_as_float(wb.x & 0xffff0000u), acc);
-      acc = __fmaf_rn(ya.z, __uint_as_float(wb.y << 16), acc);
-      acc = __fmaf_rn(ya.w, __uint_as_float(wb.y & 0xffff0000u), acc);
-      acc = __fmaf_rn(yc.x, __uint_as_float(wb.z << 16), acc);
-      acc = __fmaf_rn(yc.y, __uint_as_float(wb.z & 0xffff0000u), acc);
-      acc = __fmaf_rn(yc.z, __uint_as_float(wb.w << 16), acc);
-      acc = __fmaf_rn(yc.w, __uint_as_float(wb.w & 0xffff0000u), acc);
-    }
-    if (k64 + 1 < DEC_J / 64) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) wq[j] = wn[j];
+  if (lane < DecSmem::W2_ROWS) {
+    const uint4* wrow = reinterpret_cast<const uint4*>(w2s + lane * DecSmem::W2_STRIDE);
+    const uint4* yrow = reinterpret_cast<const uint4*>(ybuf);
+#pragma unroll 4
+    for (int k8 = 0; k8 < DEC_J / 8; ++k8) {      // logits[lane]: sequential chain over k
+      const uint4 wb = wrow[k8];
+      const uint4 yv = yrow[k8];
+      acc = __fmaf_rn(__uint_as_float(yv.x << 16), __uint_as_float(wb.x << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.x & 0xffff0000u), __uint_as_float(wb.x & 0xffff0000u), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.y << 16), __uint_as_float(wb.y << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.y & 0xffff0000u), __uint_as_float(wb.y & 0xffff0000u), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.z << 16), __uint_as_float(wb.z << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.z & 0xffff0000u), __uint_as_float(wb.z & 0xffff0000u), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.w << 16), __uint_as_float(wb.w << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.w & 0xffff0000u), __uint_as_float(wb.w & 0xffff0000u), acc);
     }
   }
   float best = __fadd_rn(acc, s_b2[lane]);
@@ -282,6 +292,8 @@ __device__ __forceinline__ void joint_update_lane(const DecParams& p, int n, int
   if (lane == 0) {
     const int sym = bidx;
     int flags = st.x, pre_g = st.z, fix_iter = st.w;
+    int sa = r.sa, ri = r.ri, ti = r.ti;
+    const int flen = r.flen;
     const bool upd_g = (sym != DEC_BLANK) && (sa != DEC_MAXSYM) && (flen != 0);
     if (upd_g) {
       ri += 1;
@@ -317,11 +329,14 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   uint16_t* wl = reinterpret_cast<uint16_t*>(smem);
   float* act = reinterpret_cast<float*>(smem + DecSmem::W_BYTES);
   float* part = reinterpret_cast<float*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES);
-  uint16_t* wp = reinterpret_cast<uint16_t*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES + DecSmem::PART_BYTES);
+  uint16_t* wp = reinterpret_cast<uint16_t*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES + DecSmem::PART_BYTES + DecSmem::PAD_BYTES);
+  uint8_t* w2s = smem + DecSmem::W_BYTES;                                    // joint-phase overlay of act | part | pad
+  uint16_t* jy = reinterpret_cast<uint16_t*>(w2s + DecSmem::JY_OFFSET);
+  bool w2_valid = false;
   __shared__ int4 s_state[DEC_MAXLG];
   __shared__ int alist[DEC_MAXLG];
   __shared__ float s_bias[2 * DEC_COLS], s_b1[DEC_J], s_b2[DEC_V];
-  __shared__ int s_na, s_unfinished, s_live;
+  __shared__ int s_na, s_unfinished, s_live, s_fail;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = blockIdx.x / DEC_S, s = blockIdx.x % DEC_S;
@@ -353,8 +368,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   // lane state init (each lane by the CTA that owns it in phase D)
   for (int li = s + tid * DEC_S; li < nl; li += DEC_S * DEC_THREADS)
     *reinterpret_cast<int4*>(p.lane_state + (size_t)(lane0 + li) * 4) = make_int4(LS_NEED, 0, p.pre_g[lane0 + li], 0);
+  if (tid == 0) s_fail = 0;
   int epoch = 0; bool ok = true;
-  group_barrier(p, g, epoch, ok);
+  group_barrier(p, g, epoch, ok, &s_fail);
 
   int iter = 0;
   int total_iters = -1;   // unknown during phase 1
@@ -415,28 +431,63 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     if (total_iters >= 0 && (iter >= total_iters || s_live == 0)) break;
     ++iter;
     const bool tr = p.trace && blockIdx.x == 0 && tid == 0 && iter <= p.trace_cap;
-    long long* trow = p.trace + (size_t)(iter - 1) * 8;
+    long long* trow = p.trace + (size_t)(iter - 1) * 16;
     if (tr) { trow[0] = clock64(); trow[7] = na; }
 
     if (na > 0) {
-      lstm_phase(p, 0, g, s, alist, na, s_state, wl, s_bias, act, part);
+      lstm_phase(p, 0, g, s, alist, na, s_state, wl, s_bias, act, part, tr ? trow + 12 : nullptr);
       if (tr) trow[1] = clock64();
-      group_barrier(p, g, epoch, ok);
+      group_barrier(p, g, epoch, ok, &s_fail);
       if (tr) trow[2] = clock64();
       lstm_phase(p, 1, g, s, alist, na, s_state, wl, s_bias, act, part);
-      group_barrier(p, g, epoch, ok);
+      group_barrier(p, g, epoch, ok, &s_fail);
       if (tr) trow[3] = clock64();
       fc1_phase(p, g, s, alist, na, s_state, wp, act);
-      group_barrier(p, g, epoch, ok);
+      group_barrier(p, g, epoch, ok, &s_fail);
       if (tr) trow[4] = clock64();
     }
-    // ---- phase D: lanes li = s, s+S, ... ; one warp per lane
-    for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
-      const int4 st = s_state[li];
-      if (!(st.x & LS_FIXED)) joint_update_lane(p, lane0 + li, iter, st, act + warp * DEC_J, s_b1, s_b2, lane);
+    // ---- phase D: lanes li = s, s+S, ... ; one warp per lane and pass.  The LSTM / fc1 phases overwrite the overlay, so
+    // the fc2 weights are staged again whenever they ran; the staging loads overlap the first pass's operand loads.
+    if (na > 0) w2_valid = false;
+    {
+      constexpr int NV = DecSmem::W2_ROWS * (DEC_J / 8);       // 16-byte vectors of W2 rows 0..28
+      constexpr int VPT = (NV + DEC_THREADS - 1) / DEC_THREADS;
+      uint4 wv[VPT];
+      if (!w2_valid) {
+#pragma unroll
+        for (int r = 0; r < VPT; ++r) {
+          const int e = tid + r * DEC_THREADS;
+          if (e < NV) wv[r] = __ldg(reinterpret_cast<const uint4*>(p.w2) + e);
+        }
+      }
+      int li = s + warp * DEC_S;
+      int4 st = make_int4(LS_FIXED, 0, 0, 0);
+      JointRegs jr = {0, 0, 0, 0};
+      uint16_t* ybuf = jy + warp * DEC_J;
+      if (li < nl) {
+        st = s_state[li];
+        if (!(st.x & LS_FIXED)) jr = joint_stage(p, lane0 + li, st, ybuf, s_b1, lane);
+      }
+      if (!w2_valid) {
+#pragma unroll
+        for (int r = 0; r < VPT; ++r) {
+          const int e = tid + r * DEC_THREADS;
+          if (e < NV) *reinterpret_cast<uint4*>(w2s + (e / (DEC_J / 8)) * DecSmem::W2_STRIDE + (e % (DEC_J / 8)) * 16) = wv[r];
+        }
+        __syncthreads();
+        w2_valid = true;
+      }
+      for (; li < nl; li += DEC_S * DEC_WARPS) {
+        if (li != s + warp * DEC_S) {
+          st = s_state[li];
+          if (!(st.x & LS_FIXED)) jr = joint_stage(p, lane0 + li, st, ybuf, s_b1, lane);
+        }
+        if (!(st.x & LS_FIXED)) joint_finish(p, lane0 + li, iter, st, jr, w2s, ybuf, s_b2, lane);
+        __syncwarp();
+      }
     }
     if (tr) trow[5] = clock64();
-    group_barrier(p, g, epoch, ok);
+    group_barrier(p, g, epoch, ok, &s_fail);
     if (tr) trow[6] = clock64();
   }
 

@@ -5,6 +5,18 @@
 
 namespace rnnt {
 
+// Ragged batches sorted by length: rows are (t, n) with rows_per_t = N rows per timestep; batch tile b = rows
+// [128 b, 128 b + 128) of every timestep is live for t < steps[b].  rows_per_t == 0 switches the test off.
+struct RowSkip {
+  int rows_per_t;
+  int steps[32];
+  __device__ __forceinline__ bool dead(long long m0) const {
+    if (rows_per_t == 0) return false;
+    const int t = (int)(m0 / rows_per_t), b = (int)(m0 % rows_per_t) >> 7;
+    return t >= steps[b];
+  }
+};
+
 // ------------------------------------------------------------------ gemm_i8.cu
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 128;   // bytes of K per stage = one 128-byte swizzle row
@@ -25,7 +37,7 @@ struct GemmSmem {
 template <int BN>
 __global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
-                                   int num_k_blocks, int* __restrict__ status);
+                                   int num_k_blocks, int* __restrict__ status, const RowSkip skip);
 __global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, int32_t* __restrict__ C,
                                         long long M, int N, int K);
 
@@ -95,7 +107,7 @@ enum : int { LIN_BF16 = 0, LIN_F32_BIAS = 1, LIN_F32 = 2, LIN_ACCUM_RELU = 3 };
 template <int MODE>
 __global__ void linear_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w,
                                    const float* __restrict__ bias, const uint16_t* __restrict__ prev, void* __restrict__ y,
-                                   long long M, int K, int O);
+                                   long long M, int K, int O, const RowSkip skip);
 __global__ void dequant_i32_f32_kernel(const int32_t* __restrict__ acc, const float* __restrict__ bias, float scale,
                                        float* __restrict__ out, long long total, int O);
 __global__ void lstm_postop_f32_kernel(const float* __restrict__ gi, const float* __restrict__ gh, const float* __restrict__ bias,
@@ -125,8 +137,13 @@ struct DecSmem {
   static constexpr int W_BYTES = 2 * 2 * DEC_COLS * DEC_KSTR * 2;          // [layer][ih|hh][col][k] bf16 = 165,888
   static constexpr int ACT_BYTES = DEC_CHUNK * 2 * DEC_P * 4;              // [lane][x|h] fp32 = 30,720 (joint: per-warp y)
   static constexpr int PART_BYTES = 2 * DEC_CHUNK * DEC_COLS * 4;          // [ih|hh][lane][col] fp32 = 6,144
+  static constexpr int PAD_BYTES = 1536;                                   // rounds the joint-phase overlay up to 38,400
   static constexpr int WP_BYTES = DEC_JC * DEC_KSTR * 2;                   // this CTA's W_pred rows, bf16 = 16,848
-  static constexpr int TOTAL = W_BYTES + ACT_BYTES + PART_BYTES + WP_BYTES;  // 219,600 (+ ~7 KB static)
+  // joint phase overlays ACT|PART|PAD: fc2 rows 0..28 (bf16, row stride 1040 B) + one bf16 y vector per warp
+  static constexpr int W2_ROWS = 29, W2_STRIDE = DEC_J * 2 + 16;
+  static constexpr int JY_OFFSET = W2_ROWS * W2_STRIDE;                    // 30,160
+  static_assert(JY_OFFSET + DEC_WARPS * DEC_J * 2 <= ACT_BYTES + PART_BYTES + PAD_BYTES, "joint overlay does not fit");
+  static constexpr int TOTAL = W_BYTES + ACT_BYTES + PART_BYTES + PAD_BYTES + WP_BYTES;  // 221,136 (+ ~9 KB static)
 };
 
 struct DecParams {

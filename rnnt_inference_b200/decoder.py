@@ -100,7 +100,8 @@ class GreedyDecoder(torch.nn.Module):
         fac = RNNTParam.stack_time_factor
         f_lens = torch.div(f_lens + (fac - 1), fac, rounding_mode="floor").to(torch.int32)
         if self.fused:
-            y1 = self.rnnt.joint.hoist_trans(f)
+            steps2 = None if lens_host is None else P.tile_steps_for(lens_host, n, fac)
+            y1 = self.rnnt.joint.hoist_trans(f, steps2)
             if self.last_iters is None or self.last_iters.device != dev:
                 self.last_iters = torch.zeros(1, dtype=torch.int32, device=dev)
             P.greedy_decode(y1, f_lens, self.rnnt.decode_weights(), self.res, self.res_idx, self.symbols_added, self.time_idx,

@@ -187,10 +187,10 @@ class Joint(torch.nn.Module):
             b2 = F.pad(b2, (0, 32 - b2.shape[-1] % 32), "constant", 0)
         self.linear2.bias = Parameter(b2, requires_grad=False)
 
-    def hoist_trans(self, f: Tensor) -> Tensor:
+    def hoist_trans(self, f: Tensor, tile_steps=None) -> Tensor:
         """y1 = bf16(f . W_trans^T) for every encoder frame at once.  The reference rounds this product to bf16 in
         memory each iteration (amx_linear.cpp:137-150), so computing it once per frame is bit-identical."""
-        return P.linear_bf16_bf16(f, self.linear1_trans.weight)
+        return P.linear_bf16_bf16(f, self.linear1_trans.weight, tile_steps)
 
     def forward(self, f: Tensor, g: Tensor, padded_batch_size: int = 1) -> Tensor:
         """f {N, 1024}, g {N, 320} -> logits {N, 32} fp32 (bf16 mode) or {N, 29} (fp32 mode)."""

@@ -132,8 +132,9 @@ def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, sk
         ts_ptr = ctypes.c_void_p(tile_steps.ctypes.data)
     # phase A: one projection GEMM over all timesteps; phase B: one persistent recurrent kernel (rnnt_lstm_layer_i8 is
     # exactly these two calls; they are issued separately so that bench.py can time each kernel with CUDA events)
+    gemm_ts = ts_ptr if n % 128 == 0 else None     # dead (t, tile) rows of the projection are skipped as well
     telemetry.bracket("gemm_i8", (t * n, k), lambda: L.check(
-        L.lib.rnnt_gemm_i8_i32(L.ptr(x), L.ptr(w_ih), L.ptr(g_ws), t * n, 4 * H, k, st)))
+        L.lib.rnnt_gemm_i8_i32_ragged(L.ptr(x), L.ptr(w_ih), L.ptr(g_ws), t * n, 4 * H, k, n, gemm_ts, st)))
     units = (t, n, bool(skip_quant_y)) if tile_steps is None else (int(tile_steps.sum()), 128, bool(skip_quant_y))
     telemetry.bracket("lstm_recurrent", units, lambda: L.check(
         L.lib.rnnt_lstm_recurrent_i8_ragged(L.ptr(g_ws), L.ptr(w_hh), L.ptr(bias), float(rb_scale), float(in_scale),
@@ -170,8 +171,9 @@ def stack_time(x, lens, factor):
     return out
 
 
-def linear_bf16_bf16(x, w):
-    """y = bf16(x . w^T) with the oracle's accumulation order (amx_linear.cpp:137-150, i16o16b0)."""
+def linear_bf16_bf16(x, w, tile_steps=None):
+    """y = bf16(x . w^T) with the oracle's accumulation order (amx_linear.cpp:137-150, i16o16b0).  tile_steps (host int32
+    per 128-row tile of a time-major {T, N, K} input, N % 64 == 0): rows past a tile's last step are not computed."""
     L.require_cuda(x, w)
     if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
         raise RuntimeError("linear_bf16_bf16 expects bfloat16")
@@ -180,8 +182,11 @@ def linear_bf16_bf16(x, w):
     o = w.shape[0]
     y = torch.empty(x.shape[:-1] + (o,), dtype=torch.bfloat16, device=x.device)
     telemetry.launches += 1
+    ts_ptr, rows = None, 0
+    if tile_steps is not None and x.dim() == 3 and x.shape[1] % 64 == 0:
+        ts_ptr, rows = ctypes.c_void_p(tile_steps.ctypes.data), x.shape[1]
     telemetry.bracket("linear_bf16", (m, k, o), lambda: L.check(
-        L.lib.rnnt_linear_bf16_bf16(L.ptr(x), L.ptr(w), L.ptr(y), m, k, o, L.stream_ptr())))
+        L.lib.rnnt_linear_bf16_bf16_ragged(L.ptr(x), L.ptr(w), L.ptr(y), m, k, o, rows, ts_ptr, L.stream_ptr())))
     return y
 
 
