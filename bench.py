@@ -115,15 +115,11 @@ def build_query(world, rank, utts_per_gpu, batch):
     """Global query = world * utts_per_gpu utterances (lengths: fixed-seed gamma fit of dev-clean), sorted by length
     descending and cut into batches of `batch` (PytorchSUT.issue_queries); batch j belongs to rank j % world
     (SURVEY.md 8(e)).  Returns this rank's list of batches, each a list of (utt_id, length)."""
-    from rnnt_inference_b200 import synthetic as S
+    from rnnt_inference_b200 import sharding, synthetic as S
     total = world * utts_per_gpu
     lens = S.utterance_lengths(UTTS_PER_GPU)            # 2513 distinct utterances, replicated beyond (like MLPerf)
-    ids = np.arange(total)
-    ulen = lens[ids % UTTS_PER_GPU]
-    order = np.argsort(-ulen, kind="stable")
-    batches = [order[i:i + batch] for i in range(0, total, batch)]
-    mine = batches[rank::world]
-    return [[(int(u), int(ulen[u])) for u in b] for b in mine], int(ulen.sum())
+    ulen = lens[np.arange(total) % UTTS_PER_GPU]
+    return sharding.shard_batches(ulen, batch, world, rank), int(ulen.sum())
 
 
 def make_model(device, batch=BATCH):
@@ -158,17 +154,30 @@ def stage_on_device(batches, feats, device):
         offsets[:len(b)] = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]))
         lens_t = torch.zeros(n_pad, dtype=torch.int32)
         lens_t[:len(b)] = torch.tensor(lens, dtype=torch.int32)
-        staged.append((packed, offsets.to(device), lens_t.to(device), max(lens), len(b), lens))
+        ids = torch.tensor([u for u, _ in b], dtype=torch.int64, device=device)
+        staged.append((packed, offsets.to(device), lens_t.to(device), max(lens), len(b), lens, ids))
     return staged
 
 
-def run_step_device(decoder, staged):
-    """One step = one pass over this rank's query, inputs already in HBM.  Returns emitted-token count tensor."""
-    total = None
-    for packed, offsets, lens, max_len, n_actual, lens_host in staged:
-        _res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len, lens_host)
+def run_step_device(decoder, staged, world=1):
+    """One step = one pass over this rank's query, inputs already in HBM; with N > 1 the step ends with the gather of
+    (sample id, length, tokens) from all ranks (the path's only collective).  Returns emitted-token count tensor."""
+    from rnnt_inference_b200 import sharding
+    total, outs = None, []
+    cap = max((m + 1) // 2 for _p, _o, _l, m, _n, _h, _i in staged) if staged else 1
+    for packed, offsets, lens, max_len, n_actual, lens_host, ids in staged:
+        res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len, lens_host)
         s = res_len[:n_actual].sum()
         total = s if total is None else total + s
+        if world > 1:
+            tok = torch.full((n_actual, cap), -1, dtype=torch.int32, device=res.device)
+            w = min(cap, res.shape[1])
+            tok[:, :w] = res[:n_actual, :w]
+            outs.append((ids, res_len[:n_actual].to(torch.int32), tok))
+    if world > 1:
+        dev = staged[0][0].device if staged else torch.device("cuda", torch.cuda.current_device())
+        cat = lambda k, dt, shape: torch.cat([o[k] for o in outs], 0) if outs else torch.empty(shape, dtype=dt, device=dev)
+        sharding.gather_transcripts(cat(0, torch.int64, (0,)), cat(1, torch.int32, (0,)), cat(2, torch.int32, (0, cap)), world)
     return total
 
 
@@ -334,7 +343,7 @@ def main():
     # ---- device-resident leg: W warm-up steps, then exactly K timed steps
     with torch.no_grad():
         for _ in range(args.warmup):
-            run_step_device(decoder, staged)
+            run_step_device(decoder, staged, world)
         ops.telemetry.events = {}
         launches0 = ops.telemetry.launches
         sampler = ClockSampler(local)
@@ -344,7 +353,7 @@ def main():
         ev0.record()
         tokens = None
         for _ in range(args.steps):
-            tokens = run_step_device(decoder, staged)
+            tokens = run_step_device(decoder, staged, world)
         ev1.record()
         barrier()
         clocks = sampler.stop()
@@ -398,7 +407,7 @@ def main():
                        "utterances_per_gpu_per_step": my_utts, "frames_per_gpu_per_step": my_frames, "batch": args.batch,
                        "batches_per_step": len(batches), "tokens_per_step_rank0": tokens_per_step,
                        "l2": "inputs and per-layer int32 projections (up to 2 GB) exceed the 126 MB L2; no explicit flush",
-                       "parallelism": f"dp{world}: sorted batches dealt round-robin to ranks"},
+                       "parallelism": f"dp{world}: length-sorted utterances dealt round-robin to ranks, transcripts gathered over NCCL"},
             "lstm_step_us": round(step_us, 3) if step_us else None,
             "kernel_ms": shares, "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": roof, "cpu_baseline": cpu}
         if micro:

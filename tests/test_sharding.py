@@ -1,0 +1,59 @@
+"""N > 1 host logic on CPU (gloo, world_size 2): the query is partitioned without overlap, every rank's batches are sorted
+by length, and the transcript gather returns every sample exactly once with its own tokens."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from rnnt_inference_b200 import sharding
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, lengths, batch, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        mine = sharding.shard_batches(lengths, batch, world, rank)
+        ids = torch.tensor([i for b in mine for i, _ in b], dtype=torch.int64)
+        lens = torch.tensor([n % 7 for b in mine for _, n in b], dtype=torch.int32)       # fake transcript lengths
+        width = int(lens.max().item()) if len(lens) else 1
+        tokens = torch.full((len(ids), width), -1, dtype=torch.int32)
+        for r, (i, n) in enumerate(zip(ids.tolist(), lens.tolist())):
+            tokens[r, :n] = torch.arange(n, dtype=torch.int32) + i                        # tokens depend on the sample id
+        g_ids, g_lens, g_tok = sharding.gather_transcripts(ids, lens, tokens, world)
+        torch.save({"mine": mine, "ids": g_ids, "lens": g_lens, "tok": g_tok}, os.path.join(out_dir, f"r{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_shard_and_gather_world2(tmp_path):
+    rng = np.random.default_rng(5)
+    lengths = rng.integers(40, 500, 203)
+    batch, world = 32, 2
+    mp.spawn(_worker, args=(world, _free_port(), lengths, batch, str(tmp_path)), nprocs=world, join=True)
+    outs = [torch.load(os.path.join(tmp_path, f"r{r}.pt")) for r in range(world)]
+    seen = sorted(i for o in outs for b in o["mine"] for i, _ in b)
+    assert seen == list(range(len(lengths)))                                              # disjoint cover of the query
+    for o in outs:
+        for b in o["mine"]:
+            ls = [n for _, n in b]
+            assert ls == sorted(ls, reverse=True) and len(b) <= batch
+    for o in outs:                                                                        # every rank holds the full gather
+        assert sorted(o["ids"].tolist()) == list(range(len(lengths)))
+        for i, n, row in zip(o["ids"].tolist(), o["lens"].tolist(), o["tok"]):
+            assert n == int(lengths[i]) % 7
+            assert row[:n].tolist() == list(range(i, i + n)) and bool((row[n:] == -1).all())
+
+
+def test_shard_single_rank_matches_issue_queries_order():
+    lengths = [5, 9, 9, 2, 7]
+    b = sharding.shard_batches(lengths, 2)
+    assert [[i for i, _ in x] for x in b] == [[1, 2], [4, 0], [3]]                        # stable descending sort
