@@ -46,7 +46,7 @@ constexpr int REC_H = 1024;
 constexpr int REC_BM = 128;          // batch rows per tile (UMMA M)
 constexpr int REC_HS = 16;           // hidden units per slice CTA (all four gates: UMMA N = 64)
 constexpr int REC_KC = 8;            // K chunks of 128 bytes per tile
-constexpr int REC_NS = 4;            // stages of the h operand ring (16 KB each)
+constexpr int REC_NS = 5;            // stages of the h operand ring (16 KB each; all the shared memory that is left)
 constexpr int REC_GS = 2;            // stages of the input-projection (G) tile ring (32 KB each)
 constexpr int REC_CTRL_WARPS = 4;    // 0: TMA producer, 1: MMA issuer, 2: TMEM alloc, 3: publisher
 constexpr int REC_EPI_WARPS = 16;

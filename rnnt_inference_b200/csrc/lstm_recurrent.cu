@@ -90,16 +90,17 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   uint16_t* lut = reinterpret_cast<uint16_t*>(smem_gen + S::LUT_OFFSET);
   const uint32_t bar_base = smem_base + S::BAR_OFFSET;
   const uint32_t full_bar = bar_base;                  // [REC_NS] h chunk landed (TMA complete_tx)
-  const uint32_t empty_bar = bar_base + 32;            // [REC_NS] h chunk consumed by the MMAs of all CS CTAs
-  const uint32_t gfull_bar = bar_base + 64;            // [REC_GS] G tile landed
-  const uint32_t gempty_bar = bar_base + 80;           // [REC_GS] G tile read by all epilogue warps
-  const uint32_t tfull_bar = bar_base + 96;            // [2] accumulator complete
-  const uint32_t done_bar = bar_base + 112;            // [2] item finished by all epilogue warps (frees the accumulator)
-  const uint32_t staged_bar = bar_base + 128;          // [2] h / y rows of the item staged in shared memory
-  const uint32_t wfull_bar = bar_base + 144;
-  const uint32_t tmem_slot = bar_base + 152;
-  const uint32_t done_cnt = bar_base + 160;            // [2] u32: monotonic "stores issued" counters for the publisher
-  int* s_steps = reinterpret_cast<int*>(smem_gen + S::BAR_OFFSET + 192);   // [REC_MAX_TILES]
+  const uint32_t empty_bar = bar_base + 48;            // [REC_NS] h chunk consumed by the MMAs of all CS CTAs
+  const uint32_t gfull_bar = bar_base + 96;            // [REC_GS] G tile landed
+  const uint32_t gempty_bar = bar_base + 112;          // [REC_GS] G tile read by all epilogue warps
+  const uint32_t tfull_bar = bar_base + 128;           // [2] accumulator complete
+  const uint32_t done_bar = bar_base + 144;            // [2] item finished by all epilogue warps (frees the accumulator)
+  const uint32_t staged_bar = bar_base + 160;          // [2] h / y rows of the item staged in shared memory
+  const uint32_t wfull_bar = bar_base + 176;
+  const uint32_t tmem_slot = bar_base + 184;
+  const uint32_t done_cnt = bar_base + 192;            // [2] u32: monotonic "stores issued" counters for the publisher
+  int* s_steps = reinterpret_cast<int*>(smem_gen + S::BAR_OFFSET + 208);   // [REC_MAX_TILES]
+  static_assert(REC_NS * 8 <= 48 && REC_GS * 8 <= 16, "barrier layout");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x;
@@ -124,8 +125,8 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       mbar_init(staged_bar + 8 * i, REC_EPI_WARPS);
     }
     mbar_init(wfull_bar, 1);
-    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 160) = 0u;
-    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 164) = 0u;
+    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 192) = 0u;
+    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 196) = 0u;
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<2 * S::UMMA_N>(tmem_slot);
