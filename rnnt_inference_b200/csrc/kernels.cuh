@@ -85,7 +85,8 @@ struct RecParams {
   float rb_scale, in_scale, out_scale;
   int T, N, num_btiles, skip_quant_y;
   int tile_steps[REC_MAX_TILES];   // timesteps to run for each batch tile (<= T); ragged batches sorted by length
-  int debug;               // profiling only (rnnt_debug_set_recurrent_flags): 1 skip MMAs, 2 skip gate math, 4 skip h loads
+  int debug;               // profiling only (rnnt_debug_set_recurrent_flags): 1 skip MMAs, 2 skip gate math, 4 skip h loads, 8 skip y/c stores,
+                           // 16 relaxed publish, 32 no proxy fence, 64 no G, 128 no c prefetch, 256 ignore the h_t flags
   long long* trace;        // optional [T][8] clock64 stamps of CTA (0,0) (profiles/trace_recurrent.py; NULL otherwise)
 };
 
