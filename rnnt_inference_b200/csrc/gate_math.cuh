@@ -71,6 +71,25 @@ __device__ __forceinline__ __half2 sigmoid_ph2(__half2 x, const HalfConsts& k, c
   return __hmul2_rn(r, k.half);
 }
 
+// Whole-function table of pade_clamped: it is an odd function of x in exact binary16 arithmetic (x only enters through
+// x*x and one final multiply; the clamp thresholds are symmetric), so tab[bits(|x|)] with the sign bit OR-ed back gives
+// the identical result for every input with |x| bits <= 0x44F9; larger magnitudes (incl. inf) clamp to entry 0x44F9 =
+// 1.0.  The table is filled by the kernel itself with pade_clamped, i.e. it is exact by construction.  NaN inputs (never
+// produced by finite accumulators) would map to +-1 instead of NaN.
+__device__ __forceinline__ __half2 tanh_tab2(__half2 x, uint32_t tab_smem) {
+  const uint32_t b = h2_bits(x);
+  const uint32_t idx = __vminu2(b & 0x7fff7fffu, 0x44f944f9u);
+  uint32_t lo, hi;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(lo) : "r"(tab_smem + ((idx & 0xffffu) << 1)));
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(hi) : "r"(tab_smem + ((idx >> 16) << 1)));
+  return bits_h2((lo | (hi << 16)) | (b & 0x80008000u));
+}
+__device__ __forceinline__ __half2 sigmoid_tab2(__half2 x, const HalfConsts& k, uint32_t tab_smem) {
+  __half2 r = tanh_tab2(__hmul2_rn(k.half, x), tab_smem);
+  r = __hadd2_rn(r, k.one);
+  return __hmul2_rn(r, k.half);
+}
+
 // _mm512_scale_min128max_i8_ph: fp16 multiply by the fp16-rounded scale, round to nearest-even integer,
 // min(127), max(-128); returns the two int8 values in the low 16 bits (byte0 = .x, byte1 = .y).
 __device__ __forceinline__ uint32_t quant_ph2(__half2 h, __half2 scale) {

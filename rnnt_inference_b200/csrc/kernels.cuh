@@ -46,7 +46,8 @@ constexpr int REC_H = 1024;
 constexpr int REC_BM = 128;          // batch rows per tile (UMMA M)
 constexpr int REC_HS = 16;           // hidden units per slice CTA (all four gates: UMMA N = 64)
 constexpr int REC_KC = 8;            // K chunks of 128 bytes per tile
-constexpr int REC_NS = 5;            // stages of the h operand ring (16 KB each; all the shared memory that is left)
+constexpr int REC_NS = 3;            // stages of the h operand ring (16 KB each; measured: depth 3..8 makes no difference)
+constexpr int REC_TAB_N = 0x44FA;    // entries of the fp16 activation table: |x| bit patterns 0 .. 0x44F9 (4.97 = 0x44F8)
 constexpr int REC_GS = 2;            // stages of the input-projection (G) tile ring (32 KB each)
 constexpr int REC_CTRL_WARPS = 4;    // 0: TMA producer, 1: MMA issuer, 2: TMEM alloc, 3: publisher
 constexpr int REC_EPI_WARPS = 16;
@@ -69,7 +70,9 @@ struct RecSmem {
   static constexpr int OUT_Y = 4 * REC_BM * 8;            // [ug][row] 8 B  = 4 KB
   static constexpr int OUT_STAGE = OUT_H + OUT_Y;
   static constexpr int LUT_OFFSET = OUT_OFFSET + 2 * OUT_STAGE;
-  static constexpr int BAR_OFFSET = LUT_OFFSET + 2048;
+  static constexpr int TAB_OFFSET = LUT_OFFSET + 2048;               // whole-function table of the Pade tanh kernel
+  static constexpr int TAB_BYTES = (REC_TAB_N * 2 + 15) / 16 * 16;   // 35,328
+  static constexpr int BAR_OFFSET = TAB_OFFSET + TAB_BYTES;
   static constexpr int TOTAL = BAR_OFFSET + 512 + 1024;   // barriers/counters + alignment slack
 };
 

@@ -88,6 +88,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   const uint32_t smem_g = smem_base + S::G_OFFSET;
   const uint32_t smem_out = smem_base + S::OUT_OFFSET;
   uint16_t* lut = reinterpret_cast<uint16_t*>(smem_gen + S::LUT_OFFSET);
+  const uint32_t tab = smem_base + S::TAB_OFFSET;
   const uint32_t bar_base = smem_base + S::BAR_OFFSET;
   const uint32_t full_bar = bar_base;                  // [REC_NS] h chunk landed (TMA complete_tx)
   const uint32_t empty_bar = bar_base + 48;            // [REC_NS] h chunk consumed by the MMAs of all CS CTAs
@@ -131,6 +132,15 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   }
   if (warp == 2) tmem_alloc<2 * S::UMMA_N>(tmem_slot);
   tc_fence_before();
+  __syncthreads();
+  {   // activation table: every reachable |x| evaluated once with the reference's instruction sequence
+    const HalfConsts kc = make_half_consts();
+    uint16_t* tabp = reinterpret_cast<uint16_t*>(smem_gen + S::TAB_OFFSET);
+    for (int i = threadIdx.x * 2; i < REC_TAB_N; i += REC_THREADS * 2) {
+      const __half2 r = pade_clamped(bits_h2((uint32_t)i | ((uint32_t)(i + 1) << 16)), kc, lut);
+      *reinterpret_cast<uint32_t*>(tabp + i) = h2_bits(r);
+    }
+  }
   __syncthreads();
   if (CS > 1) cluster_sync_all();     // peers' barriers are initialised before any multicast / remote arrive
   tc_fence_after();
@@ -356,14 +366,14 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         for (int g = 0; g < 4; ++g)
           gate[g] = __floats2half2_rn(dequant_gate((int)a[g][u], gi[g][u], bias[g][u], p.rb_scale),
                                       dequant_gate((int)a[g][u + 1], gi[g][u + 1], bias[g][u + 1], p.rb_scale));
-        const __half2 it_ = sigmoid_ph2(gate[0], k, lut);
-        const __half2 ft_ = sigmoid_ph2(gate[1], k, lut);
-        const __half2 gt_ = tanh_ph2(gate[2], k, lut);
-        const __half2 ot_ = sigmoid_ph2(gate[3], k, lut);
+        const __half2 it_ = sigmoid_tab2(gate[0], k, tab);
+        const __half2 ft_ = sigmoid_tab2(gate[1], k, tab);
+        const __half2 gt_ = tanh_tab2(gate[2], tab);
+        const __half2 ot_ = sigmoid_tab2(gate[3], k, tab);
         const __half2 c_old = bits_h2(cbits[u / 2]);
         const __half2 c_new = __hfma2(it_, gt_, __hmul2_rn(ft_, c_old));     // c = fma(i, g, f*c)
         cbits[u / 2] = h2_bits(c_new);
-        const __half2 ht = __hmul2_rn(ot_, tanh_ph2(c_new, k, lut));
+        const __half2 ht = __hmul2_rn(ot_, tanh_tab2(c_new, tab));
         const uint32_t hq = quant_ph2(ht, in_s);
         hq_pack |= hq << (8 * u);
         if (p.skip_quant_y) {
