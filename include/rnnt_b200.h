@@ -82,7 +82,7 @@ int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const fl
                                   float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
                                   const int32_t* tile_steps_host, void* workspace, void* stream);
 
-/* DEBUG: when set to a device buffer of T*8 int64, the next recurrent launches record clock64() stamps of CTA (0,0)
+/* DEBUG: when set to a device buffer of T*16 int64, the next recurrent launches record clock64() stamps of CTA (0,0)
  * per timestep (h ready, first operand chunk landed, MMAs issued, accumulator ready, TMEM read, gate math done,
  * proxy fence done, published).  NULL switches it off.  Used by profiles/trace_recurrent.py only. */
 int rnnt_debug_set_recurrent_trace(void* device_buffer);

@@ -22,7 +22,7 @@ rnnt = RNNT(S.make_checkpoint(), "quant", True).eval()
 post = rnnt.transcription.post_rnn
 w_ih, w_hh, _b, bias = post.weights[1]
 x = torch.randint(-60, 61, (T, n, 1024), dtype=torch.int8, device="cuda")
-trace = torch.zeros((T, 8), dtype=torch.int64, device="cuda")
+trace = torch.zeros((T, 16), dtype=torch.int64, device="cuda")
 names = ["h_ready", "chunk0_landed", "mma_issued", "acc_ready", "tmem_read", "math_stores_done", "publisher_saw_done", "published"]
 for rep in range(3):
     hx = torch.zeros((n, 1024), dtype=torch.int8, device="cuda")
@@ -39,6 +39,8 @@ _lib.lib.rnnt_debug_set_recurrent_trace(None)
 tr = trace.cpu().numpy().astype(np.float64)
 base = tr[:, 0:1]
 rel = tr - base
+for i, nm in enumerate(["mma: wait done_bar", "mma: wait full (sum of 8)", "epi: wait G", "epi: wait accumulator", "storer: wait staged"]):
+    print(f"  [{nm}] {np.median(tr[5:, 8 + i]):9.0f} cycles")
 print("cycles relative to h_ready of the same step (median over steps 5..):")
 for i, nm in enumerate(names):
     print(f"  {nm:14s} {np.median(rel[5:, i]):9.0f}")

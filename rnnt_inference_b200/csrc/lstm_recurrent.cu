@@ -177,7 +177,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           asm volatile("fence.acquire.gpu;" ::: "memory");
           if (!(p.debug & 32)) fence_proxy_async_all();   // generic-proxy writes of h_t (other CTAs) -> async-proxy (TMA) reads
         }
-        if (tracer && cur.i == 0) p.trace[t * 8 + 0] = clock64();
+        if (tracer && cur.i == 0) p.trace[t * 16 + 0] = clock64();
         const int hrow0 = (((t & 1) * p.num_btiles + bt) * REC_KC) * REC_BM;   // row of chunk 0 in the chunk-major h buffer
         for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
           const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
@@ -206,13 +206,18 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       uint32_t chunk = 0; int acc = 0; uint32_t acc_phase = 0;
       ItemCursor cur{0, -1};
       while (ok && cur.next(p.T, my_tiles, by, gy, s_steps)) {
+        const bool mtr = tracer && cur.i == 0;
+        long long c0 = mtr ? clock64() : 0, w_full = 0;
         if (!mbar_wait(done_bar + 8 * acc, acc_phase ^ 1u, p.status)) break;
+        if (mtr) p.trace[cur.t * 16 + 8] = clock64() - c0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * S::UMMA_N;
         for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
           const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
+          if (mtr) c0 = clock64();
           if (!mbar_wait(full_bar + 8 * st, ph, p.status)) { ok = false; break; }
-          if (kc == 0 && tracer && cur.i == 0) p.trace[cur.t * 8 + 1] = clock64();
+          if (mtr) w_full += clock64() - c0;
+          if (kc == 0 && tracer && cur.i == 0) p.trace[cur.t * 16 + 1] = clock64();
           tc_fence_after();
           const uint64_t adesc = umma_desc_sw128(smem_h + st * S::H_CHUNK);
           const uint64_t bdesc = umma_desc_sw128(smem_w + kc * S::W_CHUNK);
@@ -224,7 +229,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         }
         if (!ok) break;
         umma_commit(tfull_bar + 8 * acc);
-        if (tracer && cur.i == 0) p.trace[cur.t * 8 + 2] = clock64();
+        if (tracer && cur.i == 0) { p.trace[cur.t * 16 + 2] = clock64(); p.trace[cur.t * 16 + 9] = w_full; }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
@@ -263,14 +268,14 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           }
         }
         if (!ok) break;
-        if (tracer && cur.i == 0) p.trace[t * 8 + 6] = clock64();
+        if (tracer && cur.i == 0) p.trace[t * 16 + 6] = clock64();
         // h_{t+1}[tile bt][this slice] is written: one release increment of the tile counter (cumulative over the
         // storing warps' global stores through the shared-memory counter they released)
         if (t + 1 < s_steps[bt]) {
           if (p.debug & 16) asm volatile("red.relaxed.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
           else asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
         }
-        if (tracer && cur.i == 0) p.trace[t * 8 + 7] = clock64();
+        if (tracer && cur.i == 0) p.trace[t * 16 + 7] = clock64();
         ++item;
       }
     }
@@ -328,7 +333,9 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       // ---- operands that do not depend on the recurrent product
       int gi[4][4];
       if (!(p.debug & 64)) {
+        const long long g0 = tr ? clock64() : 0;
         if (!mbar_wait(gfull_bar + 8 * acc, acc_phase, p.status)) break;      // G ring stage == accumulator parity
+        if (tr) p.trace[t * 16 + 10] = clock64() - g0;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           const uint4 v = lds128(smem_g + acc * S::G_STAGE + g * S::G_GATE + g_off);
@@ -342,8 +349,9 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       }
       uint16_t* c_blk = p.c_ws + ((((size_t)bt * 64 + slice) * 4 + ug) * REC_BM + row) * 4;
 
+      const long long f0 = tr ? clock64() : 0;
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
-      if (tr) p.trace[t * 8 + 3] = clock64();
+      if (tr) { p.trace[t * 16 + 3] = clock64(); p.trace[t * 16 + 11] = clock64() - f0; }
       tc_fence_after();
       uint32_t a[4][4];
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * 4);
@@ -354,7 +362,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
                      : "r"(t_row + g * HS) : "memory");
       tmem_ld_wait();
       tc_fence_before();
-      if (tr) p.trace[t * 8 + 4] = clock64();
+      if (tr) p.trace[t * 16 + 4] = clock64();
 
       uint32_t hq_pack = 0, yq_pack = 0;
       uint32_t ybf[2];
@@ -400,7 +408,9 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       __syncwarp();
       if (lane == 0) mbar_arrive(staged_bar + 8 * acc);
       if (storer) {
+        const long long s0 = tr ? clock64() : 0;
         if (!mbar_wait(staged_bar + 8 * acc, acc_phase, p.status)) break;
+        if (tr) p.trace[t * 16 + 12] = clock64() - s0;
         uint4 hv;
         hv.x = lds32(out_h + (uint32_t)(0 * REC_BM + row) * 4u); hv.y = lds32(out_h + (uint32_t)(1 * REC_BM + row) * 4u);
         hv.z = lds32(out_h + (uint32_t)(2 * REC_BM + row) * 4u); hv.w = lds32(out_h + (uint32_t)(3 * REC_BM + row) * 4u);
@@ -426,7 +436,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
             *reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff) = yv;
           }
         }
-        if (tr) p.trace[t * 8 + 5] = clock64();
+        if (tr) p.trace[t * 16 + 5] = clock64();
         __syncwarp();
         if (lane == 0) red_release_cta_shared_inc(done_cnt + 4 * acc);   // publisher: this warp's rows are written
       }
