@@ -182,6 +182,9 @@ def run_step_device(decoder, staged, world=1):
 
 
 # ------------------------------------------------------------------------------------------------ roofline
+NCU_TRAFFIC_RATIO = 1.789 / 2.412
+
+
 def recurrent_roofline(events, peaks):
     """Algorithmic HBM bytes of the recurrent kernel per launch (DESIGN.md / SURVEY.md 8(d)): per (timestep, utterance)
     G int32 16384 + h_in 1024 + c read+write 4096 + h_out 1024 + y 1024 (int8) or 2048 (bf16) = 23552 / 24576 bytes."""
@@ -197,8 +200,14 @@ def recurrent_roofline(events, peaks):
     launches = len(recs)
     achieved = tot_bytes / (tot_ms * 1e-3) / 1e9
     peak = peaks.get("hbm_gbs", 6650.0)
+    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of ONE `ncu --set full` launch (N=1024, T=100, int8 y;
+    # profiles/r01/SUMMARY.md): 1.789e9 bytes against 2.412e9 algorithmic (part of G is still in L2 from the GEMM that
+    # wrote it).  The measured ratio is applied to this run's mean launch so the figure is per launch like `achieved`.
+    traffic = round(NCU_TRAFFIC_RATIO * tot_bytes / launches)
     roof = {"kernel": "lstm_recurrent_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peaks.get("_source", "fallback"),
+            "frac": round(achieved / peak, 4), "traffic": traffic,
+            "traffic_source": "ncu --set full, one launch N=1024 T=100: 1.789 GB dram r+w / 2.412 GB algorithmic = 0.742, scaled to this run's mean launch",
+            "peak_source": peaks.get("_source", "fallback"),
             "launches": launches, "avg_launch_ms": round(tot_ms / launches, 4),
             "algorithmic_bytes_per_launch": round(tot_bytes / launches), "tensor_top_s": round(tot_ops / (tot_ms * 1e-3) / 1e12, 1)}
     return roof, tot_ms * 1e3 / steps     # second value: mean us per (layer, timestep)

@@ -102,8 +102,16 @@ static int linear_launch(const uint16_t* x, const uint16_t* w, const float* bias
                          int O, cudaStream_t st, const RowSkip* skip_in = nullptr) {
   RowSkip skip;
   if (skip_in) skip = *skip_in; else memset(&skip, 0, sizeof skip);
-  dim3 grid((O + LB_TO - 1) / LB_TO, (unsigned)((M + LB_TM - 1) / LB_TM));
-  linear_bf16_kernel<MODE><<<grid, 256, 0, st>>>(x, w, bias, prev, y, M, K, O, skip);
+  // enough 128 x 128 tiles to fill the machine twice over -> the large-tile kernel (FMA-bound instead of LDS-bound)
+  const long long big_tiles = ((M + LBB_T - 1) / LBB_T) * ((O + LBB_T - 1) / LBB_T);
+  const bool aligned = (((uintptr_t)x | (uintptr_t)w) & 15) == 0 && K % LBB_TK == 0;
+  if (aligned && big_tiles >= 2 * 148 && (skip.rows_per_t % LBB_T) == 0) {
+    dim3 grid((O + LBB_T - 1) / LBB_T, (unsigned)((M + LBB_T - 1) / LBB_T));
+    linear_bf16_big_kernel<MODE><<<grid, 256, 0, st>>>(x, w, bias, prev, y, M, K, O, skip);
+  } else {
+    dim3 grid((O + LB_TO - 1) / LB_TO, (unsigned)((M + LB_TM - 1) / LB_TM));
+    linear_bf16_kernel<MODE><<<grid, 256, 0, st>>>(x, w, bias, prev, y, M, K, O, skip);
+  }
   CUDA_TRY(cudaGetLastError());
   return RNNT_OK;
 }

@@ -161,6 +161,122 @@ template __global__ void linear_bf16_kernel<LIN_F32_BIAS>(const uint16_t*, const
 template __global__ void linear_bf16_kernel<LIN_F32>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
 template __global__ void linear_bf16_kernel<LIN_ACCUM_RELU>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
 
+// ---------------------------------------------------------------------------------------------------------------
+// Large-M variant of the same contract (the hoisted f.W_trans product: M = T*N rows, K = 1024, O = 512 is 14 % of a
+// bench step).  128 x 128 output tile per CTA, 8 x 8 outputs per thread as four 4 x 4 quadrants (rows tm, tm + 64;
+// columns to, to + 64) so every shared-memory read is a conflict-free 16-byte vector and 64 FFMAs follow 4 loads; the
+// next K tile travels global -> registers while the current one is multiplied.  Operands are widened to fp32 once,
+// when they are staged, and stored k-major with the row index XOR-ed by the k octet so the transposing stores of a
+// warp hit 32 different banks.  The fp32 chain of every output is still k = 0, 1, 2, ... in order (bit-exact).
+// Requires K % 32 == 0 and 16-byte aligned x, w (api.cu falls back to the 64 x 64 kernel otherwise).
+template <int MODE>
+__device__ __forceinline__ void lin_store(float acc, long long idx, int o, const float* bias, const uint16_t* prev, void* yout) {
+  if constexpr (MODE == LIN_BF16) {
+    reinterpret_cast<uint16_t*>(yout)[idx] = (uint16_t)float_to_bf16_bits(acc);
+  } else if constexpr (MODE == LIN_F32_BIAS) {
+    reinterpret_cast<float*>(yout)[idx] = __fadd_rn(acc, bias[o]);
+  } else if constexpr (MODE == LIN_F32) {
+    reinterpret_cast<float*>(yout)[idx] = acc;
+  } else {
+    const float v = __fadd_rn(__fadd_rn(acc, bf16_bits_to_float(prev[idx])), bias[o]);
+    reinterpret_cast<uint16_t*>(yout)[idx] = (uint16_t)float_to_bf16_bits(fmaxf(v, 0.f));
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256, 2)
+linear_bf16_big_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w, const float* __restrict__ bias,
+                       const uint16_t* __restrict__ prev, void* __restrict__ yout, long long M, int K, int O, const RowSkip skip) {
+  __shared__ __align__(16) float xs[LBB_TK][LBB_T];
+  __shared__ __align__(16) float ws[LBB_TK][LBB_T];
+  const long long m0 = (long long)blockIdx.y * LBB_T;
+  const int o0 = blockIdx.x * LBB_T;
+  if (skip.dead(m0)) return;
+  const int tm = (threadIdx.x >> 4) << 2;   // 0..60 (and + 64)
+  const int to = (threadIdx.x & 15) << 2;   // 0..60 (and + 64)
+  const int lrow = threadIdx.x >> 2;        // loader: rows lrow, lrow + 64; k octet lkq
+  const int lkq = threadIdx.x & 3;
+  uint4 xr[2], wr[2];
+  auto gload = [&](int k0) {
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const long long m = m0 + lrow + 64 * p;
+      const int o = o0 + lrow + 64 * p;
+      xr[p] = (m < M) ? __ldg(reinterpret_cast<const uint4*>(x + m * K + k0 + lkq * 8)) : make_uint4(0, 0, 0, 0);
+      wr[p] = (o < O) ? __ldg(reinterpret_cast<const uint4*>(w + (long long)o * K + k0 + lkq * 8)) : make_uint4(0, 0, 0, 0);
+    }
+  };
+  auto sstore = [&]() {
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const int col = (lrow + 64 * p) ^ (lkq * 8);
+      const uint32_t xw[4] = {xr[p].x, xr[p].y, xr[p].z, xr[p].w};
+      const uint32_t ww[4] = {wr[p].x, wr[p].y, wr[p].z, wr[p].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        xs[lkq * 8 + 2 * j][col] = __uint_as_float(xw[j] << 16);
+        xs[lkq * 8 + 2 * j + 1][col] = __uint_as_float(xw[j] & 0xffff0000u);
+        ws[lkq * 8 + 2 * j][col] = __uint_as_float(ww[j] << 16);
+        ws[lkq * 8 + 2 * j + 1][col] = __uint_as_float(ww[j] & 0xffff0000u);
+      }
+    }
+  };
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+  gload(0);
+  for (int k0 = 0; k0 < K; k0 += LBB_TK) {
+    sstore();
+    __syncthreads();
+    if (k0 + LBB_TK < K) gload(k0 + LBB_TK);
+#pragma unroll 1
+    for (int kg = 0; kg < LBB_TK / 8; ++kg) {
+      const int f = kg * 8;
+#pragma unroll
+      for (int k8 = 0; k8 < 8; ++k8) {
+        const int kk = f + k8;
+        const float4 x0 = *reinterpret_cast<const float4*>(&xs[kk][tm ^ f]);
+        const float4 x1 = *reinterpret_cast<const float4*>(&xs[kk][(tm + 64) ^ f]);
+        const float4 w0 = *reinterpret_cast<const float4*>(&ws[kk][to ^ f]);
+        const float4 w1 = *reinterpret_cast<const float4*>(&ws[kk][(to + 64) ^ f]);
+        const float xa[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        const float wa[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[i][j] = __fmaf_rn(xa[i], wa[j], acc[i][j]);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const long long m = m0 + tm + (i & 3) + ((i >> 2) << 6);
+    if (m >= M) continue;
+#pragma unroll
+    for (int jh = 0; jh < 2; ++jh) {
+      const int o = o0 + to + (jh << 6);
+      const long long idx = m * O + o;
+      if (MODE == LIN_BF16 && o + 3 < O && (O & 3) == 0) {
+        uint2 v;
+        v.x = float_to_bf16_bits(acc[i][jh * 4 + 0]) | (float_to_bf16_bits(acc[i][jh * 4 + 1]) << 16);
+        v.y = float_to_bf16_bits(acc[i][jh * 4 + 2]) | (float_to_bf16_bits(acc[i][jh * 4 + 3]) << 16);
+        *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(yout) + idx) = v;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (o + j < O) lin_store<MODE>(acc[i][jh * 4 + j], idx + j, o + j, bias, prev, yout);
+      }
+    }
+  }
+}
+template __global__ void linear_bf16_big_kernel<LIN_BF16>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
+template __global__ void linear_bf16_big_kernel<LIN_F32_BIAS>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
+template __global__ void linear_bf16_big_kernel<LIN_F32>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
+template __global__ void linear_bf16_big_kernel<LIN_ACCUM_RELU>(const uint16_t*, const uint16_t*, const float*, const uint16_t*, void*, long long, int, int, const RowSkip);
+
 // dequant of an int32 accumulator (i8o32b32, tile_product_tpp.hpp:347-367 for int8): (float(acc) + bias[o]) * scale,
 // two separately rounded fp32 operations.
 __global__ void dequant_i32_f32_kernel(const int32_t* __restrict__ acc, const float* __restrict__ bias, float scale,

@@ -100,6 +100,7 @@ __global__ void lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w
 
 // ------------------------------------------------------------------ elementwise.cu
 constexpr int LB_TM = 64, LB_TO = 64, LB_TK = 32;
+constexpr int LBB_T = 128, LBB_TK = 32;     // large-M variant: 128 x 128 tile, 8 x 8 outputs per thread
 __global__ void quantize_pad_kernel(const float* __restrict__ in, int8_t* __restrict__ out, float scale, long long rows,
                                     int k_in, int k_out);
 __global__ void quantize_ragged_kernel(const float* __restrict__ packed, const long long* __restrict__ offsets,
@@ -112,6 +113,10 @@ template <int MODE>
 __global__ void linear_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w,
                                    const float* __restrict__ bias, const uint16_t* __restrict__ prev, void* __restrict__ y,
                                    long long M, int K, int O, const RowSkip skip);
+template <int MODE>
+__global__ void linear_bf16_big_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ w,
+                                       const float* __restrict__ bias, const uint16_t* __restrict__ prev, void* __restrict__ y,
+                                       long long M, int K, int O, const RowSkip skip);
 __global__ void dequant_i32_f32_kernel(const int32_t* __restrict__ acc, const float* __restrict__ bias, float scale,
                                        float* __restrict__ out, long long total, int O);
 __global__ void lstm_postop_f32_kernel(const float* __restrict__ gi, const float* __restrict__ gh, const float* __restrict__ bias,

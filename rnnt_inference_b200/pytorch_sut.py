@@ -9,8 +9,9 @@ PytorchSUT(model_path, dataset_dir, batch_size, run_mode, args) with the referen
                               (:107-118); tokens are int32
 What changes underneath on the B200: the batch travels as the UNPADDED concatenation of its utterances (one async
 copy per pinned sample on a copy stream), padding/quantisation happen in one device kernel, and the Offline loop is
-software-pipelined — batch i+1 is staged while batch i computes and batch i-1 is answered — so the GPU never waits
-for the host.  Results are identical to the synchronous order.
+software-pipelined — batch i+1 is staged while batch i computes and batch i-1 is answered, chunks running shortest
+first so that the one exposed copy is the smallest — so the GPU never waits for the host.  Results are identical to
+the synchronous order.
 """
 import math
 import os
@@ -82,6 +83,10 @@ class PytorchSUT:
                 results, results_idx = self.inference([s.index for s in chunk])
                 self.query_samples_complete(chunk, results, results_idx)
             return
+        # Shortest chunk first: its host->device copy (the only one nothing can hide) is the smallest, and every later,
+        # larger copy overlaps the previous chunk's compute.  Chunks are independent and each is answered whole, so the
+        # order in which they run changes no transcript (LoadGen accepts completions in any order).
+        chunks.reverse()
         staged = self._stage(chunks[0]) if chunks else None
         in_flight = None
         for i in range(len(chunks)):

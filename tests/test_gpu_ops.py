@@ -135,6 +135,29 @@ def test_linear_bf16_bf16(ops):
     np.testing.assert_array_equal(got, O.linear_bf16_bf16(x, w))
 
 
+@pytest.mark.parametrize("t,n,o", [(19, 500, 512), (40, 384, 500)])
+def test_linear_bf16_bf16_large_tiles(ops, t, n, o):
+    """Shapes big enough for the 128 x 128-tile kernel (>= 296 tiles), ragged edges in M and O: same bits as the oracle."""
+    rng = np.random.default_rng(t)
+    x = O.f32_to_bf16_bits(rng.normal(0, 1, (t, n, 1024)).astype(np.float32))
+    w = O.f32_to_bf16_bits(rng.normal(0, 0.05, (o, 1024)).astype(np.float32))
+    got = bits(ops.linear_bf16_bf16(bf(x), bf(w)))
+    np.testing.assert_array_equal(got, O.linear_bf16_bf16(x, w))
+
+
+def test_linear_bf16_bf16_large_tiles_ragged(ops):
+    """tile_steps: rows of batch tile b are computed for t < tile_steps[b] only, the rest is never written."""
+    t, n, o = 24, 512, 512
+    steps = np.array([24, 17, 5, 1], np.int32)
+    rng = np.random.default_rng(9)
+    x = O.f32_to_bf16_bits(rng.normal(0, 1, (t, n, 1024)).astype(np.float32))
+    w = O.f32_to_bf16_bits(rng.normal(0, 0.05, (o, 1024)).astype(np.float32))
+    ref = O.linear_bf16_bf16(x, w)
+    got = bits(ops.linear_bf16_bf16(bf(x), bf(w), steps))
+    for b, s in enumerate(steps):
+        np.testing.assert_array_equal(got[:s, 128 * b:128 * b + 128], ref[:s, 128 * b:128 * b + 128])
+
+
 @pytest.mark.parametrize("n,t2,blank_bias,seed", [(4, 6, 0.0, 1), (33, 9, 1.5, 2), (150, 12, 2.5, 3), (40, 5, -3.0, 4)])
 def test_greedy_decode(ops, n, t2, blank_bias, seed):
     """Tokens, counters and prediction state bit-exact vs the oracle's batch-lockstep loop (incl. the reference's
