@@ -336,7 +336,7 @@ int64_t rnnt_lstm_recurrent_workspace_bytes(int N) {
 // all CTAs are co-resident (they exchange h through per-tile counters).  Returns cudaErrorCooperativeLaunchTooLarge /
 // cluster errors to the caller, which falls back to a smaller cluster.
 template <int CS>
-static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th, const CUtensorMap& tg,
+static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th,
                                  const RecParams& p, int num_slices, int grid_y, cudaStream_t st) {
   auto kern = lstm_recurrent_kernel<CS>;
   static bool attr_set = false;
@@ -358,15 +358,15 @@ static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, 
     attrs[na].val.clusterDim.x = CS; attrs[na].val.clusterDim.y = 1; attrs[na].val.clusterDim.z = 1; ++na;
   }
   cfg.attrs = attrs; cfg.numAttrs = na;
-  return cudaLaunchKernelEx(&cfg, kern, tw, th0, th, tg, p);
+  return cudaLaunchKernelEx(&cfg, kern, tw, th0, th, p);
 }
-static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th, const CUtensorMap& tg,
+static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th,
                       const RecParams& p, int num_slices, int grid_y, int cs_max, cudaStream_t st) {
   cudaError_t e = cudaErrorUnknown;
-  if (cs_max >= 8) { e = rec_launch_cs<8>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
-  if (cs_max >= 4) { e = rec_launch_cs<4>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
-  if (cs_max >= 2) { e = rec_launch_cs<2>(tw, th0, th, tg, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
-  e = rec_launch_cs<1>(tw, th0, th, tg, p, num_slices, grid_y, st);
+  if (cs_max >= 8) { e = rec_launch_cs<8>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  if (cs_max >= 4) { e = rec_launch_cs<4>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  if (cs_max >= 2) { e = rec_launch_cs<2>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  e = rec_launch_cs<1>(tw, th0, th, p, num_slices, grid_y, st);
   if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "lstm_recurrent launch failed: %s", cudaGetErrorString(e));
   return RNNT_OK;
 }
@@ -396,7 +396,7 @@ int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const fl
   if (!G || !w_hh || !bias || !hx || !cx || !y || !workspace) return fail(RNNT_ERR_INVALID, "lstm_recurrent: null pointer");
   if (H != REC_H) return fail(RNNT_ERR_INVALID, "lstm_recurrent: hidden size must be 1024 (got %d)", H);
   if (T < 0 || N <= 0) return fail(RNNT_ERR_INVALID, "lstm_recurrent: need T >= 0, N > 0 (T=%d N=%d)", T, N);
-  if (!aligned(G, 16) || !aligned(w_hh, 16) || !aligned(workspace, 256) || !aligned(y, 8) || !aligned(cx, 16) || !aligned(hx, 16))
+  if (!aligned(G, 32) || !aligned(w_hh, 16) || !aligned(workspace, 256) || !aligned(y, 8) || !aligned(cx, 16) || !aligned(hx, 16))
     return fail(RNNT_ERR_INVALID, "lstm_recurrent: misaligned buffer");
   if (T == 0) return RNNT_OK;
   cudaStream_t st = (cudaStream_t)stream;
@@ -427,9 +427,9 @@ int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const fl
   uint16_t* c_ws = reinterpret_cast<uint16_t*>(h_buf + 2 * n_pad * REC_H);
 
   const int num_slices = REC_H / REC_HS;
-  const int grid_y = (num_btiles == 1) ? 1 : 2;
-  CUtensorMap tw, th0, th, tg;
-  {   // W_hh [4 gates][1024 units][1024 k]: box = 128 B of k x 16 units x 4 gates
+  const int grid_y = num_btiles < REC_GRID_Y ? num_btiles : REC_GRID_Y;
+  CUtensorMap tw, th0, th;
+  {   // W_hh [4 gates][1024 units][1024 k]: box = 128 B of k x 32 units x 4 gates
     uint64_t dims[3] = {REC_H, REC_H, 4}, str[2] = {REC_H, (uint64_t)REC_H * REC_H};
     uint32_t box[3] = {128, (uint32_t)REC_HS, 4};
     if (int r = make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, w_hh, dims, str, box)) return r;
@@ -444,17 +444,12 @@ int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const fl
     uint32_t box[2] = {128, REC_BM};
     if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, h_buf, dims, str, box)) return r;
   }
-  {   // G [T][N][4096] int32: box = 16 columns (64 B) x 128 rows, 64-byte swizzle; rows >= N read as zero
-    uint64_t dims[3] = {4 * REC_H, (uint64_t)N, (uint64_t)T}, str[2] = {16 * REC_H, (uint64_t)N * 16 * REC_H};
-    uint32_t box[3] = {REC_HS, REC_BM, 1};
-    if (int r = make_tmap(&tg, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, G, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B)) return r;
-  }
-  p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
+  p.g = G; p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
   p.T = T; p.N = N; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
   p.trace = g_rec_trace;
   p.debug = g_rec_debug;
-  return rec_launch(tw, th0, th, tg, p, num_slices, grid_y, rec_cluster_pref(), st);
+  return rec_launch(tw, th0, th, p, num_slices, grid_y, rec_cluster_pref(), st);
 }
 
 int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,

@@ -44,44 +44,44 @@ __global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8
 // ------------------------------------------------------------------ lstm_recurrent.cu
 constexpr int REC_H = 1024;
 constexpr int REC_BM = 128;          // batch rows per tile (UMMA M)
-constexpr int REC_HS = 16;           // hidden units per slice CTA (all four gates: UMMA N = 64)
+constexpr int REC_HS = 32;           // hidden units per slice CTA (all four gates: UMMA N = 128)
 constexpr int REC_KC = 8;            // K chunks of 128 bytes per tile
 constexpr int REC_NS = 3;            // stages of the h operand ring (16 KB each; measured: depth 3..8 makes no difference)
 constexpr int REC_TAB_N = 0x44FA;    // entries of the fp16 activation table: |x| bit patterns 0 .. 0x44F9 (4.97 = 0x44F8)
-constexpr int REC_GS = 2;            // stages of the input-projection (G) tile ring (32 KB each)
 constexpr int REC_CTRL_WARPS = 4;    // 0: TMA producer, 1: MMA issuer, 2: TMEM alloc, 3: publisher
 constexpr int REC_EPI_WARPS = 16;
 constexpr int REC_STORE_WARPS = 4;   // epilogue warps 0..3 also write the staged h / y rows to global memory
 constexpr int REC_THREADS = 32 * (REC_CTRL_WARPS + REC_EPI_WARPS);   // 640
 constexpr int REC_FLAG_STRIDE = 32;  // ints between per-tile counters (128 B)
 constexpr int REC_MAX_TILES = 32;    // batch tiles per launch (N <= 4096)
+constexpr int REC_GRID_Y = 4;        // batch-tile groups: 32 slices x 4 = 128 CTAs
 
 struct RecSmem {
-  static constexpr int UMMA_N = 4 * REC_HS;
-  static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice (8 KB)
-  static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 64 KB
+  static constexpr int UMMA_N = 4 * REC_HS;               // 128
+  static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice (16 KB)
+  static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 128 KB
   static constexpr int H_CHUNK = REC_BM * 128;            // 16 KB
-  static constexpr int H_BYTES = REC_NS * H_CHUNK;        // 64 KB
-  static constexpr int G_GATE = REC_BM * REC_HS * 4;      // one gate of a G tile: 128 rows x 64 B = 8 KB
-  static constexpr int G_STAGE = 4 * G_GATE;              // 32 KB
-  static constexpr int G_OFFSET = W_BYTES + H_BYTES;
-  static constexpr int OUT_OFFSET = G_OFFSET + REC_GS * G_STAGE;   // staging of h (int8) and y (int8 | bf16) rows
-  static constexpr int OUT_H = 4 * REC_BM * 4;            // [ug][row] 4 B  = 2 KB
-  static constexpr int OUT_Y = 4 * REC_BM * 8;            // [ug][row] 8 B  = 4 KB
+  static constexpr int H_BYTES = REC_NS * H_CHUNK;        // 48 KB
+  static constexpr int OUT_OFFSET = W_BYTES + H_BYTES;    // staging of h (int8) and y (int8 | bf16) rows, one item deep;
+  static constexpr int OUT_H = 8 * REC_BM * 4;            // [unit quad][row] 4 B  = 4 KB     (the rcp LUT lives here during set-up)
+  static constexpr int OUT_Y = 8 * REC_BM * 8;            // [unit quad][row] 8 B  = 8 KB
   static constexpr int OUT_STAGE = OUT_H + OUT_Y;
-  static constexpr int LUT_OFFSET = OUT_OFFSET + 2 * OUT_STAGE;
-  static constexpr int TAB_OFFSET = LUT_OFFSET + 2048;               // whole-function table of the Pade tanh kernel
+  static constexpr int LUT_OFFSET = OUT_OFFSET;
+  static constexpr int BIAS_OFFSET = OUT_OFFSET + OUT_STAGE;         // [4 gates][32 units] fp32
+  static constexpr int TAB_OFFSET = BIAS_OFFSET + 512;               // whole-function table of the Pade tanh kernel
   static constexpr int TAB_BYTES = (REC_TAB_N * 2 + 15) / 16 * 16;   // 35,328
   static constexpr int BAR_OFFSET = TAB_OFFSET + TAB_BYTES;
   static constexpr int TOTAL = BAR_OFFSET + 512 + 1024;   // barriers/counters + alignment slack
 };
+static_assert(RecSmem::TOTAL <= 232448, "recurrent kernel shared memory");
 
 struct RecParams {
+  const int32_t* g;        // [T][N][4H] int32 input projection (read straight from global: one 32-byte sector per thread and gate)
   const float* bias;       // [4H]
   int8_t* h_buf;           // [2][tiles][8 chunks][128 rows][128 B] ping-pong (workspace), K-chunk-major
   int8_t* hx;              // [N][H] caller's state: h_0 on entry (read by TMA), receives h after the last step of each tile
   uint16_t* cx;            // [N][H] binary16: c_0 on entry, final c on exit
-  uint16_t* c_ws;          // [tiles][64 slices][4][128 rows][4] binary16: c between steps, CTA-private blocked layout
+  uint16_t* c_ws;          // [tiles][32 slices][4][128 rows][8] binary16: c between steps, CTA-private blocked layout
   void* y;                 // [T][N][H] int8 or bf16
   int* flags;              // [num_btiles][REC_FLAG_STRIDE] zeroed
   int* status;
@@ -90,13 +90,12 @@ struct RecParams {
   int tile_steps[REC_MAX_TILES];   // timesteps to run for each batch tile (<= T); ragged batches sorted by length
   int debug;               // profiling only (rnnt_debug_set_recurrent_flags): 1 skip MMAs, 2 skip gate math, 4 skip h loads, 8 skip y/c stores,
                            // 16 relaxed publish, 32 no proxy fence, 64 no G, 128 no c prefetch, 256 ignore the h_t flags
-  long long* trace;        // optional [T][8] clock64 stamps of CTA (0,0) (profiles/trace_recurrent.py; NULL otherwise)
+  long long* trace;        // optional [T][16] clock64 stamps of CTA (0,0) (profiles/trace_recurrent.py; NULL otherwise)
 };
 
 template <int CS>
 __global__ void lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h0,
-                                      const __grid_constant__ CUtensorMap tmap_h, const __grid_constant__ CUtensorMap tmap_g,
-                                      const RecParams p);
+                                      const __grid_constant__ CUtensorMap tmap_h, const RecParams p);
 
 // ------------------------------------------------------------------ elementwise.cu
 constexpr int LB_TM = 64, LB_TO = 64, LB_TK = 32;

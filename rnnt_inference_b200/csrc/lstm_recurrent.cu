@@ -5,19 +5,21 @@
 // lstm_postop_tpp::ref per row (tpps/lstm_postop_tpp.cpp:12-98) — two OpenMP regions and a round trip of the
 // fp32 gates through memory per step.  Here all T steps run inside ONE cooperative launch:
 //
-//   grid = 64 hidden slices x 2 batch-tile groups (optionally clusters of CS slice-CTAs); CTA (s, y) owns hidden
-//   units [16 s, 16 s + 16) of all four gates and walks the batch tiles y, y + 2, ... of 128 rows each.
-//   * its 64 rows of W_hh (64 KB int8) are loaded ONCE by TMA and stay in shared memory for the whole sequence.
+//   grid = 32 hidden slices x 4 batch-tile groups (optionally clusters of CS slice-CTAs); CTA (s, y) owns hidden
+//   units [32 s, 32 s + 32) of all four gates and walks the batch tiles y, y + 4, ... of 128 rows each.
+//   * its 128 rows of W_hh (128 KB int8) are loaded ONCE by TMA and stay in shared memory for the whole sequence.
+//     (A tcgen05.mma M128 x N x K32 costs max(64, N/2) cycles — the A-operand fetch — so N = 128 does twice the work of
+//     N = 64 per h byte that passes through shared memory, the measured bound of the 16-unit version; profiles/r01.)
 //   * per work item (t, batch tile):
-//       - warp 0 (producer): TMA-loads the 128x1024 int8 h_t tile as eight 16 KB K-chunks through a 4-stage ring
-//         (h lives in a K-chunk-major ping-pong buffer, so a chunk is one contiguous 16 KB read), and — as early as
-//         two items ahead, it does not depend on h — the tile's input projection G[t] (4 gates x 128 rows x 16
-//         int32, 64-byte swizzle) into a 2-stage ring;
-//       - warp 1: one thread issues tcgen05.mma.kind::i8 (M=128, N=64, K=32) x 32 into a double-buffered TMEM
+//       - warp 0 (producer): TMA-loads the 128x1024 int8 h_t tile as eight 16 KB K-chunks through a 3-stage ring
+//         (h lives in a K-chunk-major ping-pong buffer, so a chunk is one contiguous 16 KB read);
+//       - warp 1: one thread issues tcgen05.mma.kind::i8 (M=128, N=128, K=32) x 32 into a double-buffered TMEM
 //         accumulator;
-//       - 16 epilogue warps: tcgen05.ld the accumulator, add G (int32, exact), dequantise, evaluate the fp16 gates,
-//         update c (kept between steps in a CTA-private blocked scratch, so its traffic is fully coalesced), stage
-//         h_{t+1} (int8) and y[t] in shared memory; 4 of them then write whole 16/32-byte row segments out;
+//       - 16 epilogue warps: thread (row, 8 units) fetches its part of the input projection G[t] straight from global
+//         memory (one 256-bit load = one full sector per gate) before waiting for the accumulator, then tcgen05.ld,
+//         add G (int32, exact), dequantise, evaluate the fp16 gates, update c (kept between steps in a CTA-private
+//         blocked scratch, so its traffic is fully coalesced), stage h_{t+1} (int8) and y[t] in shared memory; 4 of
+//         them then write whole 32/64-byte row segments out;
 //       - warp 3 (publisher): when the item's stores are issued, one release increment of the tile's counter.
 //   * the only cross-CTA dependency is "h_t of batch tile b is complete": that per-tile counter (acquire by the
 //     producers).  No grid-wide barrier.  Several batch tiles per CTA are in flight, so the publish -> poll -> load
@@ -72,11 +74,15 @@ struct ItemCursor {
   }
 };
 
+__device__ __forceinline__ void ldg256_stream(const int32_t* ptr, int (&v)[8]) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.s32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "l"(ptr));
+}
+
 template <int CS>
 __global__ void __launch_bounds__(REC_THREADS, 1)
 lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h0,
-                      const __grid_constant__ CUtensorMap tmap_h, const __grid_constant__ CUtensorMap tmap_g,
-                      const RecParams p) {
+                      const __grid_constant__ CUtensorMap tmap_h, const RecParams p) {
   using S = RecSmem;
   constexpr int HS = REC_HS;
   constexpr uint16_t MC_MASK = (uint16_t)((1u << CS) - 1u);
@@ -85,15 +91,13 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const uint32_t smem_w = smem_base;
   const uint32_t smem_h = smem_base + S::W_BYTES;
-  const uint32_t smem_g = smem_base + S::G_OFFSET;
   const uint32_t smem_out = smem_base + S::OUT_OFFSET;
   uint16_t* lut = reinterpret_cast<uint16_t*>(smem_gen + S::LUT_OFFSET);
   const uint32_t tab = smem_base + S::TAB_OFFSET;
   const uint32_t bar_base = smem_base + S::BAR_OFFSET;
   const uint32_t full_bar = bar_base;                  // [REC_NS] h chunk landed (TMA complete_tx)
   const uint32_t empty_bar = bar_base + 48;            // [REC_NS] h chunk consumed by the MMAs of all CS CTAs
-  const uint32_t gfull_bar = bar_base + 96;            // [REC_GS] G tile landed
-  const uint32_t gempty_bar = bar_base + 112;          // [REC_GS] G tile read by all epilogue warps
+  const uint32_t outfree_bar = bar_base + 96;          // staging buffer read by the storing warps (one item deep)
   const uint32_t tfull_bar = bar_base + 128;           // [2] accumulator complete
   const uint32_t done_bar = bar_base + 144;            // [2] item finished by all epilogue warps (frees the accumulator)
   const uint32_t staged_bar = bar_base + 160;          // [2] h / y rows of the item staged in shared memory
@@ -101,7 +105,8 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   const uint32_t tmem_slot = bar_base + 184;
   const uint32_t done_cnt = bar_base + 192;            // [2] u32: monotonic "stores issued" counters for the publisher
   int* s_steps = reinterpret_cast<int*>(smem_gen + S::BAR_OFFSET + 208);   // [REC_MAX_TILES]
-  static_assert(REC_NS * 8 <= 48 && REC_GS * 8 <= 16, "barrier layout");
+  float* s_bias = reinterpret_cast<float*>(smem_gen + S::BIAS_OFFSET);     // [gate][unit of the slice]
+  static_assert(REC_NS * 8 <= 48, "barrier layout");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x;
@@ -112,14 +117,14 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   const bool tracer = p.trace && blockIdx.x == 0 && blockIdx.y == 0;
 
   for (int i = threadIdx.x; i < 1024; i += REC_THREADS) lut[i] = c_rcp_lut[i];
+  if (threadIdx.x < 4 * HS) s_bias[threadIdx.x] = p.bias[(threadIdx.x / HS) * REC_H + blockIdx.x * HS + (threadIdx.x % HS)];
   if (threadIdx.x < REC_MAX_TILES) s_steps[threadIdx.x] = (threadIdx.x < p.num_btiles) ? p.tile_steps[threadIdx.x] : 0;
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_h0); tma_prefetch_desc(&tmap_h);
   }
-  if (warp == 2 && lane == 0) tma_prefetch_desc(&tmap_g);
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < REC_NS; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CS); }
-    for (int i = 0; i < REC_GS; ++i) { mbar_init(gfull_bar + 8 * i, 1); mbar_init(gempty_bar + 8 * i, REC_EPI_WARPS); }
+    mbar_init(outfree_bar, REC_STORE_WARPS);
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull_bar + 8 * i, 1);
       mbar_init(done_bar + 8 * i, REC_EPI_WARPS);
@@ -233,24 +238,6 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
-  } else if (warp == 2) {
-    // ---------------------------------------------------------------- G producer: the tile's input projection does not
-    // depend on h, so it runs ahead of everything else by the depth of its ring (as soon as the epilogue has read a stage)
-    if (lane == 0) {
-      uint32_t gk = 0;
-      ItemCursor cur{0, -1};
-      while (!(p.debug & 64) && cur.next(p.T, my_tiles, by, gy, s_steps)) {
-        const uint32_t st = gk % REC_GS, ph = (gk / REC_GS) & 1u;
-        if (!mbar_wait(gempty_bar + 8 * st, ph ^ 1u, p.status)) break;
-        const int bt = by + cur.i * gy;
-        mbar_expect_tx(gfull_bar + 8 * st, S::G_STAGE);
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          tma_load_3d(smem_g + st * S::G_STAGE + g * S::G_GATE, &tmap_g, gfull_bar + 8 * st, g * REC_H + slice * HS, bt * REC_BM,
-                      cur.t);
-        ++gk;
-      }
-    }
   } else if (warp == 3) {
     // ---------------------------------------------------------------- publisher
     if (lane == 0) {
@@ -283,157 +270,165 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     // ---------------------------------------------------------------- epilogue: gates, cell update, outputs
     const int e = warp - REC_CTRL_WARPS;
     const int q = warp & 3;                 // TMEM lane quarter accessible to this warp (warp id % 4)
-    const int ug = e >> 2;                  // unit group within the slice (4 units each)
+    const int ug = e >> 2;                  // unit group within the slice (8 units each, processed as two quads)
     const int row = q * 32 + lane;          // batch row within the tile
-    const int j0 = slice * HS + ug * 4;     // first hidden unit of this thread
+    const int j0 = slice * HS + ug * 8;     // first hidden unit of this thread
     const bool storer = e < REC_STORE_WARPS;
     const HalfConsts k = make_half_consts();
     const __half2 in_s = __float2half2_rn(p.in_scale), out_s = __float2half2_rn(p.out_scale);
     const bool same_scale = h2_bits(in_s) == h2_bits(out_s);
-    float bias[4][4];
-#pragma unroll
-    for (int g = 0; g < 4; ++g)
-#pragma unroll
-      for (int u = 0; u < 4; ++u) bias[g][u] = p.bias[g * REC_H + j0 + u];
-    const uint32_t g_off = (uint32_t)(row * 64 + ((ug ^ ((row >> 1) & 3)) << 4));   // SWIZZLE_64B position of this thread's 16 B
+    const uint32_t bias_s = smem_base + S::BIAS_OFFSET + (uint32_t)(ug * 8) * 4u;
 
     // c of an item: t == 0 from the caller's cx, else from the blocked scratch this same thread wrote one step earlier.
     // It is fetched one item ahead (cn) so that its L2 latency hides behind the previous item's gate math; when the next
     // item is the same tile (a CTA with one live tile) the freshly computed value is carried in registers instead.
-    auto load_c = [&](int t_, int bt_, uint32_t (&c)[2]) {
+    auto c_scratch = [&](int bt_) {
+      return p.c_ws + ((((size_t)bt_ * (REC_H / HS) + slice) * 4 + ug) * REC_BM + row) * 8;
+    };
+    auto load_c = [&](int t_, int bt_, uint4& c) {
       if (t_ == 0) {
         const int n_ = bt_ * REC_BM + row;
-        if (n_ < p.N) {
-          const uint2 v = *reinterpret_cast<const uint2*>(p.cx + (size_t)n_ * REC_H + j0);
-          c[0] = v.x; c[1] = v.y;
-        } else {
-          c[0] = 0u; c[1] = 0u;
-        }
+        c = (n_ < p.N) ? *reinterpret_cast<const uint4*>(p.cx + (size_t)n_ * REC_H + j0) : make_uint4(0u, 0u, 0u, 0u);
       } else {
-        const uint2 v = *reinterpret_cast<const uint2*>(p.c_ws + ((((size_t)bt_ * 64 + slice) * 4 + ug) * REC_BM + row) * 4);
-        c[0] = v.x; c[1] = v.y;
+        c = *reinterpret_cast<const uint4*>(c_scratch(bt_));
       }
     };
-    int acc = 0; uint32_t acc_phase = 0;
+    int acc = 0; uint32_t acc_phase = 0, item = 0;
     ItemCursor cur{0, -1}, nxt{0, -1};
     bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
     bool have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);     // nxt runs one item ahead of cur
     if (have_next) have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);
-    uint32_t cn[2] = {0u, 0u};
+    uint4 cn = make_uint4(0u, 0u, 0u, 0u);
     if (have) load_c(cur.t, by + cur.i * gy, cn);
-    for (; have; have = cur.next(p.T, my_tiles, by, gy, s_steps)) {
+    for (; have; have = cur.next(p.T, my_tiles, by, gy, s_steps), ++item) {
       const int t = cur.t, bt = by + cur.i * gy;
       const int steps = s_steps[bt];
       const int n = bt * REC_BM + row;
       const bool valid = n < p.N;
-      uint32_t cbits[2] = {cn[0], cn[1]};
+      uint32_t cbits[4] = {cn.x, cn.y, cn.z, cn.w};
       const bool carry = have_next && (by + nxt.i * gy) == bt;       // next item = next step of this very tile
       if (have_next && !carry && !(p.debug & 128)) load_c(nxt.t, by + nxt.i * gy, cn);
       const bool tr = tracer && cur.i == 0 && e == 0 && lane == 0;
-      // ---- operands that do not depend on the recurrent product
-      int gi[4][4];
-      if (!(p.debug & 64)) {
-        const long long g0 = tr ? clock64() : 0;
-        if (!mbar_wait(gfull_bar + 8 * acc, acc_phase, p.status)) break;      // G ring stage == accumulator parity
-        if (tr) p.trace[t * 16 + 10] = clock64() - g0;
+      // ---- operands that do not depend on the recurrent product: this row's input projection, one sector per gate
+      int gi[4][8];
+      if (valid && !(p.debug & 64)) {
+        const int32_t* gp = p.g + ((size_t)t * p.N + n) * (4 * REC_H) + j0;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const uint4 v = lds128(smem_g + acc * S::G_STAGE + g * S::G_GATE + g_off);
-          gi[g][0] = (int)v.x; gi[g][1] = (int)v.y; gi[g][2] = (int)v.z; gi[g][3] = (int)v.w;
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(gempty_bar + 8 * acc);
+        for (int g = 0; g < 4; ++g) ldg256_stream(gp + g * REC_H, gi[g]);
       } else {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) { gi[g][0] = t; gi[g][1] = n; gi[g][2] = g; gi[g][3] = lane; }
+        for (int g = 0; g < 4; ++g)
+#pragma unroll
+          for (int u = 0; u < 8; ++u) gi[g][u] = 0;
       }
-      uint16_t* c_blk = p.c_ws + ((((size_t)bt * 64 + slice) * 4 + ug) * REC_BM + row) * 4;
 
       const long long f0 = tr ? clock64() : 0;
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
       if (tr) { p.trace[t * 16 + 3] = clock64(); p.trace[t * 16 + 11] = clock64() - f0; }
       tc_fence_after();
-      uint32_t a[4][4];
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * 4);
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * 8);
+      uint32_t hq_pack[2] = {0u, 0u}, yq_pack[2] = {0u, 0u};
+      uint32_t ybf[4];
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
-        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
-                     : "=r"(a[g][0]), "=r"(a[g][1]), "=r"(a[g][2]), "=r"(a[g][3])
-                     : "r"(t_row + g * HS) : "memory");
-      tmem_ld_wait();
-      tc_fence_before();
-      if (tr) p.trace[t * 16 + 4] = clock64();
-
-      uint32_t hq_pack = 0, yq_pack = 0;
-      uint32_t ybf[2];
-#pragma unroll
-      for (int u = 0; u < 4; u += 2) {
-        if (p.debug & 2) { hq_pack ^= a[0][u] + gi[1][u]; yq_pack = hq_pack; ybf[u / 2] = hq_pack; continue; }
-        __half2 gate[4];
+      for (int half = 0; half < 2; ++half) {
+        uint32_t a[4][4];
 #pragma unroll
         for (int g = 0; g < 4; ++g)
-          gate[g] = __floats2half2_rn(dequant_gate((int)a[g][u], gi[g][u], bias[g][u], p.rb_scale),
-                                      dequant_gate((int)a[g][u + 1], gi[g][u + 1], bias[g][u + 1], p.rb_scale));
-        const __half2 it_ = sigmoid_tab2(gate[0], k, tab);
-        const __half2 ft_ = sigmoid_tab2(gate[1], k, tab);
-        const __half2 gt_ = tanh_tab2(gate[2], tab);
-        const __half2 ot_ = sigmoid_tab2(gate[3], k, tab);
-        const __half2 c_old = bits_h2(cbits[u / 2]);
-        const __half2 c_new = __hfma2(it_, gt_, __hmul2_rn(ft_, c_old));     // c = fma(i, g, f*c)
-        cbits[u / 2] = h2_bits(c_new);
-        const __half2 ht = __hmul2_rn(ot_, tanh_tab2(c_new, tab));
-        const uint32_t hq = quant_ph2(ht, in_s);
-        hq_pack |= hq << (8 * u);
-        if (p.skip_quant_y) {
-          const float2 hf = __half22float2(ht);
-          ybf[u / 2] = float_to_bf16_bits(hf.x) | (float_to_bf16_bits(hf.y) << 16);
-        } else {
-          yq_pack |= (same_scale ? hq : quant_ph2(ht, out_s)) << (8 * u);
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(a[g][0]), "=r"(a[g][1]), "=r"(a[g][2]), "=r"(a[g][3])
+                       : "r"(t_row + g * HS + half * 4) : "memory");
+        tmem_ld_wait();
+        if (half == 1) tc_fence_before();
+        if (tr && half == 0) p.trace[t * 16 + 4] = clock64();
+#pragma unroll
+        for (int u = 0; u < 4; u += 2) {
+          const int uu = half * 4 + u;
+          if (p.debug & 2) { hq_pack[half] ^= a[0][u] + gi[1][uu]; yq_pack[half] = hq_pack[half]; ybf[uu / 2] = hq_pack[half]; continue; }
+          __half2 gate[4];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const uint2 bb = lds64(bias_s + (uint32_t)(g * HS + uu) * 4u);
+            gate[g] = __floats2half2_rn(dequant_gate((int)a[g][u], gi[g][uu], __uint_as_float(bb.x), p.rb_scale),
+                                        dequant_gate((int)a[g][u + 1], gi[g][uu + 1], __uint_as_float(bb.y), p.rb_scale));
+          }
+          const __half2 it_ = sigmoid_tab2(gate[0], k, tab);
+          const __half2 ft_ = sigmoid_tab2(gate[1], k, tab);
+          const __half2 gt_ = tanh_tab2(gate[2], tab);
+          const __half2 ot_ = sigmoid_tab2(gate[3], k, tab);
+          const __half2 c_old = bits_h2(cbits[uu / 2]);
+          const __half2 c_new = __hfma2(it_, gt_, __hmul2_rn(ft_, c_old));     // c = fma(i, g, f*c)
+          cbits[uu / 2] = h2_bits(c_new);
+          const __half2 ht = __hmul2_rn(ot_, tanh_tab2(c_new, tab));
+          const uint32_t hq = quant_ph2(ht, in_s);
+          hq_pack[half] |= hq << (8 * u);
+          if (p.skip_quant_y) {
+            const float2 hf = __half22float2(ht);
+            ybf[uu / 2] = float_to_bf16_bits(hf.x) | (float_to_bf16_bits(hf.y) << 16);
+          } else {
+            yq_pack[half] |= (same_scale ? hq : quant_ph2(ht, out_s)) << (8 * u);
+          }
         }
       }
-      // ---- c: final value to the caller's array, otherwise to the CTA-private blocked scratch (coalesced 256 B per warp)
+      // ---- c: final value to the caller's array, otherwise to the CTA-private blocked scratch (coalesced 512 B per warp)
       const bool last = t + 1 == steps;
+      const uint4 cv = make_uint4(cbits[0], cbits[1], cbits[2], cbits[3]);
       if (last) {
-        if (valid) *reinterpret_cast<uint2*>(p.cx + (size_t)n * REC_H + j0) = make_uint2(cbits[0], cbits[1]);
+        if (valid) *reinterpret_cast<uint4*>(p.cx + (size_t)n * REC_H + j0) = cv;
       } else if (carry) {
-        cn[0] = cbits[0]; cn[1] = cbits[1];
+        cn = cv;
       } else if (!(p.debug & 8)) {
-        *reinterpret_cast<uint2*>(c_blk) = make_uint2(cbits[0], cbits[1]);
+        *reinterpret_cast<uint4*>(c_scratch(bt)) = cv;
       }
-      // ---- stage h_{t+1} and y[t] as [ug][row] so that four warps can write whole 16 / 32-byte row segments
-      const uint32_t out_h = smem_out + acc * S::OUT_STAGE, out_y = out_h + S::OUT_H;
-      sts32(out_h + (uint32_t)(ug * REC_BM + row) * 4u, hq_pack);
-      if (p.skip_quant_y) sts64(out_y + (uint32_t)(ug * REC_BM + row) * 8u, ybf[0], ybf[1]);
-      else sts32(out_y + (uint32_t)(ug * REC_BM + row) * 4u, yq_pack);
+      // ---- stage h_{t+1} and y[t] as [unit quad][row] so that four warps can write whole 32 / 64-byte row segments.
+      // The staging buffer is one item deep: wait until the storing warps have read the previous item out of it.
+      if (!mbar_wait(outfree_bar, (item & 1u) ^ 1u, p.status)) break;
+      const uint32_t out_h = smem_out, out_y = out_h + S::OUT_H;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const uint32_t slot = (uint32_t)((ug * 2 + half) * REC_BM + row);
+        sts32(out_h + slot * 4u, hq_pack[half]);
+        if (p.skip_quant_y) sts64(out_y + slot * 8u, ybf[half * 2], ybf[half * 2 + 1]);
+        else sts32(out_y + slot * 4u, yq_pack[half]);
+      }
       __syncwarp();
       if (lane == 0) mbar_arrive(staged_bar + 8 * acc);
       if (storer) {
         const long long s0 = tr ? clock64() : 0;
         if (!mbar_wait(staged_bar + 8 * acc, acc_phase, p.status)) break;
         if (tr) p.trace[t * 16 + 12] = clock64() - s0;
-        uint4 hv;
-        hv.x = lds32(out_h + (uint32_t)(0 * REC_BM + row) * 4u); hv.y = lds32(out_h + (uint32_t)(1 * REC_BM + row) * 4u);
-        hv.z = lds32(out_h + (uint32_t)(2 * REC_BM + row) * 4u); hv.w = lds32(out_h + (uint32_t)(3 * REC_BM + row) * 4u);
+        uint32_t hw[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) hw[i] = lds32(out_h + (uint32_t)(i * REC_BM + row) * 4u);
+        uint32_t yw[16];
+        if (p.skip_quant_y) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { const uint2 v = lds64(out_y + (uint32_t)(i * REC_BM + row) * 8u); yw[2 * i] = v.x; yw[2 * i + 1] = v.y; }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) yw[i] = lds32(out_y + (uint32_t)(i * REC_BM + row) * 4u);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(outfree_bar);
         if (!last) {
-          int8_t* hn = p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 3)) * REC_BM + row) * 128 +
-                       (slice & 7) * 16;
-          *reinterpret_cast<uint4*>(hn) = hv;
+          int8_t* hn = p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 2)) * REC_BM + row) * 128 +
+                       (slice & 3) * HS;
+          reinterpret_cast<uint4*>(hn)[0] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+          reinterpret_cast<uint4*>(hn)[1] = make_uint4(hw[4], hw[5], hw[6], hw[7]);
         } else if (valid) {   // last step of this tile: hand the state back to the caller's hx
-          *reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS) = hv;
+          uint4* hp = reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS);
+          hp[0] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+          hp[1] = make_uint4(hw[4], hw[5], hw[6], hw[7]);
         }
         if (valid && !(p.debug & 8)) {
           const size_t yoff = ((size_t)t * p.N + n) * REC_H + slice * HS;
           if (p.skip_quant_y) {
-            uint2 y0 = lds64(out_y + (uint32_t)(0 * REC_BM + row) * 8u), y1 = lds64(out_y + (uint32_t)(1 * REC_BM + row) * 8u);
-            uint2 y2 = lds64(out_y + (uint32_t)(2 * REC_BM + row) * 8u), y3 = lds64(out_y + (uint32_t)(3 * REC_BM + row) * 8u);
             uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
-            yp[0] = make_uint4(y0.x, y0.y, y1.x, y1.y);
-            yp[1] = make_uint4(y2.x, y2.y, y3.x, y3.y);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) yp[i] = make_uint4(yw[4 * i], yw[4 * i + 1], yw[4 * i + 2], yw[4 * i + 3]);
           } else {
-            uint4 yv;
-            yv.x = lds32(out_y + (uint32_t)(0 * REC_BM + row) * 4u); yv.y = lds32(out_y + (uint32_t)(1 * REC_BM + row) * 4u);
-            yv.z = lds32(out_y + (uint32_t)(2 * REC_BM + row) * 4u); yv.w = lds32(out_y + (uint32_t)(3 * REC_BM + row) * 4u);
-            *reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff) = yv;
+            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff);
+            yp[0] = make_uint4(yw[0], yw[1], yw[2], yw[3]);
+            yp[1] = make_uint4(yw[4], yw[5], yw[6], yw[7]);
           }
         }
         if (tr) p.trace[t * 16 + 5] = clock64();
@@ -441,7 +436,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (lane == 0) red_release_cta_shared_inc(done_cnt + 4 * acc);   // publisher: this warp's rows are written
       }
       // item finished by this warp.  A warp can be at most one item ahead of the slowest one (the next-but-one MMA waits
-      // on done_bar), so barriers / counters / staging buffers indexed by item parity suffice.
+      // on done_bar), so barriers / counters indexed by item parity suffice.
       __syncwarp();
       if (lane == 0) mbar_arrive(done_bar + 8 * acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
@@ -457,8 +452,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
 
 #define RNNT_REC_INST(CS)                                                                                            \
   template __global__ void lstm_recurrent_kernel<CS>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
-                                                     const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
-                                                     const RecParams);
+                                                     const __grid_constant__ CUtensorMap, const RecParams);
 RNNT_REC_INST(1) RNNT_REC_INST(2) RNNT_REC_INST(4) RNNT_REC_INST(8)
 
 }  // namespace rnnt
