@@ -92,13 +92,16 @@ __device__ __forceinline__ __half2 sigmoid_tab2(__half2 x, const HalfConsts& k, 
 
 // _mm512_scale_min128max_i8_ph: fp16 multiply by the fp16-rounded scale, round to nearest-even integer,
 // min(127), max(-128); returns the two int8 values in the low 16 bits (byte0 = .x, byte1 = .y).
+// The clamp bounds are integers and rint is monotonic, so clamping first gives the same result; the clamped value v
+// in [-128, 127] is then rounded by ONE fp16 addition: v + 1536 lies in [1024, 2048) where the spacing is 1, the add
+// rounds to nearest-even exactly like rint (1536 is even, so ties land on the same integers), and the low byte of
+// the sum's mantissa (1536 - 1024 = 512 = 0 mod 256) is the two's-complement int8.
 __device__ __forceinline__ uint32_t quant_ph2(__half2 h, __half2 scale) {
-  __half2 m = h2rint(__hmul2_rn(h, scale));
+  __half2 m = __hmul2_rn(h, scale);
   m = __hmin2(m, __float2half2_rn(127.f));
   m = __hmax2(m, __float2half2_rn(-128.f));
-  const int a = __half2int_rn(__low2half(m));
-  const int b = __half2int_rn(__high2half(m));
-  return ((uint32_t)a & 0xffu) | (((uint32_t)b & 0xffu) << 8);
+  const uint32_t r = h2_bits(__hadd2_rn(m, __float2half2_rn(1536.f)));
+  return __byte_perm(r, 0u, 0x4420);
 }
 
 // dequant_float_out_accum (tpps/tile_product_tpp.hpp:308-345): int32 add FIRST, then cvt, + bias, * scale —

@@ -35,14 +35,6 @@ namespace rnnt {
 
 __constant__ uint16_t c_rcp_lut[1024] = {RNNT_RCP_PH_LUT_VALUES};
 
-__device__ __forceinline__ uint32_t ld_acquire_cta_shared(uint32_t addr) {
-  uint32_t v;
-  asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ void red_release_cta_shared_inc(uint32_t addr) {
-  asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(addr) : "memory");
-}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
@@ -103,7 +95,6 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   const uint32_t staged_bar = bar_base + 160;          // [2] h / y rows of the item staged in shared memory
   const uint32_t wfull_bar = bar_base + 176;
   const uint32_t tmem_slot = bar_base + 184;
-  const uint32_t done_cnt = bar_base + 192;            // [2] u32: monotonic "stores issued" counters for the publisher
   int* s_steps = reinterpret_cast<int*>(smem_gen + S::BAR_OFFSET + 208);   // [REC_MAX_TILES]
   float* s_bias = reinterpret_cast<float*>(smem_gen + S::BIAS_OFFSET);     // [gate][unit of the slice]
   static_assert(REC_NS * 8 <= 48, "barrier layout");
@@ -124,15 +115,13 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < REC_NS; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CS); }
-    mbar_init(outfree_bar, REC_STORE_WARPS);
+    mbar_init(outfree_bar, 2);
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull_bar + 8 * i, 1);
       mbar_init(done_bar + 8 * i, REC_EPI_WARPS);
       mbar_init(staged_bar + 8 * i, REC_EPI_WARPS);
     }
     mbar_init(wfull_bar, 1);
-    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 192) = 0u;
-    *reinterpret_cast<volatile uint32_t*>(smem_gen + S::BAR_OFFSET + 196) = 0u;
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<2 * S::UMMA_N>(tmem_slot);
@@ -166,7 +155,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (t > 0 && !(p.debug & 256)) {
           // wait until every slice CTA has published its part of h_t for this batch tile
           const int* flag = p.flags + bt * REC_FLAG_STRIDE;
-          const int target = t * num_slices;
+          const int target = t * num_slices * 2;      // two storing warps per slice CTA
           long long t0 = clock64(); uint32_t spins = 0;
           for (;;) {
             int v;
@@ -238,33 +227,76 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
-  } else if (warp == 3) {
-    // ---------------------------------------------------------------- publisher
-    if (lane == 0) {
-      uint32_t item = 0; bool ok = true;
-      ItemCursor cur{0, -1};
-      while (ok && cur.next(p.T, my_tiles, by, gy, s_steps)) {
-        const int t = cur.t, bt = by + cur.i * gy;
-        const uint32_t target = REC_STORE_WARPS * (item / 2 + 1);
-        const uint32_t cnt = done_cnt + 4 * (item & 1u);
-        long long t0 = clock64(); uint32_t spins = 0;
-        while (ld_acquire_cta_shared(cnt) < target) {
-          if ((++spins & 255u) == 0) {
-            if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
-            if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_MBAR); ok = false; break; }
+  } else if (warp == 2 || warp == 3) {
+    // ---------------------------------------------------------------- store + publish: each of the two warps writes 64
+    // rows of the staged item (whole 32 / 64-byte row segments) and then publishes them with ONE release increment of
+    // the tile's counter.  Keeping the global stores and their gpu-scope fence off the epilogue warps takes ~1.4k
+    // cycles (the drain of the stores) out of every item's critical path.
+    const int sw = warp - 2;
+    int acc = 0; uint32_t acc_phase = 0;
+    bool ok = true;
+    ItemCursor cur{0, -1};
+    while (ok && cur.next(p.T, my_tiles, by, gy, s_steps)) {
+      const int t = cur.t, bt = by + cur.i * gy;
+      const bool last = t + 1 == s_steps[bt];
+      const bool tr = tracer && cur.i == 0 && sw == 0 && lane == 0;
+      if (!mbar_wait(staged_bar + 8 * acc, acc_phase, p.status)) break;
+      const uint32_t out_h = smem_out, out_y = out_h + S::OUT_H;
+      uint32_t hw[2][8], yw[2][16];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int row = sw * 64 + r * 32 + lane;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) hw[r][i] = lds32(out_h + (uint32_t)(i * REC_BM + row) * 4u);
+        if (p.skip_quant_y) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { const uint2 v = lds64(out_y + (uint32_t)(i * REC_BM + row) * 8u); yw[r][2 * i] = v.x; yw[r][2 * i + 1] = v.y; }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) yw[r][i] = lds32(out_y + (uint32_t)(i * REC_BM + row) * 4u);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(outfree_bar);          // staging buffer may be overwritten by the next item
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int row = sw * 64 + r * 32 + lane;
+        const int n = bt * REC_BM + row;
+        const bool valid = n < p.N;
+        if (!last) {
+          uint4* hn = reinterpret_cast<uint4*>(p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 2)) * REC_BM + row) * 128 +
+                                               (slice & 3) * HS);
+          hn[0] = make_uint4(hw[r][0], hw[r][1], hw[r][2], hw[r][3]);
+          hn[1] = make_uint4(hw[r][4], hw[r][5], hw[r][6], hw[r][7]);
+        } else if (valid) {   // last step of this tile: hand the state back to the caller's hx
+          uint4* hp = reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS);
+          hp[0] = make_uint4(hw[r][0], hw[r][1], hw[r][2], hw[r][3]);
+          hp[1] = make_uint4(hw[r][4], hw[r][5], hw[r][6], hw[r][7]);
+        }
+        if (valid && !(p.debug & 8)) {
+          const size_t yoff = ((size_t)t * p.N + n) * REC_H + slice * HS;
+          if (p.skip_quant_y) {
+            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) yp[i] = make_uint4(yw[r][4 * i], yw[r][4 * i + 1], yw[r][4 * i + 2], yw[r][4 * i + 3]);
+          } else {
+            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff);
+            yp[0] = make_uint4(yw[r][0], yw[r][1], yw[r][2], yw[r][3]);
+            yp[1] = make_uint4(yw[r][4], yw[r][5], yw[r][6], yw[r][7]);
           }
         }
-        if (!ok) break;
-        if (tracer && cur.i == 0) p.trace[t * 16 + 6] = clock64();
-        // h_{t+1}[tile bt][this slice] is written: one release increment of the tile counter (cumulative over the
-        // storing warps' global stores through the shared-memory counter they released)
-        if (t + 1 < s_steps[bt]) {
-          if (p.debug & 16) asm volatile("red.relaxed.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
-          else asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
-        }
-        if (tracer && cur.i == 0) p.trace[t * 16 + 7] = clock64();
-        ++item;
       }
+      if (tr) p.trace[t * 16 + 5] = clock64();
+      __syncwarp();
+      // h_{t+1}[tile bt][this slice][these 64 rows] is written: one release increment of the tile counter (the fence is
+      // cumulative over the other lanes' stores through the warp barrier above)
+      if (lane == 0 && !last) {
+        if (tr) p.trace[t * 16 + 6] = clock64();
+        if (p.debug & 16) asm volatile("red.relaxed.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+        else asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+        if (tr) p.trace[t * 16 + 7] = clock64();
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   } else if (warp >= REC_CTRL_WARPS) {
     // ---------------------------------------------------------------- epilogue: gates, cell update, outputs
@@ -273,7 +305,6 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     const int ug = e >> 2;                  // unit group within the slice (8 units each, processed as two quads)
     const int row = q * 32 + lane;          // batch row within the tile
     const int j0 = slice * HS + ug * 8;     // first hidden unit of this thread
-    const bool storer = e < REC_STORE_WARPS;
     const HalfConsts k = make_half_consts();
     const __half2 in_s = __float2half2_rn(p.in_scale), out_s = __float2half2_rn(p.out_scale);
     const bool same_scale = h2_bits(in_s) == h2_bits(out_s);
@@ -307,11 +338,11 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       const bool valid = n < p.N;
       uint32_t cbits[4] = {cn.x, cn.y, cn.z, cn.w};
       const bool carry = have_next && (by + nxt.i * gy) == bt;       // next item = next step of this very tile
-      if (have_next && !carry && !(p.debug & 128)) load_c(nxt.t, by + nxt.i * gy, cn);
+      if (have_next && !carry) load_c(nxt.t, by + nxt.i * gy, cn);
       const bool tr = tracer && cur.i == 0 && e == 0 && lane == 0;
       // ---- operands that do not depend on the recurrent product: this row's input projection, one sector per gate
       int gi[4][8];
-      if (valid && !(p.debug & 64)) {
+      if (valid) {
         const int32_t* gp = p.g + ((size_t)t * p.N + n) * (4 * REC_H) + j0;
 #pragma unroll
         for (int g = 0; g < 4; ++g) ldg256_stream(gp + g * REC_H, gi[g]);
@@ -329,44 +360,42 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * 8);
       uint32_t hq_pack[2] = {0u, 0u}, yq_pack[2] = {0u, 0u};
       uint32_t ybf[4];
+      // all eight units of the thread at once: four independent (pair) chains keep the table-lookup latency covered
+      __half2 gate[4][4];
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t a[4][4];
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
-                       : "=r"(a[g][0]), "=r"(a[g][1]), "=r"(a[g][2]), "=r"(a[g][3])
-                       : "r"(t_row + g * HS + half * 4) : "memory");
+      for (int g = 0; g < 4; ++g) {
+        uint32_t a[8];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7])
+                     : "r"(t_row + g * HS) : "memory");
         tmem_ld_wait();
-        if (half == 1) tc_fence_before();
-        if (tr && half == 0) p.trace[t * 16 + 4] = clock64();
 #pragma unroll
-        for (int u = 0; u < 4; u += 2) {
-          const int uu = half * 4 + u;
-          if (p.debug & 2) { hq_pack[half] ^= a[0][u] + gi[1][uu]; yq_pack[half] = hq_pack[half]; ybf[uu / 2] = hq_pack[half]; continue; }
-          __half2 gate[4];
+        for (int pr = 0; pr < 4; ++pr) {
+          const uint2 bb = lds64(bias_s + (uint32_t)(g * HS + 2 * pr) * 4u);
+          gate[g][pr] = __floats2half2_rn(dequant_gate((int)a[2 * pr], gi[g][2 * pr], __uint_as_float(bb.x), p.rb_scale),
+                                          dequant_gate((int)a[2 * pr + 1], gi[g][2 * pr + 1], __uint_as_float(bb.y), p.rb_scale));
+        }
+      }
+      tc_fence_before();
+      if (tr) p.trace[t * 16 + 4] = clock64();
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const uint2 bb = lds64(bias_s + (uint32_t)(g * HS + uu) * 4u);
-            gate[g] = __floats2half2_rn(dequant_gate((int)a[g][u], gi[g][uu], __uint_as_float(bb.x), p.rb_scale),
-                                        dequant_gate((int)a[g][u + 1], gi[g][uu + 1], __uint_as_float(bb.y), p.rb_scale));
-          }
-          const __half2 it_ = sigmoid_tab2(gate[0], k, tab);
-          const __half2 ft_ = sigmoid_tab2(gate[1], k, tab);
-          const __half2 gt_ = tanh_tab2(gate[2], tab);
-          const __half2 ot_ = sigmoid_tab2(gate[3], k, tab);
-          const __half2 c_old = bits_h2(cbits[uu / 2]);
-          const __half2 c_new = __hfma2(it_, gt_, __hmul2_rn(ft_, c_old));     // c = fma(i, g, f*c)
-          cbits[uu / 2] = h2_bits(c_new);
-          const __half2 ht = __hmul2_rn(ot_, tanh_tab2(c_new, tab));
-          const uint32_t hq = quant_ph2(ht, in_s);
-          hq_pack[half] |= hq << (8 * u);
-          if (p.skip_quant_y) {
-            const float2 hf = __half22float2(ht);
-            ybf[uu / 2] = float_to_bf16_bits(hf.x) | (float_to_bf16_bits(hf.y) << 16);
-          } else {
-            yq_pack[half] |= (same_scale ? hq : quant_ph2(ht, out_s)) << (8 * u);
-          }
+      for (int pr = 0; pr < 4; ++pr) {
+        const int half = pr >> 1, u = (pr & 1) * 2;
+        const __half2 it_ = sigmoid_tab2(gate[0][pr], k, tab);
+        const __half2 ft_ = sigmoid_tab2(gate[1][pr], k, tab);
+        const __half2 gt_ = tanh_tab2(gate[2][pr], tab);
+        const __half2 ot_ = sigmoid_tab2(gate[3][pr], k, tab);
+        const __half2 c_old = bits_h2(cbits[pr]);
+        const __half2 c_new = __hfma2(it_, gt_, __hmul2_rn(ft_, c_old));     // c = fma(i, g, f*c)
+        cbits[pr] = h2_bits(c_new);
+        const __half2 ht = __hmul2_rn(ot_, tanh_tab2(c_new, tab));
+        const uint32_t hq = quant_ph2(ht, in_s);
+        hq_pack[half] |= hq << (8 * u);
+        if (p.skip_quant_y) {
+          const float2 hf = __half22float2(ht);
+          ybf[pr] = float_to_bf16_bits(hf.x) | (float_to_bf16_bits(hf.y) << 16);
+        } else {
+          yq_pack[half] |= (same_scale ? hq : quant_ph2(ht, out_s)) << (8 * u);
         }
       }
       // ---- c: final value to the caller's array, otherwise to the CTA-private blocked scratch (coalesced 512 B per warp)
@@ -376,7 +405,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (valid) *reinterpret_cast<uint4*>(p.cx + (size_t)n * REC_H + j0) = cv;
       } else if (carry) {
         cn = cv;
-      } else if (!(p.debug & 8)) {
+      } else {
         *reinterpret_cast<uint4*>(c_scratch(bt)) = cv;
       }
       // ---- stage h_{t+1} and y[t] as [unit quad][row] so that four warps can write whole 32 / 64-byte row segments.
@@ -392,49 +421,6 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(staged_bar + 8 * acc);
-      if (storer) {
-        const long long s0 = tr ? clock64() : 0;
-        if (!mbar_wait(staged_bar + 8 * acc, acc_phase, p.status)) break;
-        if (tr) p.trace[t * 16 + 12] = clock64() - s0;
-        uint32_t hw[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) hw[i] = lds32(out_h + (uint32_t)(i * REC_BM + row) * 4u);
-        uint32_t yw[16];
-        if (p.skip_quant_y) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) { const uint2 v = lds64(out_y + (uint32_t)(i * REC_BM + row) * 8u); yw[2 * i] = v.x; yw[2 * i + 1] = v.y; }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) yw[i] = lds32(out_y + (uint32_t)(i * REC_BM + row) * 4u);
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(outfree_bar);
-        if (!last) {
-          int8_t* hn = p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 2)) * REC_BM + row) * 128 +
-                       (slice & 3) * HS;
-          reinterpret_cast<uint4*>(hn)[0] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-          reinterpret_cast<uint4*>(hn)[1] = make_uint4(hw[4], hw[5], hw[6], hw[7]);
-        } else if (valid) {   // last step of this tile: hand the state back to the caller's hx
-          uint4* hp = reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS);
-          hp[0] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-          hp[1] = make_uint4(hw[4], hw[5], hw[6], hw[7]);
-        }
-        if (valid && !(p.debug & 8)) {
-          const size_t yoff = ((size_t)t * p.N + n) * REC_H + slice * HS;
-          if (p.skip_quant_y) {
-            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) yp[i] = make_uint4(yw[4 * i], yw[4 * i + 1], yw[4 * i + 2], yw[4 * i + 3]);
-          } else {
-            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff);
-            yp[0] = make_uint4(yw[0], yw[1], yw[2], yw[3]);
-            yp[1] = make_uint4(yw[4], yw[5], yw[6], yw[7]);
-          }
-        }
-        if (tr) p.trace[t * 16 + 5] = clock64();
-        __syncwarp();
-        if (lane == 0) red_release_cta_shared_inc(done_cnt + 4 * acc);   // publisher: this warp's rows are written
-      }
       // item finished by this warp.  A warp can be at most one item ahead of the slowest one (the next-but-one MMA waits
       // on done_bar), so barriers / counters indexed by item parity suffice.
       __syncwarp();
