@@ -11,7 +11,7 @@
 namespace rnnt {
 
 // device-side error codes written to the per-launch status word
-enum : int { DEV_OK = 0, DEV_TIMEOUT_MBAR = 101, DEV_TIMEOUT_FLAG = 102, DEV_ABORTED = 103 };
+enum : int { DEV_OK = 0, DEV_TIMEOUT_MBAR = 101, DEV_TIMEOUT_FLAG = 102, DEV_ABORTED = 103, DEV_BAD_SMEM = 104 };
 
 constexpr long long kWatchdogCycles = 4000000000ll;  // ~2 s at 2 GHz
 

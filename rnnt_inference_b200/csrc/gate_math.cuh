@@ -78,11 +78,12 @@ __device__ __forceinline__ __half2 sigmoid_ph2(__half2 x, const HalfConsts& k, c
 // produced by finite accumulators) would map to +-1 instead of NaN.
 __device__ __forceinline__ __half2 tanh_tab2(__half2 x, uint32_t tab_smem) {
   const uint32_t b = h2_bits(x);
-  const uint32_t idx = __vminu2(b & 0x7fff7fffu, 0x44f944f9u);
+  uint32_t idx = __vminu2(b & 0x7fff7fffu, 0x44f944f9u);
+  idx += idx;                                   // byte offsets of both halves at once (each < 0x8000: no carry across)
   uint32_t lo, hi;
-  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(lo) : "r"(tab_smem + ((idx & 0xffffu) << 1)));
-  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(hi) : "r"(tab_smem + ((idx >> 16) << 1)));
-  return bits_h2((lo | (hi << 16)) | (b & 0x80008000u));
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(lo) : "r"(tab_smem + (idx & 0xffffu)));
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(hi) : "r"(tab_smem + (idx >> 16)));
+  return bits_h2(__byte_perm(lo, hi, 0x5410) | (b & 0x80008000u));
 }
 __device__ __forceinline__ __half2 sigmoid_tab2(__half2 x, const HalfConsts& k, uint32_t tab_smem) {
   __half2 r = tanh_tab2(__hmul2_rn(k.half, x), tab_smem);

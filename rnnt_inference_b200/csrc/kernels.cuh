@@ -71,7 +71,7 @@ struct RecSmem {
   static constexpr int TAB_OFFSET = BIAS_OFFSET + 512;               // whole-function table of the Pade tanh kernel
   static constexpr int TAB_BYTES = (REC_TAB_N * 2 + 15) / 16 * 16;   // 35,328
   static constexpr int BAR_OFFSET = TAB_OFFSET + TAB_BYTES;
-  static constexpr int TOTAL = BAR_OFFSET + 512 + 1024;   // barriers/counters + alignment slack
+  static constexpr int TOTAL = BAR_OFFSET + 512;          // barriers/counters (the window itself is 1024-byte aligned)
 };
 static_assert(RecSmem::TOTAL <= 232448, "recurrent kernel shared memory");
 

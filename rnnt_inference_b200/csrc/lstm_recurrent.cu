@@ -78,9 +78,15 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   using S = RecSmem;
   constexpr int HS = REC_HS;
   constexpr uint16_t MC_MASK = (uint16_t)((1u << CS) - 1u);
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  // 1024-byte alignment is declared (the dynamic window starts on such a boundary) rather than fixed up at run time, so
+  // every shared-memory address below is base-constant + offset and folds into the instructions' immediate fields.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = smem_u32(smem_raw);
+  uint8_t* smem_gen = smem_raw;
+  if (smem_base & 1023u) {          // never observed; uniform over the grid, so every CTA leaves before any barrier
+    if (threadIdx.x == 0) atomicCAS(p.status, DEV_OK, DEV_BAD_SMEM);
+    return;
+  }
   const uint32_t smem_w = smem_base;
   const uint32_t smem_h = smem_base + S::W_BYTES;
   const uint32_t smem_out = smem_base + S::OUT_OFFSET;
@@ -324,6 +330,22 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         c = *reinterpret_cast<const uint4*>(c_scratch(bt_));
       }
     };
+    // G of an item (this row's input projection, one full sector per gate) does not depend on the recurrent product: it
+    // is requested before the wait for the accumulator.  (Fetching it a whole item ahead was measured slower.)
+    int gi[4][8];
+    auto load_g = [&](int t_, int bt_) {
+      const int n_ = bt_ * REC_BM + row;
+      if (n_ < p.N && !(p.debug & 64)) {
+        const int32_t* gp = p.g + ((size_t)t_ * p.N + n_) * (4 * REC_H) + j0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) ldg256_stream(gp + g * REC_H, gi[g]);
+      } else {
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+#pragma unroll
+          for (int u = 0; u < 8; ++u) gi[g][u] = 0;
+      }
+    };
     int acc = 0; uint32_t acc_phase = 0, item = 0;
     ItemCursor cur{0, -1}, nxt{0, -1};
     bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
@@ -340,19 +362,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       const bool carry = have_next && (by + nxt.i * gy) == bt;       // next item = next step of this very tile
       if (have_next && !carry) load_c(nxt.t, by + nxt.i * gy, cn);
       const bool tr = tracer && cur.i == 0 && e == 0 && lane == 0;
-      // ---- operands that do not depend on the recurrent product: this row's input projection, one sector per gate
-      int gi[4][8];
-      if (valid) {
-        const int32_t* gp = p.g + ((size_t)t * p.N + n) * (4 * REC_H) + j0;
-#pragma unroll
-        for (int g = 0; g < 4; ++g) ldg256_stream(gp + g * REC_H, gi[g]);
-      } else {
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-#pragma unroll
-          for (int u = 0; u < 8; ++u) gi[g][u] = 0;
-      }
-
+      load_g(t, bt);
       const long long f0 = tr ? clock64() : 0;
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
       if (tr) { p.trace[t * 16 + 3] = clock64(); p.trace[t * 16 + 11] = clock64() - f0; }

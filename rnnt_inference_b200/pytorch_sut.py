@@ -76,7 +76,7 @@ class PytorchSUT:
     # --------------------------------------------------------------------------------------------- LoadGen entry
     def issue_queries(self, samples):
         if self.batch_sort:
-            samples.sort(key=lambda s: int(self.qsl[s.index][1]), reverse=True)
+            samples.sort(key=lambda s: self.qsl.sort_key(s.index))
         chunks = [samples[i:i + self.batch_size] for i in range(0, len(samples), self.batch_size)]
         if not self.pipelined:
             for chunk in chunks:
@@ -129,10 +129,25 @@ class PytorchSUT:
                 grow = max(total, self.batch_size * 512)
                 buf = torch.empty((grow, feats[0].shape[1]), dtype=torch.float32, device=dev)
                 self._packed[slot] = buf
-            off = 0
-            for f, n in zip(feats, lens):
-                buf[off:off + n].copy_(f, non_blocking=True)
-                off += n
+            # one DMA per run of samples that are neighbours in the QSL's pinned arena (a sorted Offline query: one run
+            # per batch); samples outside the arena are copied one by one
+            arena, aoff = self.qsl.arena, self.qsl.arena_off
+            off = i = 0
+            while i < len(chunk):
+                start = aoff.get(chunk[i].index) if arena is not None else None
+                if start is None:
+                    buf[off:off + lens[i]].copy_(feats[i], non_blocking=True)
+                    off += lens[i]
+                    i += 1
+                    continue
+                rows = lens[i]
+                j = i + 1
+                while j < len(chunk) and aoff.get(chunk[j].index) == start + rows:
+                    rows += lens[j]
+                    j += 1
+                buf[off:off + rows].copy_(arena[start:start + rows], non_blocking=True)
+                off += rows
+                i = j
             meta_host = meta.pin_memory()
             b.meta = meta_host.to(dev, non_blocking=True)
             b.packed = buf

@@ -1,7 +1,10 @@
 """Query sample library (reference: models/rnnt_qsl.py:5-34).
 
 Holds the pre-extracted features in host memory — page-locked when a GPU is present, so that the per-batch
-host->device copies of the SUT are asynchronous DMA.  `dataset_dir` is the reference's on-disk format, a torch-saved
+host->device copies of the SUT are asynchronous DMA.  The page-locked copy is ONE arena in which the loaded samples
+lie longest first (ties by sample id): an Offline query sorted by length then reads contiguous arena ranges, so the
+SUT moves a whole batch with a single DMA instead of one per sample.  Samples are still handed out one by one
+(`qsl[i]` -> (features view, length)), exactly as the reference does.  `dataset_dir` is the reference's on-disk format, a torch-saved
 dict {"x": [T_i x 240 fp32 tensors], "x_lens": [int tensors]} (datasets/convert_librispeech.py:135-163), or that
 dict itself.
 """
@@ -22,28 +25,43 @@ class RNNTQSL:
         self.count = len(self.dataset[0])
         perf_count = self.count if perf_count is None else perf_count
         self.pin_memory = torch.cuda.is_available() if pin_memory is None else pin_memory
-        self._pinned = {}                        # id(tensor) -> pinned copy (replicated samples share storage)
+        self.arena = None                        # pinned [sum T_i, 240] fp32, samples longest first
+        self.arena_off = {}                      # sample id -> first arena row
         self.sample_id_to_sample = {}
         self.qsl = lg.ConstructQSL(self.count, perf_count, self.load_query_samples, self.unload_query_samples)
         self.load_query_samples(range(self.count))
 
     def load_query_samples(self, sample_list):
-        for sample_id in sample_list:
-            if sample_id not in self.sample_id_to_sample:
-                self.sample_id_to_sample[sample_id] = self._load_sample(sample_id)
+        new = [i for i in sample_list if i not in self.sample_id_to_sample]
+        for sample_id in new:
+            self.sample_id_to_sample[sample_id] = (self.dataset[0][sample_id], self.dataset[1][sample_id])
+        if new and self.pin_memory:
+            self._build_arena()
 
     def unload_query_samples(self, sample_list):
         for sample_id in sample_list:
             self.sample_id_to_sample.pop(sample_id, None)
+            self.arena_off.pop(sample_id, None)
 
-    def _load_sample(self, index):
-        x, x_len = self.dataset[0][index], self.dataset[1][index]
-        if self.pin_memory:
-            key = id(x)
-            if key not in self._pinned:
-                self._pinned[key] = x.contiguous().pin_memory()
-            x = self._pinned[key]
-        return (x, x_len)
+    def _build_arena(self):
+        """(Re)pack every loaded sample into one page-locked arena, longest first.  Runs when samples are loaded, i.e.
+        outside LoadGen's timed region (LoadSamplesToRam)."""
+        ids = sorted(self.sample_id_to_sample, key=lambda i: (-int(self.dataset[1][i]), i))
+        rows = [int(self.dataset[0][i].shape[0]) for i in ids]
+        width = int(self.dataset[0][ids[0]].shape[1])
+        arena = torch.empty((sum(rows), width), dtype=torch.float32, pin_memory=True)
+        off = 0
+        for i, n in zip(ids, rows):
+            arena[off:off + n].copy_(self.dataset[0][i])
+            self.arena_off[i] = off
+            self.sample_id_to_sample[i] = (arena[off:off + n], self.dataset[1][i])
+            off += n
+        self.arena = arena
+
+    def sort_key(self, index):
+        """Offline sort key: feature length descending (pytorch_sut.py:58-65); equal lengths in arena order, so that a
+        sorted query walks the arena front to back."""
+        return (-int(self.dataset[1][index]), self.arena_off.get(index, index))
 
     def __getitem__(self, index):
         return self.sample_id_to_sample[index]
