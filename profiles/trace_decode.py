@@ -55,3 +55,9 @@ if len(l0):
           (np.median(l0[:, 12] - l0[:, 0]), np.median(l0[:, 13] - l0[:, 12]), np.median(l0[:, 1] - l0[:, 13])))
 per = np.diff(tr[:, 0])
 print("iteration period (cycles): median %.0f mean %.0f" % (np.median(per), per.mean()))
+print("iteration period quantiles 10/25/50/75/90/99:", [int(x) for x in np.percentile(per, [10, 25, 50, 75, 90, 99])])
+print("active lanes (group 0) quantiles 10/50/90/max:", [int(x) for x in np.percentile(tr[:, 7], [10, 50, 90, 100])])
+for lo, hi in ((0, 0), (1, 4), (5, 12), (13, 24), (25, 48), (49, 200)):
+    m = (tr[1:, 7] >= lo) & (tr[1:, 7] <= hi)
+    if m.any():
+        print("  lanes %3d..%3d: %4d iterations, mean period %.0f cycles" % (lo, hi, m.sum(), per[m[:len(per)]].mean() if len(per) == len(m) else per[m[:-1]].mean()))

@@ -189,14 +189,15 @@ class PytorchSUT:
         self._respond(b.samples, tokens, lens)
 
     def _respond(self, samples, tokens, lens):
-        """query_samples_complete (pytorch_sut.py:107-118) on host arrays: pointer into the row, n_tokens * 4 bytes."""
+        """query_samples_complete (pytorch_sut.py:107-118) on host arrays: one QuerySampleResponse per sample (pointer into
+        its row, n_tokens * 4 bytes); a chunk's responses are handed to LoadGen in one QuerySamplesComplete call."""
         base, stride = tokens.ctypes.data, tokens.strides[0]
-        debug = logger.isEnabledFor(10)
-        for i, s in enumerate(samples):
-            n = int(lens[i])
-            lg.QuerySamplesComplete([lg.QuerySampleResponse(s.id, base + i * stride, n * 4)])
-            if debug:
-                logger.debug(f"{s.index}::{seq_to_sen(tokens[i], n)}")
+        counts = lens[:len(samples)].tolist()
+        lg.QuerySamplesComplete([lg.QuerySampleResponse(s.id, base + i * stride, n * 4)
+                                 for i, (s, n) in enumerate(zip(samples, counts))])
+        if logger.isEnabledFor(10):
+            for i, s in enumerate(samples):
+                logger.debug(f"{s.index}::{seq_to_sen(tokens[i], counts[i])}")
 
     # --------------------------------------------------------------------------------------------- synchronous path
     def inference(self, batch_idx):
