@@ -66,7 +66,7 @@ int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t 
  *   gates = (float(h.W_hh^T + G[t]) + bias) * rb_scale ; lstm_postop_tpp::ref (tpps/lstm_postop_tpp.cpp:12-98)
  * as ONE persistent kernel.  G [T][N][4H] int32 (from rnnt_gemm_i8_i32), w_hh [4H][H], bias [4H] fp32,
  * hx [N][H] int8 and cx [N][H] binary16 updated IN PLACE, y [T][N][H] int8 (skip_quant_y=0) or bf16.
- * H must be 1024.
+ * H must be 1024; N <= 4096 per call.  G must be 32-byte aligned (read with 256-bit loads), w_hh / hx / cx 16-byte, y 8-byte.
  * workspace: rnnt_lstm_recurrent_workspace_bytes(N) bytes, 256-byte aligned, contents don't care. */
 int64_t rnnt_lstm_recurrent_workspace_bytes(int N);
 int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,

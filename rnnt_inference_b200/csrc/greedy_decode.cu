@@ -72,7 +72,8 @@ __device__ __forceinline__ void dot_chains(const uint16_t* wrow, const float* xb
   float acc[NL];
 #pragma unroll
   for (int i = 0; i < NL; ++i) acc[i] = 0.f;
-#pragma unroll 4
+  // few chains per thread = a latency-bound FMA chain: unroll deeper so that more operand loads are in flight per chain
+#pragma unroll(NL <= 2 ? 8 : 4)
   for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
     const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
     const float w0 = __uint_as_float(wb.x << 16), w1 = __uint_as_float(wb.x & 0xffff0000u);
@@ -217,7 +218,7 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
       const uint16_t* wrow = wp + (size_t)cl * DEC_KSTR;
       const float* xr = act + a * DEC_P;
       float acc = 0.f;
-#pragma unroll 4
+#pragma unroll 8
       for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
         const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
         const float4 xv = *reinterpret_cast<const float4*>(xr + k4 * 4);
