@@ -121,3 +121,34 @@ def test_sut_offline_query_vs_oracle(setup):
         o_res, o_len, _ = _oracle(params, [feats[i] for i in idx], pad_to=32)
         for j, i in enumerate(idx):
             np.testing.assert_array_equal(got[i], o_res[j, :o_len[j]])
+
+
+def test_qsl_arena_and_staging_runs(setup):
+    """The QSL's pinned arena holds the samples longest first (ties by id) and hands out views of it; the SUT's staging
+    copies maximal runs of arena neighbours with one DMA each — a chunk of neighbours and a chunk with gaps must both
+    arrive on the device as the plain concatenation of their samples."""
+    from rnnt_inference_b200 import loadgen_shim as lg
+    from rnnt_inference_b200.pytorch_sut import PytorchSUT
+    sd = setup[0]
+    lens = [25, 7, 31, 18, 12, 31, 3, 22, 9, 16]
+    feats = [S.make_features(n, 500 + i) for i, n in enumerate(lens)]
+    sut = PytorchSUT(sd, {"x": feats, "x_lens": [torch.tensor(n) for n in lens]}, 4, "quant", None, enable_bf16=True,
+                     scenario="Offline")
+    qsl = sut.qsl
+    assert qsl.arena is not None and qsl.arena.is_pinned()
+    order = sorted(range(len(lens)), key=qsl.sort_key)
+    assert order == sorted(range(len(lens)), key=lambda i: (-lens[i], i))
+    off = 0
+    for i in order:
+        assert qsl.arena_off[i] == off
+        x, n = qsl[i]
+        assert int(n) == lens[i] and x.data_ptr() == qsl.arena[off:].data_ptr()
+        assert torch.equal(x, feats[i])
+        off += lens[i]
+    for ids in (order[2:6], [order[0], order[3], order[4], order[9]]):      # one run / three runs
+        chunk = [lg.QuerySample(100 + i, i) for i in ids]
+        b = sut._stage(chunk)
+        b.ready.synchronize()
+        total = sum(lens[i] for i in ids)
+        assert torch.equal(b.packed[:total].cpu(), torch.cat([feats[i] for i in ids], 0))
+        assert b.meta[1, :len(ids)].cpu().tolist() == [lens[i] for i in ids]
