@@ -61,3 +61,8 @@ for lo, hi in ((0, 0), (1, 4), (5, 12), (13, 24), (25, 48), (49, 200)):
     m = (tr[1:, 7] >= lo) & (tr[1:, 7] <= hi)
     if m.any():
         print("  lanes %3d..%3d: %4d iterations, mean period %.0f cycles" % (lo, hi, m.sum(), per[m[:len(per)]].mean() if len(per) == len(m) else per[m[:-1]].mean()))
+hv = tr[tr[:, 7] >= 49]
+if len(hv):
+    m = lambda a, b: np.mean(hv[:, a] - hv[:, b])
+    print("heavy iterations (>= 49 active lanes in group 0): %d, mean lanes %.0f; mean cycles: lstm0 %.0f  barrier %.0f  lstm1+barrier %.0f  "
+          "fc1+barrier %.0f  joint/update %.0f  barrier %.0f" % (len(hv), hv[:, 7].mean(), m(1, 0), m(2, 1), m(3, 2), m(4, 3), m(5, 4), m(6, 5)))

@@ -37,7 +37,9 @@ def lstm_amx_int8(x: Tensor, hx: List[Tensor], cx: List[Tensor], all_weights: Li
                   o_scale, skip_quant_y: bool, tile_steps=None) -> Tuple[Tensor, List[Tensor], List[Tensor]]:
     """init.cpp:132-134 / lstm_amx.cpp:24-57: quantise fp32 input with i_scale[0], zero-pad K to a multiple of 64,
     then run the layers; only the last layer honours skip_quant_y.  tile_steps (extension, default off): see
-    ops.lstm_layer_i8 — ragged batches sorted by length skip the dead (timestep, 128-row tile) items."""
+    ops.lstm_layer_i8 — ragged batches sorted by length skip the dead (timestep, 128-row tile) items; their rows of
+    the result are left unwritten (every consumer on the path — the next layer's projection, stack_time, the hoisted
+    joint product, the decode loop — skips them by the same lengths)."""
     num_layers = len(all_weights)
     if x.dtype == torch.float32:
         k = x.shape[-1]
@@ -48,7 +50,7 @@ def lstm_amx_int8(x: Tensor, hx: List[Tensor], cx: List[Tensor], all_weights: Li
         w_ih, w_hh, _b_ih, b_hh = all_weights[layer]
         last = layer == num_layers - 1
         x = ops.lstm_layer_i8(x, hx[layer], cx[layer], w_ih, w_hh, b_hh, _scalar(rb_scale, layer), _scalar(i_scale, layer),
-                              _scalar(o_scale, layer), bool(skip_quant_y) and last, tile_steps=tile_steps)
+                              _scalar(o_scale, layer), bool(skip_quant_y) and last, tile_steps=tile_steps, zero_dead=False)
     return x, hx, cx
 
 

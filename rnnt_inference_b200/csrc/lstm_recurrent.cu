@@ -264,32 +264,20 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(outfree_bar);          // staging buffer may be overwritten by the next item
+      // h first: it is all the next step waits for, so only its stores are in flight when the release fence drains them
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
         const int row = sw * 64 + r * 32 + lane;
         const int n = bt * REC_BM + row;
-        const bool valid = n < p.N;
         if (!last) {
           uint4* hn = reinterpret_cast<uint4*>(p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 2)) * REC_BM + row) * 128 +
                                                (slice & 3) * HS);
           hn[0] = make_uint4(hw[r][0], hw[r][1], hw[r][2], hw[r][3]);
           hn[1] = make_uint4(hw[r][4], hw[r][5], hw[r][6], hw[r][7]);
-        } else if (valid) {   // last step of this tile: hand the state back to the caller's hx
+        } else if (n < p.N) {   // last step of this tile: hand the state back to the caller's hx
           uint4* hp = reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS);
           hp[0] = make_uint4(hw[r][0], hw[r][1], hw[r][2], hw[r][3]);
           hp[1] = make_uint4(hw[r][4], hw[r][5], hw[r][6], hw[r][7]);
-        }
-        if (valid && !(p.debug & 8)) {
-          const size_t yoff = ((size_t)t * p.N + n) * REC_H + slice * HS;
-          if (p.skip_quant_y) {
-            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) yp[i] = make_uint4(yw[r][4 * i], yw[r][4 * i + 1], yw[r][4 * i + 2], yw[r][4 * i + 3]);
-          } else {
-            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff);
-            yp[0] = make_uint4(yw[r][0], yw[r][1], yw[r][2], yw[r][3]);
-            yp[1] = make_uint4(yw[r][4], yw[r][5], yw[r][6], yw[r][7]);
-          }
         }
       }
       if (tr) p.trace[t * 16 + 5] = clock64();
@@ -301,6 +289,25 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (p.debug & 16) asm volatile("red.relaxed.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
         else asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
         if (tr) p.trace[t * 16 + 7] = clock64();
+      }
+      __syncwarp();
+      // y[t] afterwards: nothing inside this kernel reads it
+      if (!(p.debug & 8)) {
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const int n = bt * REC_BM + sw * 64 + r * 32 + lane;
+          if (n >= p.N) continue;
+          const size_t yoff = ((size_t)t * p.N + n) * REC_H + slice * HS;
+          if (p.skip_quant_y) {
+            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) yp[i] = make_uint4(yw[r][4 * i], yw[r][4 * i + 1], yw[r][4 * i + 2], yw[r][4 * i + 3]);
+          } else {
+            uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff);
+            yp[0] = make_uint4(yw[r][0], yw[r][1], yw[r][2], yw[r][3]);
+            yp[1] = make_uint4(yw[r][4], yw[r][5], yw[r][6], yw[r][7]);
+          }
+        }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }

@@ -109,16 +109,17 @@ def tile_steps_for(lens_host, n, divisor=1):
     return np.ascontiguousarray(steps.astype(np.int32))
 
 
-def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, tile_steps=None):
+def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, tile_steps=None, zero_dead=True):
     """lstm_layer_amx_int8 (lstm_amx.cpp:59-158). x int8 [T,N,K]; hx int8 [N,H], cx fp16 [N,H] updated IN PLACE.
     Returns y: int8 [T,N,H] or bf16 [T,N,H] when skip_quant_y.  tile_steps (host int32 per 128-row tile, see
     tile_steps_for): ragged batch sorted by length — (t, tile) items past a tile's last step are skipped and y is zero
-    there."""
+    there (zero_dead=False leaves those rows unwritten: for callers whose consumers skip the same items, it saves the
+    fill of the whole output)."""
     L.require_cuda(x, hx, cx, w_ih, w_hh, bias)
     t, n, k = x.shape
     if hx.dtype != torch.int8 or cx.dtype != torch.float16 or x.dtype != torch.int8:
         raise RuntimeError("lstm_layer_i8: x/hx must be int8 and cx float16")
-    alloc = torch.empty if tile_steps is None else torch.zeros
+    alloc = torch.zeros if (tile_steps is not None and zero_dead) else torch.empty
     y = alloc((t, n, H), dtype=torch.bfloat16 if skip_quant_y else torch.int8, device=x.device)
     if t == 0:
         return y
