@@ -66,3 +66,7 @@ if len(hv):
     m = lambda a, b: np.mean(hv[:, a] - hv[:, b])
     print("heavy iterations (>= 49 active lanes in group 0): %d, mean lanes %.0f; mean cycles: lstm0 %.0f  barrier %.0f  lstm1+barrier %.0f  "
           "fc1+barrier %.0f  joint/update %.0f  barrier %.0f" % (len(hv), hv[:, 7].mean(), m(1, 0), m(2, 1), m(3, 2), m(4, 3), m(5, 4), m(6, 5)))
+    h12 = hv[hv[:, 12] > 0]
+    if len(h12):
+        print("  first (full 12-lane) chunk of lstm0 in heavy iterations: staging %.0f  dot %.0f" %
+              (np.mean(h12[:, 12] - h12[:, 0]), np.mean(h12[:, 13] - h12[:, 12])))

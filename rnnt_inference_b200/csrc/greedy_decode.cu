@@ -65,30 +65,40 @@ __device__ __forceinline__ void bf16x8_to_smem(float* dst, uint4 v) {
   reinterpret_cast<float4*>(dst)[1] = b;
 }
 
-// NL independent dot-product chains of one weight row against the activations of lanes ls, ls + 2, ... (stride 2 lanes =
-// 4 * DEC_P floats); every chain is sequential in k from 0 (the oracle's order).  Results to part[...][lane][col].
+// Dot-product chains of TWO weight rows (gate columns c and c + 32) against the activations of lanes ls, ls + 4, ... (NL
+// of them; stride 4 lanes = 8 * DEC_P floats): 2 * NL independent chains per thread, every chain sequential in k from 0
+// (the oracle's order).  Two columns per thread halve the activation reads per FMA — the shared-memory pipe, not the
+// FMA pipe, bounded the one-column version (10.4K cycles per full chunk against 3.8K of FMA issue).
+// Results to part[...][lane][col].
 template <int NL>
-__device__ __forceinline__ void dot_chains(const uint16_t* wrow, const float* xbase, float* pout) {
-  float acc[NL];
+__device__ __forceinline__ void dot_chains(const uint16_t* wrow0, const uint16_t* wrow1, const float* xbase, float* pout) {
+  float acc0[NL], acc1[NL];
 #pragma unroll
-  for (int i = 0; i < NL; ++i) acc[i] = 0.f;
+  for (int i = 0; i < NL; ++i) { acc0[i] = 0.f; acc1[i] = 0.f; }
   // few chains per thread = a latency-bound FMA chain: unroll deeper so that more operand loads are in flight per chain
-#pragma unroll(NL <= 2 ? 8 : 4)
+#pragma unroll(NL <= 1 ? 8 : 4)
   for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
-    const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
-    const float w0 = __uint_as_float(wb.x << 16), w1 = __uint_as_float(wb.x & 0xffff0000u);
-    const float w2 = __uint_as_float(wb.y << 16), w3 = __uint_as_float(wb.y & 0xffff0000u);
+    const uint2 wa = *reinterpret_cast<const uint2*>(wrow0 + k4 * 4);
+    const uint2 wb = *reinterpret_cast<const uint2*>(wrow1 + k4 * 4);
+    const float a0 = __uint_as_float(wa.x << 16), a1 = __uint_as_float(wa.x & 0xffff0000u);
+    const float a2 = __uint_as_float(wa.y << 16), a3 = __uint_as_float(wa.y & 0xffff0000u);
+    const float b0 = __uint_as_float(wb.x << 16), b1 = __uint_as_float(wb.x & 0xffff0000u);
+    const float b2 = __uint_as_float(wb.y << 16), b3 = __uint_as_float(wb.y & 0xffff0000u);
 #pragma unroll
     for (int i = 0; i < NL; ++i) {
-      const float4 xv = *reinterpret_cast<const float4*>(xbase + i * 4 * DEC_P + k4 * 4);
-      acc[i] = __fmaf_rn(xv.x, w0, acc[i]);
-      acc[i] = __fmaf_rn(xv.y, w1, acc[i]);
-      acc[i] = __fmaf_rn(xv.z, w2, acc[i]);
-      acc[i] = __fmaf_rn(xv.w, w3, acc[i]);
+      const float4 xv = *reinterpret_cast<const float4*>(xbase + i * 8 * DEC_P + k4 * 4);
+      acc0[i] = __fmaf_rn(xv.x, a0, acc0[i]);
+      acc1[i] = __fmaf_rn(xv.x, b0, acc1[i]);
+      acc0[i] = __fmaf_rn(xv.y, a1, acc0[i]);
+      acc1[i] = __fmaf_rn(xv.y, b1, acc1[i]);
+      acc0[i] = __fmaf_rn(xv.z, a2, acc0[i]);
+      acc1[i] = __fmaf_rn(xv.z, b2, acc1[i]);
+      acc0[i] = __fmaf_rn(xv.w, a3, acc0[i]);
+      acc1[i] = __fmaf_rn(xv.w, b3, acc1[i]);
     }
   }
 #pragma unroll
-  for (int i = 0; i < NL; ++i) pout[2 * i * DEC_COLS] = acc[i];
+  for (int i = 0; i < NL; ++i) { pout[4 * i * DEC_COLS] = acc0[i]; pout[4 * i * DEC_COLS + 32] = acc1[i]; }
 }
 
 // One LSTM layer for the `na` active lanes listed in `alist` (group-local lane ids), chunked by DEC_CHUNK.
@@ -144,20 +154,17 @@ __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g,
     }
     __syncthreads();
     if (lt && tid == 0 && a0 == 0) lt[0] = clock64();
-    // ---- dot products: thread = (column c, matrix m, lane parity ls) owns the chains of lanes ls, ls + 2, ...;
-    // specialised by the number of lanes so that a sparse chunk issues no predicated-off instructions
+    // ---- dot products: thread = (column pair c / c + 32, matrix m, lane slot ls) owns the chains of lanes ls, ls + 4,
+    // ls + 8; specialised by the number of lanes so that a sparse chunk issues no predicated-off instructions
     {
-      const int c = tid & 63, m = (tid >> 6) & 1, ls = tid >> 7;
+      const int c = tid & 31, m = (tid >> 5) & 1, ls = tid >> 6;
       const uint16_t* wrow = wl + ((size_t)(layer * 2 + m) * DEC_COLS + c) * DEC_KSTR;
       const float* xbase = act + ls * 2 * DEC_P + m * DEC_P;
       float* pout = part + (m * DEC_CHUNK + ls) * DEC_COLS + c;
-      switch ((nc - ls + 1) / 2) {
-        case 1: dot_chains<1>(wrow, xbase, pout); break;
-        case 2: dot_chains<2>(wrow, xbase, pout); break;
-        case 3: dot_chains<3>(wrow, xbase, pout); break;
-        case 4: dot_chains<4>(wrow, xbase, pout); break;
-        case 5: dot_chains<5>(wrow, xbase, pout); break;
-        case 6: dot_chains<6>(wrow, xbase, pout); break;
+      switch ((nc - ls + 3) / 4) {
+        case 1: dot_chains<1>(wrow, wrow + 32 * DEC_KSTR, xbase, pout); break;
+        case 2: dot_chains<2>(wrow, wrow + 32 * DEC_KSTR, xbase, pout); break;
+        case 3: dot_chains<3>(wrow, wrow + 32 * DEC_KSTR, xbase, pout); break;
         default: break;
       }
     }
