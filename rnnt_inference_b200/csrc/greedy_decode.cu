@@ -220,21 +220,49 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
         if (dsti[r] >= 0) bf16x8_to_smem(act + dsti[r], v[r]);
     }
     __syncthreads();
-    for (int e = tid; e < nc * ncol; e += DEC_THREADS) {
-      const int a = e / ncol, cl = e % ncol;
-      const uint16_t* wrow = wp + (size_t)cl * DEC_KSTR;
-      const float* xr = act + a * DEC_P;
-      float acc = 0.f;
+    // thread = (column cl, lane slot lg) owns the chains of lanes lg, lg + nslot, ...: one weight read serves up to three
+    // lanes (a chain per (lane, column) with its own weight read kept the shared-memory pipe busier than the FMA pipe)
+    {
+      const int nslot = DEC_THREADS / ncol;                   // 9 lane slots of ncol threads (19 for the last, short CTA)
+      const int lg = tid / ncol, cl = tid - lg * ncol;
+      if (lg < nslot && lg < nc) {
+        const int nl = (nc - lg + nslot - 1) / nslot;         // <= 3 for nslot >= 8
+        const uint16_t* wrow = wp + (size_t)cl * DEC_KSTR;
+        const float* xr = act + lg * DEC_P;
+        const int xs = nslot * DEC_P;
+        float acc[3] = {0.f, 0.f, 0.f};
+        if (nl == 1) {
 #pragma unroll 8
-      for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
-        const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
-        const float4 xv = *reinterpret_cast<const float4*>(xr + k4 * 4);
-        acc = __fmaf_rn(xv.x, __uint_as_float(wb.x << 16), acc);
-        acc = __fmaf_rn(xv.y, __uint_as_float(wb.x & 0xffff0000u), acc);
-        acc = __fmaf_rn(xv.z, __uint_as_float(wb.y << 16), acc);
-        acc = __fmaf_rn(xv.w, __uint_as_float(wb.y & 0xffff0000u), acc);
+          for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
+            const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
+            const float4 xv = *reinterpret_cast<const float4*>(xr + k4 * 4);
+            acc[0] = __fmaf_rn(xv.x, __uint_as_float(wb.x << 16), acc[0]);
+            acc[0] = __fmaf_rn(xv.y, __uint_as_float(wb.x & 0xffff0000u), acc[0]);
+            acc[0] = __fmaf_rn(xv.z, __uint_as_float(wb.y << 16), acc[0]);
+            acc[0] = __fmaf_rn(xv.w, __uint_as_float(wb.y & 0xffff0000u), acc[0]);
+          }
+        } else {
+#pragma unroll 4
+          for (int k4 = 0; k4 < DEC_P / 4; ++k4) {
+            const uint2 wb = *reinterpret_cast<const uint2*>(wrow + k4 * 4);
+            const float w0 = __uint_as_float(wb.x << 16), w1 = __uint_as_float(wb.x & 0xffff0000u);
+            const float w2 = __uint_as_float(wb.y << 16), w3 = __uint_as_float(wb.y & 0xffff0000u);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+              if (i < nl) {
+                const float4 xv = *reinterpret_cast<const float4*>(xr + i * xs + k4 * 4);
+                acc[i] = __fmaf_rn(xv.x, w0, acc[i]);
+                acc[i] = __fmaf_rn(xv.y, w1, acc[i]);
+                acc[i] = __fmaf_rn(xv.z, w2, acc[i]);
+                acc[i] = __fmaf_rn(xv.w, w3, acc[i]);
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+          if (i < nl) p.z[(size_t)(lane0 + alist[a0 + lg + i * nslot]) * DEC_J + col0 + cl] = acc[i];
       }
-      p.z[(size_t)(lane0 + alist[a0 + a]) * DEC_J + col0 + cl] = acc;
     }
     __syncthreads();
   }
