@@ -58,6 +58,11 @@ int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, in
  * the other rows of C are left untouched (the recurrent kernel never reads them).  tile_steps_host NULL = all rows. */
 int rnnt_gemm_i8_i32_ragged(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, int rows_per_step,
                             const int32_t* tile_steps_host, void* stream);
+/* Same product for N = 4096 = 4 gates x 1024 units, stored gate-blocked for rnnt_lstm_recurrent_i8_gate_blocked_ragged:
+ * C[slice 32][gate 4][unit octet 4][row M][8] int32, element (row m, column gate*1024 + slice*32 + octet*8 + u) of the
+ * row-major result.  Same values, same ragged skipping; C 32-byte aligned. */
+int rnnt_gemm_i8_i32_gate_blocked_ragged(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, int rows_per_step,
+                                         const int32_t* tile_steps_host, void* stream);
 /* Same contract on CUDA cores (dp4a), M <= 65535.  TEST HELPER: lets the GPU tests cross-check the tcgen05
  * kernel at sizes the CPU oracle cannot reach.  Never called by the product path. */
 int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream);
@@ -81,6 +86,11 @@ int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bi
 int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
                                   float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
                                   const int32_t* tile_steps_host, void* workspace, void* stream);
+/* Same kernel reading the gate-blocked projection written by rnnt_gemm_i8_i32_gate_blocked_ragged with M = T * N rows
+ * (the 32 batch rows a warp handles are then 1 KB contiguous: 8 cache lines per load instead of 32). */
+int rnnt_lstm_recurrent_i8_gate_blocked_ragged(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale,
+                                               float in_scale, float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y,
+                                               int T, int N, int H, const int32_t* tile_steps_host, void* workspace, void* stream);
 
 /* DEBUG: when set to a device buffer of T*16 int64, the next recurrent launches record clock64() stamps of CTA (0,0)
  * per timestep (h ready, first operand chunk landed, MMAs issued, accumulator ready, TMEM read, gate math done,

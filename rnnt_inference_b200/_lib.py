@@ -37,11 +37,13 @@ _SIGS = {
     "rnnt_quantize_ragged_f32_i8": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),
     "rnnt_gemm_i8_i32": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "rnnt_gemm_i8_i32_ragged": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp]),
+    "rnnt_gemm_i8_i32_gate_blocked_ragged": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp]),
     "rnnt_linear_bf16_bf16_ragged": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp]),
     "rnnt_gemm_i8_i32_simt": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "rnnt_lstm_recurrent_workspace_bytes": (_i64, [_i]),
     "rnnt_lstm_recurrent_i8": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "rnnt_lstm_recurrent_i8_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "rnnt_lstm_recurrent_i8_gate_blocked_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_debug_set_recurrent_trace": (_i, [_vp]),
     "rnnt_debug_set_recurrent_cluster": (_i, [_i]),
     "rnnt_debug_set_recurrent_flags": (_i, [_i]),

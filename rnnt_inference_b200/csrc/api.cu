@@ -50,8 +50,8 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int rank, const void* base
               const uint64_t* strides, const uint32_t* box, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return fail(RNNT_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
-  cuuint64_t d[3], s[2];
-  cuuint32_t b[3], es[3] = {1, 1, 1};
+  cuuint64_t d[5], s[4];
+  cuuint32_t b[5], es[5] = {1, 1, 1, 1, 1};
   for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; }
   for (int i = 0; i + 1 < rank; ++i) s[i] = strides[i];
   CUresult r = enc(m, dt, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -263,7 +263,8 @@ int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t 
 
 }  // extern "C"
 template <int BN>
-static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, const RowSkip& skip, cudaStream_t st) {
+static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, const RowSkip& skip, cudaStream_t st,
+                       bool gate_blocked = false) {
   CUtensorMap ta, tb, tc;
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)K};
@@ -275,10 +276,18 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
     uint32_t box[2] = {GEMM_BK, BN};
     if (int r = make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, W, dims, str, box)) return r;
   }
-  {
+  if (!gate_blocked) {
     uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[1] = {(uint64_t)N * 4};
     uint32_t box[2] = {32, 32};
     if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 2, C, dims, str, box)) return r;
+  } else {
+    // gate-blocked projection for the recurrent kernel: C[slice 32][gate 4][unit octet 4][row M][8] int32, column
+    // gate*1024 + slice*32 + octet*8 + u of the row-major result.  A 32-column chunk of the epilogue is one (gate, slice):
+    // box = 8 units x 32 rows x 4 octets.
+    uint64_t dims[5] = {8, (uint64_t)M, 4, 4, 32};
+    uint64_t str[4] = {32, (uint64_t)M * 32, (uint64_t)M * 128, (uint64_t)M * 512};
+    uint32_t box[5] = {8, 32, 4, 1, 1};
+    if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 5, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return r;
   }
   int* status = device_status();
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
@@ -291,7 +300,7 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
   const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
   const int sms = sm_count();
   const int grid = std::max(1, std::min(sms > 0 ? sms : 148, num_m * num_n));
-  kern<<<grid, GEMM_THREADS, GemmSmem<BN>::TOTAL, st>>>(ta, tb, tc, num_m, num_n, num_k, status, skip);
+  kern<<<grid, GEMM_THREADS, GemmSmem<BN>::TOTAL, st>>>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0);
   CUDA_TRY(cudaGetLastError());
   return RNNT_OK;
 }
@@ -314,6 +323,18 @@ int rnnt_gemm_i8_i32_ragged(const int8_t* A, const int8_t* W, int32_t* C, int64_
   if (N % 256 == 0) return gemm_launch<256>(A, W, C, M, N, K, skip, st);
   if (N % 128 == 0) return gemm_launch<128>(A, W, C, M, N, K, skip, st);
   return gemm_launch<64>(A, W, C, M, N, K, skip, st);
+}
+
+int rnnt_gemm_i8_i32_gate_blocked_ragged(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, int rows_per_step,
+                                         const int32_t* tile_steps_host, void* stream) {
+  if (!A || !W || !C || M < 0 || K <= 0) return fail(RNNT_ERR_INVALID, "gemm_i8_i32_gate_blocked: null pointer or non-positive size");
+  if (N != 4 * REC_H) return fail(RNNT_ERR_INVALID, "gemm_i8_i32_gate_blocked: N must be 4096 (4 gates x 1024 units), got %d", N);
+  if ((K & 15) || !aligned(A, 16) || !aligned(W, 16) || !aligned(C, 32))
+    return fail(RNNT_ERR_INVALID, "gemm_i8_i32_gate_blocked: need K %% 16 == 0, 16-byte aligned A/W, 32-byte aligned C");
+  if (M == 0) return RNNT_OK;
+  RowSkip skip;
+  if (int r = make_skip(&skip, M, rows_per_step, tile_steps_host, GEMM_BM)) return r;
+  return gemm_launch<256>(A, W, C, M, N, K, skip, (cudaStream_t)stream, true);
 }
 
 // debug hook: device buffer [T][8] int64 receiving clock64 stamps of CTA (0,0) of the next recurrent launches (NULL = off)
@@ -390,9 +411,22 @@ int rnnt_debug_set_recurrent_cluster(int ctas) {
   g_rec_cluster = ctas;
   return RNNT_OK;
 }
+static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                   float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                   const int32_t* tile_steps_host, void* workspace, void* stream);
 int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
                                   float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
                                   const int32_t* tile_steps_host, void* workspace, void* stream) {
+  return rec_run(G, 0, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, hx, cx, y, T, N, H, tile_steps_host, workspace, stream);
+}
+int rnnt_lstm_recurrent_i8_gate_blocked_ragged(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale,
+                                               float in_scale, float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y,
+                                               int T, int N, int H, const int32_t* tile_steps_host, void* workspace, void* stream) {
+  return rec_run(G, 1, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, hx, cx, y, T, N, H, tile_steps_host, workspace, stream);
+}
+static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                   float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                   const int32_t* tile_steps_host, void* workspace, void* stream) {
   if (!G || !w_hh || !bias || !hx || !cx || !y || !workspace) return fail(RNNT_ERR_INVALID, "lstm_recurrent: null pointer");
   if (H != REC_H) return fail(RNNT_ERR_INVALID, "lstm_recurrent: hidden size must be 1024 (got %d)", H);
   if (T < 0 || N <= 0) return fail(RNNT_ERR_INVALID, "lstm_recurrent: need T >= 0, N > 0 (T=%d N=%d)", T, N);
@@ -444,7 +478,7 @@ int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const fl
     uint32_t box[2] = {128, REC_BM};
     if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, h_buf, dims, str, box)) return r;
   }
-  p.g = G; p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
+  p.g = G; p.g_blocked = g_blocked; p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
   p.T = T; p.N = N; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
   p.trace = g_rec_trace;

@@ -24,7 +24,7 @@ template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles, int num_k_blocks,
-                   int* __restrict__ status, const RowSkip skip) {
+                   int* __restrict__ status, const RowSkip skip, const int gate_blocked) {
   using S = GemmSmem<BN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -121,17 +121,30 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         // staging buffer `buf` was last read by the TMA store issued two chunks ago
         if (lane == 0) tma_store_wait_read<1>();
         __syncwarp();
-        const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 128u;
+        if (!gate_blocked) {
+          const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 128u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t a = dst + (uint32_t)((j ^ (lane & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
-                       "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t a = dst + (uint32_t)((j ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
+                         "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
+          }
+        } else {
+          // gate-blocked result (see api.cu): staging = [unit octet 4][row 32][8 units], dense (no swizzle)
+          const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 32u;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t a = dst + (uint32_t)((j >> 1) * 1024 + (j & 1) * 16);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
+                         "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
+          }
         }
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&tmap_c, cbuf0 + (uint32_t)buf * S::C_WARP_BYTES, n_blk * BN + c * 32, m_blk * GEMM_BM + q * 32);
+          const int col0 = n_blk * BN + c * 32, row0 = m_blk * GEMM_BM + q * 32;
+          if (!gate_blocked) tma_store_2d(&tmap_c, cbuf0 + (uint32_t)buf * S::C_WARP_BYTES, col0, row0);
+          else tma_store_5d(&tmap_c, cbuf0 + (uint32_t)buf * S::C_WARP_BYTES, 0, row0, 0, col0 >> 10, (col0 & 1023) >> 5);
           tma_store_commit();
         }
         buf ^= 1;
@@ -151,9 +164,9 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 }
 
 // explicit instantiations used by api.cu
-template __global__ void gemm_i8_i32_kernel<256>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip);
-template __global__ void gemm_i8_i32_kernel<128>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip);
-template __global__ void gemm_i8_i32_kernel<64>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip);
+template __global__ void gemm_i8_i32_kernel<256>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip, const int);
+template __global__ void gemm_i8_i32_kernel<128>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip, const int);
+template __global__ void gemm_i8_i32_kernel<64>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip, const int);
 
 // ---------------------------------------------------------------------------------------------
 // Plain CUDA-core int8 GEMM.  NOT a fallback: used by tests (device-side cross-check of the tcgen05 kernel at

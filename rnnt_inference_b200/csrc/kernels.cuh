@@ -37,7 +37,7 @@ struct GemmSmem {
 template <int BN>
 __global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
-                                   int num_k_blocks, int* __restrict__ status, const RowSkip skip);
+                                   int num_k_blocks, int* __restrict__ status, const RowSkip skip, const int gate_blocked);
 __global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, int32_t* __restrict__ C,
                                         long long M, int N, int K);
 
@@ -76,7 +76,8 @@ struct RecSmem {
 static_assert(RecSmem::TOTAL <= 232448, "recurrent kernel shared memory");
 
 struct RecParams {
-  const int32_t* g;        // [T][N][4H] int32 input projection (read straight from global: one 32-byte sector per thread and gate)
+  const int32_t* g;        // int32 input projection, read straight from global (one 32-byte sector per thread and gate):
+  int g_blocked;           //   0: [T][N][4H] row-major   1: [32 slices][4 gates][4 unit octets][T*N rows][8] (coalesced per warp)
   const float* bias;       // [4H]
   int8_t* h_buf;           // [2][tiles][8 chunks][128 rows][128 B] ping-pong (workspace), K-chunk-major
   int8_t* hx;              // [N][H] caller's state: h_0 on entry (read by TMA), receives h after the last step of each tile

@@ -343,9 +343,16 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     auto load_g = [&](int t_, int bt_) {
       const int n_ = bt_ * REC_BM + row;
       if (n_ < p.N && !(p.debug & 64)) {
-        const int32_t* gp = p.g + ((size_t)t_ * p.N + n_) * (4 * REC_H) + j0;
+        if (p.g_blocked) {      // a warp's 32 rows are 1 KB contiguous: 8 lines per load instead of 32
+          const size_t rows = (size_t)p.T * p.N;
+          const int32_t* gp = p.g + (((size_t)slice * 16 + ug) * rows + (size_t)t_ * p.N + n_) * 8;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) ldg256_stream(gp + g * REC_H, gi[g]);
+          for (int g = 0; g < 4; ++g) ldg256_stream(gp + (size_t)g * 4 * rows * 8, gi[g]);
+        } else {
+          const int32_t* gp = p.g + ((size_t)t_ * p.N + n_) * (4 * REC_H) + j0;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) ldg256_stream(gp + g * REC_H, gi[g]);
+        }
       } else {
 #pragma unroll
         for (int g = 0; g < 4; ++g)

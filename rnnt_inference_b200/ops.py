@@ -131,14 +131,16 @@ def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, sk
         if tile_steps.dtype.name != "int32" or len(tile_steps) != (n + 127) // 128:
             raise RuntimeError("lstm_layer_i8: tile_steps must be int32 with ceil(N/128) entries")
         ts_ptr = ctypes.c_void_p(tile_steps.ctypes.data)
-    # phase A: one projection GEMM over all timesteps; phase B: one persistent recurrent kernel (rnnt_lstm_layer_i8 is
-    # exactly these two calls; they are issued separately so that bench.py can time each kernel with CUDA events)
+    # phase A: one projection GEMM over all timesteps; phase B: one persistent recurrent kernel, issued separately so
+    # that bench.py can time each kernel with CUDA events.  The projection scratch between them is gate-blocked
+    # ([32 slices][4 gates][4 unit octets][T*N rows][8] int32): the rows a warp of the recurrent kernel reads are
+    # contiguous there, 8 lines per load instead of 32 of the row-major [T*N][4096] result.
     gemm_ts = ts_ptr if n % 128 == 0 else None     # dead (t, tile) rows of the projection are skipped as well
     telemetry.bracket("gemm_i8", (t * n, k), lambda: L.check(
-        L.lib.rnnt_gemm_i8_i32_ragged(L.ptr(x), L.ptr(w_ih), L.ptr(g_ws), t * n, 4 * H, k, n, gemm_ts, st)))
+        L.lib.rnnt_gemm_i8_i32_gate_blocked_ragged(L.ptr(x), L.ptr(w_ih), L.ptr(g_ws), t * n, 4 * H, k, n, gemm_ts, st)))
     units = (t, n, bool(skip_quant_y)) if tile_steps is None else (int(tile_steps.sum()), 128, bool(skip_quant_y))
     telemetry.bracket("lstm_recurrent", units, lambda: L.check(
-        L.lib.rnnt_lstm_recurrent_i8_ragged(L.ptr(g_ws), L.ptr(w_hh), L.ptr(bias), float(rb_scale), float(in_scale),
+        L.lib.rnnt_lstm_recurrent_i8_gate_blocked_ragged(L.ptr(g_ws), L.ptr(w_hh), L.ptr(bias), float(rb_scale), float(in_scale),
                                             float(out_scale), int(bool(skip_quant_y)), L.ptr(hx), L.ptr(cx), L.ptr(y), t, n, H,
                                             ts_ptr, L.ptr(ws), st)))
     telemetry.launches += 2
