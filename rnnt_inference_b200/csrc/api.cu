@@ -287,7 +287,7 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
     uint64_t dims[5] = {8, (uint64_t)M, 4, 4, 32};
     uint64_t str[4] = {32, (uint64_t)M * 32, (uint64_t)M * 128, (uint64_t)M * 512};
     uint32_t box[5] = {8, 32, 4, 1, 1};
-    if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 5, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return r;
+    if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 5, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return r;
   }
   int* status = device_status();
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");

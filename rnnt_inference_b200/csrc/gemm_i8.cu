@@ -130,11 +130,13 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                          "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
           }
         } else {
-          // gate-blocked result (see api.cu): staging = [unit octet 4][row 32][8 units], dense (no swizzle)
+          // gate-blocked result (see api.cu): staging = [unit octet 4][row 32][8 units] with the 32-byte TMA swizzle
+          // (16-byte half ^= bit 2 of the row), which spreads the eight lanes of a store phase over all 32 banks
           const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 32u;
+          const uint32_t hsw = (uint32_t)((lane >> 2) & 1);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const uint32_t a = dst + (uint32_t)((j >> 1) * 1024 + (j & 1) * 16);
+            const uint32_t a = dst + (uint32_t)((j >> 1) * 1024) + ((((uint32_t)j & 1u) ^ hsw) << 4);
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
                          "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
           }
