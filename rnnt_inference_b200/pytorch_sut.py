@@ -76,7 +76,8 @@ class PytorchSUT:
     # --------------------------------------------------------------------------------------------- LoadGen entry
     def issue_queries(self, samples):
         if self.batch_sort:
-            samples.sort(key=lambda s: self.qsl.sort_key(s.index))
+            keys = self.qsl._keys
+            samples.sort(key=lambda s: keys[s.index])
         chunks = [samples[i:i + self.batch_size] for i in range(0, len(samples), self.batch_size)]
         if not self.pipelined:
             for chunk in chunks:
@@ -111,8 +112,8 @@ class PytorchSUT:
         b.samples = chunk
         b.n_actual = len(chunk)
         b.n_padded = math.ceil(b.n_actual / 32) * 32          # pytorch_sut.py:90-104: pad N to a multiple of 32
-        feats = [self.qsl[s.index][0] for s in chunk]
-        lens = [int(f.shape[0]) for f in feats]
+        rows = self.qsl.rows
+        lens = [rows[s.index] for s in chunk]
         b.max_len = max(lens)
         b.lens_host = lens
         meta = torch.zeros((2, b.n_padded), dtype=torch.int64)
@@ -127,7 +128,7 @@ class PytorchSUT:
             buf = self._packed[slot]
             if buf is None or buf.shape[0] < total:
                 grow = max(total, self.batch_size * 512)
-                buf = torch.empty((grow, feats[0].shape[1]), dtype=torch.float32, device=dev)
+                buf = torch.empty((grow, self.qsl[chunk[0].index][0].shape[1]), dtype=torch.float32, device=dev)
                 self._packed[slot] = buf
             # one DMA per run of samples that are neighbours in the QSL's pinned arena (a sorted Offline query: one run
             # per batch); samples outside the arena are copied one by one
@@ -136,7 +137,7 @@ class PytorchSUT:
             while i < len(chunk):
                 start = aoff.get(chunk[i].index) if arena is not None else None
                 if start is None:
-                    buf[off:off + lens[i]].copy_(feats[i], non_blocking=True)
+                    buf[off:off + lens[i]].copy_(self.qsl[chunk[i].index][0], non_blocking=True)
                     off += lens[i]
                     i += 1
                     continue
@@ -154,7 +155,7 @@ class PytorchSUT:
             b.ready = torch.cuda.Event()
             b.ready.record(self._copy_stream)
         b.keep = (meta_host, slot)
-        b.h2d_bytes = total * feats[0].shape[1] * 4 + meta.numel() * 8
+        b.h2d_bytes = total * buf.shape[1] * 4 + meta.numel() * 8
         return b
 
     def _launch(self, b):

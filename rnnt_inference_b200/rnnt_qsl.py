@@ -27,6 +27,8 @@ class RNNTQSL:
         self.pin_memory = torch.cuda.is_available() if pin_memory is None else pin_memory
         self.arena = None                        # pinned [sum T_i, 240] fp32, samples longest first
         self.arena_off = {}                      # sample id -> first arena row
+        self.rows = [int(x.shape[0]) for x in self.dataset[0]]       # feature rows per sample, plain ints
+        self._keys = [(-int(n), i) for i, n in enumerate(self.dataset[1])]
         self.sample_id_to_sample = {}
         self.qsl = lg.ConstructQSL(self.count, perf_count, self.load_query_samples, self.unload_query_samples)
         self.load_query_samples(range(self.count))
@@ -46,8 +48,8 @@ class RNNTQSL:
     def _build_arena(self):
         """(Re)pack every loaded sample into one page-locked arena, longest first.  Runs when samples are loaded, i.e.
         outside LoadGen's timed region (LoadSamplesToRam)."""
-        ids = sorted(self.sample_id_to_sample, key=lambda i: (-int(self.dataset[1][i]), i))
-        rows = [int(self.dataset[0][i].shape[0]) for i in ids]
+        ids = sorted(self.sample_id_to_sample, key=self._keys.__getitem__)
+        rows = [self.rows[i] for i in ids]
         width = int(self.dataset[0][ids[0]].shape[1])
         arena = torch.empty((sum(rows), width), dtype=torch.float32, pin_memory=True)
         off = 0
@@ -59,9 +61,9 @@ class RNNTQSL:
         self.arena = arena
 
     def sort_key(self, index):
-        """Offline sort key: feature length descending (pytorch_sut.py:58-65); equal lengths in arena order, so that a
-        sorted query walks the arena front to back."""
-        return (-int(self.dataset[1][index]), self.arena_off.get(index, index))
+        """Offline sort key: feature length descending (pytorch_sut.py:58-65); equal lengths by sample id = arena order,
+        so that a sorted query walks the arena front to back.  Plain tuples of ints, made once."""
+        return self._keys[index]
 
     def __getitem__(self, index):
         return self.sample_id_to_sample[index]
