@@ -527,7 +527,7 @@ int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N,
       !w->b1 || !w->w2 || !w->b2)
     return fail(RNNT_ERR_INVALID, "greedy_decode: null weight pointer");
   if (T2 <= 0 || N <= 0 || L <= 0) return fail(RNNT_ERR_INVALID, "greedy_decode: need T2, N, L > 0 (T2=%d N=%d L=%d)", T2, N, L);
-  if (!aligned(workspace, 256) || !aligned(w->w_pred, 8) || !aligned(w->w2, 16) || !aligned(w->embed, 16) || !aligned(pre_hg0, 16) || !aligned(pre_hg1, 16) || !aligned(w->w_ih[0], 4) ||
+  if (!aligned(workspace, 256) || !aligned(y1, 16) || !aligned(w->b1, 16) || !aligned(w->w_pred, 8) || !aligned(w->w2, 16) || !aligned(w->embed, 16) || !aligned(pre_hg0, 16) || !aligned(pre_hg1, 16) || !aligned(w->w_ih[0], 4) ||
       !aligned(w->w_hh[0], 4) || !aligned(w->w_ih[1], 4) || !aligned(w->w_hh[1], 4))
     return fail(RNNT_ERR_INVALID, "greedy_decode: misaligned buffer");
   const int NG = 7;

@@ -279,17 +279,31 @@ __device__ __forceinline__ JointRegs joint_stage(const DecParams& p, int n, int4
   const int cur_t = st.y;
   const uint16_t* y1r = p.y1 + ((size_t)cur_t * p.N + n) * DEC_J;
   const float* zr = p.z + (size_t)n * DEC_J;
-  float zv[DEC_J / 32]; uint16_t yb[DEC_J / 32];
+  // lane owns k = 16 lane .. 16 lane + 15: four 16-byte loads of z, two of y1, four of b1 (all contiguous across the warp)
+  constexpr int KPL = DEC_J / 32;      // 16
+  float4 zv[KPL / 4]; uint4 yv[KPL / 8]; float4 bv[KPL / 4];
 #pragma unroll
-  for (int i = 0; i < DEC_J / 32; ++i) { zv[i] = __ldcg(zr + lane + 32 * i); yb[i] = __ldg(y1r + lane + 32 * i); }
+  for (int i = 0; i < KPL / 4; ++i) zv[i] = __ldcg(reinterpret_cast<const float4*>(zr + lane * KPL) + i);
+#pragma unroll
+  for (int i = 0; i < KPL / 8; ++i) yv[i] = __ldg(reinterpret_cast<const uint4*>(y1r + lane * KPL) + i);
+#pragma unroll
+  for (int i = 0; i < KPL / 4; ++i) bv[i] = __ldg(reinterpret_cast<const float4*>(p.b1 + lane * KPL) + i);
   JointRegs r = {0, 0, 0, 0};
   if (lane == 0) { r.sa = p.symbols_added[n]; r.ri = p.res_idx[n]; r.ti = p.time_idx[n]; r.flen = p.f_lens[n]; }
+  const float* zf = reinterpret_cast<const float*>(zv);
+  const float* bf = reinterpret_cast<const float*>(bv);
+  const uint32_t* yw = reinterpret_cast<const uint32_t*>(yv);
+  uint32_t out[KPL / 2];
 #pragma unroll
-  for (int i = 0; i < DEC_J / 32; ++i) {
-    const int k = lane + 32 * i;
-    const float v = __fadd_rn(__fadd_rn(zv[i], bf16_bits_to_float(yb[i])), s_b1[k]);   // (acc + y1) + bias
-    ybuf[k] = (uint16_t)float_to_bf16_bits(fmaxf(v, 0.f));                             // relu, round to bf16
+  for (int i = 0; i < KPL / 2; ++i) {
+    const float y0 = __uint_as_float(yw[i] << 16), y1f = __uint_as_float(yw[i] & 0xffff0000u);
+    const float v0 = __fadd_rn(__fadd_rn(zf[2 * i], y0), bf[2 * i]);            // (acc + y1) + bias
+    const float v1 = __fadd_rn(__fadd_rn(zf[2 * i + 1], y1f), bf[2 * i + 1]);
+    out[i] = float_to_bf16_bits(fmaxf(v0, 0.f)) | (float_to_bf16_bits(fmaxf(v1, 0.f)) << 16);   // relu, round to bf16
   }
+  uint4* yo = reinterpret_cast<uint4*>(ybuf + lane * KPL);
+  yo[0] = make_uint4(out[0], out[1], out[2], out[3]);
+  yo[1] = make_uint4(out[4], out[5], out[6], out[7]);
   __syncwarp();
   return r;
 }
