@@ -33,7 +33,7 @@ import numpy as np
 import torch
 
 UTTS_PER_GPU = 2513       # configs/mlperf.conf:13 performance_sample_count of the reference
-BATCH = 1024              # SUT batch size on B200 (the reference CPU run uses 256, run.sh:71); tiles of 128 rows pipeline inside the kernels
+BATCH = 2048              # SUT batch size on B200 (the reference CPU run uses 256, run.sh:71): more 128-row tiles per CTA in the recurrent kernel; <= 2240 decode lanes per launch, multiple of 128 for ragged tile skipping
 METRIC = "offline_utterances_per_second"
 UNIT = "utterances/s"
 
