@@ -14,23 +14,38 @@ from .config import RNNTParam
 
 INPUT_AMAX = 5.8358          # "input" range of tests/calibration_result_nv.cache in the reference
 FRAME_SECONDS = 0.03         # one stacked frame = 3 x 10 ms
-DEFAULT_LSTM_GAIN = 3.0       # encoder LSTM weights U(-g/sqrt(H), g/sqrt(H)): g = 1 (torch default) gives a nearly constant encoder
-DEFAULT_BLANK_BIAS = -2.0     # fc2 bias of BLANK relative to the labels: tuned once (with memory 0.9, penalty 3) so that ~0.8
-                              # symbols are emitted per stacked frame, LibriSpeech-like (~15 characters/s at 60 ms per frame)
+DEFAULT_LSTM_GAIN = 3.0      # encoder LSTM weights U(-g/sqrt(H), g/sqrt(H)): g = 1 (torch default) gives a nearly constant encoder
+# Decode-side constants, tuned once against the CPU oracle on the bench set (profiles/r02/decode_workload.md has the
+# histograms): greedy emissions are spread over the utterance at ~0.25 symbols per stacked frame, almost
+# never more than a handful per frame, transcripts differ between utterances, and a rare "burst" unit makes a few
+# frames run into the 30-symbol cap so that quirk (b) of SURVEY 8(a) is exercised at bench scale.
+DEFAULT_BLANK_BIAS = 2.0     # fc2 bias of BLANK relative to the labels (the emission threshold on the label evidence)
+DEFAULT_MEMORY = 0.8         # per-emitted-symbol decay of the label trace kept by the prediction LSTM
+DEFAULT_PENALTY = 8.0        # how hard a label's trace pushes its own logit down (no A-B-A-B ping-pong inside a frame)
+DEFAULT_BURST_THRESHOLD = 3.45   # pre-activation above which the burst unit fires (~5e-4 of the frames)
+DEFAULT_BURST_SEED = 0
 
 
 def make_checkpoint(seed=7, blank_bias=DEFAULT_BLANK_BIAS, with_amax=True, lstm_gain=DEFAULT_LSTM_GAIN, evidence_gain=3.0,
-                    memory=0.9, penalty=3.0):
+                    memory=DEFAULT_MEMORY, penalty=DEFAULT_PENALTY, burst_threshold=DEFAULT_BURST_THRESHOLD,
+                    burst_seed=DEFAULT_BURST_SEED):
     """Random-init MLPerf RNN-T state dict (keys as in the MLPerf checkpoint).
 
-    The encoder is plain random.  A plain random prediction/joint network is bistable under greedy decoding (either
-    never emits or emits 30 symbols on every frame), which would make the decode load meaningless, so that part is
-    random PLUS a little structure that reproduces what a trained transducer does: the prediction LSTM keeps a decaying
-    trace of the recently emitted labels, joint hidden units 0..27 read that trace and push the logit of those labels
-    down, and the remaining 484 hidden units are a random read-out of the encoder frame ("acoustic evidence")."""
+    The encoder is plain random; its output varies smoothly in time (correlation time ~5 stacked frames) and between
+    utterances.  A plain random prediction/joint network is bistable under greedy decoding (it either never emits or
+    emits 30 symbols on every frame), which would make the decode load meaningless, so that part is random PLUS the
+    little structure a trained transducer has:
+      * joint hidden units 29.. are a random read-out of the encoder frame ("acoustic evidence" for each label); BLANK has
+        no evidence, only a bias, so a label is emitted when its evidence rises above that threshold;
+      * the prediction LSTM keeps a trace of the recently emitted labels that decays by `memory` per emitted symbol; joint
+        hidden units 0..27 read it and push the logit of those labels down by `penalty` x trace, so a label is emitted
+        once per excursion of its evidence and the frame then falls back to BLANK;
+      * joint hidden unit 28 ("burst") is a rare, encoder-only detector that lifts every label far above BLANK: such a
+        frame emits until the 30-symbol cap (max_symbols_per_step) stops it."""
     g = torch.Generator().manual_seed(seed)
     H, P, J, V = (RNNTParam.trans_hidden_size, RNNTParam.pred_hidden_size, RNNTParam.joint_hidden_size, RNNTParam.num_labels)
     NL = V - 1   # 28 real labels
+    E0 = NL + 1  # first evidence unit of the joint hidden layer
 
     def uni(shape, bound):
         return (torch.rand(shape, generator=g) * 2 - 1) * bound
@@ -50,6 +65,7 @@ def make_checkpoint(seed=7, blank_bias=DEFAULT_BLANK_BIAS, with_amax=True, lstm_
     lstm("encoder.pre_rnn.lstm", RNNTParam.trans_input_size, H, RNNTParam.pre_num_layers, sd, lstm_gain)
     lstm("encoder.post_rnn.lstm", H * RNNTParam.stack_time_factor, H, RNNTParam.post_num_layers, sd, lstm_gain)
     # ---- prediction: embedding = 2 * e_k + noise; LSTM = small random + pass-through of the cell candidate
+    g = torch.Generator().manual_seed(seed + 1000)     # the decode-side draws do not depend on the encoder's
     embed = torch.randn((NL, P), generator=g) * 0.05
     embed[torch.arange(NL), torch.arange(NL)] += 2.0
     sd["prediction.embed.weight"] = embed
@@ -62,16 +78,23 @@ def make_checkpoint(seed=7, blank_bias=DEFAULT_BLANK_BIAS, with_amax=True, lstm_
         b[0:P] += 4.0                                                         # input gate open
         b[P:2 * P] += (f_bias if layer == 0 else -4.0) - 1.0                  # layer 0 remembers, layer 1 is memoryless
         b[3 * P:4 * P] += 4.0                                                 # output gate open
-    # ---- joint: hidden 0..27 = label trace (prediction half only), hidden 28.. = random evidence (encoder half only)
+    # ---- joint fc1: hidden 0..27 = label trace (prediction half only), 28 = burst detector (encoder half only),
+    #      29.. = random evidence (encoder half, plus a little of the prediction state)
     w1 = torch.zeros((J, H + P))
-    w1[NL:, :H] = torch.randn((J - NL, H), generator=g) * (evidence_gain / math.sqrt(H))
-    w1[NL:, H:] = torch.randn((J - NL, P), generator=g) * (0.5 / math.sqrt(P))
+    w1[E0:, :H] = torch.randn((J - E0, H), generator=g) * (evidence_gain / math.sqrt(H))
+    w1[E0:, H:] = torch.randn((J - E0, P), generator=g) * (0.5 / math.sqrt(P))
     w1[torch.arange(NL), H + torch.arange(NL)] = 8.0
+    b1 = torch.zeros(J)
+    gb = torch.Generator().manual_seed(seed + 2000 + burst_seed)
+    w1[NL, :H] = torch.randn(H, generator=gb) * (evidence_gain / math.sqrt(H))
+    b1[NL] = -burst_threshold
     sd["joint_net.0.weight"] = w1
-    sd["joint_net.0.bias"] = torch.zeros(J)
+    sd["joint_net.0.bias"] = b1
+    # ---- joint fc2: label logit = 10 + evidence - penalty * trace + 40 * burst; BLANK logit = 10 + blank_bias
     w2 = torch.zeros((V, J))
-    w2[:, NL:] = torch.randn((V, J - NL), generator=g) * (evidence_gain / math.sqrt(J - NL))
+    w2[:NL, E0:] = torch.randn((NL, J - E0), generator=g) * (evidence_gain / math.sqrt(J - E0))
     w2[torch.arange(NL), torch.arange(NL)] = -penalty
+    w2[:NL, NL] = 40.0
     sd["joint_net.3.weight"] = w2
     b2 = torch.full((V,), 10.0)      # keeps every real logit above the three zero pad columns of the 32-wide argmax
     b2[RNNTParam.BLANK] += blank_bias
