@@ -33,6 +33,7 @@ def lib():
         build()
         _lib = ctypes.CDLL(_LIB_PATH)
         _lib.orc_greedy_decode.restype = ctypes.c_int
+        _lib.orc_greedy_decode_trace.restype = ctypes.c_int
         _lib.orc_greedy_update.restype = ctypes.c_int
         _lib.orc_selfcheck.restype = ctypes.c_int
         assert _lib.orc_selfcheck() == 0
@@ -176,7 +177,7 @@ def greedy_update(symbols, symbols_added, res, res_idx, f, f_lens, time_idx, fi,
 
 
 def greedy_decode(f, f_lens, params, res, res_idx, symbols_added, time_idx, pre_g, pre_hg, pre_cg, y1_pre=None,
-                  max_iters=1 << 30):
+                  max_iters=1 << 30, trace=None):
     """Batch-lockstep decode loop on an encoded batch; state arrays are updated in place.
 
     params: dict with embed [28,P], pred_w_ih/pred_w_hh (lists of 2 [4P,P]), pred_bias (list of 2 [4P]),
@@ -200,12 +201,21 @@ def greedy_decode(f, f_lens, params, res, res_idx, symbols_added, time_idx, pre_
                   (pre_cg[1], np.float32)):
         assert a.dtype == dt and a.flags.c_contiguous
     f_lens = _c(f_lens, np.int32)
-    iters = lib().orc_greedy_decode(
-        _p(f), _p(f_lens), t2, n, c, p, j, _p(keep[0]), arr2(*[w.ctypes.data for w in wih]),
-        arr2(*[w.ctypes.data for w in whh]), arr2(*[b.ctypes.data for b in bs]), _p(wt), _p(wp), _p(b1), _p(w2), _p(b2),
-        _p(y1), _p(res), res.shape[1], _p(res_idx), _p(symbols_added), _p(time_idx), _p(pre_g), _p(pre_hg[0]),
-        _p(pre_hg[1]), _p(pre_cg[0]), _p(pre_cg[1]), int(max_iters))
-    return iters
+    args = [_p(f), _p(f_lens), t2, n, c, p, j, _p(keep[0]), arr2(*[w.ctypes.data for w in wih]),
+            arr2(*[w.ctypes.data for w in whh]), arr2(*[b.ctypes.data for b in bs]), _p(wt), _p(wp), _p(b1), _p(w2), _p(b2),
+            _p(y1), _p(res), res.shape[1], _p(res_idx), _p(symbols_added), _p(time_idx), _p(pre_g), _p(pre_hg[0]),
+            _p(pre_hg[1]), _p(pre_cg[0]), _p(pre_cg[1]), int(max_iters)]
+    if trace is None:
+        return lib().orc_greedy_decode(*args)
+    # trace: dict(sym int8 [N, M], margin fp32 [N, M], count int32 [N]) filled with every lane's decisions (argmax and
+    # top-2 logit margin) while the lane is unfinished
+    m = trace["sym"].shape[1]
+    assert trace["sym"].dtype == np.int8 and trace["margin"].dtype == np.float32 and trace["count"].dtype == np.int32
+    return lib().orc_greedy_decode_trace(*args, _p(trace["sym"]), _p(trace["margin"]), _p(trace["count"]), m)
+
+
+def new_decision_trace(n, m):
+    return dict(sym=np.full((n, m), -1, np.int8), margin=np.zeros((n, m), np.float32), count=np.zeros(n, np.int32))
 
 
 def elementwise(name, *arrays, out_dtype, scale=None):

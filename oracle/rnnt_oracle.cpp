@@ -517,12 +517,44 @@ ORC_API int orc_greedy_update(const int64_t* symbols, int32_t* symbols_added, in
 //   Symbols >= 28 fed back as pre_g (only the 3 zero pad columns can produce 29..31, a case in which
 //   the reference's embedding lookup raises) use a zero embedding like SOS.
 // Returns the number of loop iterations executed.
+// Optional decision trace (the top-2 logit margin report of SURVEY 7.2): for every lane, the first M decisions it took
+// while unfinished — dec_sym [N][M] int8 (the argmax) and dec_margin [N][M] fp32 (best - second best of the 32
+// logits), dec_count [N] — so that a transcript difference can be attributed to the decision it started at.
+static int greedy_decode_impl(const uint16_t* f, const int32_t* f_lens, int T2, int N, int C, int P, int J,
+                              const uint16_t* embed, const uint16_t* const* w_ih, const uint16_t* const* w_hh,
+                              const float* const* bias, const uint16_t* w_trans, const uint16_t* w_pred, const float* b1,
+                              const uint16_t* w2, const float* b2, const uint16_t* y1_pre, int32_t* res, int L,
+                              int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
+                              uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int max_iters,
+                              int8_t* dec_sym, float* dec_margin, int32_t* dec_count, int M);
 ORC_API int orc_greedy_decode(const uint16_t* f, const int32_t* f_lens, int T2, int N, int C, int P, int J,
                               const uint16_t* embed, const uint16_t* const* w_ih, const uint16_t* const* w_hh,
                               const float* const* bias, const uint16_t* w_trans, const uint16_t* w_pred, const float* b1,
                               const uint16_t* w2, const float* b2, const uint16_t* y1_pre, int32_t* res, int L,
                               int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
                               uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int max_iters) {
+  return greedy_decode_impl(f, f_lens, T2, N, C, P, J, embed, w_ih, w_hh, bias, w_trans, w_pred, b1, w2, b2, y1_pre, res, L,
+                            res_idx, symbols_added, time_idx, pre_g, pre_hg0, pre_hg1, pre_cg0, pre_cg1, max_iters, nullptr,
+                            nullptr, nullptr, 0);
+}
+ORC_API int orc_greedy_decode_trace(const uint16_t* f, const int32_t* f_lens, int T2, int N, int C, int P, int J,
+                                    const uint16_t* embed, const uint16_t* const* w_ih, const uint16_t* const* w_hh,
+                                    const float* const* bias, const uint16_t* w_trans, const uint16_t* w_pred, const float* b1,
+                                    const uint16_t* w2, const float* b2, const uint16_t* y1_pre, int32_t* res, int L,
+                                    int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
+                                    uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int max_iters,
+                                    int8_t* dec_sym, float* dec_margin, int32_t* dec_count, int M) {
+  return greedy_decode_impl(f, f_lens, T2, N, C, P, J, embed, w_ih, w_hh, bias, w_trans, w_pred, b1, w2, b2, y1_pre, res, L,
+                            res_idx, symbols_added, time_idx, pre_g, pre_hg0, pre_hg1, pre_cg0, pre_cg1, max_iters, dec_sym,
+                            dec_margin, dec_count, M);
+}
+static int greedy_decode_impl(const uint16_t* f, const int32_t* f_lens, int T2, int N, int C, int P, int J,
+                              const uint16_t* embed, const uint16_t* const* w_ih, const uint16_t* const* w_hh,
+                              const float* const* bias, const uint16_t* w_trans, const uint16_t* w_pred, const float* b1,
+                              const uint16_t* w2, const float* b2, const uint16_t* y1_pre, int32_t* res, int L,
+                              int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
+                              uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int max_iters,
+                              int8_t* dec_sym, float* dec_margin, int32_t* dec_count, int M) {
   std::vector<uint16_t> fi((size_t)N * C), x((size_t)N * P), hg0((size_t)N * P), hg1((size_t)N * P), y((size_t)N * J);
   std::vector<uint16_t> y1((size_t)N * J);
   std::vector<int32_t> cur_t(N, 0);   // frame index whose features are in fi
@@ -557,6 +589,13 @@ ORC_API int orc_greedy_decode(const uint16_t* f, const int32_t* f_lens, int T2, 
       int best = 0;
       for (int k = 1; k < 32; ++k) if (l[k] > l[best]) best = k;   // first maximum, like torch.argmax
       symbols[n] = best;
+      if (dec_sym && time_idx[n] < f_lens[n] && dec_count[n] < M) {
+        float second = -INFINITY;
+        for (int k = 0; k < 32; ++k) if (k != best && l[k] > second) second = l[k];
+        dec_sym[(size_t)n * M + dec_count[n]] = (int8_t)best;
+        dec_margin[(size_t)n * M + dec_count[n]] = l[best] - second;
+        ++dec_count[n];
+      }
     }
     int done = orc_greedy_update(symbols.data(), symbols_added, res, res_idx, f, f_lens, time_idx, fi.data(), pre_g,
                                  pre_hg0, pre_hg1, pre_cg0, pre_cg1, hg0.data(), hg1.data(), cg0.data(), cg1.data(), N, L, C, P);

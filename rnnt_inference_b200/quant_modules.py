@@ -1,187 +1,148 @@
-"""Quantizers and weight packing (reference: models/quant_modules.py).
+"""Symmetric int8 quantisers and weight packing for the B200 path.
 
-Same classes, buffers and scale algebra as the reference (scale = 127/amax, round-half-even, clamp
-[-128,127], `_amax` registered as a buffer so calibrated checkpoints load).  The one deliberate difference:
-`transpose_tile_weight{,_bf16}` keep their names and call signature but do not produce the AMX VNNI tiles of
-quant_modules.py:177-208 — an x86 detail.  The sm_100a kernels read weights K-major through TMA
-(SWIZZLE_128B) straight into tcgen05 shared-memory descriptors, for which the natural packed form is the
-plain row-major [out_features, in_features] matrix, K zero-padded to a multiple of 64 (int8) / 32 (bf16)
-when `padding` is set.
+Interface contract with the reference (models/quant_modules.py), kept so that calibrated MLPerf checkpoints and the
+loader code of quant_lstm.py / quant_linear.py work unchanged:
+  * a quantiser is an nn.Module whose range lives in a buffer named `_amax` (that is the key calibrated checkpoints
+    carry), exposes `.amax`, `.scale` (= 127 / amax), `.mode`, and is called on a tensor;
+  * mode "quant" -> int8 = clamp(round_half_even(x * scale), -128, 127); "fake_quant" -> the same grid back in fp32;
+    "calib" -> passes x through and widens amax to cover it; None / "f32" -> identity;
+  * descriptors QUANT_{LSTM,LINEAR}_{ACTIVA,WEIGHT} are the mutable mode switches the LSTM / Linear builders flip
+    before constructing their quantisers;
+  * `transpose_tile_weight{,_bf16}(w_t, padding)` take the logical W^T [K, OC] like the reference's packers.
+Everything else is this package's own: there is no VNNI / AMX tiling (quant_modules.py:177-208 is an x86 layout) —
+the sm_100a kernels read weights K-major through TMA (SWIZZLE_128B) straight into tcgen05 shared-memory
+descriptors, so the packed form is the plain row-major [OC, K] matrix, K zero-padded to 64 (int8) on request.
 """
 import torch
-import torch.nn as nn
-from torch import Tensor
+from torch import Tensor, nn
+
+INT8_MAX = 127.0
+INT8_MIN = -128.0
 
 
-def round_and_clamp(inputs: Tensor, _min: float, _max: float):
-    return torch.clamp(inputs.round(), _min, _max)
-
-
-def clamp_and_round(inputs: Tensor, _min: float, _max: float):
-    return torch.round(torch.clamp(inputs, _min, _max))
+def round_and_clamp(x: Tensor, lo: float, hi: float) -> Tensor:
+    """Round half to even, then saturate (the order matters only at +-0.5 beyond the bounds, where both agree)."""
+    return x.round().clamp_(lo, hi)
 
 
 class QuantDescriptor:
-    def __init__(self, axis=None, amax=None, mode="quant", **kwargs):
-        self._axis = axis
-        self._amax = amax
-        self._mode = mode
-        self._update_amax = kwargs.pop("update_amax", False)
-        self._narrow_bound = kwargs.pop("narrow_bound", False)
+    """Mode switch shared by the quantisers built from it: mode in {None, "f32", "calib", "quant", "fake_quant"}."""
 
-    @property
-    def axis(self):
-        return self._axis
-
-    @property
-    def amax(self):
-        return self._amax
-
-    @property
-    def mode(self):
-        return self._mode
-
-    @mode.setter
-    def mode(self, mode):
-        self._mode = mode
-
-    @property
-    def update_amax(self):
-        return self._update_amax
-
-    @property
-    def narrow_bound(self):
-        return self._narrow_bound
+    def __init__(self, axis=None, amax=None, mode="quant", update_amax=False, narrow_bound=False):
+        self.axis = axis
+        self.amax = amax
+        self.mode = mode
+        self.update_amax = update_amax
+        self.narrow_bound = narrow_bound
 
 
-QUANT_LINEAR_ACTIVA = QuantDescriptor(axis=None, amax=None, mode="fake_quant", update_amax=False)
-QUANT_LINEAR_WEIGHT = QuantDescriptor(axis=None, amax=None, mode="fake_quant")
-QUANT_LSTM_ACTIVA = QuantDescriptor(axis=None, amax=None, mode="fake_quant", update_amax=False)
-QUANT_LSTM_WEIGHT = QuantDescriptor(axis=None, amax=None, mode="fake_quant")
+QUANT_LINEAR_ACTIVA = QuantDescriptor(mode="fake_quant")
+QUANT_LINEAR_WEIGHT = QuantDescriptor(mode="fake_quant")
+QUANT_LSTM_ACTIVA = QuantDescriptor(mode="fake_quant")
+QUANT_LSTM_WEIGHT = QuantDescriptor(mode="fake_quant")
 
 
 class TensorQuantizer(nn.Module):
-    """Per-tensor symmetric int8 quantizer; modes calib / quant / fake_quant (quant_modules.py:59-152)."""
+    """Per-tensor symmetric int8 quantiser of activations."""
 
-    def __init__(self, quant_desc=QuantDescriptor(), **kwargs):
+    def __init__(self, quant_desc=None, name="TensorQuantizer"):
         super().__init__()
-        self._mode = quant_desc.mode
-        self._axis = quant_desc._axis
-        self._max_bound = torch.tensor(127.0, dtype=torch.float32)
-        self._min_bound = -self._max_bound if quant_desc.narrow_bound else -self._max_bound - 1
-        self.amax = torch.tensor(quant_desc._amax) if quant_desc._amax is not None else torch.tensor(0.0)
-        self._scale = torch.tensor(0.0)
-        self._name = kwargs.pop("name", "TensorQuantizer")
-        self._update_amax = quant_desc.update_amax
-        self._track_amax = False
-        self._amaxs = []
+        desc = quant_desc if quant_desc is not None else QuantDescriptor()
+        self._mode = desc.mode
+        self._axis = desc.axis
+        self._update_amax = desc.update_amax
+        self._lo = -INT8_MAX if desc.narrow_bound else INT8_MIN
+        self._name = name
+        self.register_buffer("_amax", torch.tensor(float(desc.amax) if desc.amax is not None else 0.0))
 
+    # -- range / scale
     @property
     def mode(self):
         return self._mode
 
     @property
-    def amax(self):
-        return self._amax if hasattr(self, "_amax") else None
+    def amax(self) -> Tensor:
+        return self._amax
 
     @amax.setter
     def amax(self, value):
-        if not hasattr(self, "_amax"):
-            self.register_buffer("_amax", value)
-        else:
-            self._amax = value
+        self._amax = torch.as_tensor(value, dtype=torch.float32).detach().to(self._amax.device)
 
     @property
-    def scale(self):
-        return self._max_bound.to(self.amax.device) / self.amax
+    def scale(self) -> Tensor:
+        return INT8_MAX / self._amax          # fp32 division, like the reference's `_max_bound / amax`
 
-    @scale.setter
-    def scale(self, value):
-        self._scale = value
+    def _range_of(self, x: Tensor) -> Tensor:
+        if self._axis is None:
+            return x.abs().max()
+        return x.abs().max(self._axis).values.unsqueeze(self._axis)
 
-    def calib_amax(self, inputs):
-        cur_amax = inputs.abs().max()
-        self.amax = torch.max(self.amax.to(cur_amax.device), cur_amax)
-        if self._track_amax:
-            self._amaxs.append(cur_amax)
+    def calib_amax(self, x: Tensor):
+        self.amax = torch.maximum(self._amax, x.abs().max().to(self._amax.device))
 
-    def _quant_forward(self, inputs: Tensor) -> Tensor:
-        outputs = round_and_clamp(inputs * self.scale, float(self._min_bound), float(self._max_bound))
-        return outputs.type(torch.int8)
+    # -- the three mappings
+    def _grid(self, x: Tensor) -> Tensor:
+        return round_and_clamp(x * self.scale, self._lo, INT8_MAX)
 
-    def _fake_quant_forward(self, inputs):
+    def _quant_forward(self, x: Tensor) -> Tensor:
+        return self._grid(x).to(torch.int8)
+
+    def _fake_quant_forward(self, x: Tensor) -> Tensor:
         if self._update_amax:
-            if self._axis is not None:
-                self.amax = torch.max(inputs.abs(), self._axis).values.unsqueeze(self._axis)
-            else:
-                self.amax = torch.max(inputs.abs())
-        outputs = round_and_clamp(inputs * self.scale, float(self._min_bound), float(self._max_bound))
-        outputs /= self.scale
-        return outputs
+            self.amax = self._range_of(x)
+        return self._grid(x) / self.scale
 
-    def forward(self, inputs: Tensor) -> Tensor:
-        outputs = inputs
+    def forward(self, x: Tensor) -> Tensor:
         if self._mode == "calib":
-            self.calib_amax(inputs)
-        elif self._mode == "quant":
-            outputs = self._quant_forward(inputs)
-        elif self._mode == "fake_quant":
-            outputs = self._fake_quant_forward(inputs)
-        return outputs
+            self.calib_amax(x)
+            return x
+        if self._mode == "quant":
+            return self._quant_forward(x)
+        if self._mode == "fake_quant":
+            return self._fake_quant_forward(x)
+        return x
 
-    def __str__(self):
-        return (f" name=${self._name}\n mode=${self._mode}\n axis=${self._axis}\n amax=${self._amax}\n"
-                f" scale=${self._scale}\n max_bound=${self._max_bound}\n min_bound=${self._min_bound}")
-
-
-def _pack_k_major(weight: Tensor, padding: bool, k_mult: int) -> Tensor:
-    """weight: logical W^T of shape [K, OC] (the reference passes w.transpose(1, 0)).  Returns [OC, K(_padded)]."""
-    k, oc = weight.shape
-    packed = weight.transpose(1, 0)
-    if padding and k % k_mult != 0:
-        packed = torch.nn.functional.pad(packed, (0, k_mult - k % k_mult), "constant", 0)
-    return packed.contiguous()
-
-
-def transpose_tile_weight_bf16(weight, padding: bool = False):
-    """Same call as quant_modules.py:177-193; B200 layout: K-major [OC(_pad to 32 when padding), K] bf16."""
-    packed = _pack_k_major(weight, False, 32)
-    if padding and packed.shape[0] % 32 != 0:
-        packed = torch.nn.functional.pad(packed, (0, 0, 0, 32 - packed.shape[0] % 32), "constant", 0.0)
-    return packed.contiguous()
-
-
-def transpose_tile_weight(weight, padding: bool = False):
-    """Same call as quant_modules.py:196-212; B200 layout: K-major [OC, K(_pad to 64 when padding)] int8."""
-    return _pack_k_major(weight, padding, 64)
+    def extra_repr(self):
+        return f"name={self._name}, mode={self._mode}, axis={self._axis}, amax={float(self._amax.max()):.6g}"
 
 
 class WeightQuantizer(TensorQuantizer):
-    def __init__(self, quant_desc=QuantDescriptor(), **kwargs):
-        super().__init__(quant_desc)
+    """Per-layer symmetric int8 quantiser of weights; never calibrates from data (its amax is set from the weights)."""
 
-    def _quant_forward(self, inputs: Tensor, first_layer: bool = False) -> Tensor:
-        outputs = round_and_clamp(inputs * self.scale, float(self._min_bound), float(self._max_bound))
-        outputs = outputs.type(torch.int8)
-        if first_layer:
-            return transpose_tile_weight(outputs.transpose(1, 0), True)
-        return transpose_tile_weight(outputs.transpose(1, 0))
+    def __init__(self, quant_desc=None, name="WeightQuantizer"):
+        super().__init__(quant_desc, name)
 
-    def _fake_quant_forward(self, inputs):
-        if self._scale is None:
-            if self._axis is not None:
-                self.amax = torch.max(inputs.abs(), self._axis).values.unsqueeze(self._axis)
-            else:
-                self.amax = torch.max(inputs.abs())
-            self.scale = self._max_bound / self.amax
-        outputs = round_and_clamp(inputs * self.scale, float(self._min_bound), float(self._max_bound))
-        outputs /= self.scale
-        return outputs
+    def _quant_forward(self, w: Tensor, first_layer: bool = False) -> Tensor:
+        """[OC, K] fp32 -> packed int8 [OC, K] (K zero-padded to a multiple of 64 for the first layer, 240 -> 256)."""
+        return transpose_tile_weight(self._grid(w).to(torch.int8).transpose(1, 0), padding=first_layer)
 
-    def forward(self, inputs: Tensor) -> Tensor:
-        outputs = inputs
+    def forward(self, w: Tensor) -> Tensor:
         if self._mode == "quant":
-            outputs = self._quant_forward(inputs)
-        elif self._mode == "fake_quant":
-            outputs = self._fake_quant_forward(inputs)
-        return outputs
+            return self._quant_forward(w)
+        if self._mode == "fake_quant":
+            if float(self._amax.max()) == 0.0:
+                self.amax = self._range_of(w)
+            return self._grid(w) / self.scale
+        return w
+
+
+def _k_major(w_t: Tensor, k_multiple: int, pad_k: bool) -> Tensor:
+    """w_t: logical W^T [K, OC] -> contiguous [OC, K], K zero-padded up to `k_multiple` when asked."""
+    w = w_t.transpose(1, 0)
+    k = w.shape[1]
+    if pad_k and k % k_multiple:
+        w = torch.nn.functional.pad(w, (0, k_multiple - k % k_multiple))
+    return w.contiguous()
+
+
+def transpose_tile_weight(weight: Tensor, padding: bool = False) -> Tensor:
+    """int8 packer: K-major [OC, K], K padded to a multiple of 64 when `padding` (one 128-byte TMA row = 2 x 64)."""
+    return _k_major(weight, 64, padding)
+
+
+def transpose_tile_weight_bf16(weight: Tensor, padding: bool = False) -> Tensor:
+    """bf16 packer: K-major [OC, K]; `padding` rounds OC up to 32 rows of zeros (fc2: 29 -> 32 logits)."""
+    w = _k_major(weight, 32, False)
+    if padding and w.shape[0] % 32:
+        w = torch.nn.functional.pad(w, (0, 0, 0, 32 - w.shape[0] % 32))
+    return w.contiguous()
