@@ -1,18 +1,26 @@
 #!/usr/bin/env python
 """bench.py — Offline utterances/s of the int8 RNN-T hot path on N B200s (+ encoder LSTM-step us).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--scaling weak|strong]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (BASELINE.json config 3, per-GPU share): one STEP = one Offline query of 2513 synthetic utterances per GPU
-(dev-clean-like length distribution, 240-dim stacked filterbank features, random-init weights with synthetic
-calibration ranges), sorted by length and cut into ragged batches of <= 256 like PytorchSUT.issue_queries.  Weak
-scaling: every rank decodes its own query; the only collective is the gather of transcripts at the end of a query.
+Workload (BASELINE.json config 3): one STEP = one Offline query of synthetic utterances (dev-clean-like length
+distribution, 240-dim stacked filterbank features, random-init weights with synthetic calibration ranges), sorted by
+length descending like PytorchSUT.issue_queries; the sorted utterances are dealt round-robin to the ranks and every rank
+cuts its share into ragged batches of <= --batch (2048 on B200; the reference's CPU run uses 256).  Weak scaling
+(default): 2513 utterances per GPU per step.  Strong scaling (--scaling strong): ONE query of 24576 samples
+(configs/mlperf.conf:63) for the whole job.  The only collective is the single all_gather of (id, length, tokens) that
+ends a query.
 
-  value  utterances/s with the query's features already in HBM (device-timed, CUDA events, max over ranks)
+  value  utterances/s with the query's features already in HBM (device-timed with CUDA events, max over ranks); no
+         per-kernel instrumentation runs inside this timed region
   e2e    the same metric through PytorchSUT + the LoadGen shim with HOST (pinned) features: host->device copies and
          the device->host token read are inside the timed region
-  roofline      the persistent recurrent LSTM kernel (the dominant kernel), timed live with CUDA events
+  roofline      the persistent recurrent LSTM kernel (the dominant kernel), bracketed by CUDA events in a separate,
+                untimed pass over the same step; bytes = TRUE (frame, utterance) pairs x the per-unit figure
+  lstm_step_us_c2 / encoder_microbench   BASELINE config 2: encoder only, 256 x 500 frames
+  parity        transcripts of the cpu_baseline's utterances decoded by the GPU path in the same batches, compared with
+                the CPU oracle's (identical utterances, token agreement, WER, top-2 margin attribution)
   cpu_baseline  the CPU oracle (a restatement of the reference's AMX path) on the host cores, bounded sample
 `--impl reference` prints the reference arm: the same CPU path timed on the host cores on a bounded sample.
 """
@@ -34,6 +42,7 @@ import torch
 
 UTTS_PER_GPU = 2513       # configs/mlperf.conf:13 performance_sample_count of the reference
 BATCH = 2048              # SUT batch size on B200 (the reference CPU run uses 256, run.sh:71): more 128-row tiles per CTA in the recurrent kernel; <= 2240 decode lanes per launch, multiple of 128 for ragged tile skipping
+QUERY_TOKEN_CAP = 256     # token columns of the transcript gather: the longest utterance has 250 stacked frames; a longer row is clipped in the gather (never observed: ~0.27 tokens per stacked frame)
 METRIC = "offline_utterances_per_second"
 UNIT = "utterances/s"
 
@@ -49,7 +58,10 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--microbench", action="store_true", help="also run config 2: encoder only, 256 x 500 frames")
+    ap.add_argument("--no-microbench", action="store_true", help="skip config 2 (encoder only, 256 x 500 frames)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the post-run transcript check against the CPU oracle")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--query", type=int, default=24576, help="samples of the one query of --scaling strong (configs/mlperf.conf:63)")
     return ap.parse_args()
 
 
@@ -111,13 +123,14 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ workload
-def build_query(world, rank, utts_per_gpu, batch):
-    """Global query = world * utts_per_gpu utterances (lengths: fixed-seed gamma fit of dev-clean), sorted by length
-    descending and cut into batches of `batch` (PytorchSUT.issue_queries); batch j belongs to rank j % world
-    (SURVEY.md 8(e)).  Returns this rank's list of batches, each a list of (utt_id, length)."""
+def build_query(world, rank, utts_per_gpu, batch, total=None):
+    """Global query = `total` utterances (default world * utts_per_gpu; lengths: fixed-seed gamma fit of dev-clean, the
+    2513 distinct utterances replicated beyond like MLPerf does), sorted by length descending
+    (PytorchSUT.issue_queries) and dealt round-robin to the ranks; each rank cuts its share into batches of `batch`
+    (SURVEY.md 8(e)).  Returns this rank's list of batches, each a list of (utt_id, length), and the query's frames."""
     from rnnt_inference_b200 import sharding, synthetic as S
-    total = world * utts_per_gpu
-    lens = S.utterance_lengths(UTTS_PER_GPU)            # 2513 distinct utterances, replicated beyond (like MLPerf)
+    total = world * utts_per_gpu if total is None else total
+    lens = S.utterance_lengths(UTTS_PER_GPU)
     ulen = lens[np.arange(total) % UTTS_PER_GPU]
     return sharding.shard_batches(ulen, batch, world, rank), int(ulen.sum())
 
@@ -159,9 +172,10 @@ def stage_on_device(batches, feats, device):
     return staged
 
 
-def run_step_device(decoder, staged, world=1):
-    """One step = one pass over this rank's query, inputs already in HBM; with N > 1 the step ends with the gather of
-    (sample id, length, tokens) from all ranks (the path's only collective).  Returns emitted-token count tensor."""
+def run_step_device(decoder, staged, world=1, n_max=None):
+    """One step = one pass over this rank's query, inputs already in HBM; with N > 1 the step ends with the ONE
+    all_gather of (sample id, length, tokens) from all ranks (the path's only collective; n_max = rows per rank and the
+    token width are known from the query, so no shape exchange).  Returns (emitted-token count tensor, outputs)."""
     from rnnt_inference_b200 import sharding
     total, outs = None, []
     cap = max((m + 1) // 2 for _p, _o, _l, m, _n, _h, _i in staged) if staged else 1
@@ -177,7 +191,8 @@ def run_step_device(decoder, staged, world=1):
     if world > 1:
         dev = staged[0][0].device if staged else torch.device("cuda", torch.cuda.current_device())
         cat = lambda k, dt, shape: torch.cat([o[k] for o in outs], 0) if outs else torch.empty(shape, dtype=dt, device=dev)
-        sharding.gather_transcripts(cat(0, torch.int64, (0,)), cat(1, torch.int32, (0,)), cat(2, torch.int32, (0, cap)), world)
+        sharding.gather_transcripts(cat(0, torch.int64, (0,)), cat(1, torch.int32, (0,)), cat(2, torch.int32, (0, cap)), world,
+                                    n_max=n_max, l_max=QUERY_TOKEN_CAP)
     return total
 
 
@@ -191,12 +206,12 @@ def recurrent_roofline(events, peaks):
     recs = events.get("lstm_recurrent", [])
     if not recs:
         return None, None
-    tot_ms, tot_bytes, tot_ops, steps = 0.0, 0.0, 0.0, 0
-    for start, end, (t, n, last) in recs:
+    tot_ms, tot_bytes, tot_ops, items = 0.0, 0.0, 0.0, 0
+    for start, end, (rows, tile_items, last) in recs:   # rows = TRUE (frame, utterance) pairs of the launch (ops.lstm_layer_i8)
         tot_ms += start.elapsed_time(end)
-        tot_bytes += float(t) * n * (24576 if last else 23552)
-        tot_ops += float(t) * n * 2 * 1024 * 4096
-        steps += t
+        tot_bytes += float(rows) * (24576 if last else 23552)
+        tot_ops += float(rows) * 2 * 1024 * 4096
+        items += tile_items
     launches = len(recs)
     achieved = tot_bytes / (tot_ms * 1e-3) / 1e9
     peak = peaks.get("hbm_gbs", 6650.0)
@@ -206,11 +221,12 @@ def recurrent_roofline(events, peaks):
     traffic = round(NCU_TRAFFIC_RATIO * tot_bytes / launches)
     roof = {"kernel": "lstm_recurrent_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
             "frac": round(achieved / peak, 4), "traffic": traffic,
+            "bytes_basis": "true (frame, utterance) pairs x 23552 B (24576 B for the bf16 last layer); tile padding and rows past an utterance's end are not counted",
             "traffic_source": "ncu --set full, one launch N=1024 T=100: 1.789 GB dram r+w / 2.412 GB algorithmic = 0.742, scaled to this run's mean launch",
             "peak_source": peaks.get("_source", "fallback"),
             "launches": launches, "avg_launch_ms": round(tot_ms / launches, 4),
             "algorithmic_bytes_per_launch": round(tot_bytes / launches), "tensor_top_s": round(tot_ops / (tot_ms * 1e-3) / 1e12, 1)}
-    return roof, tot_ms * 1e3 / steps     # second value: mean us per (layer, timestep)
+    return roof, tot_ms * 1e3 / items     # second value: mean us per (layer, timestep, 128-row tile) item
 
 
 def kernel_shares(events):
@@ -233,35 +249,79 @@ def load_peaks():
 
 
 # ------------------------------------------------------------------------------------------------ CPU baseline
-def cpu_baseline(sd, world_batches, mean_frames, budget_s):
+def host_threads():
+    """Threads the CPU arm may use: every core this process is allowed on (torch.distributed.run exports
+    OMP_NUM_THREADS=1, which must not turn the baseline into a single-thread run)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_baseline(sd, world_batches, mean_frames, budget_s, keep_chunks=False):
     """The CPU oracle (restatement of the reference's int8/bf16 path, OpenMP over the batch) on the host cores, on
     contiguous chunks of the length-sorted query taken at spread quantiles.  Throughput is frames-weighted:
     (frames processed / seconds) / mean frames per utterance of the query, so a short sample is not biased by the
-    lengths it happened to contain."""
+    lengths it happened to contain.  keep_chunks: also return [(utterances, tokens, decision trace)] per chunk for the
+    transcript check of the GPU path."""
+    from oracle import oracle as O
     from oracle import pipeline as OP
     from rnnt_inference_b200 import synthetic as S
-    cores = os.cpu_count() or 1
+    cores = O.set_num_threads(host_threads())
     chunk = int(min(256, max(32, cores)))
     flat = [u for b in world_batches for u in b]          # (utt_id, length), sorted by length descending
     params = OP.prepare_params(sd)
-    frames, utts, elapsed, used = 0, 0, 0.0, []
+    frames, utts, elapsed, used, kept = 0, 0, 0.0, [], []
     for q in (0.5, 0.25, 0.75, 0.125, 0.625, 0.375, 0.875):
         start = int(q * max(0, len(flat) - chunk))
         part = flat[start:start + chunk]
         feats = [S.make_features(n, u % UTTS_PER_GPU) for u, n in part]
         x, xl = OP.pad_batch(feats, pad_to=32)
+        trace = O.new_decision_trace(x.shape[1], int(xl.max()) + 96) if keep_chunks else None
         t0 = time.perf_counter()
-        OP.greedy_decode_batch(params, x, xl)
+        res, res_len, _ = OP.greedy_decode_batch(params, x, xl, trace=trace)
         elapsed += time.perf_counter() - t0
         frames += int(sum(n for _, n in part))
         utts += len(part)
         used.append(q)
+        if keep_chunks:
+            kept.append((part, [list(res[i, :res_len[i]]) for i in range(len(part))], trace))
         if elapsed >= budget_s:
             break
     value = (frames / elapsed) / mean_frames
-    return {"value": round(value, 3), "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{utts} utterances ({frames} frames) in {len(used)} length-sorted chunks of {chunk} at quantiles {used}, "
-                      f"{elapsed:.1f} s; frames-weighted to the query's mean of {mean_frames:.1f} frames/utterance"}
+    out = {"value": round(value, 3), "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"{utts} utterances ({frames} frames) in {len(used)} length-sorted chunks of {chunk} at quantiles {used}, "
+                     f"{elapsed:.1f} s; frames-weighted to the query's mean of {mean_frames:.1f} frames/utterance"}
+    return (out, kept) if keep_chunks else out
+
+
+def parity_check(decoder, chunks, device):
+    """Decode the cpu_baseline's chunks on the GPU in the same batches (same utterances, same order, N padded to 32) and
+    compare the transcripts with the oracle's: identical utterances, token agreement, WER against the oracle, and the
+    top-2 logit margin at the decision every difference starts at (the hoisted f.W_trans runs on the tensor cores, so a
+    near-tie may flip — SURVEY 7.2)."""
+    from rnnt_inference_b200 import eval_accuracy as E
+    from rnnt_inference_b200 import synthetic as S
+    test, truth, traces = [], [], []
+    for part, toks, trace in chunks:
+        feats = {u % UTTS_PER_GPU: S.make_features(n, u % UTTS_PER_GPU) for u, n in part}
+        (packed, offsets, lens, max_len, n_actual, lens_host, _ids), = stage_on_device([part], feats, device)
+        with torch.no_grad():
+            res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len, lens_host)
+        res, res_len = res.cpu().numpy(), res_len.cpu().numpy()
+        test += [list(res[i, :res_len[i]]) for i in range(n_actual)]
+        truth += toks
+        traces.append({k: v[:n_actual] for k, v in trace.items()})
+    m = max(t["sym"].shape[1] for t in traces)
+    pad = lambda a, fill: np.pad(a, ((0, 0), (0, m - a.shape[1])), constant_values=fill)
+    trace = {"sym": np.concatenate([pad(t["sym"], -1) for t in traces]), "margin": np.concatenate([pad(t["margin"], 0) for t in traces]),
+             "count": np.concatenate([t["count"] for t in traces])}
+    rep = E.compare_transcripts(test, truth, trace, margin_tol=0.05)
+    return {"utterances": rep["utterances"], "identical_utterances": rep["identical_utterances"],
+            "tokens": rep["tokens_truth"], "token_agreement": round(rep["token_agreement"], 6),
+            "wer_vs_oracle": round(rep["wer_vs_truth"], 6), "differing": [(d["utterance"], d["first_differing_token"], round(d.get("margin", -1), 5)) for d in rep["differences"]][:16],
+            "differences_not_at_a_near_tie": len(rep["unexplained"]), "margin_tol": 0.05,
+            "margin_quantiles": {str(k): round(v, 5) for k, v in rep.get("margin_quantiles", {}).items()}}
 
 
 def reference_arm(args):
@@ -277,6 +337,8 @@ def reference_arm(args):
     per_step = max(3.0, min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup)))
     for _ in range(min(args.warmup, 1)):
         cpu_baseline(sd, batches, mean_frames, 0.0)
+    print(f"[bench] reference arm: {host_threads()} host threads (OMP_NUM_THREADS in the environment was "
+          f"{os.environ.get('OMP_NUM_THREADS', 'unset')}; the oracle's team size is set explicitly)", file=sys.stderr)
     vals, last = [], None
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -287,7 +349,7 @@ def reference_arm(args):
     last["value"] = round(value, 3)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(ms, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": args.warmup, "ms_per_step": round(ms, 1), "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "int8", "data": "synthetic",
         "config": {"workload": f"C3 Offline: {args.utts} synthetic dev-clean-length utterances per GPU, sorted, batch {args.batch}, full int8 RNN-T greedy decode",
                    "note": "CPU restatement of the reference path (oracle/), bounded sample per step"},
@@ -343,17 +405,20 @@ def main():
 
     from rnnt_inference_b200 import ops
     sd, decoder = make_model(device, args.batch)
-    batches, _ = build_query(world, rank, args.utts, args.batch)
+    strong = args.scaling == "strong"
+    total = args.query if strong else None
+    batches, _ = build_query(world, rank, args.utts, args.batch, total)
+    n_max = ((total if strong else world * args.utts) + world - 1) // world
     feats = features_for(batches)
     staged = stage_on_device(batches, feats, device)
     my_utts = sum(len(b) for b in batches)
     my_frames = sum(n for b in batches for _, n in b)
 
-    # ---- device-resident leg: W warm-up steps, then exactly K timed steps
+    # ---- device-resident leg: W warm-up steps, then exactly K timed steps (no per-kernel instrumentation inside)
     with torch.no_grad():
         for _ in range(args.warmup):
-            run_step_device(decoder, staged, world)
-        ops.telemetry.events = {}
+            run_step_device(decoder, staged, world, n_max)
+        ops.telemetry.events = None
         launches0 = ops.telemetry.launches
         sampler = ClockSampler(local)
         barrier()
@@ -362,13 +427,17 @@ def main():
         ev0.record()
         tokens = None
         for _ in range(args.steps):
-            tokens = run_step_device(decoder, staged, world)
+            tokens = run_step_device(decoder, staged, world, n_max)
         ev1.record()
         barrier()
         clocks = sampler.stop()
+        launches = ops.telemetry.launches - launches0
+        # ---- the same step once more, untimed, with every kernel of the library bracketed by CUDA events
+        ops.telemetry.events = {}
+        run_step_device(decoder, staged, world, n_max)
+        torch.cuda.synchronize()
         events = ops.telemetry.events
         ops.telemetry.events = None
-        launches = ops.telemetry.launches - launches0
     from rnnt_inference_b200 import _lib
     _lib.check_device_status()
     ms_total = reduce_scalar(ev0.elapsed_time(ev1), dist.ReduceOp.MAX if world > 1 else None)
@@ -402,23 +471,32 @@ def main():
         e2e = {"value": round(done_all / sec, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d / k_e2e),
                "d2h_bytes_per_step": int(d2h / k_e2e), "steps": k_e2e, "api": "PytorchSUT.issue_queries via loadgen_shim.StartTest"}
 
-    micro = encoder_microbench(decoder, device) if (args.microbench and rank == 0) else None
-    cpu = None
+    micro = encoder_microbench(decoder, device) if (rank == 0 and not args.no_microbench) else None
+    cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         full, total_frames = build_query(1, 0, args.utts, args.batch)
-        cpu = cpu_baseline(sd, full, total_frames / args.utts, args.cpu_seconds)
+        cpu, chunks = cpu_baseline(sd, full, total_frames / args.utts, args.cpu_seconds, keep_chunks=True)
+        if not args.no_parity:
+            parity = parity_check(decoder, chunks, device)
+            _lib.check_device_status()
     if rank == 0:
+        workload = (f"C3 Offline, strong scaling: ONE query of {total} synthetic dev-clean-length utterances for the whole job"
+                    if strong else f"C3 Offline: {args.utts} synthetic dev-clean-length utterances per GPU")
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": round(ms_per_step, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": round(ms_per_step, 2), "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "int8", "data": "synthetic",
-            "config": {"workload": f"C3 Offline: {args.utts} synthetic dev-clean-length utterances per GPU, sorted, batch {args.batch}, full int8 RNN-T greedy decode",
+            "config": {"workload": workload + f", sorted, batch {args.batch}, full int8 RNN-T greedy decode",
                        "utterances_per_gpu_per_step": my_utts, "frames_per_gpu_per_step": my_frames, "batch": args.batch,
                        "batches_per_step": len(batches), "tokens_per_step_rank0": tokens_per_step,
+                       "tokens_per_stacked_frame": round(tokens_per_step / max(1, sum((n + 1) // 2 for b in batches for _, n in b)), 4),
                        "l2": "inputs and per-layer int32 projections (up to 2 GB) exceed the 126 MB L2; no explicit flush",
-                       "parallelism": f"dp{world}: length-sorted utterances dealt round-robin to ranks, transcripts gathered over NCCL"},
+                       "parallelism": f"dp{world}: length-sorted utterances dealt round-robin to ranks, transcripts gathered with one NCCL all_gather per query"},
             "lstm_step_us": round(step_us, 3) if step_us else None,
-            "kernel_ms": shares, "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": roof, "cpu_baseline": cpu}
+            "lstm_step_us_note": "recurrent kernel, mean per (layer, timestep, 128-row batch tile) item of this workload",
+            "lstm_step_us_c2": micro["lstm_step_us"] if micro else None,
+            "kernel_ms": shares, "kernel_ms_note": "one untimed, event-bracketed pass over the same step",
+            "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": roof, "cpu_baseline": cpu, "parity": parity}
         if micro:
             line["encoder_microbench"] = micro
         print(json.dumps(line))
@@ -452,12 +530,14 @@ def encoder_microbench(decoder, device, n=256, t=500, reps=3):
         torch.cuda.synchronize()
         events = ops.telemetry.events
         ops.telemetry.events = None
-    roof, step_us = recurrent_roofline(events, load_peaks())
+    roof, item_us = recurrent_roofline(events, load_peaks())
+    step_us = item_us * ((n + 127) // 128)          # one (layer, timestep) of the whole 256-utterance batch = 2 tile items
     shares = kernel_shares(events)
     gemm_ms = shares.get("gemm_i8", 0.0) / reps
     gemm_ops = 2.0 * n * (t * (4096 * 256 + 4096 * 1024) + (t // 2) * (4096 * 2048 + 2 * 4096 * 1024))
     return {"workload": f"C2 encoder only, {n} x {t} frames", "encoder_ms": round(ev0.elapsed_time(ev1) / reps, 3),
-            "lstm_step_us": round(step_us, 3), "recurrent_roofline": roof, "gemm_ms": round(gemm_ms, 3),
+            "lstm_step_us": round(step_us, 3), "lstm_step_us_note": "recurrent kernel time / (layers x timesteps): one LSTM step of the 256-utterance batch",
+            "recurrent_roofline": roof, "gemm_ms": round(gemm_ms, 3),
             "gemm_top_s": round(gemm_ops / (gemm_ms * 1e-3) / 1e12, 1) if gemm_ms else None,
             "kernel_ms": {k: round(v / reps, 3) for k, v in shares.items()}}
 

@@ -37,6 +37,12 @@ int rnnt_device_sm_count(void);
  * instead of hanging the GPU) record a code in a 4-byte status word owned by the library.  This call
  * synchronises `stream`, returns RNNT_ERR_DEVICE if a code was recorded, and clears it. */
 int rnnt_check_device_status(void* stream);
+/* Non-synchronising pair for pipelined callers (the SUT): enqueue a copy of the status word into *host_dst (pinned host
+ * int32) on `stream`, look at it after the caller's own synchronisation point; non-zero = a watchdog fired and every
+ * result produced since is invalid.  The word is per device and sticky: later kernels of this library on the device
+ * bail out early until it is cleared (rnnt_clear_device_status, or rnnt_check_device_status). */
+int rnnt_peek_device_status(int32_t* host_dst, void* stream);
+int rnnt_clear_device_status(void* stream);
 
 /* quant_tpp::quant_ps_epi8 + K zero-pad (mlperf_plugins/csrc/lstm_amx.cpp:35-50, tpps/quant_tpp.cpp:6-17)
  * in [rows][k_in] fp32 -> out [rows][k_out] int8, out[:,k_in:] = 0.  q = clamp(rne(x*scale),-128,127) */
@@ -92,16 +98,10 @@ int rnnt_lstm_recurrent_i8_gate_blocked_ragged(const int32_t* G, const int8_t* w
                                                float in_scale, float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y,
                                                int T, int N, int H, const int32_t* tile_steps_host, void* workspace, void* stream);
 
-/* DEBUG: when set to a device buffer of T*16 int64, the next recurrent launches record clock64() stamps of CTA (0,0)
- * per timestep (h ready, first operand chunk landed, MMAs issued, accumulator ready, TMEM read, gate math done,
- * proxy fence done, published).  NULL switches it off.  Used by profiles/trace_recurrent.py only. */
-int rnnt_debug_set_recurrent_trace(void* device_buffer);
-/* TUNING/DEBUG: slice-CTAs per thread-block cluster of the recurrent kernel (1, 2 or 4; default 4, or the environment
- * variable RNNT_REC_CLUSTER).  The h tile of a batch tile is TMA-multicast inside a cluster.  Results do not depend on it. */
-int rnnt_debug_set_recurrent_cluster(int ctas);
-/* PROFILING ONLY (results become garbage): bit 0 skip the MMAs, bit 1 skip the gate math, bit 2 skip the h loads.
- * Used by profiles/trace_recurrent.py to attribute the step time; 0 = normal operation. */
-int rnnt_debug_set_recurrent_flags(int flags);
+/* TUNING (process-wide, results do not depend on it): slice-CTAs per thread-block cluster of the recurrent kernel, 1, 2, 4
+ * or 8 (default 1, or the environment variable RNNT_REC_CLUSTER); the h tile of a batch tile is TMA-multicast inside a
+ * cluster.  Measured on B200: no gain over 1 (profiles/r01/rec_cluster_v5.txt). */
+int rnnt_tune_recurrent_cluster(int ctas);
 
 /* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.
  * x [T][N][K] int8 (K % 16 == 0).  g_ws: T*N*4H int32 scratch for the projection. */
@@ -120,6 +120,24 @@ int rnnt_linear_bf16_bf16(const uint16_t* x, const uint16_t* w, uint16_t* y, int
 /* Ragged variant (see rnnt_gemm_i8_i32_ragged; rows_per_step % 64 == 0): dead rows of y are left untouched. */
 int rnnt_linear_bf16_bf16_ragged(const uint16_t* x, const uint16_t* w, uint16_t* y, int64_t M, int K, int O, int rows_per_step,
                                  const int32_t* tile_steps_host, void* stream);
+
+/* The same product on the tensor cores (tcgen05.mma kind::f16, BF16 x BF16 -> FP32 in TMEM, bf16 RNE epilogue, TMA in/out):
+ * the path the pipeline uses for the hoisted transcription half.  C[M][N] bf16 = bf16(A[M][K] . W[N][K]^T).  The order of
+ * the fp32 accumulation inside the tensor core is not the oracle's (nor AMX's): results agree to <= 1 bf16 ulp (pinned
+ * against AMX hardware output, tests/test_amx_golden.py).  K % 8 == 0, N % 64 == 0, 16-byte aligned pointers. */
+int rnnt_gemm_bf16_bf16(const uint16_t* A, const uint16_t* W, uint16_t* C, int64_t M, int N, int K, void* stream);
+/* Ragged variant (rows_per_step % 128 == 0, see rnnt_gemm_i8_i32_ragged): dead rows of C are left untouched. */
+int rnnt_gemm_bf16_bf16_ragged(const uint16_t* A, const uint16_t* W, uint16_t* C, int64_t M, int N, int K, int rows_per_step,
+                               const int32_t* tile_steps_host, void* stream);
+
+/* lstm_postop (init.cpp:126-128; lstm_postop.cpp:14-72 -> tpps/lstm_postop_tpp.cpp:12-98) as a stand-alone operator:
+ * it/ft/gt/ot fp32 [N][H] with a row pitch of `ld` floats (the four chunks of one [N][4H] tensor work in place);
+ * ct [N][H] binary16 updated IN PLACE; h_q [N][H] int8 = quant(h, in_scale); y_q int8 = quant(h, out_scale) when
+ * skip_quant_y == 0, else y_bf16 = bf16(h) (the other output pointer may be NULL).  fp16 gate math identical to the
+ * fused recurrent kernel (Pade [5/6] + VRCPPH table).  H and ld even. */
+int rnnt_lstm_postop_fp16(const float* it, const float* ft, const float* gt, const float* ot, int64_t ld, uint16_t* ct,
+                          float in_scale, float out_scale, int skip_quant_y, uint16_t* y_bf16, int8_t* y_q, int8_t* h_q, int N,
+                          int H, void* stream);
 
 /* Per-iteration operators of the reference's decode loop, for callers that keep the Python loop of
  * models/decoder.py:188-211 (the fused rnnt_greedy_decode below is the fast path; these share its arithmetic).
@@ -159,10 +177,7 @@ typedef struct {
 } rnnt_decode_weights;
 
 int64_t rnnt_greedy_decode_workspace_bytes(int N);
-/* DEBUG: device buffer of max_iters*16 int64 receiving clock64 stamps of CTA 0 per decode iteration (iteration start, LSTM
- * layer 0 done, after barrier, layer 1 + barrier, fc1 + barrier, joint/update done, after barrier, active lanes). NULL = off. */
-int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);
-/* y1 [T2][N][J] bf16 (from rnnt_linear_bf16_bf16), f_lens [N] STACKED lengths.
+/* y1 [T2][N][J] bf16 (from rnnt_gemm_bf16_bf16 or rnnt_linear_bf16_bf16), f_lens [N] STACKED lengths.
  * In/out state: res [N][L] int32, res_idx/symbols_added/time_idx/pre_g [N] int32,
  * pre_hg0/1 [N][P] bf16, pre_cg0/1 [N][P] fp32.  iters_out (device int32[1], may be NULL) receives
  * the number of batch-lockstep iterations the reference loop would have run. */

@@ -1,0 +1,21 @@
+/* rnnt_b200_debug.h — profiling hooks of the DEBUG build of the library only (`make -C rnnt_inference_b200/csrc debug`
+ * -> lib/librnnt_b200_dbg.so, compiled with -DRNNT_DEBUG_HOOKS).  The product library librnnt_b200.so exports none of
+ * these and its kernels contain none of the trace / switch-off branches.  Used by profiles/trace_*.py. */
+#ifndef RNNT_B200_DEBUG_H_
+#define RNNT_B200_DEBUG_H_
+#ifdef __cplusplus
+extern "C" {
+#endif
+/* Device buffer of T*16 int64: the next recurrent launches record clock64() stamps of CTA (0,0) per timestep (h ready,
+ * first operand chunk landed, MMAs issued, accumulator ready, TMEM read, gate math done, stores issued, published ...).
+ * NULL switches it off. */
+int rnnt_debug_set_recurrent_trace(void* device_buffer);
+/* PROFILING ONLY (results become garbage): bit 0 skip the MMAs, 1 skip the gate math, 2 skip the h loads, 3 skip y/c
+ * stores, 4 relaxed publish, 5 no proxy fence, 6 no G, 7 no c prefetch, 8 ignore the h_t flags; 0 = normal operation. */
+int rnnt_debug_set_recurrent_flags(int flags);
+/* Device buffer of max_iters*16 int64 receiving clock64 stamps of CTA 0 per decode iteration. NULL = off. */
+int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);
+#ifdef __cplusplus
+}
+#endif
+#endif

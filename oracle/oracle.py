@@ -40,6 +40,12 @@ def lib():
     return _lib
 
 
+def set_num_threads(n):
+    """OpenMP threads used by the oracle's batch-parallel loops; returns the team size now in effect."""
+    lib().orc_set_num_threads.restype = ctypes.c_int
+    return int(lib().orc_set_num_threads(int(n)))
+
+
 def _p(a):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
 

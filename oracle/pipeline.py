@@ -100,7 +100,7 @@ def new_decode_state(n, max_len):
                 pre_cg=[np.zeros((n, P), np.float32) for _ in range(PRED_LAYERS)])
 
 
-def greedy_decode_batch(params, x, x_lens, split_len=-1):
+def greedy_decode_batch(params, x, x_lens, split_len=-1, trace=None):
     """GreedyDecoder.forward in quant mode (models/decoder.py:21-94,171-212).  x {T,N,240} fp32 padded, x_lens {N}.
     Returns (res {N, 30*max(x_lens)} int32, res_len {N} int32, iterations)."""
     x = np.ascontiguousarray(x, np.float32)
@@ -119,7 +119,7 @@ def greedy_decode_batch(params, x, x_lens, split_len=-1):
         ds["symbols_added"][:] = 0                            # decoder.py:173-174: counters restart per chunk
         ds["time_idx"][:] = 0
         iters += O.greedy_decode(f, f_lens, params["dec"], ds["res"], ds["res_idx"], ds["symbols_added"], ds["time_idx"],
-                                 ds["pre_g"], ds["pre_hg"], ds["pre_cg"])
+                                 ds["pre_g"], ds["pre_hg"], ds["pre_cg"], trace=trace)
     return ds["res"], ds["res_idx"] + 1, iters
 
 

@@ -21,6 +21,9 @@
 // activations time-major {T,N,C}.  bf16/fp16 travel as uint16_t bit patterns.
 #include <cstdint>
 #include <cstring>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <cmath>
 #include <vector>
 #include <algorithm>
@@ -604,6 +607,18 @@ static int greedy_decode_impl(const uint16_t* f, const int32_t* f_lens, int T2, 
   }
   delete wtrans;
   return iters;
+}
+
+// OpenMP team size of the batch-parallel loops.  bench.py sets it explicitly: under torch.distributed.run the
+// environment carries OMP_NUM_THREADS=1, which would silently turn the CPU baseline into a single-thread run.
+ORC_API int orc_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
 }
 
 // self-check of the binary16 constants used above; returns 0 when consistent.

@@ -16,7 +16,7 @@ T = int(sys.argv[2]) if len(sys.argv) > 2 else 60
 if len(sys.argv) > 4:
     _lib.check(_lib.lib.rnnt_debug_set_recurrent_flags(int(sys.argv[4])))
 if len(sys.argv) > 3:
-    _lib.check(_lib.lib.rnnt_debug_set_recurrent_cluster(int(sys.argv[3])))
+    _lib.check(_lib.lib.rnnt_tune_recurrent_cluster(int(sys.argv[3])))
 torch.cuda.set_device(0)
 rnnt = RNNT(S.make_checkpoint(), "quant", True).eval()
 post = rnnt.transcription.post_rnn

@@ -34,7 +34,7 @@ def lstm_layer_amx_int8(x: Tensor, hx: Tensor, cx: Tensor, w_ih: Tensor, w_hh: T
 
 
 def lstm_amx_int8(x: Tensor, hx: List[Tensor], cx: List[Tensor], all_weights: List[List[Tensor]], rb_scale, i_scale,
-                  o_scale, skip_quant_y: bool, tile_steps=None) -> Tuple[Tensor, List[Tensor], List[Tensor]]:
+                  o_scale, skip_quant_y: bool, tile_steps=None, true_rows=None) -> Tuple[Tensor, List[Tensor], List[Tensor]]:
     """init.cpp:132-134 / lstm_amx.cpp:24-57: quantise fp32 input with i_scale[0], zero-pad K to a multiple of 64,
     then run the layers; only the last layer honours skip_quant_y.  tile_steps (extension, default off): see
     ops.lstm_layer_i8 — ragged batches sorted by length skip the dead (timestep, 128-row tile) items; their rows of
@@ -50,7 +50,8 @@ def lstm_amx_int8(x: Tensor, hx: List[Tensor], cx: List[Tensor], all_weights: Li
         w_ih, w_hh, _b_ih, b_hh = all_weights[layer]
         last = layer == num_layers - 1
         x = ops.lstm_layer_i8(x, hx[layer], cx[layer], w_ih, w_hh, b_hh, _scalar(rb_scale, layer), _scalar(i_scale, layer),
-                              _scalar(o_scale, layer), bool(skip_quant_y) and last, tile_steps=tile_steps, zero_dead=False)
+                              _scalar(o_scale, layer), bool(skip_quant_y) and last, tile_steps=tile_steps, zero_dead=False,
+                              true_rows=true_rows)
     return x, hx, cx
 
 
@@ -70,6 +71,12 @@ def linear(x: Tensor, weight: Tensor, bias: Tensor, scale, zero=None) -> Tensor:
     """P.linear as used by iLinear (quant_linear.py:62-64): int8 x int8 -> fp32 with scale (oneDNN int8 inner
     product in the reference, asserted equal to amx_linear_i8o32 by test_amx_linear.py:118-126)."""
     return amx_linear_i8o32(x, weight, bias, scale)
+
+
+def lstm_postop(it: Tensor, ft: Tensor, gt: Tensor, ot: Tensor, ct: Tensor, i_scale, o_scale, skip_quant_y: bool):
+    """init.cpp:126-128 / lstm_postop.cpp:14-72: the fp16 gate math of one LSTM step as a stand-alone operator; ct is
+    mutated in place.  Returns [y_bf16, y_q, h_q, ct]."""
+    return ops.lstm_postop(it, ft, gt, ot, ct, _scalar(i_scale), _scalar(o_scale), bool(skip_quant_y))
 
 
 def amx_linear_bf16_accum_relu(x0: Tensor, w0: Tensor, x1: Tensor, w1: Tensor, bias: Tensor) -> Tensor:
@@ -118,6 +125,7 @@ def prepack_lstm_weights(w_ih: Tensor, w_hh: Tensor):
 
 # ---- fused entry points (new; used by GreedyDecoder / Transcription of this package) ------------------------
 linear_bf16_bf16 = ops.linear_bf16_bf16
+gemm_bf16_bf16 = ops.gemm_bf16_bf16
 make_decode_weights = ops.make_decode_weights
 greedy_decode = ops.greedy_decode
 quantize_pad = ops.quantize_pad

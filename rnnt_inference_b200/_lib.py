@@ -10,7 +10,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "librnnt_b200.so")
+# RNNT_B200_LIB selects another build of the same ABI (profiles/trace_*.py load lib/librnnt_b200_dbg.so, `make debug`)
+LIB_PATH = os.environ.get("RNNT_B200_LIB") or os.path.join(_HERE, "lib", "librnnt_b200.so")
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -33,6 +34,8 @@ _SIGS = {
     "rnnt_abi_version": (_i, []),
     "rnnt_device_sm_count": (_i, []),
     "rnnt_check_device_status": (_i, [_vp]),
+    "rnnt_peek_device_status": (_i, [_vp, _vp]),
+    "rnnt_clear_device_status": (_i, [_vp]),
     "rnnt_quantize_pad_f32_i8": (_i, [_vp, _vp, _f, _i64, _i, _i, _vp]),
     "rnnt_quantize_ragged_f32_i8": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),
     "rnnt_gemm_i8_i32": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
@@ -44,27 +47,39 @@ _SIGS = {
     "rnnt_lstm_recurrent_i8": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "rnnt_lstm_recurrent_i8_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_lstm_recurrent_i8_gate_blocked_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
-    "rnnt_debug_set_recurrent_trace": (_i, [_vp]),
-    "rnnt_debug_set_recurrent_cluster": (_i, [_i]),
-    "rnnt_debug_set_recurrent_flags": (_i, [_i]),
+    "rnnt_tune_recurrent_cluster": (_i, [_i]),
     "rnnt_lstm_layer_i8": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_stack_time_i8": (_i, [_vp, _vp, _i, _vp, _i, _i, _i, _vp]),
     "rnnt_linear_bf16_bf16": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
+    "rnnt_gemm_bf16_bf16": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
+    "rnnt_gemm_bf16_bf16_ragged": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp]),
+    "rnnt_lstm_postop_fp16": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _f, _f, _i, _vp, _vp, _vp, _i, _i, _vp]),
     "rnnt_linear_bf16_f32": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _vp]),
     "rnnt_linear_bf16_accum_relu": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp]),
     "rnnt_dequant_i32_f32": (_i, [_vp, _vp, _f, _vp, _i64, _i, _vp]),
     "rnnt_lstm_cell_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "rnnt_greedy_decode_update": (_i, [_vp] * 17 + [_i, _i, _i, _i, _vp, _vp]),
     "rnnt_greedy_decode_workspace_bytes": (_i64, [_i]),
-    "rnnt_debug_set_decode_trace": (_i, [_vp, _i]),
     "rnnt_greedy_decode": (_i, [_vp, _vp, _i, _i, ctypes.POINTER(DecodeWeights), _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp,
                                 _vp, _vp, _vp, _vp, _vp]),
 }
 EXPORTS = tuple(_SIGS)
+# profiling hooks of the debug build (include/rnnt_b200_debug.h); absent from the product library
+_DEBUG_SIGS = {
+    "rnnt_debug_set_recurrent_trace": (_i, [_vp]),
+    "rnnt_debug_set_recurrent_flags": (_i, [_i]),
+    "rnnt_debug_set_decode_trace": (_i, [_vp, _i]),
+}
 for _name, (_res, _args) in _SIGS.items():
     _fn = getattr(lib, _name)      # AttributeError here = the .so does not match the header
     _fn.restype = _res
     _fn.argtypes = _args
+HAS_DEBUG_HOOKS = hasattr(lib, "rnnt_debug_set_recurrent_trace")
+if HAS_DEBUG_HOOKS:
+    for _name, (_res, _args) in _DEBUG_SIGS.items():
+        _fn = getattr(lib, _name)
+        _fn.restype = _res
+        _fn.argtypes = _args
 
 
 def check(rc):

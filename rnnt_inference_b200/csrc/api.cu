@@ -8,6 +8,9 @@
 #include <mutex>
 
 #include "../../include/rnnt_b200.h"
+#ifdef RNNT_DEBUG_HOOKS
+#include "../../include/rnnt_b200_debug.h"
+#endif
 #include "kernels.cuh"
 
 using namespace rnnt;
@@ -139,6 +142,21 @@ int rnnt_check_device_status(void* stream) {
   return RNNT_OK;
 }
 
+// Non-synchronising variant for pipelined callers: enqueues a copy of the status word into *host_dst (pinned host memory)
+// on `stream`; the caller looks at it after its own synchronisation point and calls rnnt_clear_device_status on error.
+int rnnt_peek_device_status(int32_t* host_dst, void* stream) {
+  int* st = device_status();
+  if (!st || !host_dst) return fail(RNNT_ERR_CUDA, "peek_device_status: no usable CUDA device or null destination");
+  CUDA_TRY(cudaMemcpyAsync(host_dst, st, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return RNNT_OK;
+}
+int rnnt_clear_device_status(void* stream) {
+  int* st = device_status();
+  if (!st) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+  CUDA_TRY(cudaMemsetAsync(st, 0, sizeof(int), (cudaStream_t)stream));
+  return RNNT_OK;
+}
+
 int rnnt_quantize_pad_f32_i8(const float* in, int8_t* out, float scale, int64_t rows, int k_in, int k_out, void* stream) {
   if (!in || !out || rows < 0 || k_in <= 0 || k_out < k_in || (k_out & 3) || !aligned(out, 4))
     return fail(RNNT_ERR_INVALID, "quantize_pad: need k_out >= k_in > 0, k_out %% 4 == 0 (got rows=%lld k_in=%d k_out=%d)",
@@ -219,6 +237,22 @@ int rnnt_dequant_i32_f32(const int32_t* acc, const float* bias, float scale, flo
   return RNNT_OK;
 }
 
+int rnnt_lstm_postop_fp16(const float* it, const float* ft, const float* gt, const float* ot, int64_t ld, uint16_t* ct,
+                          float in_scale, float out_scale, int skip_quant_y, uint16_t* y_bf16, int8_t* y_q, int8_t* h_q, int N,
+                          int H, void* stream) {
+  if (!it || !ft || !gt || !ot || !ct || !h_q || (skip_quant_y ? !y_bf16 : !y_q) || N < 0 || H <= 0 || (H & 1) || ld < H || (ld & 1))
+    return fail(RNNT_ERR_INVALID, "lstm_postop: null pointer or bad size (N=%d H=%d ld=%lld; H and ld must be even)", N, H, (long long)ld);
+  if (!aligned(ct, 4) || !aligned(h_q, 2) || (y_q && !aligned(y_q, 2)) || (y_bf16 && !aligned(y_bf16, 4)))
+    return fail(RNNT_ERR_INVALID, "lstm_postop: misaligned buffer");
+  if (N == 0) return RNNT_OK;
+  const long long total = (long long)N * (H / 2);
+  const int blocks = (int)std::min<long long>((total + 255) / 256, 148ll * 8);
+  lstm_postop_fp16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(it, ft, gt, ot, ld, ct, in_scale, out_scale, skip_quant_y ? 1 : 0,
+                                                                    y_bf16, y_q, h_q, N, H);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
 int rnnt_lstm_cell_bf16(const uint16_t* x, const uint16_t* h, const float* c, const uint16_t* w_ih, const uint16_t* w_hh,
                         const float* bias, uint16_t* hy, float* cy, int N, int K, int P, float* gates_ws, void* stream) {
   if (!x || !h || !c || !w_ih || !w_hh || !bias || !hy || !cy || !gates_ws || N <= 0 || K <= 0 || P <= 0)
@@ -292,11 +326,8 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
   int* status = device_status();
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
   auto kern = gemm_i8_i32_kernel<BN>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::TOTAL));
-    attr_set = true;
-  }
+  // the opt-in is per device/context: set on every launch (a cached per-process flag would skip it on a second GPU)
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::TOTAL));
   const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
   const int sms = sm_count();
   const int grid = std::max(1, std::min(sms > 0 ? sms : 148, num_m * num_n));
@@ -337,9 +368,64 @@ int rnnt_gemm_i8_i32_gate_blocked_ragged(const int8_t* A, const int8_t* W, int32
   return gemm_launch<256>(A, W, C, M, N, K, skip, (cudaStream_t)stream, true);
 }
 
-// debug hook: device buffer [T][8] int64 receiving clock64 stamps of CTA (0,0) of the next recurrent launches (NULL = off)
+}  // extern "C"
+
+template <int BN>
+static int gemm_bf16_launch(const uint16_t* A, const uint16_t* W, uint16_t* C, int64_t M, int N, int K, const RowSkip& skip,
+                            cudaStream_t st) {
+  using S = GemmBf16Smem<BN>;
+  CUtensorMap ta, tb, tc;
+  {
+    uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)K * 2};
+    uint32_t box[2] = {(uint32_t)S::BK_ELEMS, GEMM_BM};
+    if (int r = make_tmap(&ta, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, dims, str, box)) return r;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)K, (uint64_t)N}, str[1] = {(uint64_t)K * 2};
+    uint32_t box[2] = {(uint32_t)S::BK_ELEMS, (uint32_t)BN};
+    if (int r = make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, dims, str, box)) return r;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[1] = {(uint64_t)N * 2};
+    uint32_t box[2] = {32, 32};
+    if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B)) return r;
+  }
+  int* status = device_status();
+  if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+  auto kern = gemm_bf16_bf16_kernel<BN>;
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+  const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + S::BK_ELEMS - 1) / S::BK_ELEMS;
+  const int sms = sm_count();
+  const int grid = std::max(1, std::min(sms > 0 ? sms : 148, num_m * num_n));
+  kern<<<grid, GEMM_THREADS, S::TOTAL, st>>>(ta, tb, tc, num_m, num_n, num_k, status, skip);
+  CUDA_TRY(cudaGetLastError());
+  return RNNT_OK;
+}
+
+extern "C" {
+int rnnt_gemm_bf16_bf16_ragged(const uint16_t* A, const uint16_t* W, uint16_t* C, int64_t M, int N, int K, int rows_per_step,
+                               const int32_t* tile_steps_host, void* stream) {
+  if (!A || !W || !C || M < 0 || N <= 0 || K <= 0) return fail(RNNT_ERR_INVALID, "gemm_bf16_bf16: null pointer or non-positive size");
+  if ((K & 7) || (N & 63) || !aligned(A, 16) || !aligned(W, 16) || !aligned(C, 16))
+    return fail(RNNT_ERR_INVALID, "gemm_bf16_bf16: need K %% 8 == 0, N %% 64 == 0, 16-byte aligned pointers (M=%lld N=%d K=%d)",
+                (long long)M, N, K);
+  if (M == 0) return RNNT_OK;
+  RowSkip skip;
+  if (int r = make_skip(&skip, M, rows_per_step, tile_steps_host, GEMM_BM)) return r;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (N % 256 == 0) return gemm_bf16_launch<256>(A, W, C, M, N, K, skip, st);
+  if (N % 128 == 0) return gemm_bf16_launch<128>(A, W, C, M, N, K, skip, st);
+  return gemm_bf16_launch<64>(A, W, C, M, N, K, skip, st);
+}
+int rnnt_gemm_bf16_bf16(const uint16_t* A, const uint16_t* W, uint16_t* C, int64_t M, int N, int K, void* stream) {
+  return rnnt_gemm_bf16_bf16_ragged(A, W, C, M, N, K, 0, nullptr, stream);
+}
+
+#ifdef RNNT_DEBUG_HOOKS
+// debug hook: device buffer [T][16] int64 receiving clock64 stamps of CTA (0,0) of the next recurrent launches (NULL = off)
 static long long* g_rec_trace = nullptr;
 int rnnt_debug_set_recurrent_trace(void* device_buffer) { g_rec_trace = reinterpret_cast<long long*>(device_buffer); return RNNT_OK; }
+#endif
 
 // ------------------------------------------------------------------------------------------------
 // recurrent kernel.  workspace: [0,1024) reserved | flags [num_btiles][32] int | h ping-pong [2][N_pad][1024] int8 (K-chunk-major)
@@ -360,12 +446,8 @@ template <int CS>
 static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th,
                                  const RecParams& p, int num_slices, int grid_y, cudaStream_t st) {
   auto kern = lstm_recurrent_kernel<CS>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, RecSmem::TOTAL);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, RecSmem::TOTAL);   // per device
+  if (e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(num_slices, grid_y);
   cfg.blockDim = dim3(REC_THREADS);
@@ -404,9 +486,11 @@ static int rec_cluster_pref() {
 }
 
 extern "C" {
+#ifdef RNNT_DEBUG_HOOKS
 static int g_rec_debug = 0;
 int rnnt_debug_set_recurrent_flags(int flags) { g_rec_debug = flags; return RNNT_OK; }
-int rnnt_debug_set_recurrent_cluster(int ctas) {
+#endif
+int rnnt_tune_recurrent_cluster(int ctas) {
   if (ctas != 1 && ctas != 2 && ctas != 4 && ctas != 8) return fail(RNNT_ERR_INVALID, "recurrent cluster size must be 1, 2, 4 or 8");
   g_rec_cluster = ctas;
   return RNNT_OK;
@@ -481,9 +565,22 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
   p.g = G; p.g_blocked = g_blocked; p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
   p.T = T; p.N = N; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
+#ifdef RNNT_DEBUG_HOOKS
   p.trace = g_rec_trace;
   p.debug = g_rec_debug;
-  return rec_launch(tw, th0, th, p, num_slices, grid_y, rec_cluster_pref(), st);
+#else
+  p.trace = nullptr;
+  p.debug = 0;
+#endif
+  if (int r = rec_launch(tw, th0, th, p, num_slices, grid_y, rec_cluster_pref(), st)) return r;
+  // tiles that ran a single step left their final h in the ping-pong buffer (see lstm_recurrent.cu): move it to hx
+  unsigned one_step = 0;
+  for (int b = 0; b < num_btiles; ++b) one_step |= (p.tile_steps[b] == 1) ? (1u << b) : 0u;
+  if (one_step) {
+    rec_copy_h1_kernel<<<num_btiles, 256, 0, st>>>(h_buf, hx, num_btiles, N, one_step);
+    CUDA_TRY(cudaGetLastError());
+  }
+  return RNNT_OK;
 }
 
 int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
@@ -506,11 +603,13 @@ int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* 
 // ------------------------------------------------------------------------------------------------
 // greedy decode.  workspace: [0,256) global_sync | group_cnt [8][32] int | lane_state [N][8] int | z [N][512] f32 |
 //                            hg1 [2][N][320] bf16 | cg1 [2][N][320] f32
+#ifdef RNNT_DEBUG_HOOKS
 static long long* g_dec_trace = nullptr;
 static int g_dec_trace_cap = 0;
 int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters) {
   g_dec_trace = reinterpret_cast<long long*>(device_buffer); g_dec_trace_cap = max_iters; return RNNT_OK;
 }
+#endif
 int64_t rnnt_greedy_decode_workspace_bytes(int N) {
   if (N <= 0) return 0;
   return 256 + 1024 + round_up((int64_t)N * 32, 256) + round_up((int64_t)N * DEC_J * 4, 256) +
@@ -553,13 +652,13 @@ int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N,
   p.hg[0][0] = pre_hg0; p.hg[0][1] = pre_hg1; p.hg[1][0] = hg1; p.hg[1][1] = hg1 + (size_t)N * DEC_P;
   p.cg[0][0] = pre_cg0; p.cg[0][1] = pre_cg1; p.cg[1][0] = cg1; p.cg[1][1] = cg1 + (size_t)N * DEC_P;
   p.iters_out = iters_out; p.status = status; p.NG = NG; p.LG = LG;
+#ifdef RNNT_DEBUG_HOOKS
   p.trace = g_dec_trace; p.trace_cap = g_dec_trace_cap;
+#else
+  p.trace = nullptr; p.trace_cap = 0;
+#endif
   CUDA_TRY(cudaMemsetAsync(ws, 0, 256 + 1024, st));
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(greedy_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DecSmem::TOTAL));
-    attr_set = true;
-  }
+  CUDA_TRY(cudaFuncSetAttribute(greedy_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DecSmem::TOTAL));   // per device
   void* args[1] = {(void*)&p};
   CUDA_TRY(cudaLaunchCooperativeKernel((const void*)greedy_decode_kernel, dim3(NG * DEC_S), dim3(DEC_THREADS), args,
                                        DecSmem::TOTAL, st));

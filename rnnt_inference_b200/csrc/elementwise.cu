@@ -2,8 +2,63 @@
 // stack_time, and the (CUDA-core, order-defined) bf16 linear used to hoist Joint's transcription half.
 #include "kernels.cuh"
 #include "gate_math.cuh"
+#include "../../include/rnnt_rcp_ph_lut.h"
 
 namespace rnnt {
+
+__constant__ uint16_t c_rcp_lut_ew[1024] = {RNNT_RCP_PH_LUT_VALUES};
+
+// lstm_postop (init.cpp:126-128; lstm_postop.cpp:14-72 -> lstm_postop_tpp::ref, tpps/lstm_postop_tpp.cpp:12-98) as a
+// stand-alone operator: fp32 gates (rows `ld` floats apart, so the four chunks of a [N][4H] tensor work in place) ->
+// fp16 gate math with the reference's instruction sequence (Pade [5/6] + VRCPPH table) -> c updated IN PLACE,
+// y int8 (out_scale) or bf16, h int8 (in_scale).  One thread = two adjacent units of one row.
+__global__ void lstm_postop_fp16_kernel(const float* __restrict__ it, const float* __restrict__ ft, const float* __restrict__ gt,
+                                        const float* __restrict__ ot, long long ld, uint16_t* __restrict__ ct, float in_scale,
+                                        float out_scale, int skip_quant_y, uint16_t* __restrict__ y_bf16,
+                                        int8_t* __restrict__ y_q, int8_t* __restrict__ h_q, int N, int H) {
+  __shared__ uint16_t lut[1024];
+  for (int i = threadIdx.x; i < 1024; i += blockDim.x) lut[i] = c_rcp_lut_ew[i];
+  __syncthreads();
+  const HalfConsts k = make_half_consts();
+  const __half2 in_s = __float2half2_rn(in_scale), out_s = __float2half2_rn(out_scale);
+  const int pairs = H >> 1;
+  const long long total = (long long)N * pairs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long n = i / pairs;
+    const int j = (int)(i - n * pairs) * 2;
+    const long long g = n * ld + j, o = n * H + j;
+    const __half2 ig = sigmoid_ph2(__floats2half2_rn(it[g], it[g + 1]), k, lut);
+    const __half2 fg = sigmoid_ph2(__floats2half2_rn(ft[g], ft[g + 1]), k, lut);
+    const __half2 gg = tanh_ph2(__floats2half2_rn(gt[g], gt[g + 1]), k, lut);
+    const __half2 og = sigmoid_ph2(__floats2half2_rn(ot[g], ot[g + 1]), k, lut);
+    const __half2 c_old = bits_h2(*reinterpret_cast<const uint32_t*>(ct + o));
+    const __half2 c_new = __hfma2(ig, gg, __hmul2_rn(fg, c_old));
+    *reinterpret_cast<uint32_t*>(ct + o) = h2_bits(c_new);
+    const __half2 h = __hmul2_rn(og, tanh_ph2(c_new, k, lut));
+    *reinterpret_cast<uint16_t*>(h_q + o) = (uint16_t)quant_ph2(h, in_s);
+    if (skip_quant_y) {
+      const float2 hf = __half22float2(h);
+      *reinterpret_cast<uint32_t*>(y_bf16 + o) = float_to_bf16_bits(hf.x) | (float_to_bf16_bits(hf.y) << 16);
+    } else {
+      *reinterpret_cast<uint16_t*>(y_q + o) = (uint16_t)quant_ph2(h, out_s);
+    }
+  }
+}
+
+// Final h of batch tiles that ran exactly ONE step: the recurrent kernel leaves it in slot 1 of its K-chunk-major
+// ping-pong buffer (writing the caller's hx inside the kernel would race with slice CTAs still reading h_0 from it);
+// this copies it to hx [N][1024].  grid = batch tiles, bit b of `mask` selects tile b.
+__global__ void rec_copy_h1_kernel(const int8_t* __restrict__ h_buf, int8_t* __restrict__ hx, int num_btiles, int N,
+                                   unsigned mask) {
+  const int b = blockIdx.x;
+  if (!((mask >> b) & 1u)) return;
+  const uint4* src = reinterpret_cast<const uint4*>(h_buf + ((size_t)(num_btiles + b) * REC_KC) * REC_BM * 128);
+  for (int i = threadIdx.x; i < REC_KC * REC_BM * 8; i += blockDim.x) {      // 16-byte pieces: [chunk 8][row 128][8]
+    const int kc = i / (REC_BM * 8), row = (i / 8) % REC_BM, part = i % 8;
+    const int n = b * REC_BM + row;
+    if (n < N) reinterpret_cast<uint4*>(hx + (size_t)n * REC_H + kc * 128)[part] = src[i];
+  }
+}
 
 // quant_tpp::quant_ps_epi8 (tpps/quant_tpp.cpp:6-17) + zero pad of K (lstm_amx.cpp:48-50).
 // One thread produces 4 output bytes; out rows are k_out bytes (k_out % 4 == 0).

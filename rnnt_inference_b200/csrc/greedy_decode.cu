@@ -480,8 +480,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     }
     if (total_iters >= 0 && (iter >= total_iters || s_live == 0)) break;
     ++iter;
-    const bool tr = p.trace && blockIdx.x == 0 && tid == 0 && iter <= p.trace_cap;
-    long long* trow = p.trace + (size_t)(iter - 1) * 16;
+    long long* const trace = RNNT_TRACE_PTR(p);
+    const bool tr = trace && blockIdx.x == 0 && tid == 0 && iter <= p.trace_cap;
+    long long* trow = trace + (size_t)(iter - 1) * 16;
     if (tr) { trow[0] = clock64(); trow[7] = na; }
 
     if (na > 0) {

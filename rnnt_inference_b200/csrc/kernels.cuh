@@ -3,6 +3,16 @@
 #pragma once
 #include "common.cuh"
 
+// Profiling hooks (cycle traces, switch-off flags) exist only in the debug build of the library (`make debug`,
+// -DRNNT_DEBUG_HOOKS, include/rnnt_b200_debug.h); in the product build these fold to constants and the branches vanish.
+#ifdef RNNT_DEBUG_HOOKS
+#define RNNT_DBG(p, bits) ((p).debug & (bits))
+#define RNNT_TRACE_PTR(p) ((p).trace)
+#else
+#define RNNT_DBG(p, bits) 0
+#define RNNT_TRACE_PTR(p) ((long long*)nullptr)
+#endif
+
 namespace rnnt {
 
 // Ragged batches sorted by length: rows are (t, n) with rows_per_t = N rows per timestep; batch tile b = rows
@@ -40,6 +50,23 @@ __global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, c
                                    int num_k_blocks, int* __restrict__ status, const RowSkip skip, const int gate_blocked);
 __global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, int32_t* __restrict__ C,
                                         long long M, int N, int K);
+
+// ------------------------------------------------------------------ gemm_bf16.cu
+template <int BN>
+struct GemmBf16Smem {
+  static constexpr int BK_ELEMS = 64;                         // bf16 elements of K per stage = one 128-byte swizzle row
+  static constexpr int A_BYTES = GEMM_BM * 128;               // 16 KB
+  static constexpr int B_BYTES = BN * 128;                    // 32 KB at BN=256
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int C_WARP_BYTES = 32 * 64;                // 32 rows x 32 bf16
+  static constexpr int C_BYTES = 4 /*warps*/ * 2 /*buffers*/ * C_WARP_BYTES;  // 16 KB
+  static constexpr int BAR_OFFSET = GEMM_STAGES * STAGE_BYTES + C_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;       // barriers + alignment slack
+};
+template <int BN>
+__global__ void gemm_bf16_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                                      const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
+                                      int num_k_blocks, int* __restrict__ status, const RowSkip skip);
 
 // ------------------------------------------------------------------ lstm_recurrent.cu
 constexpr int REC_H = 1024;
@@ -122,6 +149,12 @@ __global__ void dequant_i32_f32_kernel(const int32_t* __restrict__ acc, const fl
 __global__ void lstm_postop_f32_kernel(const float* __restrict__ gi, const float* __restrict__ gh, const float* __restrict__ bias,
                                        const float* __restrict__ c_in, uint16_t* __restrict__ hy, float* __restrict__ cy,
                                        int N, int P);
+__global__ void lstm_postop_fp16_kernel(const float* __restrict__ it, const float* __restrict__ ft, const float* __restrict__ gt,
+                                        const float* __restrict__ ot, long long ld, uint16_t* __restrict__ ct, float in_scale,
+                                        float out_scale, int skip_quant_y, uint16_t* __restrict__ y_bf16,
+                                        int8_t* __restrict__ y_q, int8_t* __restrict__ h_q, int N, int H);
+__global__ void rec_copy_h1_kernel(const int8_t* __restrict__ h_buf, int8_t* __restrict__ hx, int num_btiles, int N,
+                                   unsigned mask);
 __global__ void greedy_update_kernel(const long long* __restrict__ symbols, int32_t* symbols_added, int32_t* res, int32_t* res_idx,
                                      const uint16_t* __restrict__ f, const int32_t* __restrict__ f_lens, int32_t* time_idx,
                                      uint16_t* fi, int32_t* pre_g, uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0,

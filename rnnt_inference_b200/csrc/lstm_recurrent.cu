@@ -111,7 +111,8 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   const int by = blockIdx.y, gy = gridDim.y;
   const int my_tiles = (p.num_btiles - by + gy - 1) / gy;
   const uint32_t cta_rank = (CS > 1) ? cluster_ctarank() : 0u;
-  const bool tracer = p.trace && blockIdx.x == 0 && blockIdx.y == 0;
+  long long* const trace = RNNT_TRACE_PTR(p);
+  const bool tracer = trace && blockIdx.x == 0 && blockIdx.y == 0;
 
   for (int i = threadIdx.x; i < 1024; i += REC_THREADS) lut[i] = c_rcp_lut[i];
   if (threadIdx.x < 4 * HS) s_bias[threadIdx.x] = p.bias[(threadIdx.x / HS) * REC_H + blockIdx.x * HS + (threadIdx.x % HS)];
@@ -158,7 +159,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
       while (have && ok) {
         const int t = cur.t, bt = by + cur.i * gy;
-        if (t > 0 && !(p.debug & 256)) {
+        if (t > 0 && !RNNT_DBG(p, 256)) {
           // wait until every slice CTA has published its part of h_t for this batch tile
           const int* flag = p.flags + bt * REC_FLAG_STRIDE;
           const int target = t * num_slices * 2;      // two storing warps per slice CTA
@@ -175,15 +176,15 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           }
           if (!ok) break;
           asm volatile("fence.acquire.gpu;" ::: "memory");
-          if (!(p.debug & 32)) fence_proxy_async_all();   // generic-proxy writes of h_t (other CTAs) -> async-proxy (TMA) reads
+          if (!RNNT_DBG(p, 32)) fence_proxy_async_all();   // generic-proxy writes of h_t (other CTAs) -> async-proxy (TMA) reads
         }
-        if (tracer && cur.i == 0) p.trace[t * 16 + 0] = clock64();
+        if (tracer && cur.i == 0) trace[t * 16 + 0] = clock64();
         const int hrow0 = (((t & 1) * p.num_btiles + bt) * REC_KC) * REC_BM;   // row of chunk 0 in the chunk-major h buffer
         for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
           const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
           // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
           if (!mbar_wait(empty_bar + 8 * st, ph ^ 1u, p.status)) { ok = false; break; }
-          if (p.debug & 4) { mbar_arrive(full_bar + 8 * st); continue; }
+          if (RNNT_DBG(p, 4)) { mbar_arrive(full_bar + 8 * st); continue; }
           mbar_expect_tx(full_bar + 8 * st, S::H_CHUNK);
           if (CS > 1 && (uint32_t)(kc % CS) != cta_rank) continue;
           const uint32_t dst = smem_h + st * S::H_CHUNK, bar = full_bar + 8 * st;
@@ -209,7 +210,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         const bool mtr = tracer && cur.i == 0;
         long long c0 = mtr ? clock64() : 0, w_full = 0;
         if (!mbar_wait(done_bar + 8 * acc, acc_phase ^ 1u, p.status)) break;
-        if (mtr) p.trace[cur.t * 16 + 8] = clock64() - c0;
+        if (mtr) trace[cur.t * 16 + 8] = clock64() - c0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * S::UMMA_N;
         for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
@@ -217,19 +218,19 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           if (mtr) c0 = clock64();
           if (!mbar_wait(full_bar + 8 * st, ph, p.status)) { ok = false; break; }
           if (mtr) w_full += clock64() - c0;
-          if (kc == 0 && tracer && cur.i == 0) p.trace[cur.t * 16 + 1] = clock64();
+          if (kc == 0 && tracer && cur.i == 0) trace[cur.t * 16 + 1] = clock64();
           tc_fence_after();
           const uint64_t adesc = umma_desc_sw128(smem_h + st * S::H_CHUNK);
           const uint64_t bdesc = umma_desc_sw128(smem_w + kc * S::W_CHUNK);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            if (!(p.debug & 1)) umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) != 0);
+            if (!RNNT_DBG(p, 1)) umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) != 0);
           if (CS == 1) umma_commit(empty_bar + 8 * st);
           else umma_commit_mc(empty_bar + 8 * st, MC_MASK);
         }
         if (!ok) break;
         umma_commit(tfull_bar + 8 * acc);
-        if (tracer && cur.i == 0) { p.trace[cur.t * 16 + 2] = clock64(); p.trace[cur.t * 16 + 9] = w_full; }
+        if (tracer && cur.i == 0) { trace[cur.t * 16 + 2] = clock64(); trace[cur.t * 16 + 9] = w_full; }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
@@ -269,7 +270,9 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       for (int r = 0; r < 2; ++r) {
         const int row = sw * 64 + r * 32 + lane;
         const int n = bt * REC_BM + row;
-        if (!last) {
+        // A tile that runs a single step keeps its final h in the ping-pong buffer too: other slice CTAs may still be
+        // reading h_0 from hx (nothing orders t = 0 across CTAs); rec_copy_h1_kernel moves it to hx after the launch.
+        if (!last || t == 0) {
           uint4* hn = reinterpret_cast<uint4*>(p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 2)) * REC_BM + row) * 128 +
                                                (slice & 3) * HS);
           hn[0] = make_uint4(hw[r][0], hw[r][1], hw[r][2], hw[r][3]);
@@ -280,19 +283,19 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           hp[1] = make_uint4(hw[r][4], hw[r][5], hw[r][6], hw[r][7]);
         }
       }
-      if (tr) p.trace[t * 16 + 5] = clock64();
+      if (tr) trace[t * 16 + 5] = clock64();
       __syncwarp();
       // h_{t+1}[tile bt][this slice][these 64 rows] is written: one release increment of the tile counter (the fence is
       // cumulative over the other lanes' stores through the warp barrier above)
       if (lane == 0 && !last) {
-        if (tr) p.trace[t * 16 + 6] = clock64();
-        if (p.debug & 16) asm volatile("red.relaxed.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
+        if (tr) trace[t * 16 + 6] = clock64();
+        if (RNNT_DBG(p, 16)) asm volatile("red.relaxed.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
         else asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.flags + bt * REC_FLAG_STRIDE) : "memory");
-        if (tr) p.trace[t * 16 + 7] = clock64();
+        if (tr) trace[t * 16 + 7] = clock64();
       }
       __syncwarp();
       // y[t] afterwards: nothing inside this kernel reads it
-      if (!(p.debug & 8)) {
+      if (!RNNT_DBG(p, 8)) {
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
           const int n = bt * REC_BM + sw * 64 + r * 32 + lane;
@@ -342,7 +345,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     int gi[4][8];
     auto load_g = [&](int t_, int bt_) {
       const int n_ = bt_ * REC_BM + row;
-      if (n_ < p.N && !(p.debug & 64)) {
+      if (n_ < p.N && !RNNT_DBG(p, 64)) {
         if (p.g_blocked) {      // a warp's 32 rows are 1 KB contiguous: 8 lines per load instead of 32
           const size_t rows = (size_t)p.T * p.N;
           const int32_t* gp = p.g + (((size_t)slice * 16 + ug) * rows + (size_t)t_ * p.N + n_) * 8;
@@ -379,7 +382,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       load_g(t, bt);
       const long long f0 = tr ? clock64() : 0;
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
-      if (tr) { p.trace[t * 16 + 3] = clock64(); p.trace[t * 16 + 11] = clock64() - f0; }
+      if (tr) { trace[t * 16 + 3] = clock64(); trace[t * 16 + 11] = clock64() - f0; }
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * 8);
       uint32_t hq_pack[2] = {0u, 0u}, yq_pack[2] = {0u, 0u};
@@ -401,7 +404,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         }
       }
       tc_fence_before();
-      if (tr) p.trace[t * 16 + 4] = clock64();
+      if (tr) trace[t * 16 + 4] = clock64();
 #pragma unroll
       for (int pr = 0; pr < 4; ++pr) {
         const int half = pr >> 1, u = (pr & 1) * 2;

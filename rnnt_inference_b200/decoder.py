@@ -15,13 +15,21 @@ from .config import RNNTParam
 
 
 class GreedyDecoder(torch.nn.Module):
-    def __init__(self, model, run_mode, enable_bf16=False, split_len=-1, batch_size=1, fused=True):
+    def __init__(self, model, run_mode, enable_bf16=False, split_len=-1, batch_size=1, fused=True, exact_order=False,
+                 keep_intermediates=False):
+        """fused / exact_order / keep_intermediates are extensions (quant mode): fused=False runs the reference's
+        per-iteration operator loop; exact_order=True computes the hoisted f.W_trans on CUDA cores in the CPU oracle's
+        accumulation order instead of the tcgen05 GEMM (bit-exact cross-checks); keep_intermediates leaves the encoder
+        output and the hoisted product of the last call in self.last_f / self.last_y1 (tests, reports)."""
         super().__init__()
         self.rnnt = model
         self.split_len = split_len
         self.enable_bf16 = enable_bf16
         self.run_mode = run_mode
         self.fused = fused
+        self.exact_order = exact_order
+        self.keep_intermediates = keep_intermediates
+        self.last_f = self.last_y1 = None
         self.padded_batch_size = batch_size   # the AMX thread-count padding of decoder.py:18-19 has no GPU meaning
         self.last_iters = None                # device int32[1]: lock-step iterations of the last fused decode
 
@@ -101,7 +109,9 @@ class GreedyDecoder(torch.nn.Module):
         f_lens = torch.div(f_lens + (fac - 1), fac, rounding_mode="floor").to(torch.int32)
         if self.fused:
             steps2 = None if lens_host is None else P.tile_steps_for(lens_host, n, fac)
-            y1 = self.rnnt.joint.hoist_trans(f, steps2)
+            y1 = self.rnnt.joint.hoist_trans(f, steps2, self.exact_order)
+            if self.keep_intermediates:
+                self.last_f, self.last_y1 = f, y1
             if self.last_iters is None or self.last_iters.device != dev:
                 self.last_iters = torch.zeros(1, dtype=torch.int32, device=dev)
             P.greedy_decode(y1, f_lens, self.rnnt.decode_weights(), self.res, self.res_idx, self.symbols_added, self.time_idx,

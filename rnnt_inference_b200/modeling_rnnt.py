@@ -114,10 +114,13 @@ class Transcription(torch.nn.Module):
             # post: stacked frames); the skipped tail is exactly what stack_time / the decode loop never read
             from . import ops
             n = x.size(1)
-            x, pre_hx, pre_cx = self.pre_rnn(x, pre_hx, pre_cx, tile_steps=ops.tile_steps_for(lens_host, n))
+            fac = RNNTParam.stack_time_factor
+            frames = int(sum(lens_host))                                   # true (frame, utterance) pairs: telemetry only
+            frames2 = int(sum((int(v) + fac - 1) // fac for v in lens_host))
+            x, pre_hx, pre_cx = self.pre_rnn(x, pre_hx, pre_cx, tile_steps=ops.tile_steps_for(lens_host, n), true_rows=frames)
             x = self.stack_time(x, x_lens)
-            x, post_hx, post_cx = self.post_rnn(
-                x, post_hx, post_cx, tile_steps=ops.tile_steps_for(lens_host, n, RNNTParam.stack_time_factor))
+            x, post_hx, post_cx = self.post_rnn(x, post_hx, post_cx, tile_steps=ops.tile_steps_for(lens_host, n, fac),
+                                                true_rows=frames2)
             return x, pre_hx, pre_cx, post_hx, post_cx
         x, pre_hx, pre_cx = self.pre_rnn(x, pre_hx, pre_cx)
         x = self.stack_time(x, x_lens)
@@ -187,10 +190,14 @@ class Joint(torch.nn.Module):
             b2 = F.pad(b2, (0, 32 - b2.shape[-1] % 32), "constant", 0)
         self.linear2.bias = Parameter(b2, requires_grad=False)
 
-    def hoist_trans(self, f: Tensor, tile_steps=None) -> Tensor:
+    def hoist_trans(self, f: Tensor, tile_steps=None, exact_order=False) -> Tensor:
         """y1 = bf16(f . W_trans^T) for every encoder frame at once.  The reference rounds this product to bf16 in
-        memory each iteration (amx_linear.cpp:137-150), so computing it once per frame is bit-identical."""
-        return P.linear_bf16_bf16(f, self.linear1_trans.weight, tile_steps)
+        memory each iteration (amx_linear.cpp:137-150), so it depends on the frame only and is computed once — on the
+        tensor cores (tcgen05 bf16 GEMM).  exact_order=True uses the CUDA-core operator whose fp32 accumulation order is
+        the CPU oracle's (bit-exact cross-checks); the two agree to <= 1 bf16 ulp."""
+        if exact_order:
+            return P.linear_bf16_bf16(f, self.linear1_trans.weight, tile_steps)
+        return P.gemm_bf16_bf16(f, self.linear1_trans.weight, tile_steps)
 
     def forward(self, f: Tensor, g: Tensor, padded_batch_size: int = 1) -> Tensor:
         """f {N, 1024}, g {N, 320} -> logits {N, 32} fp32 (bf16 mode) or {N, 29} (fp32 mode)."""

@@ -16,19 +16,22 @@ V_PAD = 32        # num_labels 29 padded to 32 (modeling_rnnt.py:241-250)
 
 
 class Workspace:
-    """Grow-only cache of device scratch buffers keyed by (name, device); the C ABI never allocates."""
+    """Grow-only cache of device scratch buffers; the C ABI never allocates.  Keyed by (name, device, stream): two
+    streams (the pipelined SUT's compute stream and a caller on the default stream, or two SUT instances) never share
+    the recurrent kernel's flags / h ping-pong or the decode scratch."""
 
     def __init__(self):
         self._bufs = {}
 
     def get(self, name, nbytes, device):
-        key = (name, str(device))
+        nbytes = int(nbytes)
+        key = (name, str(device), torch.cuda.current_stream(device).cuda_stream)
         buf = self._bufs.get(key)
-        if buf is None or buf.numel() < nbytes:
-            buf = torch.empty(max(int(nbytes), 256) + 256, dtype=torch.uint8, device=device)
+        if buf is None or buf.numel() < nbytes + 256:
+            buf = torch.empty(max(nbytes, 256) + 256, dtype=torch.uint8, device=device)
             self._bufs[key] = buf
         off = (-buf.data_ptr()) % 256
-        return buf[off:off + int(nbytes)]
+        return buf[off:off + nbytes]
 
 
 _ws = Workspace()
@@ -109,7 +112,8 @@ def tile_steps_for(lens_host, n, divisor=1):
     return np.ascontiguousarray(steps.astype(np.int32))
 
 
-def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, tile_steps=None, zero_dead=True):
+def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, tile_steps=None, zero_dead=True,
+                  true_rows=None):
     """lstm_layer_amx_int8 (lstm_amx.cpp:59-158). x int8 [T,N,K]; hx int8 [N,H], cx fp16 [N,H] updated IN PLACE.
     Returns y: int8 [T,N,H] or bf16 [T,N,H] when skip_quant_y.  tile_steps (host int32 per 128-row tile, see
     tile_steps_for): ragged batch sorted by length — (t, tile) items past a tile's last step are skipped and y is zero
@@ -138,7 +142,10 @@ def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, sk
     gemm_ts = ts_ptr if n % 128 == 0 else None     # dead (t, tile) rows of the projection are skipped as well
     telemetry.bracket("gemm_i8", (t * n, k), lambda: L.check(
         L.lib.rnnt_gemm_i8_i32_gate_blocked_ragged(L.ptr(x), L.ptr(w_ih), L.ptr(g_ws), t * n, 4 * H, k, n, gemm_ts, st)))
-    units = (t, n, bool(skip_quant_y)) if tile_steps is None else (int(tile_steps.sum()), 128, bool(skip_quant_y))
+    # telemetry units of the recurrent kernel: (TRUE (frame, utterance) pairs the layer has to process — tile padding and
+    # rows past an utterance's end are not algorithmic work —, (timestep, 128-row tile) items the kernel runs, bf16 output)
+    items = t * ((n + 127) // 128) if tile_steps is None else int(tile_steps.sum())
+    units = (int(true_rows) if true_rows is not None else t * n, items, bool(skip_quant_y))
     telemetry.bracket("lstm_recurrent", units, lambda: L.check(
         L.lib.rnnt_lstm_recurrent_i8_gate_blocked_ragged(L.ptr(g_ws), L.ptr(w_hh), L.ptr(bias), float(rb_scale), float(in_scale),
                                             float(out_scale), int(bool(skip_quant_y)), L.ptr(hx), L.ptr(cx), L.ptr(y), t, n, H,
@@ -191,6 +198,49 @@ def linear_bf16_bf16(x, w, tile_steps=None):
     telemetry.bracket("linear_bf16", (m, k, o), lambda: L.check(
         L.lib.rnnt_linear_bf16_bf16_ragged(L.ptr(x), L.ptr(w), L.ptr(y), m, k, o, rows, ts_ptr, L.stream_ptr())))
     return y
+
+
+def gemm_bf16_bf16(x, w, tile_steps=None):
+    """y = bf16(x . w^T) on the tensor cores (tcgen05 kind::f16, fp32 accumulation in TMEM): the hoisted transcription
+    half of the joint fc1 (amx_linear.cpp:137-150).  Agrees with the order-defined linear_bf16_bf16 to <= 1 bf16 ulp.
+    tile_steps: as in linear_bf16_bf16 (time-major {T, N, K} input, N % 128 == 0)."""
+    L.require_cuda(x, w)
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
+        raise RuntimeError("gemm_bf16_bf16 expects bfloat16")
+    k = x.shape[-1]
+    m = x.numel() // k
+    o = w.shape[0]
+    if w.shape[1] != k:
+        raise RuntimeError(f"gemm_bf16_bf16: K mismatch {k} vs {w.shape[1]}")
+    y = torch.empty(x.shape[:-1] + (o,), dtype=torch.bfloat16, device=x.device)
+    telemetry.launches += 1
+    ts_ptr, rows = None, 0
+    if tile_steps is not None and x.dim() == 3 and x.shape[1] % 128 == 0:
+        ts_ptr, rows = ctypes.c_void_p(tile_steps.ctypes.data), x.shape[1]
+    telemetry.bracket("gemm_bf16", (m, k, o), lambda: L.check(
+        L.lib.rnnt_gemm_bf16_bf16_ragged(L.ptr(x), L.ptr(w), L.ptr(y), m, o, k, rows, ts_ptr, L.stream_ptr())))
+    return y
+
+
+def lstm_postop(it, ft, gt, ot, ct, in_scale, out_scale, skip_quant_y):
+    """lstm_postop (init.cpp:126-128; lstm_postop.cpp:14-72): fp32 gate chunks [N, H] (may be the four column chunks of
+    one [N, 4H] tensor), ct fp16 [N, H] updated IN PLACE.  Returns [y_bf16, y_q, h_q, ct] like the reference (the y
+    output the flag does not select is zero-filled; the reference leaves it uninitialised)."""
+    L.require_cuda(ct)
+    for g in (it, ft, gt, ot):
+        if not g.is_cuda or g.dtype != torch.float32 or g.dim() != 2 or g.stride(1) != 1 or g.stride(0) != it.stride(0):
+            raise RuntimeError("lstm_postop: gates must be fp32 CUDA [N, H] tensors with unit column stride and equal row pitch")
+    if ct.dtype != torch.float16:
+        raise RuntimeError("lstm_postop: ct must be float16")
+    n, h = it.shape
+    y_bf16 = torch.zeros((n, h), dtype=torch.bfloat16, device=it.device)
+    y_q = torch.zeros((n, h), dtype=torch.int8, device=it.device)
+    h_q = torch.empty((n, h), dtype=torch.int8, device=it.device)
+    telemetry.launches += 1
+    L.check(L.lib.rnnt_lstm_postop_fp16(L.ptr(it), L.ptr(ft), L.ptr(gt), L.ptr(ot), it.stride(0), L.ptr(ct), float(in_scale),
+                                        float(out_scale), int(bool(skip_quant_y)), L.ptr(y_bf16), L.ptr(y_q), L.ptr(h_q), n, h,
+                                        L.stream_ptr()))
+    return [y_bf16, y_q, h_q, ct]
 
 
 def make_decode_weights(embed, w_ih, w_hh, bias, w_pred, b1, w2, b2):

@@ -25,19 +25,20 @@ try:
 except ImportError:   # not installed offline
     from . import loadgen_shim as lg
 
+from . import _lib
 from .decoder import GreedyDecoder
 from .modeling_rnnt import RNNT
 from .rnnt_qsl import RNNTQSL
 from .utils import logger, seq_to_sen
 
 _DEFAULT_ARGS = dict(enable_bf16=False, split_len=-1, scenario="Offline", load_jit=False, save_jit=False,
-                     enable_process=False, toml_path="", processor_path="")
+                     enable_process=False, toml_path="", processor_path="", exact_order=False)
 
 
 class _Batch:
     """One staged / in-flight batch of the pipelined Offline loop."""
     __slots__ = ("samples", "n_actual", "n_padded", "max_len", "packed", "meta", "ready", "done", "res", "res_len", "tok_host",
-                 "len_host", "cap", "h2d_bytes", "keep", "lens_host")
+                 "len_host", "cap", "h2d_bytes", "keep", "lens_host", "status_host")
 
 
 class PytorchSUT:
@@ -56,7 +57,8 @@ class PytorchSUT:
         self.run_mode = run_mode
         self.device = kwargs.get("device")
         rnnt = RNNT(model_path, run_mode, args.enable_bf16, args.load_jit, device=self.device).eval()
-        self.model = GreedyDecoder(rnnt, run_mode, args.enable_bf16, args.split_len, self.batch_size)
+        self.model = GreedyDecoder(rnnt, run_mode, args.enable_bf16, args.split_len, self.batch_size,
+                                   exact_order=args.exact_order)
         self.scenario = args.scenario if run_mode != "calib" else None
         self.batch_sort = self.scenario == "Offline"
         self.pipelined = run_mode == "quant" and args.split_len == -1
@@ -112,8 +114,8 @@ class PytorchSUT:
         b.samples = chunk
         b.n_actual = len(chunk)
         b.n_padded = math.ceil(b.n_actual / 32) * 32          # pytorch_sut.py:90-104: pad N to a multiple of 32
-        rows = self.qsl.rows
-        lens = [rows[s.index] for s in chunk]
+        x_lens = self.qsl.x_lens_host        # the dataset's x_lens like the reference (pytorch_sut.py:88), = rows (checked by the QSL)
+        lens = [x_lens[s.index] for s in chunk]
         b.max_len = max(lens)
         b.lens_host = lens
         meta = torch.zeros((2, b.n_padded), dtype=torch.int64)
@@ -171,12 +173,16 @@ class PytorchSUT:
             b.len_host = torch.empty((b.n_padded,), dtype=torch.int32, pin_memory=True)
             b.tok_host.copy_(b.res[:, :b.cap], non_blocking=True)
             b.len_host.copy_(b.res_len, non_blocking=True)
+            # device-side watchdog word of this batch's kernels, copied behind them on the same stream (checked in _finish)
+            b.status_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+            _lib.check(_lib.lib.rnnt_peek_device_status(_lib.ptr(b.status_host), _lib.stream_ptr()))
             b.done = torch.cuda.Event()
             b.done.record(self._compute_stream)
         self._prev_done[b.keep[1]] = b.done
 
     def _finish(self, b):
         b.done.synchronize()
+        self._raise_on_device_error(int(b.status_host[0]))
         lens = b.len_host.numpy()
         tokens = b.tok_host.numpy()
         self.h2d_bytes += b.h2d_bytes
@@ -188,6 +194,13 @@ class PytorchSUT:
             tokens = full.numpy()
             self.d2h_bytes += tokens.nbytes
         self._respond(b.samples, tokens, lens)
+
+    def _raise_on_device_error(self, code):
+        """A kernel's bounded wait fired (protocol error): res / res_len of the batch are garbage and must not reach
+        LoadGen as transcripts.  Clears the (sticky, per-device) word so that a caller who handles the error can go on."""
+        if code != 0:
+            _lib.check(_lib.lib.rnnt_clear_device_status(_lib.stream_ptr()))
+            raise RuntimeError(f"librnnt_b200: device-side watchdog/protocol error {code} in this batch; no response sent")
 
     def _respond(self, samples, tokens, lens):
         """query_samples_complete (pytorch_sut.py:107-118) on host arrays: one QuerySampleResponse per sample (pointer into
@@ -214,6 +227,7 @@ class PytorchSUT:
                 fea_lens = torch.nn.functional.pad(fea_lens, (0, pad_n), "constant", 0)
             self.h2d_bytes += feas.numel() * 4 + fea_lens.numel() * 8
             results = self.model(feas, fea_lens)
+            _lib.check_device_status()          # synchronises; raises instead of returning garbage transcripts
         self.batches_run += 1
         return results
 

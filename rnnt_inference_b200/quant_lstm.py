@@ -73,14 +73,14 @@ class iLSTM(torch.nn.LSTM):
         self.weights = [[fn(t) for t in layer] for layer in self.weights]
         return out
 
-    def forward(self, x: Tensor, hx: Optional[List[Tensor]], cx: Optional[List[Tensor]], tile_steps=None
+    def forward(self, x: Tensor, hx: Optional[List[Tensor]], cx: Optional[List[Tensor]], tile_steps=None, true_rows=None
                 ) -> Tuple[Tensor, List[Tensor], List[Tensor]]:
         if hx is None and cx is None:
             n = x.size(1)
             hx = [torch.zeros((n, self.hidden_size), dtype=torch.int8, device=x.device) for _ in range(self.num_layers)]
             cx = [torch.zeros((n, self.hidden_size), dtype=torch.float16, device=x.device) for _ in range(self.num_layers)]
         return P.lstm_amx_int8(x, hx, cx, self.weights, self.rb_scale, self.in_scale, self.out_scale, self.skip_quant_y,
-                               tile_steps=tile_steps)
+                               tile_steps=tile_steps, true_rows=true_rows)
 
 
 class QuantLSTM(iLSTM):

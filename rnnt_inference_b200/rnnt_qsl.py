@@ -27,8 +27,15 @@ class RNNTQSL:
         self.pin_memory = torch.cuda.is_available() if pin_memory is None else pin_memory
         self.arena = None                        # pinned [sum T_i, 240] fp32, samples longest first
         self.arena_off = {}                      # sample id -> first arena row
-        self.rows = [int(x.shape[0]) for x in self.dataset[0]]       # feature rows per sample, plain ints
-        self._keys = [(-int(n), i) for i, n in enumerate(self.dataset[1])]
+        # lengths come from the dataset's x_lens like the reference (pytorch_sut.py:88; the sort key too); a sample whose
+        # tensor holds more rows than x_lens says is used up to x_lens only (the encoder is causal and everything
+        # downstream reads t < x_lens, so the tail can never reach a transcript); fewer rows than x_lens is an error
+        self.x_lens_host = [int(n) for n in self.dataset[1]]
+        for i, (x, n) in enumerate(zip(self.dataset[0], self.x_lens_host)):
+            if int(x.shape[0]) < n:
+                raise RuntimeError(f"RNNTQSL: sample {i} has {int(x.shape[0])} feature rows but x_lens says {n}")
+        self.rows = list(self.x_lens_host)                           # feature rows used per sample, plain ints
+        self._keys = [(-n, i) for i, n in enumerate(self.x_lens_host)]
         self.sample_id_to_sample = {}
         self.qsl = lg.ConstructQSL(self.count, perf_count, self.load_query_samples, self.unload_query_samples)
         self.load_query_samples(range(self.count))
@@ -54,7 +61,7 @@ class RNNTQSL:
         arena = torch.empty((sum(rows), width), dtype=torch.float32, pin_memory=True)
         off = 0
         for i, n in zip(ids, rows):
-            arena[off:off + n].copy_(self.dataset[0][i])
+            arena[off:off + n].copy_(self.dataset[0][i][:n])
             self.arena_off[i] = off
             self.sample_id_to_sample[i] = (arena[off:off + n], self.dataset[1][i])
             off += n

@@ -29,6 +29,10 @@ def _worker(rank, world, port, lengths, batch, out_dir):
         for r, (i, n) in enumerate(zip(ids.tolist(), lens.tolist())):
             tokens[r, :n] = torch.arange(n, dtype=torch.int32) + i                        # tokens depend on the sample id
         g_ids, g_lens, g_tok = sharding.gather_transcripts(ids, lens, tokens, world)
+        # the single-collective form: every rank knows the shard sizes and the token width from the query itself
+        n_max = (len(lengths) + world - 1) // world
+        h_ids, h_lens, h_tok = sharding.gather_transcripts(ids, lens, tokens, world, n_max=n_max, l_max=6)
+        assert torch.equal(g_ids, h_ids) and torch.equal(g_lens, h_lens) and torch.equal(g_tok[:, :6], h_tok[:, :g_tok.shape[1]])
         torch.save({"mine": mine, "ids": g_ids, "lens": g_lens, "tok": g_tok}, os.path.join(out_dir, f"r{rank}.pt"))
     finally:
         dist.destroy_process_group()
