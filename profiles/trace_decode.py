@@ -4,7 +4,10 @@ import ctypes
 import os
 import sys
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+# the cycle traces exist in the debug build only (make -C rnnt_inference_b200/csrc debug)
+os.environ.setdefault("RNNT_B200_LIB", os.path.join(ROOT, "rnnt_inference_b200", "lib", "librnnt_b200_dbg.so"))
 import numpy as np
 import torch
 

