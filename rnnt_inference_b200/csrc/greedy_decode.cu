@@ -25,12 +25,39 @@
 //     (greedy_decode_update_tpp.cpp:22-29 masks only f_lens == 0), which is reproduced exactly: phase 1 runs
 //     every group until its lanes finished, one grid-wide rendezvous yields the batch iteration count, phase 2
 //     replays the remaining iterations for the still-live lanes only.
+//
+// Two instantiations of the same loop (template parameter TC):
+//   TC = true  (rnnt_greedy_decode, the product path): the three contractions of an iteration — prediction-LSTM gates
+//     [active lanes x 640] . [640 x 64 per CTA], g.W_pred [lanes x 320] . [320 x 26] and fc2 [16 lanes x 512] . [512 x 32]
+//     — run on the tensor cores (mma.sync m16n8k16, bf16 operands from XOR-swizzled shared memory through ldmatrix, fp32
+//     accumulators).  With emissions spread over the utterance ~20 % of the lanes re-evaluate the prediction network
+//     per iteration (40..60 lanes per group) and the CUDA-core chains were 85 % of the kernel's time.  The fp32
+//     accumulation order is the tensor core's, not the oracle's or AMX's: hg / logits agree to fp32 rounding, tokens
+//     agree except at near-ties of the top-2 logits (tolerance + margin report).
+//   TC = false (rnnt_greedy_decode_exact_order): the CUDA-core chains in the oracle's order described above, kept for
+//     bit-exact cross-checks of the state machine and of everything downstream of a given y1.
 #include "kernels.cuh"
 #include "gate_math.cuh"
 
 namespace rnnt {
 
 enum : int { LS_CUR = 1, LS_NEED = 2, LS_FINISHED = 4, LS_FIXED = 8 };
+
+// ---------------------------------------------------------------- mma.sync / ldmatrix (TC variant)
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// 16-byte chunk `chunk` of row `row` in a matrix of `row_bytes`-byte rows whose chunks are XOR-swizzled with the low three
+// bits of the row (row_bytes % 128 == 0): the eight rows of an ldmatrix 8x8 tile then fall into eight different bank groups
+__device__ __forceinline__ uint32_t swz(uint32_t base, int row, int row_bytes, int chunk) {
+  return base + (uint32_t)(row * row_bytes) + (uint32_t)((chunk ^ (row & 7)) << 4);
+}
 
 __device__ __forceinline__ void group_barrier(const DecParams& p, int g, int& epoch, bool& ok, int* s_fail) {
   __syncthreads();
@@ -268,6 +295,189 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
   }
 }
 
+// ---------------------------------------------------------------------------------------------- TC variant
+// One LSTM layer for the active lanes on the tensor cores, in chunks of DEC_TC_LANES = 32 lanes (two m16 tiles):
+//   act (shared, swizzled rows of 1280 B) = [lane][x 320 | h 320] bf16, copied as they are (no fp32 expansion);
+//   warp w owns gate columns [8 w, 8 w + 8) of this CTA's 64: B fragments (W_ih then W_hh rows of those columns, K
+//   contiguous = the "col" operand) by ldmatrix.x4 — two k-steps per instruction —, A fragments of both m tiles by
+//   ldmatrix.x4, 2 x 20 k-steps x m-tiles MMAs into fp32 accumulators holding x.W_ih + h.W_hh;
+//   the sums go through shared memory (overlaying act) to the cell update, thread = (unit, lane) as in the exact variant.
+__device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int g, int s, const int* alist, int na,
+                                              const int4* s_state, uint32_t wl_s, const float* s_bias, uint8_t* act_g,
+                                              uint32_t act_s, long long* lt = nullptr) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int lane0 = g * p.LG;
+  float* part = reinterpret_cast<float*>(act_g);          // [32 lanes][64 columns] fp32, after the MMAs
+  for (int a0 = 0; a0 < na; a0 += DEC_TC_LANES) {
+    const int nc = min(DEC_TC_LANES, na - a0);
+    const int mt = (nc + 15) >> 4;
+    // ---- cell-update operand prefetch: thread = (unit uu, lanes ua and ua + 16)
+    const int uu = tid & 15, ua = tid >> 4;
+    float c_old[2] = {0.f, 0.f}; int un[2] = {0, 0}, ucur[2] = {0, 0};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int a = ua + 16 * h;
+      if (a < nc) {
+        const int li = alist[a0 + a];
+        un[h] = lane0 + li;
+        ucur[h] = s_state[li].x & LS_CUR;
+        c_old[h] = p.cg[ucur[h]][layer][(size_t)un[h] * DEC_P + s * DEC_U + uu];
+      }
+    }
+    // ---- stage x | h of the chunk's lanes: 80 16-byte pieces per lane, all loads issued before any store
+    {
+      constexpr int VPL = 2 * DEC_P / 8;      // 80
+      constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;   // 10
+      uint4 v[R]; int dst[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int e = tid + r * DEC_THREADS;
+        const int a = e / VPL, q = e % VPL;
+        dst[r] = -1;
+        v[r] = make_uint4(0u, 0u, 0u, 0u);
+        if (a < nc) {
+          const int li = alist[a0 + a];
+          const int4 st = s_state[li];
+          const int n = lane0 + li, cur = st.x & LS_CUR;
+          dst[r] = a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4);
+          if (q < VPL / 2) {
+            if (layer == 0) {
+              const int sym = st.z;
+              if (sym >= 0 && sym <= 27) v[r] = __ldg(reinterpret_cast<const uint4*>(p.embed + sym * DEC_P) + q);
+            } else {
+              v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][0] + (size_t)n * DEC_P) + q);
+            }
+          } else {
+            v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur][layer] + (size_t)n * DEC_P) + (q - VPL / 2));
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (dst[r] >= 0) *reinterpret_cast<uint4*>(act_g + dst[r]) = v[r];
+    }
+    __syncthreads();
+    if (lt && tid == 0 && a0 == 0) lt[0] = clock64();
+    // ---- tensor-core contraction
+    float acc[2][4];
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[mi][i] = 0.f;
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const int wrow = (layer * 2 + m) * DEC_COLS + warp * 8 + (lane & 7);      // this thread's ldmatrix row of the B tile
+#pragma unroll 2
+      for (int kp = 0; kp < DEC_P / 32; ++kp) {
+        uint32_t b[4];
+        ldsm_x4(swz(wl_s, wrow, DEC_P * 2, kp * 4 + (lane >> 3)), b);
+#pragma unroll
+        for (int k2 = 0; k2 < 2; ++k2) {
+          const int chunk = m * (DEC_P / 8) + (kp * 2 + k2) * 2 + (lane >> 4);
+#pragma unroll
+          for (int mi = 0; mi < 2; ++mi) {
+            if (mi < mt) {
+              uint32_t a[4];
+              ldsm_x4(swz(act_s, mi * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * DEC_P * 2, chunk), a);
+              mma_bf16_16816(acc[mi], a, b[2 * k2], b[2 * k2 + 1]);
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();                       // every warp is done reading act: reuse it for the gate sums
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi) {
+      if (mi < mt) {
+        const int r0 = mi * 16 + (lane >> 2), c0 = warp * 8 + 2 * (lane & 3);
+        *reinterpret_cast<float2*>(part + r0 * DEC_COLS + c0) = make_float2(acc[mi][0], acc[mi][1]);
+        *reinterpret_cast<float2*>(part + (r0 + 8) * DEC_COLS + c0) = make_float2(acc[mi][2], acc[mi][3]);
+      }
+    }
+    __syncthreads();
+    if (lt && tid == 0 && a0 == 0) lt[1] = clock64();
+    // ---- cell update: thread = (unit uu, lanes ua, ua + 16)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int a = ua + 16 * h;
+      if (a < nc) {
+        const int j = s * DEC_U + uu;
+        float gate[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) gate[q] = __fadd_rn(part[a * DEC_COLS + q * DEC_U + uu], s_bias[layer * DEC_COLS + q * DEC_U + uu]);
+        const float it = sigmoid_ps(gate[0]), ft = sigmoid_ps(gate[1]), gt = tanh_ps(gate[2]), ot = sigmoid_ps(gate[3]);
+        const float c_new = __fmaf_rn(it, gt, __fmul_rn(ft, c_old[h]));
+        const float ht = __fmul_rn(ot, tanh_ps(c_new));
+        p.cg[ucur[h] ^ 1][layer][(size_t)un[h] * DEC_P + j] = c_new;
+        p.hg[ucur[h] ^ 1][layer][(size_t)un[h] * DEC_P + j] = (uint16_t)float_to_bf16_bits(ht);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// z[n][col] = sum_k g[n][k] * W_pred[col][k] on the tensor cores: chunk of 32 lanes x this CTA's <= 26 columns (four n8
+// tiles; the rows past ncol of the B tile alias row ncol - 1 and their results are dropped).
+__device__ __forceinline__ void fc1_phase_tc(const DecParams& p, int g, int s, const int* alist, int na, const int4* s_state,
+                                             uint32_t wp_s, uint8_t* act_g, uint32_t act_s) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int lane0 = g * p.LG;
+  const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
+  for (int a0 = 0; a0 < na; a0 += DEC_TC_LANES) {
+    const int nc = min(DEC_TC_LANES, na - a0);
+    const int mt = (nc + 15) >> 4;
+    {
+      constexpr int VPL = DEC_P / 8;          // 40
+      constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;   // 5
+      uint4 v[R]; int dst[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int e = tid + r * DEC_THREADS;
+        const int a = e / VPL, q = e % VPL;
+        dst[r] = -1;
+        v[r] = make_uint4(0u, 0u, 0u, 0u);
+        if (a < nc) {
+          const int li = alist[a0 + a];
+          const int cur = s_state[li].x & LS_CUR;
+          dst[r] = a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4);
+          v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li) * DEC_P) + q);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (dst[r] >= 0) *reinterpret_cast<uint4*>(act_g + dst[r]) = v[r];
+    }
+    __syncthreads();
+    const int mi = warp >> 2, ni = warp & 3;
+    if (mi < mt) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const int brow = min(ni * 8 + (lane & 7), ncol - 1);
+#pragma unroll 2
+      for (int kp = 0; kp < DEC_P / 32; ++kp) {
+        uint32_t b[4];
+        ldsm_x4(swz(wp_s, brow, DEC_P * 2, kp * 4 + (lane >> 3)), b);
+#pragma unroll
+        for (int k2 = 0; k2 < 2; ++k2) {
+          uint32_t a[4];
+          ldsm_x4(swz(act_s, mi * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * DEC_P * 2, (kp * 2 + k2) * 2 + (lane >> 4)), a);
+          mma_bf16_16816(acc, a, b[2 * k2], b[2 * k2 + 1]);
+        }
+      }
+      const int r0 = mi * 16 + (lane >> 2), c0 = ni * 8 + 2 * (lane & 3);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int r = r0 + 8 * h;
+        if (r < nc) {
+          float* zr = p.z + (size_t)(lane0 + alist[a0 + r]) * DEC_J + col0;
+          if (c0 < ncol) zr[c0] = acc[2 * h];
+          if (c0 + 1 < ncol) zr[c0 + 1] = acc[2 * h + 1];
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // Phase D for one lane, executed by one warp, in two halves so that the block-wide staging of the fc2 weights into
 // shared memory overlaps the first half's global loads.
 //   joint_stage : fc1 epilogue  y = bf16(relu((z + y1[cur_t]) + b1))  -> per-warp bf16 vector in shared memory
@@ -308,28 +518,11 @@ __device__ __forceinline__ JointRegs joint_stage(const DecParams& p, int n, int4
   return r;
 }
 
-__device__ __forceinline__ void joint_finish(const DecParams& p, int n, int iter, int4 st, JointRegs r, const uint8_t* w2s,
-                                             const uint16_t* ybuf, const float* s_b2, int lane) {
+// argmax over the 32 logits (lane = column, first maximum wins ties like torch.argmax) + the greedy_decode_update state
+// machine of the lane (greedy_decode_update.cpp:13-96); the lane's new state word goes back to global memory.
+__device__ __forceinline__ void joint_update(const DecParams& p, int n, int iter, int4 st, JointRegs r, float logit, int lane) {
   const int cur_t = st.y;
-  float acc = 0.f;
-  if (lane < DecSmem::W2_ROWS) {
-    const uint4* wrow = reinterpret_cast<const uint4*>(w2s + lane * DecSmem::W2_STRIDE);
-    const uint4* yrow = reinterpret_cast<const uint4*>(ybuf);
-#pragma unroll 4
-    for (int k8 = 0; k8 < DEC_J / 8; ++k8) {      // logits[lane]: sequential chain over k
-      const uint4 wb = wrow[k8];
-      const uint4 yv = yrow[k8];
-      acc = __fmaf_rn(__uint_as_float(yv.x << 16), __uint_as_float(wb.x << 16), acc);
-      acc = __fmaf_rn(__uint_as_float(yv.x & 0xffff0000u), __uint_as_float(wb.x & 0xffff0000u), acc);
-      acc = __fmaf_rn(__uint_as_float(yv.y << 16), __uint_as_float(wb.y << 16), acc);
-      acc = __fmaf_rn(__uint_as_float(yv.y & 0xffff0000u), __uint_as_float(wb.y & 0xffff0000u), acc);
-      acc = __fmaf_rn(__uint_as_float(yv.z << 16), __uint_as_float(wb.z << 16), acc);
-      acc = __fmaf_rn(__uint_as_float(yv.z & 0xffff0000u), __uint_as_float(wb.z & 0xffff0000u), acc);
-      acc = __fmaf_rn(__uint_as_float(yv.w << 16), __uint_as_float(wb.w << 16), acc);
-      acc = __fmaf_rn(__uint_as_float(yv.w & 0xffff0000u), __uint_as_float(wb.w & 0xffff0000u), acc);
-    }
-  }
-  float best = __fadd_rn(acc, s_b2[lane]);
+  float best = logit;
   int bidx = lane;
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) {   // first maximum wins ties (torch.argmax)
@@ -372,6 +565,29 @@ __device__ __forceinline__ void joint_finish(const DecParams& p, int n, int iter
     const uint16_t* nr = p.y1 + ((size_t)next_t * p.N + n) * DEC_J + lane * 16;
     asm volatile("prefetch.global.L2 [%0];" ::"l"(nr));
   }
+}
+
+__device__ __forceinline__ void joint_finish(const DecParams& p, int n, int iter, int4 st, JointRegs r, const uint8_t* w2s,
+                                             const uint16_t* ybuf, const float* s_b2, int lane) {
+  float acc = 0.f;
+  if (lane < DecSmem::W2_ROWS) {
+    const uint4* wrow = reinterpret_cast<const uint4*>(w2s + lane * DecSmem::W2_STRIDE);
+    const uint4* yrow = reinterpret_cast<const uint4*>(ybuf);
+#pragma unroll 4
+    for (int k8 = 0; k8 < DEC_J / 8; ++k8) {      // logits[lane]: sequential chain over k
+      const uint4 wb = wrow[k8];
+      const uint4 yv = yrow[k8];
+      acc = __fmaf_rn(__uint_as_float(yv.x << 16), __uint_as_float(wb.x << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.x & 0xffff0000u), __uint_as_float(wb.x & 0xffff0000u), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.y << 16), __uint_as_float(wb.y << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.y & 0xffff0000u), __uint_as_float(wb.y & 0xffff0000u), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.z << 16), __uint_as_float(wb.z << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.z & 0xffff0000u), __uint_as_float(wb.z & 0xffff0000u), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.w << 16), __uint_as_float(wb.w << 16), acc);
+      acc = __fmaf_rn(__uint_as_float(yv.w & 0xffff0000u), __uint_as_float(wb.w & 0xffff0000u), acc);
+    }
+  }
+  joint_update(p, n, iter, st, r, __fadd_rn(acc, s_b2[lane]), lane);
 }
 
 __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const DecParams p) {

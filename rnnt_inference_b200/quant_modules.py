@@ -70,7 +70,10 @@ class TensorQuantizer(nn.Module):
 
     @property
     def scale(self) -> Tensor:
-        return INT8_MAX / self._amax          # fp32 division, like the reference's `_max_bound / amax`
+        # ONE correctly rounded fp32 division, tensor / tensor like the reference's `_max_bound / amax`.  (A Python float
+        # divided by a tensor is evaluated by torch as reciprocal() * scalar — two roundings, one ulp off for some amax,
+        # which moves weights that sit on a .5 rounding tie.)
+        return torch.full_like(self._amax, INT8_MAX) / self._amax
 
     def _range_of(self, x: Tensor) -> Tensor:
         if self._axis is None:

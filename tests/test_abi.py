@@ -75,3 +75,49 @@ def test_qsl_uses_dataset_x_lens(tmp_path):
     assert int(n) == 4 and torch.equal(x[:4], xs[1][:4])
     with pytest.raises(RuntimeError, match="x_lens"):
         RNNTQSL({"x": xs, "x_lens": [torch.tensor(9), torch.tensor(6), torch.tensor(7)]}, pin_memory=False)
+
+
+def test_quantizer_scale_is_one_correctly_rounded_division():
+    """scale = 127 / amax as ONE fp32 division (the reference divides two tensors): compared with numpy's float32
+    division over many amax values.  torch evaluates `python_float / tensor` as reciprocal * scalar, which is one ulp
+    off for some inputs (e.g. amax = 0.09375) and flips weights that sit on a rounding tie."""
+    import numpy as np
+    import torch
+    from rnnt_inference_b200.quant_modules import QuantDescriptor, TensorQuantizer
+    q = TensorQuantizer(QuantDescriptor(mode="quant"))
+    rng = np.random.default_rng(0)
+    for amax in [0.09375, 5.8358, 1.0, 0.0937499] + rng.uniform(0.01, 8.0, 2000).astype(np.float32).tolist():
+        q.amax = torch.tensor(amax, dtype=torch.float32)
+        want = np.float32(127.0) / np.float32(amax)
+        assert np.float32(q.scale.item()) == want, amax
+
+
+def test_module_quantised_parameters_match_oracle_on_cpu():
+    """Scale algebra / weight quantisation of the modules (quant_lstm.py:193-215, modeling_rnnt.py:62-77) against the
+    oracle's independent restatement, for the BENCH checkpoint (seed 7) and the test checkpoint (seed 11): int8
+    weights, folded biases and every scale bit-equal.  Loading needs no GPU."""
+    import numpy as np
+    import torch
+    from oracle import pipeline as OP
+    from rnnt_inference_b200 import synthetic as S
+    from rnnt_inference_b200.modeling_rnnt import RNNT
+    for seed in (7, 11):
+        sd = S.make_checkpoint(seed=seed)
+        rnnt = RNNT(sd, "quant", True, device=torch.device("cpu")).eval()
+        params = OP.prepare_params(sd)
+        i = 0
+        for rnn in (rnnt.transcription.pre_rnn, rnnt.transcription.post_rnn):
+            for layer in range(rnn.num_layers):
+                w_ih, w_hh, _b, bias = rnn.weights[layer]
+                p = params["enc"][i]
+                np.testing.assert_array_equal(w_ih.numpy(), p["w_ih"], err_msg=f"seed {seed} layer {i} w_ih")
+                np.testing.assert_array_equal(w_hh.numpy(), p["w_hh"], err_msg=f"seed {seed} layer {i} w_hh")
+                np.testing.assert_array_equal(bias.numpy().view(np.uint32), p["bias"].view(np.uint32))
+                assert float(rnn.rb_scale[layer]) == p["rb_scale"] and float(rnn.in_scale[layer]) == p["in_scale"]
+                i += 1
+        d = params["dec"]
+        bits = lambda t: t.detach().contiguous().view(torch.int16).numpy().view(np.uint16)
+        np.testing.assert_array_equal(bits(rnnt.joint.linear1_trans.weight), d["w_trans"])
+        np.testing.assert_array_equal(bits(rnnt.joint.linear1_pred.weight), d["w_pred"])
+        np.testing.assert_array_equal(bits(rnnt.joint.linear2.weight), d["w2"])
+        np.testing.assert_array_equal(rnnt.joint.linear1_bias.detach().numpy(), d["b1"])
