@@ -180,11 +180,20 @@ int64_t rnnt_greedy_decode_workspace_bytes(int N);
 /* y1 [T2][N][J] bf16 (from rnnt_gemm_bf16_bf16 or rnnt_linear_bf16_bf16), f_lens [N] STACKED lengths.
  * In/out state: res [N][L] int32, res_idx/symbols_added/time_idx/pre_g [N] int32,
  * pre_hg0/1 [N][P] bf16, pre_cg0/1 [N][P] fp32.  iters_out (device int32[1], may be NULL) receives
- * the number of batch-lockstep iterations the reference loop would have run. */
+ * the number of batch-lockstep iterations the reference loop would have run.  N <= 2240 per call.
+ * The three contractions of an iteration (prediction-LSTM gates, g.W_pred, fc2) run on the tensor cores (mma.sync bf16,
+ * fp32 accumulation): their summation order is neither the CPU oracle's nor AMX's, so transcripts agree with either
+ * except where the top-2 logits are a near-tie (tolerance + margin report).  Weights 16-byte aligned. */
 int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w_host,
                        int32_t* res, int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
                        uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int32_t* iters_out,
                        void* workspace, void* stream);
+/* Same loop with the contractions on CUDA cores as fp32 FMA chains sequential in k — the accumulation order the CPU
+ * oracle defines —, bit-exact against it: the cross-check of the state machine and of everything downstream of y1. */
+int rnnt_greedy_decode_exact_order(const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w_host,
+                                   int32_t* res, int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx,
+                                   int32_t* pre_g, uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1,
+                                   int32_t* iters_out, void* workspace, void* stream);
 
 #ifdef __cplusplus
 }

@@ -62,6 +62,8 @@ _SIGS = {
     "rnnt_greedy_decode_workspace_bytes": (_i64, [_i]),
     "rnnt_greedy_decode": (_i, [_vp, _vp, _i, _i, ctypes.POINTER(DecodeWeights), _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp,
                                 _vp, _vp, _vp, _vp, _vp]),
+    "rnnt_greedy_decode_exact_order": (_i, [_vp, _vp, _i, _i, ctypes.POINTER(DecodeWeights), _vp, _i, _vp, _vp, _vp, _vp, _vp,
+                                            _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 EXPORTS = tuple(_SIGS)
 # profiling hooks of the debug build (include/rnnt_b200_debug.h); absent from the product library

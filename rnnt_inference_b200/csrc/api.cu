@@ -616,9 +616,10 @@ int64_t rnnt_greedy_decode_workspace_bytes(int N) {
          round_up((int64_t)2 * N * DEC_P * 2, 256) + round_up((int64_t)2 * N * DEC_P * 4, 256);
 }
 
-int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w, int32_t* res,
-                       int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g, uint16_t* pre_hg0,
-                       uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int32_t* iters_out, void* workspace, void* stream) {
+static int decode_run(bool tensor_cores, const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w,
+                      int32_t* res, int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
+                      uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int32_t* iters_out, void* workspace,
+                      void* stream) {
   if (!y1 || !f_lens || !w || !res || !res_idx || !symbols_added || !time_idx || !pre_g || !pre_hg0 || !pre_hg1 ||
       !pre_cg0 || !pre_cg1 || !workspace)
     return fail(RNNT_ERR_INVALID, "greedy_decode: null pointer");
@@ -629,6 +630,9 @@ int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N,
   if (!aligned(workspace, 256) || !aligned(y1, 16) || !aligned(w->b1, 16) || !aligned(w->w_pred, 8) || !aligned(w->w2, 16) || !aligned(w->embed, 16) || !aligned(pre_hg0, 16) || !aligned(pre_hg1, 16) || !aligned(w->w_ih[0], 4) ||
       !aligned(w->w_hh[0], 4) || !aligned(w->w_ih[1], 4) || !aligned(w->w_hh[1], 4))
     return fail(RNNT_ERR_INVALID, "greedy_decode: misaligned buffer");
+  if (tensor_cores && (!aligned(w->w_ih[0], 16) || !aligned(w->w_hh[0], 16) || !aligned(w->w_ih[1], 16) || !aligned(w->w_hh[1], 16) ||
+                       !aligned(w->w_pred, 16)))
+    return fail(RNNT_ERR_INVALID, "greedy_decode: prediction / joint weights must be 16-byte aligned");
   const int NG = 7;
   const int LG = (N + NG - 1) / NG;
   if (LG > DEC_MAXLG) return fail(RNNT_ERR_INVALID, "greedy_decode: N <= %d per call (got %d)", NG * DEC_MAXLG, N);
@@ -658,11 +662,26 @@ int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N,
   p.trace = nullptr; p.trace_cap = 0;
 #endif
   CUDA_TRY(cudaMemsetAsync(ws, 0, 256 + 1024, st));
-  CUDA_TRY(cudaFuncSetAttribute(greedy_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DecSmem::TOTAL));   // per device
+  const void* kern = tensor_cores ? (const void*)greedy_decode_kernel<true> : (const void*)greedy_decode_kernel<false>;
+  const int smem_bytes = tensor_cores ? DecSmemTC::TOTAL : DecSmem::TOTAL;
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));   // per device
   void* args[1] = {(void*)&p};
-  CUDA_TRY(cudaLaunchCooperativeKernel((const void*)greedy_decode_kernel, dim3(NG * DEC_S), dim3(DEC_THREADS), args,
-                                       DecSmem::TOTAL, st));
+  CUDA_TRY(cudaLaunchCooperativeKernel(kern, dim3(NG * DEC_S), dim3(DEC_THREADS), args, smem_bytes, st));
   return RNNT_OK;
+}
+
+int rnnt_greedy_decode(const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w, int32_t* res,
+                       int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g, uint16_t* pre_hg0,
+                       uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int32_t* iters_out, void* workspace, void* stream) {
+  return decode_run(true, y1, f_lens, T2, N, w, res, L, res_idx, symbols_added, time_idx, pre_g, pre_hg0, pre_hg1, pre_cg0, pre_cg1,
+                    iters_out, workspace, stream);
+}
+int rnnt_greedy_decode_exact_order(const uint16_t* y1, const int32_t* f_lens, int T2, int N, const rnnt_decode_weights* w,
+                                   int32_t* res, int L, int32_t* res_idx, int32_t* symbols_added, int32_t* time_idx, int32_t* pre_g,
+                                   uint16_t* pre_hg0, uint16_t* pre_hg1, float* pre_cg0, float* pre_cg1, int32_t* iters_out,
+                                   void* workspace, void* stream) {
+  return decode_run(false, y1, f_lens, T2, N, w, res, L, res_idx, symbols_added, time_idx, pre_g, pre_hg0, pre_hg1, pre_cg0,
+                    pre_cg1, iters_out, workspace, stream);
 }
 
 }  // extern "C"

@@ -590,14 +590,20 @@ __device__ __forceinline__ void joint_finish(const DecParams& p, int n, int iter
   joint_update(p, n, iter, st, r, __fadd_rn(acc, s_b2[lane]), lane);
 }
 
+template <bool TC>
 __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const DecParams p) {
-  extern __shared__ __align__(16) uint8_t smem[];
+  extern __shared__ __align__(128) uint8_t smem[];
+  // exact variant: wl | act | part | pad | wp (padded rows, fp32 activations); TC variant: wl | act | wp (swizzled bf16)
+  constexpr int W_BYTES = TC ? DecSmemTC::W_BYTES : DecSmem::W_BYTES;
+  constexpr int WP_OFFSET = TC ? DecSmemTC::W_BYTES + DecSmemTC::ACT_BYTES
+                               : DecSmem::W_BYTES + DecSmem::ACT_BYTES + DecSmem::PART_BYTES + DecSmem::PAD_BYTES;
   uint16_t* wl = reinterpret_cast<uint16_t*>(smem);
-  float* act = reinterpret_cast<float*>(smem + DecSmem::W_BYTES);
-  float* part = reinterpret_cast<float*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES);
-  uint16_t* wp = reinterpret_cast<uint16_t*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES + DecSmem::PART_BYTES + DecSmem::PAD_BYTES);
-  uint8_t* w2s = smem + DecSmem::W_BYTES;                                    // joint-phase overlay of act | part | pad
+  float* act = reinterpret_cast<float*>(smem + W_BYTES);
+  float* part = reinterpret_cast<float*>(smem + DecSmem::W_BYTES + DecSmem::ACT_BYTES);       // exact variant only
+  uint16_t* wp = reinterpret_cast<uint16_t*>(smem + WP_OFFSET);
+  uint8_t* w2s = smem + W_BYTES;                                             // exact: joint-phase overlay of act | part | pad
   uint16_t* jy = reinterpret_cast<uint16_t*>(w2s + DecSmem::JY_OFFSET);
+  const uint32_t wl_s = smem_u32(smem), act_s = smem_u32(smem + W_BYTES), wp_s = smem_u32(smem + WP_OFFSET);
   bool w2_valid = false;
   __shared__ int4 s_state[DEC_MAXLG];
   __shared__ int alist[DEC_MAXLG];
@@ -611,19 +617,34 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
 
   // resident weights: wl[layer][m][c][k], c = gate*16 + u  <-  W[(gate*320 + s*16 + u)][k]
-  for (int e = tid; e < 2 * 2 * DEC_COLS * (DEC_P / 2); e += DEC_THREADS) {
-    const int k2 = e % (DEC_P / 2);
-    int r = e / (DEC_P / 2);
-    const int c = r % DEC_COLS; r /= DEC_COLS;
-    const int m = r & 1, layer = r >> 1;
-    const uint16_t* src = (m == 0 ? p.w_ih[layer] : p.w_hh[layer]) + (size_t)((c / DEC_U) * DEC_P + s * DEC_U + (c % DEC_U)) * DEC_P;
-    reinterpret_cast<uint32_t*>(wl + ((size_t)(layer * 2 + m) * DEC_COLS + c) * DEC_KSTR)[k2] =
-        reinterpret_cast<const uint32_t*>(src)[k2];
-  }
-  for (int e = tid; e < ncol * (DEC_P / 2); e += DEC_THREADS) {
-    const int k2 = e % (DEC_P / 2), cl = e / (DEC_P / 2);
-    reinterpret_cast<uint32_t*>(wp + (size_t)cl * DEC_KSTR)[k2] =
-        reinterpret_cast<const uint32_t*>(p.w_pred + (size_t)(col0 + cl) * DEC_P)[k2];
+  if constexpr (TC) {
+    constexpr int CPR = DEC_P / 8;        // 40 16-byte chunks per row
+    for (int e = tid; e < 2 * 2 * DEC_COLS * CPR; e += DEC_THREADS) {
+      const int q = e % CPR, r = e / CPR;                 // r = (layer * 2 + m) * 64 + c
+      const int c = r % DEC_COLS, m = (r / DEC_COLS) & 1, layer = r / (2 * DEC_COLS);
+      const uint16_t* src = (m == 0 ? p.w_ih[layer] : p.w_hh[layer]) + (size_t)((c / DEC_U) * DEC_P + s * DEC_U + (c % DEC_U)) * DEC_P;
+      *reinterpret_cast<uint4*>(smem + r * (DEC_P * 2) + ((q ^ (r & 7)) << 4)) = __ldg(reinterpret_cast<const uint4*>(src) + q);
+    }
+    for (int e = tid; e < ncol * CPR; e += DEC_THREADS) {
+      const int q = e % CPR, cl = e / CPR;
+      *reinterpret_cast<uint4*>(smem + WP_OFFSET + cl * (DEC_P * 2) + ((q ^ (cl & 7)) << 4)) =
+          __ldg(reinterpret_cast<const uint4*>(p.w_pred + (size_t)(col0 + cl) * DEC_P) + q);
+    }
+  } else {
+    for (int e = tid; e < 2 * 2 * DEC_COLS * (DEC_P / 2); e += DEC_THREADS) {
+      const int k2 = e % (DEC_P / 2);
+      int r = e / (DEC_P / 2);
+      const int c = r % DEC_COLS; r /= DEC_COLS;
+      const int m = r & 1, layer = r >> 1;
+      const uint16_t* src = (m == 0 ? p.w_ih[layer] : p.w_hh[layer]) + (size_t)((c / DEC_U) * DEC_P + s * DEC_U + (c % DEC_U)) * DEC_P;
+      reinterpret_cast<uint32_t*>(wl + ((size_t)(layer * 2 + m) * DEC_COLS + c) * DEC_KSTR)[k2] =
+          reinterpret_cast<const uint32_t*>(src)[k2];
+    }
+    for (int e = tid; e < ncol * (DEC_P / 2); e += DEC_THREADS) {
+      const int k2 = e % (DEC_P / 2), cl = e / (DEC_P / 2);
+      reinterpret_cast<uint32_t*>(wp + (size_t)cl * DEC_KSTR)[k2] =
+          reinterpret_cast<const uint32_t*>(p.w_pred + (size_t)(col0 + cl) * DEC_P)[k2];
+    }
   }
   for (int e = tid; e < 2 * DEC_COLS; e += DEC_THREADS) {
     const int layer = e / DEC_COLS, c = e % DEC_COLS;
@@ -702,17 +723,69 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     if (tr) { trow[0] = clock64(); trow[7] = na; }
 
     if (na > 0) {
-      lstm_phase(p, 0, g, s, alist, na, s_state, wl, s_bias, act, part, tr ? trow + 12 : nullptr);
+      if constexpr (TC) lstm_phase_tc(p, 0, g, s, alist, na, s_state, wl_s, s_bias, smem + W_BYTES, act_s, tr ? trow + 12 : nullptr);
+      else lstm_phase(p, 0, g, s, alist, na, s_state, wl, s_bias, act, part, tr ? trow + 12 : nullptr);
       if (tr) trow[1] = clock64();
       group_barrier(p, g, epoch, ok, &s_fail);
       if (tr) trow[2] = clock64();
-      lstm_phase(p, 1, g, s, alist, na, s_state, wl, s_bias, act, part);
+      if constexpr (TC) lstm_phase_tc(p, 1, g, s, alist, na, s_state, wl_s, s_bias, smem + W_BYTES, act_s);
+      else lstm_phase(p, 1, g, s, alist, na, s_state, wl, s_bias, act, part);
       group_barrier(p, g, epoch, ok, &s_fail);
       if (tr) trow[3] = clock64();
-      fc1_phase(p, g, s, alist, na, s_state, wp, act);
+      if constexpr (TC) fc1_phase_tc(p, g, s, alist, na, s_state, wp_s, smem + W_BYTES, act_s);
+      else fc1_phase(p, g, s, alist, na, s_state, wp, act);
       group_barrier(p, g, epoch, ok, &s_fail);
       if (tr) trow[4] = clock64();
     }
+    if constexpr (TC) {
+      // ---- phase D on the tensor cores: this CTA's lanes li = s + 20 j (j < 16) form ONE m16 tile.
+      //   1. warp w stages y = bf16(relu((z + y1[cur_t]) + b1)) of lanes j = w and w + 8 as rows of a [16][512] bf16 matrix
+      //      (row pitch 1040 B: ldmatrix rows in different bank groups);
+      //   2. warps 0..3: logits[16][8 w .. 8 w + 8) = y . W2^T, 32 k-steps; B fragments straight from global memory (W2 is
+      //      32 KB, read-only, L1-resident), fp32 logits + b2 to shared memory;
+      //   3. the staging warps run argmax + the update state machine on their lanes.
+      uint8_t* jy_g = smem + W_BYTES;
+      const uint32_t jy_s = act_s;
+      float* lg = reinterpret_cast<float*>(smem + W_BYTES + DecSmemTC::JY_BYTES);
+      JointRegs jr[2]; int4 st2[2]; bool on[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int j = warp + 8 * h, li = s + j * DEC_S;
+        on[h] = false;
+        jr[h] = JointRegs{0, 0, 0, 0};
+        st2[h] = make_int4(LS_FIXED, 0, 0, 0);
+        if (li < nl) {
+          st2[h] = s_state[li];
+          on[h] = !(st2[h].x & LS_FIXED);
+          if (on[h]) jr[h] = joint_stage(p, lane0 + li, st2[h], reinterpret_cast<uint16_t*>(jy_g + j * DecSmemTC::JY_PITCH), s_b1, lane);
+        }
+      }
+      __syncthreads();
+      if (warp < 4) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const uint16_t* wrow = p.w2 + (size_t)(warp * 8 + (lane >> 2)) * DEC_J + 2 * (lane & 3);
+        const uint32_t arow = jy_s + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * DecSmemTC::JY_PITCH) + (uint32_t)((lane >> 4) << 4);
+#pragma unroll 4
+        for (int ks = 0; ks < DEC_J / 16; ++ks) {
+          const uint32_t b0 = __ldg(reinterpret_cast<const uint32_t*>(wrow + ks * 16));
+          const uint32_t b1 = __ldg(reinterpret_cast<const uint32_t*>(wrow + ks * 16 + 8));
+          uint32_t a[4];
+          ldsm_x4(arow + ks * 32, a);
+          mma_bf16_16816(acc, a, b0, b1);
+        }
+        const int r0 = lane >> 2, c0 = warp * 8 + 2 * (lane & 3);
+        lg[r0 * DEC_V + c0] = __fadd_rn(acc[0], s_b2[c0]);
+        lg[r0 * DEC_V + c0 + 1] = __fadd_rn(acc[1], s_b2[c0 + 1]);
+        lg[(r0 + 8) * DEC_V + c0] = __fadd_rn(acc[2], s_b2[c0]);
+        lg[(r0 + 8) * DEC_V + c0 + 1] = __fadd_rn(acc[3], s_b2[c0 + 1]);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int j = warp + 8 * h;
+        if (on[h]) joint_update(p, lane0 + s + j * DEC_S, iter, st2[h], jr[h], lg[j * DEC_V + lane], lane);
+      }
+    } else {
     // ---- phase D: lanes li = s, s+S, ... ; one warp per lane and pass.  The LSTM / fc1 phases overwrite the overlay, so
     // the fc2 weights are staged again whenever they ran; the staging loads overlap the first pass's operand loads.
     if (na > 0) w2_valid = false;
@@ -753,6 +826,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         __syncwarp();
       }
     }
+    }
     if (tr) trow[5] = clock64();
     group_barrier(p, g, epoch, ok, &s_fail);
     if (tr) trow[6] = clock64();
@@ -777,5 +851,8 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     if (blockIdx.x == 0 && tid == 0 && p.iters_out) *p.iters_out = total_iters;
   }
 }
+
+template __global__ void greedy_decode_kernel<true>(const DecParams);
+template __global__ void greedy_decode_kernel<false>(const DecParams);
 
 }  // namespace rnnt

@@ -209,6 +209,22 @@ struct DecParams {
   int trace_cap;
 };
 
+// tensor-core variant: bf16 weights / activations as XOR-swizzled 16-byte chunks (conflict-free ldmatrix), no row padding
+constexpr int DEC_TC_LANES = 32;      // active lanes per LSTM / fc1 pass (two m16 tiles)
+struct DecSmemTC {
+  static constexpr int W_BYTES = 2 * 2 * DEC_COLS * DEC_P * 2;             // [layer][ih|hh][col][k] bf16 = 163,840
+  static constexpr int ACT_BYTES = DEC_TC_LANES * 2 * DEC_P * 2;           // [lane][x|h] bf16 = 40,960 (then the fp32 gate sums)
+  static constexpr int WP_BYTES = DEC_JC * DEC_P * 2;                      // this CTA's W_pred rows = 16,640
+  // joint phase overlays act: y of the CTA's <= 16 lanes (bf16 rows of 512, pitch 1040 B) + fp32 logits [16][32]
+  static constexpr int JY_PITCH = DEC_J * 2 + 16;
+  static constexpr int JY_BYTES = 16 * JY_PITCH;                           // 16,640
+  static_assert(JY_BYTES + 16 * DEC_V * 4 <= ACT_BYTES, "joint overlay does not fit");
+  static_assert(DEC_MAXLG <= 16 * DEC_S, "a CTA's lanes must fit one m16 tile");
+  static_assert(DEC_TC_LANES * DEC_COLS * 4 <= ACT_BYTES, "gate sums do not fit");
+  static constexpr int TOTAL = W_BYTES + ACT_BYTES + WP_BYTES;             // 221,440 (+ ~9 KB static)
+};
+
+template <bool TC>
 __global__ void greedy_decode_kernel(const DecParams p);
 
 }  // namespace rnnt

@@ -18,8 +18,9 @@ class GreedyDecoder(torch.nn.Module):
     def __init__(self, model, run_mode, enable_bf16=False, split_len=-1, batch_size=1, fused=True, exact_order=False,
                  keep_intermediates=False):
         """fused / exact_order / keep_intermediates are extensions (quant mode): fused=False runs the reference's
-        per-iteration operator loop; exact_order=True computes the hoisted f.W_trans on CUDA cores in the CPU oracle's
-        accumulation order instead of the tcgen05 GEMM (bit-exact cross-checks); keep_intermediates leaves the encoder
+        per-iteration operator loop; exact_order=True computes every bf16 contraction (the hoisted f.W_trans and the
+        decode loop's) on CUDA cores in the CPU oracle's accumulation order instead of on the tensor cores (bit-exact
+        cross-checks); keep_intermediates leaves the encoder
         output and the hoisted product of the last call in self.last_f / self.last_y1 (tests, reports)."""
         super().__init__()
         self.rnnt = model
@@ -115,7 +116,7 @@ class GreedyDecoder(torch.nn.Module):
             if self.last_iters is None or self.last_iters.device != dev:
                 self.last_iters = torch.zeros(1, dtype=torch.int32, device=dev)
             P.greedy_decode(y1, f_lens, self.rnnt.decode_weights(), self.res, self.res_idx, self.symbols_added, self.time_idx,
-                            self.pre_g.view(-1), self.pre_hg, self.pre_cg, self.last_iters)
+                            self.pre_g.view(-1), self.pre_hg, self.pre_cg, self.last_iters, exact_order=self.exact_order)
             return self.res
         # reference loop, one operator per step (decoder.py:186-211); fi aliases f[0] like the reference
         fi = f[0]

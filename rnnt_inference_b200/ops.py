@@ -260,8 +260,11 @@ def make_decode_weights(embed, w_ih, w_hh, bias, w_pred, b1, w2, b2):
     return dw
 
 
-def greedy_decode(y1, f_lens, dw, res, res_idx, symbols_added, time_idx, pre_g, pre_hg, pre_cg, iters_out=None):
-    """Device-resident decode loop (decoder.py:188-211). State tensors are updated in place."""
+def greedy_decode(y1, f_lens, dw, res, res_idx, symbols_added, time_idx, pre_g, pre_hg, pre_cg, iters_out=None,
+                  exact_order=False):
+    """Device-resident decode loop (decoder.py:188-211). State tensors are updated in place.  exact_order=False: the
+    contractions run on the tensor cores; True: CUDA-core chains in the CPU oracle's accumulation order (bit-exact
+    cross-checks)."""
     L.require_cuda(y1, f_lens, res, res_idx, symbols_added, time_idx, pre_g, *pre_hg, *pre_cg)
     t2, n, j = y1.shape
     assert j == J and y1.dtype == torch.bfloat16
@@ -271,7 +274,8 @@ def greedy_decode(y1, f_lens, dw, res, res_idx, symbols_added, time_idx, pre_g, 
     ws = _ws.get("decode", L.lib.rnnt_greedy_decode_workspace_bytes(n), y1.device)
     st = L.stream_ptr()
     telemetry.launches += 1
-    telemetry.bracket("greedy_decode", (t2, n), lambda: L.check(L.lib.rnnt_greedy_decode(
+    fn = L.lib.rnnt_greedy_decode_exact_order if exact_order else L.lib.rnnt_greedy_decode
+    telemetry.bracket("greedy_decode", (t2, n), lambda: L.check(fn(
         L.ptr(y1), L.ptr(f_lens), t2, n, ctypes.byref(dw), L.ptr(res), res.shape[1], L.ptr(res_idx), L.ptr(symbols_added),
         L.ptr(time_idx), L.ptr(pre_g), L.ptr(pre_hg[0]), L.ptr(pre_hg[1]), L.ptr(pre_cg[0]), L.ptr(pre_cg[1]), L.ptr(iters_out),
         L.ptr(ws), st)))

@@ -3,10 +3,10 @@
 Two tiers, as SURVEY 7.2 rules:
   * int8 / fp16 tier (encoder) and the decode state machine: bit-exact.  With `exact_order=True` the hoisted f.W_trans runs
     on CUDA cores in the oracle's accumulation order and whole transcripts are bit-exact.
-  * default path: the hoisted product runs on the tensor cores (tcgen05); it may differ from the oracle's (and AMX's) order
-    by 1 bf16 ulp on ~1e-4 of the elements.  Checked as: encoder output bit-exact; y1 <= 1 ulp; transcripts bit-exact
-    against the oracle decoding THE SAME y1; and against the pure oracle every differing utterance must have started at a
-    near-tie of the top-2 logits (margin report, rnnt_inference_b200.eval_accuracy)."""
+  * default path: the bf16 contractions (hoisted f.W_trans: tcgen05; decode loop: mma.sync) run on the tensor cores, whose
+    fp32 accumulation order is neither the oracle's nor AMX's.  Checked as: encoder output bit-exact; y1 <= 1 bf16 ulp;
+    every transcript that differs from the oracle's must have departed at a near-tie of the top-2 logits (margin report,
+    rnnt_inference_b200.eval_accuracy), and >= 90 % of the transcripts are identical."""
 import numpy as np
 import pytest
 import torch
@@ -110,12 +110,14 @@ def test_decoder_tensor_core_hoist_vs_oracle(setup):
 
     got = [list(res[i, :res_len[i]]) for i in range(len(feats))]
     assert sum(len(t) for t in got) > 100
-    assert got == oracle_decode(y1_gpu)                                          # same y1 -> bit-exact transcripts
-    trace = O.new_decision_trace(len(feats), 2 * int(f_lens.max()) + 64)
-    truth = oracle_decode(y1_o, trace)
-    rep = E.compare_transcripts(got, truth, trace, margin_tol=MARGIN_TOL)
-    assert rep["unexplained"] == [], rep["differences"]
-    assert rep["identical_utterances"] >= 0.9 * len(feats)
+    # the decode loop's contractions run on the tensor cores as well: against the oracle decoding the SAME y1, and against
+    # the pure oracle, a transcript may only depart at a near-tie of the top-2 logits
+    for y1 in (y1_gpu, y1_o):
+        trace = O.new_decision_trace(len(feats), 2 * int(f_lens.max()) + 64)
+        truth = oracle_decode(y1, trace)
+        rep = E.compare_transcripts(got, truth, trace, margin_tol=MARGIN_TOL)
+        assert rep["unexplained"] == [], rep["differences"]
+        assert rep["identical_utterances"] >= 0.9 * len(feats)
 
 
 def test_decoder_split_len_vs_oracle(setup):
