@@ -43,6 +43,7 @@ import torch
 UTTS_PER_GPU = 2513       # configs/mlperf.conf:13 performance_sample_count of the reference
 BATCH = 2048              # SUT batch size on B200 (the reference CPU run uses 256, run.sh:71): more 128-row tiles per CTA in the recurrent kernel; <= 2240 decode lanes per launch, multiple of 128 for ragged tile skipping
 QUERY_TOKEN_CAP = 256     # token columns of the transcript gather: the longest utterance has 250 stacked frames; a longer row is clipped in the gather (never observed: ~0.27 tokens per stacked frame)
+DECODE_MARGIN_TOL = 0.3   # one bf16 ulp of the prediction state moves a logit of the synthetic joint by up to 8 * 8 * 2^-8 = 0.25 (tests/test_gpu_pipeline.py)
 METRIC = "offline_utterances_per_second"
 UNIT = "utterances/s"
 
@@ -233,6 +234,8 @@ def kernel_shares(events):
     out = {}
     for name, recs in events.items():
         out[name] = round(sum(s.elapsed_time(e) for s, e, _ in recs), 3)
+    if "greedy_decode" in events:       # one launch per batch: (lanes, stacked frames of the longest, ms)
+        out["greedy_decode_per_batch"] = [(u[1], u[0], round(s.elapsed_time(e), 3)) for s, e, u in events["greedy_decode"]]
     return out
 
 
@@ -316,11 +319,11 @@ def parity_check(decoder, chunks, device):
     pad = lambda a, fill: np.pad(a, ((0, 0), (0, m - a.shape[1])), constant_values=fill)
     trace = {"sym": np.concatenate([pad(t["sym"], -1) for t in traces]), "margin": np.concatenate([pad(t["margin"], 0) for t in traces]),
              "count": np.concatenate([t["count"] for t in traces])}
-    rep = E.compare_transcripts(test, truth, trace, margin_tol=0.05)
+    rep = E.compare_transcripts(test, truth, trace, margin_tol=DECODE_MARGIN_TOL)
     return {"utterances": rep["utterances"], "identical_utterances": rep["identical_utterances"],
             "tokens": rep["tokens_truth"], "token_agreement": round(rep["token_agreement"], 6),
             "wer_vs_oracle": round(rep["wer_vs_truth"], 6), "differing": [(d["utterance"], d["first_differing_token"], round(d.get("margin", -1), 5)) for d in rep["differences"]][:16],
-            "differences_not_at_a_near_tie": len(rep["unexplained"]), "margin_tol": 0.05,
+            "differences_not_at_a_near_tie": len(rep["unexplained"]), "margin_tol": DECODE_MARGIN_TOL,
             "margin_quantiles": {str(k): round(v, 5) for k, v in rep.get("margin_quantiles", {}).items()}}
 
 

@@ -17,12 +17,14 @@ from rnnt_inference_b200.modeling_rnnt import RNNT
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 cap_frames = int(sys.argv[2]) if len(sys.argv) > 2 else 500
+offset = int(sys.argv[3]) if len(sys.argv) > 3 else 0          # skip the `offset` longest utterances (second bench batch: 465 2048)
 torch.cuda.set_device(0)
 rnnt = RNNT(S.make_checkpoint(), "quant", True).eval()
 dec = GreedyDecoder(rnnt, "quant", True, -1, n)
-lens = np.sort(S.utterance_lengths(2513))[::-1][:n]
+lens = np.sort(S.utterance_lengths(2513))[::-1][offset:offset + n]
 lens = np.minimum(lens, cap_frames)
-feats = [S.make_features(int(l), i) for i, l in enumerate(lens)]
+order = np.argsort(-S.utterance_lengths(2513), kind="stable")[offset:offset + n]      # the bench's utterances, not look-alikes
+feats = [S.make_features(int(l), int(i)) for i, l in zip(order, lens)]
 packed = torch.cat(feats, 0).cuda()
 offsets = torch.tensor(np.concatenate([[0], np.cumsum(lens[:-1])]), dtype=torch.int64).cuda()
 lens_t = torch.tensor(lens.copy(), dtype=torch.int32).cuda()

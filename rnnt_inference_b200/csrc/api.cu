@@ -296,44 +296,101 @@ int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t 
 }
 
 }  // extern "C"
+// cluster size of the projection GEMM: CTAs of a cluster share the W operand of an n tile by TMA multicast (gemm_i8.cu).
+// Process-wide tuning knob (results do not depend on it): rnnt_tune_gemm_cluster / environment variable RNNT_GEMM_CLUSTER.
+static int g_gemm_cluster = -1;
+static int gemm_cluster_pref() {
+  int& v = g_gemm_cluster;
+  if (v < 0) {
+    const char* s = getenv("RNNT_GEMM_CLUSTER");
+    v = s ? atoi(s) : 2;
+    if (v != 1 && v != 2 && v != 4) v = 2;
+  }
+  return v;
+}
+
+template <int BN, int CM>
+static int gemm_launch_cm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int num_m, int num_n, int num_k,
+                          int* status, const RowSkip& skip, bool gate_blocked, cudaStream_t st, bool* unsupported) {
+  auto kern = gemm_i8_i32_kernel<BN, CM>;
+  // the opt-in is per device/context: set on every launch (a cached per-process flag would skip it on a second GPU)
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::TOTAL));
+  const int sms = sm_count();
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = GemmSmem<BN>::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  int clusters = std::max(1, (sms > 0 ? sms : 148) / CM);
+  if (CM > 1) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CM; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    // a persistent kernel must not ask for more clusters than can be resident at once (GPC boundaries limit them)
+    cfg.gridDim = dim3(clusters * CM);
+    int max_active = 0;
+    if (cudaOccupancyMaxActiveClusters(&max_active, kern, &cfg) != cudaSuccess || max_active < 1) {
+      cudaGetLastError();
+      *unsupported = true;
+      return RNNT_OK;
+    }
+    clusters = std::min(clusters, max_active);
+  }
+  const int num_super = ((num_m + CM - 1) / CM) * num_n;
+  clusters = std::max(1, std::min(clusters, num_super));
+  cfg.gridDim = dim3(clusters * CM);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0);
+  if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "gemm_i8_i32 launch failed: %s", cudaGetErrorString(e));
+  return RNNT_OK;
+}
+
 template <int BN>
 static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, const RowSkip& skip, cudaStream_t st,
                        bool gate_blocked = false) {
-  CUtensorMap ta, tb, tc;
-  {
-    uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)K};
-    uint32_t box[2] = {GEMM_BK, GEMM_BM};
-    if (int r = make_tmap(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, A, dims, str, box)) return r;
-  }
-  {
-    uint64_t dims[2] = {(uint64_t)K, (uint64_t)N}, str[1] = {(uint64_t)K};
-    uint32_t box[2] = {GEMM_BK, BN};
-    if (int r = make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, W, dims, str, box)) return r;
-  }
-  if (!gate_blocked) {
-    uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[1] = {(uint64_t)N * 4};
-    uint32_t box[2] = {32, 32};
-    if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 2, C, dims, str, box)) return r;
-  } else {
-    // gate-blocked projection for the recurrent kernel: C[slice 32][gate 4][unit octet 4][row M][8] int32, column
-    // gate*1024 + slice*32 + octet*8 + u of the row-major result.  A 32-column chunk of the epilogue is one (gate, slice):
-    // box = 8 units x 32 rows x 4 octets.
-    uint64_t dims[5] = {8, (uint64_t)M, 4, 4, 32};
-    uint64_t str[4] = {32, (uint64_t)M * 32, (uint64_t)M * 128, (uint64_t)M * 512};
-    uint32_t box[5] = {8, 32, 4, 1, 1};
-    if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 5, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return r;
-  }
+  const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
+  // clusters pay off when there are several m tiles per n tile; small problems and BN < 256 run as single CTAs
+  int cm = (BN == 256 && num_m >= 8) ? gemm_cluster_pref() : 1;
   int* status = device_status();
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
-  auto kern = gemm_i8_i32_kernel<BN>;
-  // the opt-in is per device/context: set on every launch (a cached per-process flag would skip it on a second GPU)
-  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::TOTAL));
-  const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
-  const int sms = sm_count();
-  const int grid = std::max(1, std::min(sms > 0 ? sms : 148, num_m * num_n));
-  kern<<<grid, GEMM_THREADS, GemmSmem<BN>::TOTAL, st>>>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0);
-  CUDA_TRY(cudaGetLastError());
-  return RNNT_OK;
+  for (;;) {
+    CUtensorMap ta, tb, tc;
+    {
+      uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)K};
+      uint32_t box[2] = {GEMM_BK, GEMM_BM};
+      if (int r = make_tmap(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, A, dims, str, box)) return r;
+    }
+    {
+      uint64_t dims[2] = {(uint64_t)K, (uint64_t)N}, str[1] = {(uint64_t)K};
+      uint32_t box[2] = {GEMM_BK, (uint32_t)(BN / cm)};
+      if (int r = make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, W, dims, str, box)) return r;
+    }
+    if (!gate_blocked) {
+      uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[1] = {(uint64_t)N * 4};
+      uint32_t box[2] = {32, 32};
+      if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 2, C, dims, str, box)) return r;
+    } else {
+      // gate-blocked projection for the recurrent kernel: C[slice 32][gate 4][unit octet 4][row M][8] int32, column
+      // gate*1024 + slice*32 + octet*8 + u of the row-major result.  A 32-column chunk of the epilogue is one (gate, slice):
+      // box = 8 units x 32 rows x 4 octets.
+      uint64_t dims[5] = {8, (uint64_t)M, 4, 4, 32};
+      uint64_t str[4] = {32, (uint64_t)M * 32, (uint64_t)M * 128, (uint64_t)M * 512};
+      uint32_t box[5] = {8, 32, 4, 1, 1};
+      if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 5, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return r;
+    }
+    bool unsupported = false;
+    int r;
+    if constexpr (BN == 256) {
+      if (cm == 4) r = gemm_launch_cm<256, 4>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+      else if (cm == 2) r = gemm_launch_cm<256, 2>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+      else r = gemm_launch_cm<256, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+    } else {
+      r = gemm_launch_cm<BN, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+    }
+    if (r) return r;
+    if (!unsupported) return RNNT_OK;
+    cm >>= 1;                                    // cluster launch not possible here: halve the cluster
+    if (cm < 1) return fail(RNNT_ERR_CUDA, "gemm_i8_i32: no launchable configuration");
+  }
 }
 
 extern "C" {
@@ -490,6 +547,11 @@ extern "C" {
 static int g_rec_debug = 0;
 int rnnt_debug_set_recurrent_flags(int flags) { g_rec_debug = flags; return RNNT_OK; }
 #endif
+int rnnt_tune_gemm_cluster(int ctas) {
+  if (ctas != 1 && ctas != 2 && ctas != 4) return fail(RNNT_ERR_INVALID, "gemm cluster size must be 1, 2 or 4");
+  g_gemm_cluster = ctas;
+  return RNNT_OK;
+}
 int rnnt_tune_recurrent_cluster(int ctas) {
   if (ctas != 1 && ctas != 2 && ctas != 4 && ctas != 8) return fail(RNNT_ERR_INVALID, "recurrent cluster size must be 1, 2, 4 or 8");
   g_rec_cluster = ctas;

@@ -12,6 +12,11 @@
 //   warp 2   : TMEM allocator
 //   warps 4-7: epilogue       — tcgen05.ld 32 lanes x 32 columns -> swizzled smem staging -> TMA store of a
 //                               32-row x 128-byte box per warp (fully coalesced int32 rows in HBM)
+// Clusters (template parameter CM = 1, 2, 4): the kernel is bound by the L2 -> SM operand traffic (ncu round 1: L2 71 %,
+// tensor pipe 45 %, DRAM 45 %): a 128 x 256 tile reads (128 + 256) x K bytes.  CM CTAs of a thread-block cluster work on CM
+// consecutive m tiles of the SAME n tile and share its W operand: each CTA fetches 1/CM of the W box and TMA-multicasts
+// it into the same stage of every CTA of the cluster, so a CTA-tile costs (128 + 256 / CM) x K bytes of L2 reads.  A stage
+// is free when the MMAs of ALL CM CTAs have consumed it (multicast tcgen05.commit onto every CTA's empty barrier).
 // The int32 result is stored unscaled on purpose: the reference adds the recurrent int32 accumulator BEFORE
 // converting to float (tile_product_tpp.hpp:336-342), and |acc| may exceed 2^24, so pre-scaling to float would
 // break bit-exactness.  Bound: HBM write of C (16 B * 4H... = 4*N bytes per row) vs tensor pipe at large K.
@@ -20,12 +25,22 @@
 namespace rnnt {
 
 
-template <int BN>
+template <int BN, int CM>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles, int num_k_blocks,
                    int* __restrict__ status, const RowSkip skip, const int gate_blocked) {
   using S = GemmSmem<BN>;
+  constexpr uint16_t MC_MASK = (uint16_t)((1u << CM) - 1u);
+  const int rank = (CM > 1) ? (int)cluster_ctarank() : 0;
+  const int cluster_id = blockIdx.x / CM, num_clusters = gridDim.x / CM;
+  const int num_m_super = (num_m_tiles + CM - 1) / CM;
+  const int num_super = num_m_super * num_n_tiles;
+  // tile of this CTA inside super tile st: m tile (st / num_n) * CM + rank; it is `alive` unless past the matrix or a
+  // dead (timestep, batch tile) of a ragged batch; a super tile is skipped by the whole cluster when no CTA is alive
+  auto m_of = [&](int st, int r) { return (st / num_n_tiles) * CM + r; };
+  auto alive_at = [&](int st, int r) { const int m = m_of(st, r); return m < num_m_tiles && !skip.dead((long long)m * GEMM_BM); };
+  auto any_alive = [&](int st) { bool a = false; for (int r = 0; r < CM; ++r) a |= alive_at(st, r); return a; };
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_a = smem_base;
@@ -41,7 +56,6 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = num_m_tiles * num_n_tiles;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -49,13 +63,14 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     tma_prefetch_desc(&tmap_c);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < GEMM_STAGES; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, 1); }
+    for (int i = 0; i < GEMM_STAGES; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CM); }
     for (int i = 0; i < 2; ++i) { mbar_init(tfull_bar + 8 * i, 1); mbar_init(tempty_bar + 8 * i, 4); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<2 * BN>(tmem_slot);
   tc_fence_before();
   __syncthreads();
+  if (CM > 1) cluster_sync_all();     // peers' barriers are initialised before any multicast / remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *(volatile uint32_t*)(smem_gen + (tmem_slot - smem_base));
 
@@ -63,14 +78,21 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0; bool ok = true;
-      for (int tile = blockIdx.x; tile < num_tiles && ok; tile += gridDim.x) {
-        const int m_blk = tile / num_n_tiles, n_blk = tile % num_n_tiles;
-        if (skip.dead((long long)m_blk * GEMM_BM)) continue;
+      for (int st = cluster_id; st < num_super && ok; st += num_clusters) {
+        if (!any_alive(st)) continue;
+        const bool alive = alive_at(st, rank);
+        const int m_blk = m_of(st, rank), n_blk = st % num_n_tiles;
         for (int kb = 0; kb < num_k_blocks; ++kb) {
+          // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
           if (!mbar_wait(empty_bar + 8 * stage, phase ^ 1, status)) { ok = false; break; }
-          mbar_expect_tx(full_bar + 8 * stage, S::STAGE_BYTES);
-          tma_load_2d(smem_a + stage * S::A_BYTES, &tmap_a, full_bar + 8 * stage, kb * GEMM_BK, m_blk * GEMM_BM);
-          tma_load_2d(smem_b + stage * S::B_BYTES, &tmap_b, full_bar + 8 * stage, kb * GEMM_BK, n_blk * BN);
+          mbar_expect_tx(full_bar + 8 * stage, (alive ? S::A_BYTES : 0) + S::B_BYTES);
+          if (alive) tma_load_2d(smem_a + stage * S::A_BYTES, &tmap_a, full_bar + 8 * stage, kb * GEMM_BK, m_blk * GEMM_BM);
+          if (CM == 1) {
+            tma_load_2d(smem_b + stage * S::B_BYTES, &tmap_b, full_bar + 8 * stage, kb * GEMM_BK, n_blk * BN);
+          } else {        // this CTA's 1/CM of the W box, into the same place of every CTA's stage
+            tma_load_2d_mc(smem_b + stage * S::B_BYTES + rank * (BN / CM) * GEMM_BK, &tmap_b, full_bar + 8 * stage, kb * GEMM_BK,
+                           n_blk * BN + rank * (BN / CM), MC_MASK);
+          }
           if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -80,25 +102,35 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_i8(GEMM_BM, BN);
       int stage = 0; uint32_t phase = 0; int acc = 0; uint32_t acc_phase = 0; bool ok = true;
-      for (int tile = blockIdx.x; tile < num_tiles && ok; tile += gridDim.x) {
-        if (skip.dead((long long)(tile / num_n_tiles) * GEMM_BM)) continue;
-        if (!mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, status)) break;
-        tc_fence_after();
+      for (int st = cluster_id; st < num_super && ok; st += num_clusters) {
+        if (!any_alive(st)) continue;
+        const bool alive = alive_at(st, rank);
+        if (alive) {
+          if (!mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, status)) break;
+          tc_fence_after();
+        }
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           if (!mbar_wait(full_bar + 8 * stage, phase, status)) { ok = false; break; }
           tc_fence_after();
-          const uint64_t adesc = umma_desc_sw128(smem_a + stage * S::A_BYTES);
-          const uint64_t bdesc = umma_desc_sw128(smem_b + stage * S::B_BYTES);
+          if (alive) {
+            const uint64_t adesc = umma_desc_sw128(smem_a + stage * S::A_BYTES);
+            const uint64_t bdesc = umma_desc_sw128(smem_b + stage * S::B_BYTES);
 #pragma unroll
-          for (int k = 0; k < GEMM_BK / 32; ++k)
-            umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-          umma_commit(empty_bar + 8 * stage);   // frees the smem stage when these MMAs retire
+            for (int k = 0; k < GEMM_BK / 32; ++k)
+              umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          }
+          // frees the stage (in every CTA of the cluster) when the MMAs issued so far have retired; a CTA without a live
+          // tile still takes part: its peers multicast into its stage too
+          if (CM == 1) umma_commit(empty_bar + 8 * stage);
+          else umma_commit_mc(empty_bar + 8 * stage, MC_MASK);
           if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
         }
         if (!ok) break;
-        umma_commit(tfull_bar + 8 * acc);       // accumulator complete -> epilogue
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        if (alive) {
+          umma_commit(tfull_bar + 8 * acc);       // accumulator complete -> epilogue
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
       }
     }
   } else if (warp >= 4) {
@@ -106,9 +138,9 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     const int q = warp & 3;                       // TMEM lane quarter this warp may access
     const uint32_t cbuf0 = smem_c + (uint32_t)(q * 2) * S::C_WARP_BYTES;
     int acc = 0; uint32_t acc_phase = 0; int buf = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_blk = tile / num_n_tiles, n_blk = tile % num_n_tiles;
-      if (skip.dead((long long)m_blk * GEMM_BM)) continue;
+    for (int st = cluster_id; st < num_super; st += num_clusters) {
+      if (!alive_at(st, rank)) continue;
+      const int m_blk = m_of(st, rank), n_blk = st % num_n_tiles;
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, status)) break;
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
@@ -162,13 +194,16 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 
   tc_fence_before();
   __syncthreads();
+  if (CM > 1) cluster_sync_all();     // no CTA leaves while peers may still multicast into it / arrive on its barriers
   if (warp == 2) { tc_fence_after(); tmem_dealloc<2 * BN>(tmem_base); }
 }
 
 // explicit instantiations used by api.cu
-template __global__ void gemm_i8_i32_kernel<256>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip, const int);
-template __global__ void gemm_i8_i32_kernel<128>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip, const int);
-template __global__ void gemm_i8_i32_kernel<64>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__, const RowSkip, const int);
+#define RNNT_GEMM_INST(BN, CM)                                                                                              \
+  template __global__ void gemm_i8_i32_kernel<BN, CM>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
+                                                      const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__,  \
+                                                      const RowSkip, const int);
+RNNT_GEMM_INST(256, 1) RNNT_GEMM_INST(256, 2) RNNT_GEMM_INST(256, 4) RNNT_GEMM_INST(128, 1) RNNT_GEMM_INST(64, 1)
 
 // ---------------------------------------------------------------------------------------------
 // Plain CUDA-core int8 GEMM.  NOT a fallback: used by tests (device-side cross-check of the tcgen05 kernel at

@@ -44,7 +44,7 @@ struct GemmSmem {
   static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;       // barriers + alignment slack
 };
 
-template <int BN>
+template <int BN, int CM>
 __global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
                                    int num_k_blocks, int* __restrict__ status, const RowSkip skip, const int gate_blocked);

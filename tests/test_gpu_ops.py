@@ -8,6 +8,9 @@ from tests import helpers as Hh
 
 pytestmark = pytest.mark.gpu
 
+# see tests/test_gpu_pipeline.py: one bf16 ulp of the prediction state moves a logit of the synthetic joint by up to 0.25
+DECODE_MARGIN_TOL = 0.3
+
 
 @pytest.fixture(scope="module")
 def ops():
@@ -458,7 +461,7 @@ def test_greedy_decode_at_benched_shape(ops, exact_order):
         return
     got = [list(res[i, :res_idx[lanes[i]] + 1]) for i in range(len(lanes))]
     truth = [list(so["res"][i, :so["res_idx"][i] + 1]) for i in range(len(lanes))]
-    rep = E.compare_transcripts(got, truth, trace, margin_tol=0.05)
+    rep = E.compare_transcripts(got, truth, trace, margin_tol=DECODE_MARGIN_TOL)
     assert rep["unexplained"] == [], rep["differences"]
     assert rep["identical_utterances"] >= 0.9 * len(lanes), rep["differences"]
     same = [i for i in range(len(lanes)) if got[i] == truth[i]]
@@ -507,9 +510,43 @@ def test_greedy_decode_tensor_cores_small(ops, n, t2):
     got = [list(res[i, :res_idx[i] + 1]) for i in range(n)]
     truth = [list(so["res"][i, :so["res_idx"][i] + 1]) for i in range(n)]
     assert sum(len(t) for t in truth) > n // 2
-    rep = E.compare_transcripts(got, truth, trace, margin_tol=0.05)
+    rep = E.compare_transcripts(got, truth, trace, margin_tol=DECODE_MARGIN_TOL)
     assert rep["unexplained"] == [], rep["differences"]
     assert rep["identical_utterances"] >= 0.9 * n, rep["differences"]
     if rep["identical_utterances"] == n:
         assert int(iters_out.item()) == iters
     assert (res_idx[f_lens == 0] == -1).all()
+
+
+@pytest.mark.parametrize("cm", [1, 2, 4])
+def test_gemm_i8_clusters(ops, cm):
+    """Projection GEMM with CM CTAs per cluster sharing the W operand by TMA multicast: same int32 results as the
+    CUDA-core GEMM for a large problem (several tiles per CTA, edge m tile) and, for a ragged batch whose super tiles
+    straddle timesteps and mix live and dead m tiles, live rows exact and dead rows untouched."""
+    import ctypes
+    from rnnt_inference_b200 import _lib
+    _lib.check(_lib.lib.rnnt_tune_gemm_cluster(cm))
+    try:
+        g = torch.Generator(device="cuda").manual_seed(cm)
+        m, n, k = 20000 + 77, 4096, 1024
+        a = torch.randint(-128, 128, (m, k), dtype=torch.int8, device="cuda", generator=g)
+        w = torch.randint(-128, 128, (n, k), dtype=torch.int8, device="cuda", generator=g)
+        got = ops.gemm_i8_i32(a, w)
+        ref = ops.gemm_i8_i32(a, w, simt=True)
+        _lib.check_device_status()
+        assert torch.equal(got, ref)
+        # ragged: 6 timesteps x 1280 rows (10 batch tiles), tile b alive for t < steps[b]
+        t, rows, k = 6, 1280, 256
+        steps = np.array([6, 6, 5, 5, 4, 3, 3, 2, 1, 0], np.int32)
+        a = torch.randint(-128, 128, (t * rows, k), dtype=torch.int8, device="cuda", generator=g)
+        c = torch.full((t * rows, n), 123456789, dtype=torch.int32, device="cuda")
+        _lib.check(_lib.lib.rnnt_gemm_i8_i32_ragged(_lib.ptr(a), _lib.ptr(w[:, :k].contiguous()), _lib.ptr(c), t * rows, n, k, rows,
+                                                    ctypes.c_void_p(steps.ctypes.data), _lib.stream_ptr()))
+        ref = ops.gemm_i8_i32(a, w[:, :k].contiguous(), simt=True)
+        _lib.check_device_status()
+        c, ref = c.view(t, 10, 128, n), ref.view(t, 10, 128, n)
+        for b, s in enumerate(steps):
+            assert torch.equal(c[:s, b], ref[:s, b]), f"tile {b}"
+            assert bool((c[s:, b] == 123456789).all()), f"dead rows of tile {b} were written"
+    finally:
+        _lib.lib.rnnt_tune_gemm_cluster(2)

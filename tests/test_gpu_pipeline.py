@@ -74,7 +74,12 @@ def test_decoder_forward_vs_oracle(setup, fused):
         assert int(dec.last_iters.item()) == o_iters
 
 
-MARGIN_TOL = 0.05     # a transcript difference must start at a decision whose top-2 logit margin is below this
+# A transcript difference must start at a decision whose top-2 logit margin is below this.  The bound is the sensitivity
+# of a logit to ONE bf16 ulp of the prediction state, which any change of the fp32 accumulation order can flip (AMX's
+# TDPBF16PS differs from the oracle's order just the same): h ~ 1 has ulp 2^-8; the synthetic joint reads the label trace
+# with weight 8 and pushes the label's logit with weight -8 (synthetic.py), so one ulp moves a logit by up to
+# 8 * 8 * 2^-8 = 0.25.  (The encoder-side product alone moves logits by < 1e-3.)
+MARGIN_TOL = DECODE_MARGIN_TOL = 0.3
 
 
 def test_decoder_tensor_core_hoist_vs_oracle(setup):
