@@ -102,9 +102,9 @@ int rnnt_lstm_recurrent_i8_gate_blocked_ragged(const int32_t* G, const int8_t* w
  * or 8 (default 1, or the environment variable RNNT_REC_CLUSTER); the h tile of a batch tile is TMA-multicast inside a
  * cluster.  Measured on B200: no gain over 1 (profiles/r01/rec_cluster_v5.txt). */
 int rnnt_tune_recurrent_cluster(int ctas);
-/* TUNING (process-wide, results do not depend on it): CTAs per cluster of the projection GEMM (1, 2 or 4; default 2, or the
+/* TUNING (process-wide, results do not depend on it): CTAs per cluster of the projection GEMM (1, 2 or 4; default 1, or the
  * environment variable RNNT_GEMM_CLUSTER).  The CTAs of a cluster compute consecutive m tiles of one n tile and share
- * its W operand by TMA multicast, which cuts the L2 -> SM operand traffic that bounds the kernel. */
+ * its W operand by TMA multicast.  Measured on B200 (profiles/r02): no gain — the operand traffic does not bound the kernel. */
 int rnnt_tune_gemm_cluster(int ctas);
 
 /* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.

@@ -303,15 +303,16 @@ static int gemm_cluster_pref() {
   int& v = g_gemm_cluster;
   if (v < 0) {
     const char* s = getenv("RNNT_GEMM_CLUSTER");
-    v = s ? atoi(s) : 2;
-    if (v != 1 && v != 2 && v != 4) v = 2;
+    v = s ? atoi(s) : 1;        // measured on B200: 10.2 / 10.4 / 12.1 ms per bench step for 1 / 2 / 4 — the operand traffic is not the bound
+    if (v != 1 && v != 2 && v != 4) v = 1;
   }
   return v;
 }
 
 template <int BN, int CM>
 static int gemm_launch_cm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int num_m, int num_n, int num_k,
-                          int* status, const RowSkip& skip, bool gate_blocked, cudaStream_t st, bool* unsupported) {
+                          int* status, const RowSkip& skip, bool gate_blocked, cudaStream_t st, bool* unsupported,
+                          int32_t* c_direct, long long M, int ldc) {
   auto kern = gemm_i8_i32_kernel<BN, CM>;
   // the opt-in is per device/context: set on every launch (a cached per-process flag would skip it on a second GPU)
   CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::TOTAL));
@@ -339,7 +340,7 @@ static int gemm_launch_cm(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   const int num_super = ((num_m + CM - 1) / CM) * num_n;
   clusters = std::max(1, std::min(clusters, num_super));
   cfg.gridDim = dim3(clusters * CM);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0, c_direct, M, ldc);
   if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "gemm_i8_i32 launch failed: %s", cudaGetErrorString(e));
   return RNNT_OK;
 }
@@ -350,6 +351,9 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
   const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
   // clusters pay off when there are several m tiles per n tile; small problems and BN < 256 run as single CTAs
   int cm = (BN == 256 && num_m >= 8) ? gemm_cluster_pref() : 1;
+  // epilogue: registers -> global directly (default) or staged in shared memory and written by TMA (RNNT_GEMM_EPILOGUE=tma)
+  static const bool tma_epilogue = [] { const char* e = getenv("RNNT_GEMM_EPILOGUE"); return e && !strcmp(e, "tma"); }();
+  int32_t* c_direct = tma_epilogue ? nullptr : C;
   int* status = device_status();
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
   for (;;) {
@@ -380,11 +384,11 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
     bool unsupported = false;
     int r;
     if constexpr (BN == 256) {
-      if (cm == 4) r = gemm_launch_cm<256, 4>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
-      else if (cm == 2) r = gemm_launch_cm<256, 2>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
-      else r = gemm_launch_cm<256, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+      if (cm == 4) r = gemm_launch_cm<256, 4>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
+      else if (cm == 2) r = gemm_launch_cm<256, 2>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
+      else r = gemm_launch_cm<256, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
     } else {
-      r = gemm_launch_cm<BN, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+      r = gemm_launch_cm<BN, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
     }
     if (r) return r;
     if (!unsupported) return RNNT_OK;

@@ -29,7 +29,8 @@ template <int BN, int CM>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles, int num_k_blocks,
-                   int* __restrict__ status, const RowSkip skip, const int gate_blocked) {
+                   int* __restrict__ status, const RowSkip skip, const int gate_blocked, int32_t* __restrict__ c_direct,
+                   const long long M, const int ldc) {
   using S = GemmSmem<BN>;
   constexpr uint16_t MC_MASK = (uint16_t)((1u << CM) - 1u);
   const int rank = (CM > 1) ? (int)cluster_ctarank() : 0;
@@ -150,6 +151,29 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         RNNT_TMEM_LD_X16(t_row + c * 32, v);
         RNNT_TMEM_LD_X16(t_row + c * 32 + 16, v + 16);
         tmem_ld_wait();
+        if (c_direct) {
+          // straight from registers to global memory: a thread owns 32 consecutive columns of one row = one full 128-byte
+          // line (row-major) or four 32-byte sectors, each part of a 1 KB run written by the warp (gate-blocked).  No
+          // staging, no TMA-store read latency in the loop (the TMA-store epilogue wrote at 11 B/clk/SM).
+          const long long row = (long long)m_blk * GEMM_BM + q * 32 + lane;
+          if (row < M) {
+            const int col0 = n_blk * BN + c * 32;
+            if (!gate_blocked) {
+              int4* dst = reinterpret_cast<int4*>(c_direct + row * ldc + col0);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) dst[j] = make_int4((int)v[4 * j], (int)v[4 * j + 1], (int)v[4 * j + 2], (int)v[4 * j + 3]);
+            } else {
+              const int gate = col0 >> 10, slice = (col0 & 1023) >> 5;
+#pragma unroll
+              for (int o = 0; o < 4; ++o) {
+                int4* dst = reinterpret_cast<int4*>(c_direct + ((((long long)slice * 4 + gate) * 4 + o) * M + row) * 8);
+                dst[0] = make_int4((int)v[8 * o], (int)v[8 * o + 1], (int)v[8 * o + 2], (int)v[8 * o + 3]);
+                dst[1] = make_int4((int)v[8 * o + 4], (int)v[8 * o + 5], (int)v[8 * o + 6], (int)v[8 * o + 7]);
+              }
+            }
+          }
+          continue;
+        }
         // staging buffer `buf` was last read by the TMA store issued two chunks ago
         if (lane == 0) tma_store_wait_read<1>();
         __syncwarp();
@@ -202,7 +226,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 #define RNNT_GEMM_INST(BN, CM)                                                                                              \
   template __global__ void gemm_i8_i32_kernel<BN, CM>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
                                                       const __grid_constant__ CUtensorMap, int, int, int, int* __restrict__,  \
-                                                      const RowSkip, const int);
+                                                      const RowSkip, const int, int32_t* __restrict__, const long long, const int);
 RNNT_GEMM_INST(256, 1) RNNT_GEMM_INST(256, 2) RNNT_GEMM_INST(256, 4) RNNT_GEMM_INST(128, 1) RNNT_GEMM_INST(64, 1)
 
 // ---------------------------------------------------------------------------------------------

@@ -478,50 +478,40 @@ __device__ __forceinline__ void fc1_phase_tc(const DecParams& p, int g, int s, c
   }
 }
 
-// Phase D for one lane, executed by one warp, in two halves so that the block-wide staging of the fc2 weights into
-// shared memory overlaps the first half's global loads.
-//   joint_stage : fc1 epilogue  y = bf16(relu((z + y1[cur_t]) + b1))  -> per-warp bf16 vector in shared memory
-//   joint_finish: fc2 from shared memory (rows 29..31 of W2 are zero by contract, modeling_rnnt.py:241-246), argmax,
-//                 greedy_decode_update state machine; the lane's new state word goes back to global memory.
+// ---------------------------------------------------------------------------------------------- phase D (joint + update)
+// A lane's decisions depend on nothing but its own state, so phase D lets every lane RUN AHEAD: as long as its
+// decisions are blank (or the forced advance after 30 symbols) it only needs the next transcription row y1[t] — z, the
+// prediction half of fc1, is unchanged — and takes decision after decision without any group barrier.  A lane stops
+// when it accepts a symbol (the prediction network must be re-evaluated: next round), when it finishes, or — in the
+// replay phase of quirk (b) — when it has taken as many decisions as the batch-lockstep loop of the reference runs.
+// The per-lane decision count `dc` (lane_state.w) is what the reference's loop index would be.
 struct JointRegs { int sa, ri, ti, flen; };
 
-__device__ __forceinline__ JointRegs joint_stage(const DecParams& p, int n, int4 st, uint16_t* ybuf, const float* s_b1, int lane) {
-  const int cur_t = st.y;
-  const uint16_t* y1r = p.y1 + ((size_t)cur_t * p.N + n) * DEC_J;
-  const float* zr = p.z + (size_t)n * DEC_J;
-  // lane owns k = 16 lane .. 16 lane + 15: four 16-byte loads of z, two of y1, four of b1 (all contiguous across the warp)
-  constexpr int KPL = DEC_J / 32;      // 16
-  float4 zv[KPL / 4]; uint4 yv[KPL / 8]; float4 bv[KPL / 4];
-#pragma unroll
-  for (int i = 0; i < KPL / 4; ++i) zv[i] = __ldcg(reinterpret_cast<const float4*>(zr + lane * KPL) + i);
-#pragma unroll
-  for (int i = 0; i < KPL / 8; ++i) yv[i] = __ldg(reinterpret_cast<const uint4*>(y1r + lane * KPL) + i);
-#pragma unroll
-  for (int i = 0; i < KPL / 4; ++i) bv[i] = __ldg(reinterpret_cast<const float4*>(p.b1 + lane * KPL) + i);
-  JointRegs r = {0, 0, 0, 0};
-  if (lane == 0) { r.sa = p.symbols_added[n]; r.ri = p.res_idx[n]; r.ti = p.time_idx[n]; r.flen = p.f_lens[n]; }
-  const float* zf = reinterpret_cast<const float*>(zv);
-  const float* bf = reinterpret_cast<const float*>(bv);
+// y = bf16(relu((z + y1[t]) + b1)) for k = 16 lane .. 16 lane + 15 of one lane -> 32 bytes of its row in shared memory.
+__device__ __forceinline__ void joint_y(const float (&zf)[16], const uint4 (&yv)[2], const float (&bf)[16], uint16_t* yrow, int lane) {
   const uint32_t* yw = reinterpret_cast<const uint32_t*>(yv);
-  uint32_t out[KPL / 2];
+  uint32_t out[8];
 #pragma unroll
-  for (int i = 0; i < KPL / 2; ++i) {
+  for (int i = 0; i < 8; ++i) {
     const float y0 = __uint_as_float(yw[i] << 16), y1f = __uint_as_float(yw[i] & 0xffff0000u);
     const float v0 = __fadd_rn(__fadd_rn(zf[2 * i], y0), bf[2 * i]);            // (acc + y1) + bias
     const float v1 = __fadd_rn(__fadd_rn(zf[2 * i + 1], y1f), bf[2 * i + 1]);
     out[i] = float_to_bf16_bits(fmaxf(v0, 0.f)) | (float_to_bf16_bits(fmaxf(v1, 0.f)) << 16);   // relu, round to bf16
   }
-  uint4* yo = reinterpret_cast<uint4*>(ybuf + lane * KPL);
+  uint4* yo = reinterpret_cast<uint4*>(yrow + lane * 16);
   yo[0] = make_uint4(out[0], out[1], out[2], out[3]);
   yo[1] = make_uint4(out[4], out[5], out[6], out[7]);
-  __syncwarp();
-  return r;
+}
+__device__ __forceinline__ void load_y1(const DecParams& p, int n, int t, uint4 (&yv)[2], int lane) {
+  const uint4* src = reinterpret_cast<const uint4*>(p.y1 + ((size_t)t * p.N + n) * DEC_J + lane * 16);
+  yv[0] = __ldg(src);
+  yv[1] = __ldg(src + 1);
 }
 
 // argmax over the 32 logits (lane = column, first maximum wins ties like torch.argmax) + the greedy_decode_update state
-// machine of the lane (greedy_decode_update.cpp:13-96); the lane's new state word goes back to global memory.
-__device__ __forceinline__ void joint_update(const DecParams& p, int n, int iter, int4 st, JointRegs r, float logit, int lane) {
-  const int cur_t = st.y;
+// machine of one decision (greedy_decode_update.cpp:13-96).  `st` / `r` are updated in place (all threads of the warp
+// hold the same st afterwards); returns true if the lane may take another decision right away.
+__device__ __forceinline__ bool joint_update(const DecParams& p, int n, int4& st, JointRegs& r, float logit, int lane, int total) {
   float best = logit;
   int bidx = lane;
 #pragma unroll
@@ -530,51 +520,61 @@ __device__ __forceinline__ void joint_update(const DecParams& p, int n, int iter
     const int oi = __shfl_xor_sync(0xffffffffu, bidx, off);
     if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
   }
-  __syncwarp();
-  int next_t = cur_t;
-  if (lane == 0) {
-    const int sym = bidx;
-    int flags = st.x, pre_g = st.z, fix_iter = st.w;
-    int sa = r.sa, ri = r.ri, ti = r.ti;
-    const int flen = r.flen;
-    const bool upd_g = (sym != DEC_BLANK) && (sa != DEC_MAXSYM) && (flen != 0);
-    if (upd_g) {
-      ri += 1;
-      p.res_idx[n] = ri;
-      if (ri >= 0 && ri < p.L) p.res[(size_t)n * p.L + ri] = sym;
-      p.symbols_added[n] = sa + 1;
-      p.pre_g[n] = sym;
-      pre_g = sym;
-      flags ^= LS_CUR;       // candidate becomes the committed state
-      flags |= LS_NEED;      // prediction network must be re-evaluated
-    } else {
-      p.symbols_added[n] = 0;
-      ti += 1;
-      p.time_idx[n] = ti;
-      flags &= ~LS_NEED;
-    }
-    const bool finished = ti >= flen;
-    if (!finished) next_t = ti;                 // fi = f[time_idx]
-    flags = finished ? (flags | LS_FINISHED) : (flags & ~LS_FINISHED);
-    if (finished && !upd_g && (sym == DEC_BLANK || flen == 0)) { flags |= LS_FIXED; fix_iter = iter; }   // fixed point
-    *reinterpret_cast<int4*>(p.lane_state + (size_t)n * 4) = make_int4(flags, next_t, pre_g, fix_iter);
+  const int sym = bidx;                       // identical in every lane of the warp
+  int flags = st.x, cur_t = st.y, pre_g = st.z;
+  const int dc = st.w + 1;
+  const bool upd_g = (sym != DEC_BLANK) && (r.sa != DEC_MAXSYM) && (r.flen != 0);
+  if (upd_g) {
+    r.ri += 1;
+    r.sa += 1;
+    if (lane == 0 && r.ri >= 0 && r.ri < p.L) p.res[(size_t)n * p.L + r.ri] = sym;
+    pre_g = sym;
+    flags ^= LS_CUR;       // candidate becomes the committed state
+    flags |= LS_NEED;      // prediction network must be re-evaluated
+  } else {
+    r.sa = 0;
+    r.ti += 1;
+    flags &= ~LS_NEED;
   }
-  // warm the L2 with the transcription row the next iteration of this lane will read
-  next_t = __shfl_sync(0xffffffffu, next_t, 0);
-  if (next_t != cur_t) {
-    const uint16_t* nr = p.y1 + ((size_t)next_t * p.N + n) * DEC_J + lane * 16;
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(nr));
+  const bool finished = r.ti >= r.flen;
+  if (!finished) cur_t = r.ti;                // fi = f[time_idx]
+  flags = finished ? (flags | LS_FINISHED) : (flags & ~LS_FINISHED);
+  if (finished && !upd_g && (sym == DEC_BLANK || r.flen == 0)) flags |= LS_FIXED;   // fixed point of the reference loop
+  st = make_int4(flags, cur_t, pre_g, dc);
+  if (upd_g || (flags & LS_FIXED)) return false;
+  if (finished) return total >= 0 && dc < total;        // capped on its last frame: parked until the replay phase
+  return true;
+}
+// r.* live in every thread of the warp (loaded by lane 0 and broadcast); lane 0 writes them back
+__device__ __forceinline__ JointRegs load_counters(const DecParams& p, int n, int lane) {
+  JointRegs r = {0, 0, 0, 0};
+  if (lane == 0) { r.sa = p.symbols_added[n]; r.ri = p.res_idx[n]; r.ti = p.time_idx[n]; r.flen = p.f_lens[n]; }
+  r.sa = __shfl_sync(0xffffffffu, r.sa, 0); r.ri = __shfl_sync(0xffffffffu, r.ri, 0);
+  r.ti = __shfl_sync(0xffffffffu, r.ti, 0); r.flen = __shfl_sync(0xffffffffu, r.flen, 0);
+  return r;
+}
+__device__ __forceinline__ void store_lane(const DecParams& p, int n, int4 st, JointRegs r, int lane) {
+  if (lane == 0) {
+    p.symbols_added[n] = r.sa; p.res_idx[n] = r.ri; p.time_idx[n] = r.ti; p.pre_g[n] = st.z;
+    *reinterpret_cast<int4*>(p.lane_state + (size_t)n * 4) = st;
   }
 }
+// may this lane take decisions in this round?  phase 1 (total < 0): every unfinished lane; replay phase: the lanes that
+// finished on the 30-symbol cap, until they have taken `total` decisions
+__device__ __forceinline__ bool runnable(int4 st, int total) {
+  if (st.x & LS_FIXED) return false;
+  if (total < 0) return !(st.x & LS_FINISHED);
+  return (st.x & LS_FINISHED) && st.w < total;
+}
 
-__device__ __forceinline__ void joint_finish(const DecParams& p, int n, int iter, int4 st, JointRegs r, const uint8_t* w2s,
-                                             const uint16_t* ybuf, const float* s_b2, int lane) {
+// exact variant: logits[lane] = y . W2[lane]^T as one sequential chain over k (the oracle's order), W2 rows in shared memory
+__device__ __forceinline__ float fc2_chain(const uint8_t* w2s, const uint16_t* ybuf, int lane) {
   float acc = 0.f;
   if (lane < DecSmem::W2_ROWS) {
     const uint4* wrow = reinterpret_cast<const uint4*>(w2s + lane * DecSmem::W2_STRIDE);
     const uint4* yrow = reinterpret_cast<const uint4*>(ybuf);
 #pragma unroll 4
-    for (int k8 = 0; k8 < DEC_J / 8; ++k8) {      // logits[lane]: sequential chain over k
+    for (int k8 = 0; k8 < DEC_J / 8; ++k8) {
       const uint4 wb = wrow[k8];
       const uint4 yv = yrow[k8];
       acc = __fmaf_rn(__uint_as_float(yv.x << 16), __uint_as_float(wb.x << 16), acc);
@@ -587,7 +587,7 @@ __device__ __forceinline__ void joint_finish(const DecParams& p, int n, int iter
       acc = __fmaf_rn(__uint_as_float(yv.w & 0xffff0000u), __uint_as_float(wb.w & 0xffff0000u), acc);
     }
   }
-  joint_update(p, n, iter, st, r, __fadd_rn(acc, s_b2[lane]), lane);
+  return acc;
 }
 
 template <bool TC>
@@ -604,11 +604,10 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   uint8_t* w2s = smem + W_BYTES;                                             // exact: joint-phase overlay of act | part | pad
   uint16_t* jy = reinterpret_cast<uint16_t*>(w2s + DecSmem::JY_OFFSET);
   const uint32_t wl_s = smem_u32(smem), act_s = smem_u32(smem + W_BYTES), wp_s = smem_u32(smem + WP_OFFSET);
-  bool w2_valid = false;
   __shared__ int4 s_state[DEC_MAXLG];
   __shared__ int alist[DEC_MAXLG];
-  __shared__ float s_bias[2 * DEC_COLS], s_b1[DEC_J], s_b2[DEC_V];
-  __shared__ int s_na, s_unfinished, s_live, s_fail;
+  __shared__ float s_bias[2 * DEC_COLS], s_b2[DEC_V];
+  __shared__ int s_na, s_unfinished, s_live, s_maxdc, s_fail;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = blockIdx.x / DEC_S, s = blockIdx.x % DEC_S;
@@ -650,8 +649,24 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     const int layer = e / DEC_COLS, c = e % DEC_COLS;
     s_bias[e] = p.bias[layer][(c / DEC_U) * DEC_P + s * DEC_U + (c % DEC_U)];
   }
-  for (int e = tid; e < DEC_J; e += DEC_THREADS) s_b1[e] = p.b1[e];
   if (tid < DEC_V) s_b2[tid] = p.b2[tid];
+  // fc1 bias of this thread's 16 columns (phase D: thread = columns 16 lane .. 16 lane + 15 of its warp's lanes)
+  float b1r[16];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p.b1 + lane * 16) + i);
+    b1r[4 * i] = v.x; b1r[4 * i + 1] = v.y; b1r[4 * i + 2] = v.z; b1r[4 * i + 3] = v.w;
+  }
+  // TC variant: fc2 B fragments stay in registers for the whole kernel: warp = (n tile w & 3, K half w >> 2), 16 k-steps
+  uint32_t w2f[TC ? 32 : 1];
+  if constexpr (TC) {
+    const uint16_t* wrow = p.w2 + (size_t)((warp & 3) * 8 + (lane >> 2)) * DEC_J + (warp >> 2) * (DEC_J / 2) + 2 * (lane & 3);
+#pragma unroll
+    for (int ks = 0; ks < 16; ++ks) {
+      w2f[2 * ks] = __ldg(reinterpret_cast<const uint32_t*>(wrow + ks * 16));
+      w2f[2 * ks + 1] = __ldg(reinterpret_cast<const uint32_t*>(wrow + ks * 16 + 8));
+    }
+  }
   // lane state init (each lane by the CTA that owns it in phase D)
   for (int li = s + tid * DEC_S; li < nl; li += DEC_S * DEC_THREADS)
     *reinterpret_cast<int4*>(p.lane_state + (size_t)(lane0 + li) * 4) = make_int4(LS_NEED, 0, p.pre_g[lane0 + li], 0);
@@ -659,42 +674,48 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   int epoch = 0; bool ok = true;
   group_barrier(p, g, epoch, ok, &s_fail);
 
-  int iter = 0;
-  int total_iters = -1;   // unknown during phase 1
+  int round = 0;
+  int total = -1;         // batch-lockstep iteration count of the reference loop; unknown during phase 1
+  bool w2_valid = false;
   for (;;) {
-    // ---- snapshot the group's lane states (one 16-byte load per lane), build the active (need_lstm) list
-    if (tid == 0) { s_na = 0; s_unfinished = 0; s_live = 0; }
+    // ---- snapshot the group's lane states (one 16-byte load per lane), build the list of lanes whose prediction
+    // network has to be re-evaluated, count the lanes still to finish (phase 1) / still to replay (phase 2)
+    if (tid == 0) { s_na = 0; s_unfinished = 0; s_live = 0; s_maxdc = 0; }
     for (int li = tid; li < nl; li += DEC_THREADS)
       s_state[li] = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li) * 4));
     __syncthreads();
     if (tid < 32) {
       for (int base = 0; base < nl; base += 32) {
         const int li = base + tid;
-        int need = 0, unfin = 0, live = 0;
+        int need = 0, unfin = 0, live = 0, dc = 0;
         if (li < nl) {
-          const int f = s_state[li].x;
-          need = (f & LS_NEED) && !(f & LS_FIXED);
-          unfin = !(f & LS_FINISHED);
-          live = !(f & LS_FIXED);
+          const int4 st = s_state[li];
+          const bool replay = total >= 0 && (st.x & LS_FINISHED) && !(st.x & LS_FIXED) && st.w < total;
+          unfin = !(st.x & LS_FINISHED);
+          live = unfin || replay;
+          need = (st.x & LS_NEED) && !(st.x & LS_FIXED) && live;
+          dc = st.w;
         }
         const unsigned mneed = __ballot_sync(0xffffffffu, need);
         const unsigned munf = __ballot_sync(0xffffffffu, unfin);
         const unsigned mlive = __ballot_sync(0xffffffffu, live);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) dc = max(dc, __shfl_xor_sync(0xffffffffu, dc, off));
         if (need) alist[s_na + __popc(mneed & ((1u << tid) - 1))] = li;
         __syncwarp();
-        if (tid == 0) { s_na += __popc(mneed); s_unfinished += __popc(munf); s_live += __popc(mlive); }
+        if (tid == 0) { s_na += __popc(mneed); s_unfinished += __popc(munf); s_live += __popc(mlive); s_maxdc = max(s_maxdc, dc); }
         __syncwarp();
       }
     }
     __syncthreads();
     const int na = s_na;
-    const bool phase1 = total_iters < 0;
     if (!ok) break;
-    if (phase1 && s_unfinished == 0) {
-      // ---- every lane of the group has finished: rendezvous of all groups, learn the batch iteration count
+    if (total < 0 && s_unfinished == 0) {
+      // ---- every lane of the group has finished: rendezvous of all groups; the largest decision count any lane needed to
+      // finish is the number of iterations of the reference's lock-step loop
       if (tid == 0) {
         if (s == 0) {
-          atomicMax(p.global_sync + 1, iter);
+          atomicMax(p.global_sync + 1, s_maxdc);
           __threadfence();
           atomicAdd(p.global_sync + 0, 1);
         }
@@ -711,15 +732,16 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         s_unfinished = *(volatile int*)(p.global_sync + 1);
       }
       __syncthreads();
-      total_iters = s_unfinished;
+      total = s_unfinished;
       __syncthreads();
       if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
+      continue;            // rebuild the lists with `total` known: the lanes parked on the cap become live again
     }
-    if (total_iters >= 0 && (iter >= total_iters || s_live == 0)) break;
-    ++iter;
+    if (total >= 0 && s_live == 0) break;
+    ++round;
     long long* const trace = RNNT_TRACE_PTR(p);
-    const bool tr = trace && blockIdx.x == 0 && tid == 0 && iter <= p.trace_cap;
-    long long* trow = trace + (size_t)(iter - 1) * 16;
+    const bool tr = trace && blockIdx.x == 0 && tid == 0 && round <= p.trace_cap;
+    long long* trow = trace + (size_t)(round - 1) * 16;
     if (tr) { trow[0] = clock64(); trow[7] = na; }
 
     if (na > 0) {
@@ -737,108 +759,122 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       group_barrier(p, g, epoch, ok, &s_fail);
       if (tr) trow[4] = clock64();
     }
+    int decisions = 0;
     if constexpr (TC) {
-      // ---- phase D on the tensor cores: this CTA's lanes li = s + 20 j (j < 16) form ONE m16 tile.
-      //   1. warp w stages y = bf16(relu((z + y1[cur_t]) + b1)) of lanes j = w and w + 8 as rows of a [16][512] bf16 matrix
-      //      (row pitch 1040 B: ldmatrix rows in different bank groups);
-      //   2. warps 0..3: logits[16][8 w .. 8 w + 8) = y . W2^T, 32 k-steps; B fragments straight from global memory (W2 is
-      //      32 KB, read-only, L1-resident), fp32 logits + b2 to shared memory;
-      //   3. the staging warps run argmax + the update state machine on their lanes.
+      // ---- phase D on the tensor cores: this CTA's lanes li = s + 20 j (j < 16) form ONE m16 tile; warp w drives the
+      // lanes j = w and w + 8.  Sub-iteration: every running lane stages y of its current frame as a row of a [16][512]
+      // bf16 matrix (row pitch 1040 B: ldmatrix rows in different bank groups); all 8 warps multiply it with W2
+      // (warp = n tile x K half, B fragments in registers); the two partial sums + b2 go through shared memory to the
+      // lanes' warps, which take the decision; repeat while any lane of the CTA keeps running.
       uint8_t* jy_g = smem + W_BYTES;
-      const uint32_t jy_s = act_s;
-      float* lg = reinterpret_cast<float*>(smem + W_BYTES + DecSmemTC::JY_BYTES);
-      JointRegs jr[2]; int4 st2[2]; bool on[2];
+      float* lg = reinterpret_cast<float*>(smem + W_BYTES + DecSmemTC::JY_BYTES);       // [K half][16][32] fp32
+      JointRegs jr[2]; int4 st2[2]; bool run[2]; float zf[2][16]; uint4 yv[2][2];
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const int j = warp + 8 * h, li = s + j * DEC_S;
-        on[h] = false;
+        run[h] = false;
         jr[h] = JointRegs{0, 0, 0, 0};
         st2[h] = make_int4(LS_FIXED, 0, 0, 0);
         if (li < nl) {
           st2[h] = s_state[li];
-          on[h] = !(st2[h].x & LS_FIXED);
-          if (on[h]) jr[h] = joint_stage(p, lane0 + li, st2[h], reinterpret_cast<uint16_t*>(jy_g + j * DecSmemTC::JY_PITCH), s_b1, lane);
+          run[h] = runnable(st2[h], total);
         }
-      }
-      __syncthreads();
-      if (warp < 4) {
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        const uint16_t* wrow = p.w2 + (size_t)(warp * 8 + (lane >> 2)) * DEC_J + 2 * (lane & 3);
-        const uint32_t arow = jy_s + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * DecSmemTC::JY_PITCH) + (uint32_t)((lane >> 4) << 4);
-#pragma unroll 4
-        for (int ks = 0; ks < DEC_J / 16; ++ks) {
-          const uint32_t b0 = __ldg(reinterpret_cast<const uint32_t*>(wrow + ks * 16));
-          const uint32_t b1 = __ldg(reinterpret_cast<const uint32_t*>(wrow + ks * 16 + 8));
-          uint32_t a[4];
-          ldsm_x4(arow + ks * 32, a);
-          mma_bf16_16816(acc, a, b0, b1);
-        }
-        const int r0 = lane >> 2, c0 = warp * 8 + 2 * (lane & 3);
-        lg[r0 * DEC_V + c0] = __fadd_rn(acc[0], s_b2[c0]);
-        lg[r0 * DEC_V + c0 + 1] = __fadd_rn(acc[1], s_b2[c0 + 1]);
-        lg[(r0 + 8) * DEC_V + c0] = __fadd_rn(acc[2], s_b2[c0]);
-        lg[(r0 + 8) * DEC_V + c0 + 1] = __fadd_rn(acc[3], s_b2[c0 + 1]);
-      }
-      __syncthreads();
+        if (run[h]) {
+          const int n = lane0 + li;
+          jr[h] = load_counters(p, n, lane);
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int j = warp + 8 * h;
-        if (on[h]) joint_update(p, lane0 + s + j * DEC_S, iter, st2[h], jr[h], lg[j * DEC_V + lane], lane);
+          for (int i = 0; i < 4; ++i) {
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(p.z + (size_t)n * DEC_J + lane * 16) + i);
+            zf[h][4 * i] = v.x; zf[h][4 * i + 1] = v.y; zf[h][4 * i + 2] = v.z; zf[h][4 * i + 3] = v.w;
+          }
+          load_y1(p, n, st2[h].y, yv[h], lane);
+        }
+      }
+      const uint32_t arow = act_s + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * DecSmemTC::JY_PITCH) +
+                            (uint32_t)((warp >> 2) * DEC_J) + (uint32_t)((lane >> 4) << 4);
+      while (__syncthreads_or(run[0] || run[1])) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+          if (run[h]) joint_y(zf[h], yv[h], b1r, reinterpret_cast<uint16_t*>(jy_g + (warp + 8 * h) * DecSmemTC::JY_PITCH), lane);
+        __syncthreads();
+        {
+          float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int ks = 0; ks < 16; ++ks) {
+            uint32_t a[4];
+            ldsm_x4(arow + ks * 32, a);
+            mma_bf16_16816(acc, a, w2f[2 * ks], w2f[2 * ks + 1]);
+          }
+          float* out = lg + (warp >> 2) * (16 * DEC_V);
+          const int r0 = lane >> 2, c0 = (warp & 3) * 8 + 2 * (lane & 3);
+          *reinterpret_cast<float2*>(out + r0 * DEC_V + c0) = make_float2(acc[0], acc[1]);
+          *reinterpret_cast<float2*>(out + (r0 + 8) * DEC_V + c0) = make_float2(acc[2], acc[3]);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (run[h]) {
+            const int j = warp + 8 * h, n = lane0 + s + j * DEC_S;
+            const float logit = __fadd_rn(__fadd_rn(lg[j * DEC_V + lane], lg[16 * DEC_V + j * DEC_V + lane]), s_b2[lane]);
+            const int t_before = st2[h].y;
+            run[h] = joint_update(p, n, st2[h], jr[h], logit, lane, total);
+            ++decisions;
+            if (run[h] && st2[h].y != t_before) load_y1(p, n, st2[h].y, yv[h], lane);
+            if (!run[h]) store_lane(p, n, st2[h], jr[h], lane);
+          }
+        }
       }
     } else {
-    // ---- phase D: lanes li = s, s+S, ... ; one warp per lane and pass.  The LSTM / fc1 phases overwrite the overlay, so
-    // the fc2 weights are staged again whenever they ran; the staging loads overlap the first pass's operand loads.
-    if (na > 0) w2_valid = false;
-    {
-      constexpr int NV = DecSmem::W2_ROWS * (DEC_J / 8);       // 16-byte vectors of W2 rows 0..28
-      constexpr int VPT = (NV + DEC_THREADS - 1) / DEC_THREADS;
-      uint4 wv[VPT];
+      // ---- phase D, exact variant: lanes li = s, s + S, ...; one warp per lane, decision after decision.  The LSTM / fc1
+      // phases overwrite the overlay, so the fc2 weights are staged again whenever they ran.
+      if (na > 0) w2_valid = false;
       if (!w2_valid) {
-#pragma unroll
-        for (int r = 0; r < VPT; ++r) {
-          const int e = tid + r * DEC_THREADS;
-          if (e < NV) wv[r] = __ldg(reinterpret_cast<const uint4*>(p.w2) + e);
-        }
-      }
-      int li = s + warp * DEC_S;
-      int4 st = make_int4(LS_FIXED, 0, 0, 0);
-      JointRegs jr = {0, 0, 0, 0};
-      uint16_t* ybuf = jy + warp * DEC_J;
-      if (li < nl) {
-        st = s_state[li];
-        if (!(st.x & LS_FIXED)) jr = joint_stage(p, lane0 + li, st, ybuf, s_b1, lane);
-      }
-      if (!w2_valid) {
-#pragma unroll
-        for (int r = 0; r < VPT; ++r) {
-          const int e = tid + r * DEC_THREADS;
-          if (e < NV) *reinterpret_cast<uint4*>(w2s + (e / (DEC_J / 8)) * DecSmem::W2_STRIDE + (e % (DEC_J / 8)) * 16) = wv[r];
-        }
+        constexpr int NV = DecSmem::W2_ROWS * (DEC_J / 8);       // 16-byte vectors of W2 rows 0..28
+        for (int e = tid; e < NV; e += DEC_THREADS)
+          *reinterpret_cast<uint4*>(w2s + (e / (DEC_J / 8)) * DecSmem::W2_STRIDE + (e % (DEC_J / 8)) * 16) =
+              __ldg(reinterpret_cast<const uint4*>(p.w2) + e);
         __syncthreads();
         w2_valid = true;
       }
-      for (; li < nl; li += DEC_S * DEC_WARPS) {
-        if (li != s + warp * DEC_S) {
-          st = s_state[li];
-          if (!(st.x & LS_FIXED)) jr = joint_stage(p, lane0 + li, st, ybuf, s_b1, lane);
+      uint16_t* ybuf = jy + warp * DEC_J;
+      for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
+        int4 st = s_state[li];
+        if (!runnable(st, total)) continue;
+        const int n = lane0 + li;
+        JointRegs jr = load_counters(p, n, lane);
+        float zf[16]; uint4 yv[2];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(p.z + (size_t)n * DEC_J + lane * 16) + i);
+          zf[4 * i] = v.x; zf[4 * i + 1] = v.y; zf[4 * i + 2] = v.z; zf[4 * i + 3] = v.w;
         }
-        if (!(st.x & LS_FIXED)) joint_finish(p, lane0 + li, iter, st, jr, w2s, ybuf, s_b2, lane);
-        __syncwarp();
+        load_y1(p, n, st.y, yv, lane);
+        bool go = true;
+        while (go) {
+          joint_y(zf, yv, b1r, ybuf, lane);
+          __syncwarp();
+          const float logit = __fadd_rn(fc2_chain(w2s, ybuf, lane), s_b2[lane]);
+          const int t_before = st.y;
+          go = joint_update(p, n, st, jr, logit, lane, total);
+          ++decisions;
+          if (go && st.y != t_before) load_y1(p, n, st.y, yv, lane);
+          __syncwarp();
+        }
+        store_lane(p, n, st, jr, lane);
       }
     }
-    }
-    if (tr) trow[5] = clock64();
+    if (tr) { trow[5] = clock64(); trow[8] = decisions; }
     group_barrier(p, g, epoch, ok, &s_fail);
     if (tr) trow[6] = clock64();
   }
 
-  // ---- epilogue: reference-visible state of lanes that were skipped at their fixed point, committed h/c back
-  // into the caller's arrays (s_state holds the final states: it was refreshed after the last barrier).
-  if (ok && total_iters >= 0) {
+  // ---- epilogue: reference-visible state of lanes that sat at their fixed point while the lock-step loop went on,
+  // committed h/c back into the caller's arrays (s_state holds the final states: it was refreshed after the last barrier).
+  if (ok && total >= 0) {
     for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
       const int n = lane0 + li;
       const int4 st = s_state[li];
-      if (lane == 0 && (st.x & LS_FIXED)) p.time_idx[n] += total_iters - st.w;
+      if (lane == 0 && (st.x & LS_FIXED)) p.time_idx[n] += total - st.w;
       if (st.x & LS_CUR) {
         for (int k = lane; k < DEC_P; k += 32) {
           p.hg[0][0][(size_t)n * DEC_P + k] = __ldcg(p.hg[1][0] + (size_t)n * DEC_P + k);
@@ -848,7 +884,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         }
       }
     }
-    if (blockIdx.x == 0 && tid == 0 && p.iters_out) *p.iters_out = total_iters;
+    if (blockIdx.x == 0 && tid == 0 && p.iters_out) *p.iters_out = total;
   }
 }
 

@@ -47,7 +47,8 @@ struct GemmSmem {
 template <int BN, int CM>
 __global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
-                                   int num_k_blocks, int* __restrict__ status, const RowSkip skip, const int gate_blocked);
+                                   int num_k_blocks, int* __restrict__ status, const RowSkip skip, const int gate_blocked,
+                                   int32_t* __restrict__ c_direct, const long long M, const int ldc);
 __global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, int32_t* __restrict__ C,
                                         long long M, int N, int K);
 
@@ -218,7 +219,7 @@ struct DecSmemTC {
   // joint phase overlays act: y of the CTA's <= 16 lanes (bf16 rows of 512, pitch 1040 B) + fp32 logits [16][32]
   static constexpr int JY_PITCH = DEC_J * 2 + 16;
   static constexpr int JY_BYTES = 16 * JY_PITCH;                           // 16,640
-  static_assert(JY_BYTES + 16 * DEC_V * 4 <= ACT_BYTES, "joint overlay does not fit");
+  static_assert(JY_BYTES + 2 * 16 * DEC_V * 4 <= ACT_BYTES, "joint overlay does not fit");
   static_assert(DEC_MAXLG <= 16 * DEC_S, "a CTA's lanes must fit one m16 tile");
   static_assert(DEC_TC_LANES * DEC_COLS * 4 <= ACT_BYTES, "gate sums do not fit");
   static constexpr int TOTAL = W_BYTES + ACT_BYTES + WP_BYTES;             // 221,440 (+ ~9 KB static)
