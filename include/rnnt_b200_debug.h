@@ -13,6 +13,9 @@ int rnnt_debug_set_recurrent_trace(void* device_buffer);
 /* PROFILING ONLY (results become garbage): bit 0 skip the MMAs, 1 skip the gate math, 2 skip the h loads, 3 skip y/c
  * stores, 4 relaxed publish, 5 no proxy fence, 6 no G, 7 no c prefetch, 8 ignore the h_t flags; 0 = normal operation. */
 int rnnt_debug_set_recurrent_flags(int flags);
+/* PROFILING ONLY (results become garbage): projection GEMM with bit 0 no operand loads, bit 1 no MMAs, bit 2 no result
+ * stores — attributes the kernel time to its three pipelines (profiles/gemm_attrib.py). */
+int rnnt_debug_set_gemm_flags(int flags);
 /* Device buffer of max_iters*16 int64 receiving clock64 stamps of CTA 0 per decode iteration. NULL = off. */
 int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);
 #ifdef __cplusplus

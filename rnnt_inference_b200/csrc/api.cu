@@ -296,6 +296,10 @@ int rnnt_gemm_i8_i32_simt(const int8_t* A, const int8_t* W, int32_t* C, int64_t 
 }
 
 }  // extern "C"
+#ifdef RNNT_DEBUG_HOOKS
+static int g_gemm_debug = 0;
+extern "C" int rnnt_debug_set_gemm_flags(int flags) { g_gemm_debug = flags; return RNNT_OK; }
+#endif
 // cluster size of the projection GEMM: CTAs of a cluster share the W operand of an n tile by TMA multicast (gemm_i8.cu).
 // Process-wide tuning knob (results do not depend on it): rnnt_tune_gemm_cluster / environment variable RNNT_GEMM_CLUSTER.
 static int g_gemm_cluster = -1;
@@ -340,7 +344,11 @@ static int gemm_launch_cm(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   const int num_super = ((num_m + CM - 1) / CM) * num_n;
   clusters = std::max(1, std::min(clusters, num_super));
   cfg.gridDim = dim3(clusters * CM);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0, c_direct, M, ldc);
+  int gb = gate_blocked ? 1 : 0;
+#ifdef RNNT_DEBUG_HOOKS
+  gb |= g_gemm_debug << 8;
+#endif
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gb, c_direct, M, ldc);
   if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "gemm_i8_i32 launch failed: %s", cudaGetErrorString(e));
   return RNNT_OK;
 }

@@ -29,9 +29,15 @@ template <int BN, int CM>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles, int num_k_blocks,
-                   int* __restrict__ status, const RowSkip skip, const int gate_blocked, int32_t* __restrict__ c_direct,
+                   int* __restrict__ status, const RowSkip skip, const int gate_blocked_and_debug, int32_t* __restrict__ c_direct,
                    const long long M, const int ldc) {
   using S = GemmSmem<BN>;
+#ifdef RNNT_DEBUG_HOOKS
+  const int dbg = gate_blocked_and_debug >> 8;        // profiling only: 1 no operand loads, 2 no MMAs, 4 no result stores
+#else
+  constexpr int dbg = 0;
+#endif
+  const int gate_blocked = gate_blocked_and_debug & 0xff;
   constexpr uint16_t MC_MASK = (uint16_t)((1u << CM) - 1u);
   const int rank = (CM > 1) ? (int)cluster_ctarank() : 0;
   const int cluster_id = blockIdx.x / CM, num_clusters = gridDim.x / CM;
@@ -86,6 +92,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
           if (!mbar_wait(empty_bar + 8 * stage, phase ^ 1, status)) { ok = false; break; }
+          if (dbg & 1) { mbar_arrive(full_bar + 8 * stage); if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; } continue; }
           mbar_expect_tx(full_bar + 8 * stage, (alive ? S::A_BYTES : 0) + S::B_BYTES);
           if (alive) tma_load_2d(smem_a + stage * S::A_BYTES, &tmap_a, full_bar + 8 * stage, kb * GEMM_BK, m_blk * GEMM_BM);
           if (CM == 1) {
@@ -114,7 +121,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           if (!mbar_wait(full_bar + 8 * stage, phase, status)) { ok = false; break; }
           tc_fence_after();
-          if (alive) {
+          if (alive && !(dbg & 2)) {
             const uint64_t adesc = umma_desc_sw128(smem_a + stage * S::A_BYTES);
             const uint64_t bdesc = umma_desc_sw128(smem_b + stage * S::B_BYTES);
 #pragma unroll
@@ -151,6 +158,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         RNNT_TMEM_LD_X16(t_row + c * 32, v);
         RNNT_TMEM_LD_X16(t_row + c * 32 + 16, v + 16);
         tmem_ld_wait();
+        if (dbg & 4) continue;
         if (c_direct) {
           // straight from registers to global memory: a thread owns 32 consecutive columns of one row = one full 128-byte
           // line (row-major) or four 32-byte sectors, each part of a 1 KB run written by the warp (gate-blocked).  No

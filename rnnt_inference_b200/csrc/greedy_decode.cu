@@ -302,15 +302,60 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
 //   contiguous = the "col" operand) by ldmatrix.x4 — two k-steps per instruction —, A fragments of both m tiles by
 //   ldmatrix.x4, 2 x 20 k-steps x m-tiles MMAs into fp32 accumulators holding x.W_ih + h.W_hh;
 //   the sums go through shared memory (overlaying act) to the cell update, thread = (unit, lane) as in the exact variant.
+// x | h of one chunk of active lanes as 16-byte pieces in registers (80 per lane, 10 per thread): issued one chunk ahead so
+// that their L2 round trip hides behind the previous chunk's MMAs
+struct LstmStage { uint4 v[DEC_TC_LANES * (2 * DEC_P / 8) / DEC_THREADS]; };
+__device__ __forceinline__ void lstm_stage_load(const DecParams& p, int layer, int lane0, const int* alist, int a0, int nc,
+                                                const int4* s_state, LstmStage& sg) {
+  constexpr int VPL = 2 * DEC_P / 8;      // 80
+  constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;   // 10
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int e = threadIdx.x + r * DEC_THREADS;
+    const int a = e / VPL, q = e % VPL;
+    sg.v[r] = make_uint4(0u, 0u, 0u, 0u);
+    if (a < nc) {
+      const int li = alist[a0 + a];
+      const int4 st = s_state[li];
+      const int n = lane0 + li, cur = st.x & LS_CUR;
+      if (q < VPL / 2) {
+        if (layer == 0) {
+          const int sym = st.z;
+          if (sym >= 0 && sym <= 27) sg.v[r] = __ldg(reinterpret_cast<const uint4*>(p.embed + sym * DEC_P) + q);
+        } else {
+          sg.v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][0] + (size_t)n * DEC_P) + q);
+        }
+      } else {
+        sg.v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur][layer] + (size_t)n * DEC_P) + (q - VPL / 2));
+      }
+    }
+  }
+}
+__device__ __forceinline__ void lstm_stage_store(uint8_t* act_g, int nc, const LstmStage& sg) {
+  constexpr int VPL = 2 * DEC_P / 8;
+  constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int e = threadIdx.x + r * DEC_THREADS;
+    const int a = e / VPL, q = e % VPL;
+    if (a < nc) *reinterpret_cast<uint4*>(act_g + a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4)) = sg.v[r];
+  }
+}
+
 __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int g, int s, const int* alist, int na,
                                               const int4* s_state, uint32_t wl_s, const float* s_bias, uint8_t* act_g,
                                               uint32_t act_s, long long* lt = nullptr) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int lane0 = g * p.LG;
   float* part = reinterpret_cast<float*>(act_g);          // [32 lanes][64 columns] fp32, after the MMAs
+  LstmStage sg;
+  lstm_stage_load(p, layer, lane0, alist, 0, min(DEC_TC_LANES, na), s_state, sg);
   for (int a0 = 0; a0 < na; a0 += DEC_TC_LANES) {
     const int nc = min(DEC_TC_LANES, na - a0);
     const int mt = (nc + 15) >> 4;
+    lstm_stage_store(act_g, nc, sg);
+    __syncthreads();
+    if (a0 + DEC_TC_LANES < na) lstm_stage_load(p, layer, lane0, alist, a0 + DEC_TC_LANES, min(DEC_TC_LANES, na - a0 - DEC_TC_LANES), s_state, sg);
     // ---- cell-update operand prefetch: thread = (unit uu, lanes ua and ua + 16)
     const int uu = tid & 15, ua = tid >> 4;
     float c_old[2] = {0.f, 0.f}; int un[2] = {0, 0}, ucur[2] = {0, 0};
@@ -324,51 +369,16 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
         c_old[h] = p.cg[ucur[h]][layer][(size_t)un[h] * DEC_P + s * DEC_U + uu];
       }
     }
-    // ---- stage x | h of the chunk's lanes: 80 16-byte pieces per lane, all loads issued before any store
-    {
-      constexpr int VPL = 2 * DEC_P / 8;      // 80
-      constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;   // 10
-      uint4 v[R]; int dst[R];
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int e = tid + r * DEC_THREADS;
-        const int a = e / VPL, q = e % VPL;
-        dst[r] = -1;
-        v[r] = make_uint4(0u, 0u, 0u, 0u);
-        if (a < nc) {
-          const int li = alist[a0 + a];
-          const int4 st = s_state[li];
-          const int n = lane0 + li, cur = st.x & LS_CUR;
-          dst[r] = a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4);
-          if (q < VPL / 2) {
-            if (layer == 0) {
-              const int sym = st.z;
-              if (sym >= 0 && sym <= 27) v[r] = __ldg(reinterpret_cast<const uint4*>(p.embed + sym * DEC_P) + q);
-            } else {
-              v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][0] + (size_t)n * DEC_P) + q);
-            }
-          } else {
-            v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur][layer] + (size_t)n * DEC_P) + (q - VPL / 2));
-          }
-        }
-      }
-#pragma unroll
-      for (int r = 0; r < R; ++r)
-        if (dst[r] >= 0) *reinterpret_cast<uint4*>(act_g + dst[r]) = v[r];
-    }
-    __syncthreads();
     if (lt && tid == 0 && a0 == 0) lt[0] = clock64();
-    // ---- tensor-core contraction
-    float acc[2][4];
+    // ---- tensor-core contraction: accumulators per (matrix, k-step parity, m tile) = independent MMA chains
+    float acc[2][2][2][4];
 #pragma unroll
-    for (int mi = 0; mi < 2; ++mi)
+    for (int i = 0; i < 32; ++i) (&acc[0][0][0][0])[i] = 0.f;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) acc[mi][i] = 0.f;
+    for (int kp = 0; kp < DEC_P / 32; ++kp) {
 #pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      const int wrow = (layer * 2 + m) * DEC_COLS + warp * 8 + (lane & 7);      // this thread's ldmatrix row of the B tile
-#pragma unroll 2
-      for (int kp = 0; kp < DEC_P / 32; ++kp) {
+      for (int m = 0; m < 2; ++m) {
+        const int wrow = (layer * 2 + m) * DEC_COLS + warp * 8 + (lane & 7);      // this thread's ldmatrix row of the B tile
         uint32_t b[4];
         ldsm_x4(swz(wl_s, wrow, DEC_P * 2, kp * 4 + (lane >> 3)), b);
 #pragma unroll
@@ -379,7 +389,7 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
             if (mi < mt) {
               uint32_t a[4];
               ldsm_x4(swz(act_s, mi * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * DEC_P * 2, chunk), a);
-              mma_bf16_16816(acc[mi], a, b[2 * k2], b[2 * k2 + 1]);
+              mma_bf16_16816(acc[m][k2][mi], a, b[2 * k2], b[2 * k2 + 1]);
             }
           }
         }
@@ -389,9 +399,13 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
 #pragma unroll
     for (int mi = 0; mi < 2; ++mi) {
       if (mi < mt) {
+        float sum[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)          // (h.W_hh + x.W_ih), like float_out_accum: accumulator of the hh product + the ih product
+          sum[i] = __fadd_rn(__fadd_rn(acc[1][0][mi][i], acc[1][1][mi][i]), __fadd_rn(acc[0][0][mi][i], acc[0][1][mi][i]));
         const int r0 = mi * 16 + (lane >> 2), c0 = warp * 8 + 2 * (lane & 3);
-        *reinterpret_cast<float2*>(part + r0 * DEC_COLS + c0) = make_float2(acc[mi][0], acc[mi][1]);
-        *reinterpret_cast<float2*>(part + (r0 + 8) * DEC_COLS + c0) = make_float2(acc[mi][2], acc[mi][3]);
+        *reinterpret_cast<float2*>(part + r0 * DEC_COLS + c0) = make_float2(sum[0], sum[1]);
+        *reinterpret_cast<float2*>(part + (r0 + 8) * DEC_COLS + c0) = make_float2(sum[2], sum[3]);
       }
     }
     __syncthreads();
@@ -768,7 +782,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       // lanes' warps, which take the decision; repeat while any lane of the CTA keeps running.
       uint8_t* jy_g = smem + W_BYTES;
       float* lg = reinterpret_cast<float*>(smem + W_BYTES + DecSmemTC::JY_BYTES);       // [K half][16][32] fp32
-      JointRegs jr[2]; int4 st2[2]; bool run[2]; float zf[2][16]; uint4 yv[2][2];
+      JointRegs jr[2]; int4 st2[2]; bool run[2]; float zf[2][16]; uint4 yv[2][2], yn[2][2];
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const int j = warp + 8 * h, li = s + j * DEC_S;
@@ -788,6 +802,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
             zf[h][4 * i] = v.x; zf[h][4 * i + 1] = v.y; zf[h][4 * i + 2] = v.z; zf[h][4 * i + 3] = v.w;
           }
           load_y1(p, n, st2[h].y, yv[h], lane);
+          load_y1(p, n, min(st2[h].y + 1, p.T2 - 1), yn[h], lane);      // the frame after: needed if this decision is a blank
         }
       }
       const uint32_t arow = act_s + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * DecSmemTC::JY_PITCH) +
@@ -798,17 +813,17 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
           if (run[h]) joint_y(zf[h], yv[h], b1r, reinterpret_cast<uint16_t*>(jy_g + (warp + 8 * h) * DecSmemTC::JY_PITCH), lane);
         __syncthreads();
         {
-          float acc[4] = {0.f, 0.f, 0.f, 0.f};
+          float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll
           for (int ks = 0; ks < 16; ++ks) {
             uint32_t a[4];
             ldsm_x4(arow + ks * 32, a);
-            mma_bf16_16816(acc, a, w2f[2 * ks], w2f[2 * ks + 1]);
+            mma_bf16_16816(acc[ks & 1], a, w2f[2 * ks], w2f[2 * ks + 1]);
           }
           float* out = lg + (warp >> 2) * (16 * DEC_V);
           const int r0 = lane >> 2, c0 = (warp & 3) * 8 + 2 * (lane & 3);
-          *reinterpret_cast<float2*>(out + r0 * DEC_V + c0) = make_float2(acc[0], acc[1]);
-          *reinterpret_cast<float2*>(out + (r0 + 8) * DEC_V + c0) = make_float2(acc[2], acc[3]);
+          *reinterpret_cast<float2*>(out + r0 * DEC_V + c0) = make_float2(acc[0][0] + acc[1][0], acc[0][1] + acc[1][1]);
+          *reinterpret_cast<float2*>(out + (r0 + 8) * DEC_V + c0) = make_float2(acc[0][2] + acc[1][2], acc[0][3] + acc[1][3]);
         }
         __syncthreads();
 #pragma unroll
@@ -819,7 +834,10 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
             const int t_before = st2[h].y;
             run[h] = joint_update(p, n, st2[h], jr[h], logit, lane, total);
             ++decisions;
-            if (run[h] && st2[h].y != t_before) load_y1(p, n, st2[h].y, yv[h], lane);
+            if (run[h] && st2[h].y != t_before) {        // advanced by one frame: the prefetched row becomes current
+              yv[h][0] = yn[h][0]; yv[h][1] = yn[h][1];
+              load_y1(p, n, min(st2[h].y + 1, p.T2 - 1), yn[h], lane);
+            }
             if (!run[h]) store_lane(p, n, st2[h], jr[h], lane);
           }
         }

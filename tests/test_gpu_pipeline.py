@@ -254,3 +254,39 @@ def test_qsl_arena_and_staging_runs(setup):
         total = sum(lens[i] for i in ids)
         assert torch.equal(b.packed[:total].cpu(), torch.cat([feats[i] for i in ids], 0))
         assert b.meta[1, :len(ids)].cpu().tolist() == [lens[i] for i in ids]
+
+
+def test_server_sut_slot_batching_vs_oracle():
+    """Server scenario (csrc/torch_sut.cpp:354-571, metadata.cpp:111-194): samples arrive one by one, run in 8 slots with
+    chunked encoding (split_len 8, state carried), early response after >= 2 finished slots, long samples parked.
+    Every transcript must equal the oracle's for that utterance decoded with the same chunk length (checkpoint without
+    burst frames, so that a transcript cannot depend on what shares the batch; exact_order: bit-exact)."""
+    import time
+    from rnnt_inference_b200 import loadgen_shim as lg
+    from rnnt_inference_b200.server_sut import ServerSUT
+    sd = S.make_checkpoint(seed=11, burst_threshold=1e9)
+    params = OP.prepare_params(sd)
+    lens = [25, 7, 31, 18, 12, 44, 3, 22, 9, 16, 37, 28, 5, 40, 14, 20, 33, 11, 26, 8]
+    feats = [S.make_features(n, 1300 + i) for i, n in enumerate(lens)]
+    data = {"x": feats, "x_lens": [torch.tensor(n) for n in lens]}
+    sut = ServerSUT(sd, data, batch_size=8, split_len=8, response_size=2, length_threshold=38, exact_order=True)
+    try:
+        settings = lg.TestSettings()
+        settings.scenario = lg.TestScenario.Server
+        settings.mode = lg.TestMode.AccuracyOnly
+        settings.server_target_qps = 400.0
+        settings.server_duration_s = 1.0
+        settings.min_query_count = len(lens)
+        out = lg.StartTest(sut.sut, sut.qsl.qsl, settings)
+    finally:
+        sut.close()
+    assert out["completed"] == len(lens)
+    assert out["latency_p99_ms"] is not None and sut.iterations >= 3
+    got = {e["qsl_idx"]: list(np.frombuffer(bytes.fromhex(e["data"]), np.int32)) for e in out["accuracy_log"]}
+    total = 0
+    for i, f in enumerate(feats):
+        x, xl = OP.pad_batch([f], pad_to=32)
+        o_res, o_len, _ = OP.greedy_decode_batch(params, x, xl, split_len=8)
+        assert got[i] == list(o_res[0, :o_len[0]]), f"utterance {i}"
+        total += int(o_len[0])
+    assert total > 20
