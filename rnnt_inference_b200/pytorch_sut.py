@@ -64,6 +64,7 @@ class PytorchSUT:
         self.pipelined = run_mode == "quant" and args.split_len == -1
         self.qsl = RNNTQSL(dataset_dir)
         self.sut = lg.ConstructSUT(self.issue_queries, self.flush_queries)
+        self.response_hook = None   # callable(samples, tokens, counts) replacing lg.QuerySamplesComplete
         self.h2d_bytes = 0          # running totals, read by bench.py
         self.d2h_bytes = 0
         self.batches_run = 0
@@ -215,6 +216,9 @@ class PytorchSUT:
         its row, n_tokens * 4 bytes); a chunk's responses are handed to LoadGen in one QuerySamplesComplete call."""
         base, stride = tokens.ctypes.data, tokens.strides[0]
         counts = lens[:len(samples)].tolist()
+        if self.response_hook is not None:      # a front that answers LoadGen itself (sharding.DistributedOfflineSUT)
+            self.response_hook(samples, tokens, counts)
+            return
         lg.QuerySamplesComplete([lg.QuerySampleResponse(s.id, base + i * stride, n * 4)
                                  for i, (s, n) in enumerate(zip(samples, counts))])
         if logger.isEnabledFor(10):

@@ -51,3 +51,65 @@ def gather_transcripts(ids, lens, tokens, world=1, group=None, n_max=None, l_max
     all_ids = rows[:, 0:2].contiguous().view(torch.int64).view(-1)
     keep = all_ids >= 0
     return all_ids[keep], rows[keep, 2].contiguous(), rows[keep, 3:].contiguous()
+
+
+class DistributedOfflineSUT:
+    """ONE LoadGen-facing SUT for the whole box (the reference's C++ harness owns all its instances behind
+    one SUT likewise, csrc/torch_sut.cpp:88-122).  Built on every rank over the same dataset:
+      * rank 0 receives the Offline query from LoadGen, broadcasts its (sample id, QSL index) pairs;
+      * every rank sorts the query by length exactly like PytorchSUT.issue_queries and decodes the samples
+        rank, rank + world, ... of that order on its own GPU (`run_shard`);
+      * ONE all_gather brings (sample id, length, tokens) of all ranks together and rank 0 answers LoadGen.
+    Ranks other than 0 sit in `serve()` until rank 0 calls `shutdown()`.
+
+    run_shard(samples) -> (ids int64 {n}, lens int32 {n}, tokens int32 {n, L}) on `device`; `lengths[index]` are the
+    feature lengths of the QSL (the sort key); `complete(responses)` defaults to lg.QuerySamplesComplete."""
+
+    def __init__(self, run_shard, lengths, device, l_max=256, complete=None, make_sample=None, make_response=None):
+        self.run_shard, self.lengths, self.device, self.l_max = run_shard, list(lengths), device, int(l_max)
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.complete, self.make_sample, self.make_response = complete, make_sample, make_response
+        self.queries = 0
+
+    def _round(self, pairs):
+        """pairs: int64 {n, 2} (id, index) on rank 0, None elsewhere.  Returns the gathered (ids, lens, tokens)."""
+        head = torch.tensor([pairs.shape[0] if self.rank == 0 else 0], dtype=torch.int64, device=self.device)
+        dist.broadcast(head, 0)
+        n = int(head.item())
+        if n == 0:
+            return None
+        if self.rank != 0:
+            pairs = torch.empty((n, 2), dtype=torch.int64, device=self.device)
+        dist.broadcast(pairs, 0)
+        host = pairs.cpu().numpy()
+        lens = np.array([self.lengths[i] for i in host[:, 1]])
+        mine = np.argsort(-lens, kind="stable")[self.rank::self.world]
+        samples = [self.make_sample(int(host[k, 0]), int(host[k, 1])) for k in mine]
+        ids, out_lens, tokens = self.run_shard(samples)
+        self.queries += 1
+        return gather_transcripts(ids, out_lens, tokens, self.world, n_max=(n + self.world - 1) // self.world, l_max=self.l_max)
+
+    def issue_queries(self, samples):
+        """LoadGen entry point (rank 0 only)."""
+        assert self.rank == 0
+        pairs = torch.tensor([[s.id, s.index] for s in samples], dtype=torch.int64, device=self.device).view(-1, 2)
+        ids, lens, tokens = self._round(pairs)
+        ids, lens = ids.cpu().numpy(), lens.cpu().numpy()
+        tokens = np.ascontiguousarray(tokens.cpu().numpy())
+        base, stride = tokens.ctypes.data, tokens.strides[0]
+        self.complete([self.make_response(int(ids[k]), base + k * stride, int(min(lens[k], tokens.shape[1])) * 4)
+                       for k in range(len(ids))])
+        self._keep = tokens          # the responses point into it until LoadGen has copied them
+
+    def flush_queries(self):
+        pass
+
+    def serve(self):
+        """Ranks != 0: take part in every query until shutdown."""
+        assert self.rank != 0
+        while self._round(None) is not None:
+            pass
+
+    def shutdown(self):
+        if self.rank == 0:
+            self._round(torch.empty((0, 2), dtype=torch.int64, device=self.device))

@@ -61,3 +61,63 @@ def test_shard_single_rank_matches_issue_queries_order():
     lengths = [5, 9, 9, 2, 7]
     b = sharding.shard_batches(lengths, 2)
     assert [[i for i, _ in x] for x in b] == [[1, 2], [4, 0], [3]]                        # stable descending sort
+
+
+class _Sample:
+    def __init__(self, id, index):
+        self.id, self.index = id, index
+
+
+def _front_worker(rank, world, port, lengths, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ran = []
+
+        def run_shard(samples):            # stands in for the GPU pipeline: tokens derive from the sample index
+            ran.append([s.index for s in samples])
+            ids = torch.tensor([s.id for s in samples], dtype=torch.int64)
+            lens = torch.tensor([s.index % 5 for s in samples], dtype=torch.int32)
+            tok = torch.full((len(samples), 4), -1, dtype=torch.int32)
+            for r, s in enumerate(samples):
+                tok[r, :s.index % 5] = torch.arange(s.index % 5, dtype=torch.int32) + 10 * s.index
+            return ids, lens, tok
+
+        answered = {}
+
+        def complete(responses):
+            import ctypes
+            for rid, ptr, size in responses:
+                answered[rid] = np.frombuffer(ctypes.string_at(ptr, size), np.int32).tolist() if size else []
+
+        front = sharding.DistributedOfflineSUT(run_shard, lengths, torch.device("cpu"), l_max=4, complete=complete,
+                                               make_sample=_Sample, make_response=lambda i, p, n: (i, p, n))
+        if rank == 0:
+            for q in range(2):          # two queries through the same front
+                samples = [_Sample(1000 * q + k, (7 * k + q) % len(lengths)) for k in range(37)]
+                front.issue_queries(samples)
+                for s in samples:
+                    n = s.index % 5
+                    assert answered[s.id] == [10 * s.index + j for j in range(n)], (s.id, s.index, answered[s.id])
+            front.shutdown()
+        else:
+            front.serve()
+        torch.save({"ran": ran}, os.path.join(out_dir, f"f{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_distributed_offline_front_world2(tmp_path):
+    """One LoadGen-facing front on rank 0: the query is broadcast, every rank decodes its share of the length-sorted
+    order, one gather brings the transcripts back and rank 0 answers every sample with its own tokens."""
+    lengths = [int(v) for v in np.random.default_rng(3).integers(40, 500, 50)]
+    world = 2
+    mp.spawn(_front_worker, args=(world, _free_port(), lengths, str(tmp_path)), nprocs=world, join=True)
+    outs = [torch.load(os.path.join(tmp_path, f"f{r}.pt")) for r in range(world)]
+    for q in range(2):
+        shares = [o["ran"][q] for o in outs]
+        assert sorted(shares[0] + shares[1]) == sorted((7 * k + q) % 50 for k in range(37))      # disjoint cover of the query
+        for sh in shares:
+            ls = [lengths[i] for i in sh]
+            assert ls == sorted(ls, reverse=True)                                                   # each share longest first
+        assert abs(len(shares[0]) - len(shares[1])) <= 1
