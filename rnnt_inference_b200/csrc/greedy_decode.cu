@@ -347,7 +347,7 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
                                               uint32_t act_s, long long* lt = nullptr) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int lane0 = g * p.LG;
-  float* part = reinterpret_cast<float*>(act_g);          // [32 lanes][64 columns] fp32, after the MMAs
+  float* part = reinterpret_cast<float*>(act_g);          // [ih | hh][32 lanes][64 columns] fp32 partial sums, after the MMAs
   LstmStage sg;
   lstm_stage_load(p, layer, lane0, alist, 0, min(DEC_TC_LANES, na), s_state, sg);
   for (int a0 = 0; a0 < na; a0 += DEC_TC_LANES) {
@@ -370,17 +370,21 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
       }
     }
     if (lt && tid == 0 && a0 == 0) lt[0] = clock64();
-    // ---- tensor-core contraction: accumulators per (matrix, k-step parity, m tile) = independent MMA chains
+    // ---- tensor-core contraction.  Warp w = (matrix m = w >> 2: x.W_ih or h.W_hh, gate-column tiles 2 (w & 3) and
+    // 2 (w & 3) + 1): an A fragment (ldmatrix.x4 of the lanes' activations) serves two n tiles, a B fragment two m tiles —
+    // 60 ldmatrix for 80 MMAs per warp; the shared-memory reads (not the tensor pipe) bound this loop.  Accumulators per
+    // (n tile, m tile, k-step parity) are independent MMA chains.
     float acc[2][2][2][4];
 #pragma unroll
     for (int i = 0; i < 32; ++i) (&acc[0][0][0][0])[i] = 0.f;
+    {
+      const int m = warp >> 2, np = warp & 3;
 #pragma unroll
-    for (int kp = 0; kp < DEC_P / 32; ++kp) {
+      for (int kp = 0; kp < DEC_P / 32; ++kp) {
+        uint32_t b[2][4];
 #pragma unroll
-      for (int m = 0; m < 2; ++m) {
-        const int wrow = (layer * 2 + m) * DEC_COLS + warp * 8 + (lane & 7);      // this thread's ldmatrix row of the B tile
-        uint32_t b[4];
-        ldsm_x4(swz(wl_s, wrow, DEC_P * 2, kp * 4 + (lane >> 3)), b);
+        for (int nt = 0; nt < 2; ++nt)
+          ldsm_x4(swz(wl_s, (layer * 2 + m) * DEC_COLS + (2 * np + nt) * 8 + (lane & 7), DEC_P * 2, kp * 4 + (lane >> 3)), b[nt]);
 #pragma unroll
         for (int k2 = 0; k2 < 2; ++k2) {
           const int chunk = m * (DEC_P / 8) + (kp * 2 + k2) * 2 + (lane >> 4);
@@ -389,24 +393,27 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
             if (mi < mt) {
               uint32_t a[4];
               ldsm_x4(swz(act_s, mi * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * DEC_P * 2, chunk), a);
-              mma_bf16_16816(acc[m][k2][mi], a, b[2 * k2], b[2 * k2 + 1]);
+#pragma unroll
+              for (int nt = 0; nt < 2; ++nt) mma_bf16_16816(acc[nt][mi][k2], a, b[nt][2 * k2], b[nt][2 * k2 + 1]);
             }
           }
         }
       }
     }
-    __syncthreads();                       // every warp is done reading act: reuse it for the gate sums
+    __syncthreads();                       // every warp is done reading act: reuse it for the partial gate sums
+    {                                       // part[m][lane][col] fp32
+      const int m = warp >> 2, np = warp & 3;
 #pragma unroll
-    for (int mi = 0; mi < 2; ++mi) {
-      if (mi < mt) {
-        float sum[4];
+      for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
-        for (int i = 0; i < 4; ++i)          // (h.W_hh + x.W_ih), like float_out_accum: accumulator of the hh product + the ih product
-          sum[i] = __fadd_rn(__fadd_rn(acc[1][0][mi][i], acc[1][1][mi][i]), __fadd_rn(acc[0][0][mi][i], acc[0][1][mi][i]));
-        const int r0 = mi * 16 + (lane >> 2), c0 = warp * 8 + 2 * (lane & 3);
-        *reinterpret_cast<float2*>(part + r0 * DEC_COLS + c0) = make_float2(sum[0], sum[1]);
-        *reinterpret_cast<float2*>(part + (r0 + 8) * DEC_COLS + c0) = make_float2(sum[2], sum[3]);
-      }
+        for (int mi = 0; mi < 2; ++mi) {
+          if (mi < mt) {
+            const int r0 = mi * 16 + (lane >> 2), c0 = (2 * np + nt) * 8 + 2 * (lane & 3);
+            float* dst = part + (m * DEC_TC_LANES + r0) * DEC_COLS + c0;
+            *reinterpret_cast<float2*>(dst) = make_float2(acc[nt][mi][0][0] + acc[nt][mi][1][0], acc[nt][mi][0][1] + acc[nt][mi][1][1]);
+            *reinterpret_cast<float2*>(dst + 8 * DEC_COLS) = make_float2(acc[nt][mi][0][2] + acc[nt][mi][1][2], acc[nt][mi][0][3] + acc[nt][mi][1][3]);
+          }
+        }
     }
     __syncthreads();
     if (lt && tid == 0 && a0 == 0) lt[1] = clock64();
@@ -418,7 +425,9 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
         const int j = s * DEC_U + uu;
         float gate[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) gate[q] = __fadd_rn(part[a * DEC_COLS + q * DEC_U + uu], s_bias[layer * DEC_COLS + q * DEC_U + uu]);
+        for (int q = 0; q < 4; ++q)        // float_out_accum: (h.W_hh + x.W_ih) + bias
+          gate[q] = __fadd_rn(__fadd_rn(part[(DEC_TC_LANES + a) * DEC_COLS + q * DEC_U + uu], part[a * DEC_COLS + q * DEC_U + uu]),
+                              s_bias[layer * DEC_COLS + q * DEC_U + uu]);
         const float it = sigmoid_ps(gate[0]), ft = sigmoid_ps(gate[1]), gt = tanh_ps(gate[2]), ot = sigmoid_ps(gate[3]);
         const float c_new = __fmaf_rn(it, gt, __fmul_rn(ft, c_old[h]));
         const float ht = __fmul_rn(ot, tanh_ps(c_new));
@@ -783,6 +792,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       uint8_t* jy_g = smem + W_BYTES;
       float* lg = reinterpret_cast<float*>(smem + W_BYTES + DecSmemTC::JY_BYTES);       // [K half][16][32] fp32
       JointRegs jr[2]; int4 st2[2]; bool run[2]; float zf[2][16]; uint4 yv[2][2], yn[2][2];
+      int budget = p.max_run;          // decisions a lane may take per round: keeps the CTAs of a group in step
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const int j = warp + 8 * h, li = s + j * DEC_S;
@@ -808,6 +818,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       const uint32_t arow = act_s + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * DecSmemTC::JY_PITCH) +
                             (uint32_t)((warp >> 2) * DEC_J) + (uint32_t)((lane >> 4) << 4);
       while (__syncthreads_or(run[0] || run[1])) {
+        --budget;
 #pragma unroll
         for (int h = 0; h < 2; ++h)
           if (run[h]) joint_y(zf[h], yv[h], b1r, reinterpret_cast<uint16_t*>(jy_g + (warp + 8 * h) * DecSmemTC::JY_PITCH), lane);
@@ -832,7 +843,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
             const int j = warp + 8 * h, n = lane0 + s + j * DEC_S;
             const float logit = __fadd_rn(__fadd_rn(lg[j * DEC_V + lane], lg[16 * DEC_V + j * DEC_V + lane]), s_b2[lane]);
             const int t_before = st2[h].y;
-            run[h] = joint_update(p, n, st2[h], jr[h], logit, lane, total);
+            run[h] = joint_update(p, n, st2[h], jr[h], logit, lane, total) && budget > 0;
             ++decisions;
             if (run[h] && st2[h].y != t_before) {        // advanced by one frame: the prefetched row becomes current
               yv[h][0] = yn[h][0]; yv[h][1] = yn[h][1];
@@ -868,12 +879,13 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         }
         load_y1(p, n, st.y, yv, lane);
         bool go = true;
+        int budget = p.max_run;
         while (go) {
           joint_y(zf, yv, b1r, ybuf, lane);
           __syncwarp();
           const float logit = __fadd_rn(fc2_chain(w2s, ybuf, lane), s_b2[lane]);
           const int t_before = st.y;
-          go = joint_update(p, n, st, jr, logit, lane, total);
+          go = joint_update(p, n, st, jr, logit, lane, total) && --budget > 0;
           ++decisions;
           if (go && st.y != t_before) load_y1(p, n, st.y, yv, lane);
           __syncwarp();

@@ -206,6 +206,7 @@ struct DecParams {
   int32_t* global_sync; // [0] groups done, [1] max iterations
   int32_t* iters_out; int* status;
   int NG, LG;           // groups, lanes per group
+  int max_run;          // decisions a lane may take per round without a group barrier (run-ahead through blank frames)
   long long* trace;     // optional [iters][8] clock64 stamps of CTA 0 (profiles/trace_decode.py; NULL otherwise)
   int trace_cap;
 };
@@ -221,7 +222,7 @@ struct DecSmemTC {
   static constexpr int JY_BYTES = 16 * JY_PITCH;                           // 16,640
   static_assert(JY_BYTES + 2 * 16 * DEC_V * 4 <= ACT_BYTES, "joint overlay does not fit");
   static_assert(DEC_MAXLG <= 16 * DEC_S, "a CTA's lanes must fit one m16 tile");
-  static_assert(DEC_TC_LANES * DEC_COLS * 4 <= ACT_BYTES, "gate sums do not fit");
+  static_assert(2 * DEC_TC_LANES * DEC_COLS * 4 <= ACT_BYTES, "gate sums do not fit");
   static constexpr int TOTAL = W_BYTES + ACT_BYTES + WP_BYTES;             // 221,440 (+ ~9 KB static)
 };
 
