@@ -304,41 +304,47 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
 //   the sums go through shared memory (overlaying act) to the cell update, thread = (unit, lane) as in the exact variant.
 // x | h of one chunk of active lanes as 16-byte pieces in registers (80 per lane, 10 per thread): issued one chunk ahead so
 // that their L2 round trip hides behind the previous chunk's MMAs
-struct LstmStage { uint4 v[DEC_TC_LANES * (2 * DEC_P / 8) / DEC_THREADS]; };
+// Thread mapping of the staging: warp w moves the activations of the chunk's lanes 4 w .. 4 w + 3; per lane its 32 threads
+// take the pieces l, l + 32 and (l < 16) l + 64 of the 80 — no index arithmetic per piece, the lane's state is one
+// broadcast shared-memory read per warp.
+struct LstmStage { uint4 v[4][3]; };
 __device__ __forceinline__ void lstm_stage_load(const DecParams& p, int layer, int lane0, const int* alist, int a0, int nc,
                                                 const int4* s_state, LstmStage& sg) {
-  constexpr int VPL = 2 * DEC_P / 8;      // 80
-  constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;   // 10
+  constexpr int HALF = DEC_P / 8;      // 40 pieces of x, then 40 of h
+  const int warp = threadIdx.x >> 5, l = threadIdx.x & 31;
 #pragma unroll
-  for (int r = 0; r < R; ++r) {
-    const int e = threadIdx.x + r * DEC_THREADS;
-    const int a = e / VPL, q = e % VPL;
-    sg.v[r] = make_uint4(0u, 0u, 0u, 0u);
+  for (int i = 0; i < 4; ++i) {
+    const int a = warp * 4 + i;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) sg.v[i][j] = make_uint4(0u, 0u, 0u, 0u);
     if (a < nc) {
       const int li = alist[a0 + a];
       const int4 st = s_state[li];
       const int n = lane0 + li, cur = st.x & LS_CUR;
-      if (q < VPL / 2) {
-        if (layer == 0) {
-          const int sym = st.z;
-          if (sym >= 0 && sym <= 27) sg.v[r] = __ldg(reinterpret_cast<const uint4*>(p.embed + sym * DEC_P) + q);
-        } else {
-          sg.v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][0] + (size_t)n * DEC_P) + q);
-        }
-      } else {
-        sg.v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur][layer] + (size_t)n * DEC_P) + (q - VPL / 2));
-      }
+      const uint4* hsrc = reinterpret_cast<const uint4*>(p.hg[cur][layer] + (size_t)n * DEC_P);
+      const uint4* xsrc = nullptr;
+      if (layer == 0) { if (st.z >= 0 && st.z <= 27) xsrc = reinterpret_cast<const uint4*>(p.embed + st.z * DEC_P); }
+      else xsrc = reinterpret_cast<const uint4*>(p.hg[cur ^ 1][0] + (size_t)n * DEC_P);
+      // piece q = l: x[l] (l < 32 < 40); q = l + 32: x[l + 32] for l < 8, else h[l - 8]; q = l + 64 (l < 16): h[l + 24]
+      if (xsrc) sg.v[i][0] = (layer == 0) ? __ldg(xsrc + l) : __ldcg(xsrc + l);
+      if (l < 8) { if (xsrc) sg.v[i][1] = (layer == 0) ? __ldg(xsrc + l + 32) : __ldcg(xsrc + l + 32); }
+      else sg.v[i][1] = __ldcg(hsrc + (l - 8));
+      if (l < 16) sg.v[i][2] = __ldcg(hsrc + (l + 24));
     }
   }
 }
 __device__ __forceinline__ void lstm_stage_store(uint8_t* act_g, int nc, const LstmStage& sg) {
-  constexpr int VPL = 2 * DEC_P / 8;
-  constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;
+  const int warp = threadIdx.x >> 5, l = threadIdx.x & 31;
 #pragma unroll
-  for (int r = 0; r < R; ++r) {
-    const int e = threadIdx.x + r * DEC_THREADS;
-    const int a = e / VPL, q = e % VPL;
-    if (a < nc) *reinterpret_cast<uint4*>(act_g + a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4)) = sg.v[r];
+  for (int i = 0; i < 4; ++i) {
+    const int a = warp * 4 + i;
+    if (a < nc) {
+      uint8_t* row = act_g + a * (2 * DEC_P * 2);
+      const int x7 = a & 7;
+      *reinterpret_cast<uint4*>(row + ((l ^ x7) << 4)) = sg.v[i][0];
+      *reinterpret_cast<uint4*>(row + (((l + 32) ^ x7) << 4)) = sg.v[i][1];
+      if (l < 16) *reinterpret_cast<uint4*>(row + (((l + 64) ^ x7) << 4)) = sg.v[i][2];
+    }
   }
 }
 
