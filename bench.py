@@ -372,6 +372,84 @@ def make_sut(sd, batches, feats, device, batch):
     return sut, len(xs)
 
 
+def e2e_strong(sd, args, device, world, rank, barrier, reduce_scalar):
+    """End-to-end leg of --scaling strong with N > 1: ONE LoadGen-facing SUT on rank 0 (sharding.DistributedOfflineSUT).
+    Rank 0 receives the Offline query of args.query samples from the LoadGen shim, broadcasts it, every rank decodes its
+    share of the length-sorted order from its own pinned features through its PytorchSUT pipeline, one all_gather
+    brings the transcripts back and rank 0 calls QuerySamplesComplete.  Timed on rank 0 around StartTest."""
+    from rnnt_inference_b200 import loadgen_shim as lg
+    from rnnt_inference_b200 import sharding, synthetic as S
+    from rnnt_inference_b200.pytorch_sut import PytorchSUT
+    total = args.query
+    lens = S.utterance_lengths(UTTS_PER_GPU)
+    ulen = [int(v) for v in lens[np.arange(total) % UTTS_PER_GPU]]
+    order = np.argsort(-np.asarray(ulen), kind="stable")[rank::world]
+    mine = sorted(set(int(i) for i in order))
+    feats = {}
+    for i in mine:
+        key = i % UTTS_PER_GPU
+        if key not in feats:
+            feats[key] = S.make_features(ulen[i], key)
+    placeholder = torch.zeros((1, 240))
+    xs = [feats.get(i % UTTS_PER_GPU, placeholder) if (i % UTTS_PER_GPU) in feats else placeholder for i in range(total)]
+    data = {"x": xs, "x_lens": [torch.tensor(n if (i % UTTS_PER_GPU) in feats else 1, dtype=torch.int64) for i, n in enumerate(ulen)]}
+    sut = PytorchSUT(sd, data, args.batch, "quant", None, enable_bf16=True, scenario="Offline", device=device, preload=False)
+    sut.qsl.load_query_samples(mine)
+    collected = []
+    sut.response_hook = lambda samples, tokens, counts: collected.append(([s.id for s in samples], np.array(tokens[:len(samples)], copy=True), list(counts)))
+
+    def run_shard(samples):
+        collected.clear()
+        sut.issue_queries(list(samples))
+        n = sum(len(c[0]) for c in collected)
+        ids = torch.tensor([i for c in collected for i in c[0]], dtype=torch.int64)
+        cnt = torch.tensor([v for c in collected for v in c[2]], dtype=torch.int32)
+        tok = torch.full((n, QUERY_TOKEN_CAP), -1, dtype=torch.int32)
+        r = 0
+        for _ids, t, _c in collected:
+            w = min(t.shape[1], QUERY_TOKEN_CAP)
+            tok[r:r + t.shape[0], :w] = torch.from_numpy(t[:, :w])
+            r += t.shape[0]
+        return ids.to(device), cnt.to(device), tok.to(device)
+
+    front = sharding.DistributedOfflineSUT(run_shard, ulen, device, l_max=QUERY_TOKEN_CAP, complete=lg.QuerySamplesComplete,
+                                           make_sample=lg.QuerySample, make_response=lg.QuerySampleResponse)
+    k_e2e = max(1, min(args.steps, 3))
+    result = None
+    if rank == 0:
+        handle = lg.ConstructSUT(front.issue_queries, front.flush_queries)
+        qsl = lg.ConstructQSL(total, total, lambda ids: None, lambda ids: None)
+        settings = lg.TestSettings()
+        settings.scenario = lg.TestScenario.Offline
+        settings.min_query_count = total
+        lg.StartTest(handle, qsl, settings)                 # warm-up query
+        h0, d0 = sut.h2d_bytes, sut.d2h_bytes
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        done = 0
+        for _ in range(k_e2e):
+            done += lg.StartTest(handle, qsl, settings)["completed"]
+        sec = time.perf_counter() - t0
+        front.shutdown()
+        result = {"value": round(done / sec, 1), "unit": UNIT, "steps": k_e2e, "query_samples": total,
+                  "h2d_bytes_per_step_rank0": int((sut.h2d_bytes - h0) / k_e2e), "d2h_bytes_per_step_rank0": int((sut.d2h_bytes - d0) / k_e2e),
+                  "api": "one LoadGen-facing DistributedOfflineSUT on rank 0 (loadgen_shim.StartTest); ranks shard the sorted query, one all_gather of transcripts"}
+    else:
+        front.serve()
+    barrier()
+    h2d = reduce_scalar(float(sut.h2d_bytes), dist_sum())
+    d2h = reduce_scalar(float(sut.d2h_bytes), dist_sum())
+    if result is not None:
+        result["h2d_bytes_per_step"] = int(h2d / (k_e2e + 1))
+        result["d2h_bytes_per_step"] = int(d2h / (k_e2e + 1))
+    return result
+
+
+def dist_sum():
+    import torch.distributed as dist
+    return dist.ReduceOp.SUM
+
+
 def run_e2e_query(sut, count):
     """One Offline query through the LoadGen shim: host features -> transcripts on the host."""
     from rnnt_inference_b200 import loadgen_shim as lg
@@ -453,7 +531,9 @@ def main():
 
     # ---- e2e leg: PytorchSUT + LoadGen shim, host features
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and strong and world > 1:
+        e2e = e2e_strong(sd, args, device, world, rank, barrier, reduce_scalar)
+    elif not args.no_e2e:
         sut, count = make_sut(sd, batches, feats, device, args.batch)
         for _ in range(2):
             run_e2e_query(sut, count)

@@ -62,7 +62,7 @@ class PytorchSUT:
         self.scenario = args.scenario if run_mode != "calib" else None
         self.batch_sort = self.scenario == "Offline"
         self.pipelined = run_mode == "quant" and args.split_len == -1
-        self.qsl = RNNTQSL(dataset_dir)
+        self.qsl = RNNTQSL(dataset_dir, preload=kwargs.get("preload", True))
         self.sut = lg.ConstructSUT(self.issue_queries, self.flush_queries)
         self.response_hook = None   # callable(samples, tokens, counts) replacing lg.QuerySamplesComplete
         self.h2d_bytes = 0          # running totals, read by bench.py

@@ -19,7 +19,7 @@ except ImportError:   # not installed offline
 
 
 class RNNTQSL:
-    def __init__(self, dataset_dir, perf_count=None, pin_memory=None):
+    def __init__(self, dataset_dir, perf_count=None, pin_memory=None, preload=True):
         data = torch.load(dataset_dir) if isinstance(dataset_dir, (str, os.PathLike)) else dataset_dir
         self.dataset = list(data.values())      # [x list, x_lens list]
         self.count = len(self.dataset[0])
@@ -38,7 +38,8 @@ class RNNTQSL:
         self._keys = [(-n, i) for i, n in enumerate(self.x_lens_host)]
         self.sample_id_to_sample = {}
         self.qsl = lg.ConstructQSL(self.count, perf_count, self.load_query_samples, self.unload_query_samples)
-        self.load_query_samples(range(self.count))
+        if preload:          # the reference loads the whole set at construction (rnnt_qsl.py:11-14); a rank of a multi-GPU front
+            self.load_query_samples(range(self.count))     # loads only the samples it will be dealt (preload=False)
 
     def load_query_samples(self, sample_list):
         new = [i for i in sample_list if i not in self.sample_id_to_sample]
