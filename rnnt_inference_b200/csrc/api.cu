@@ -1,6 +1,7 @@
 // api.cu — the C ABI of librnnt_b200.so (include/rnnt_b200.h): argument validation, TMA tensor-map
 // construction, workspace carving and kernel launches.  No torch types, no allocation of caller-visible
 // buffers, no exceptions; errors are codes + a thread-local message.
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -636,6 +637,42 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
     uint64_t dims[2] = {128, (uint64_t)(2 * n_pad * REC_KC)}, str[1] = {128};
     uint32_t box[2] = {128, REC_BM};
     if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, h_buf, dims, str, box)) return r;
+  }
+  // ---- deal the batch tiles to the grid's tile groups.  Cost model from the traces (profiles/r02): a work item costs a CTA
+  // ~8K cycles of throughput, but one (tile, step) dependency chain is ~16K cycles long, so a group with 1 or 2 tiles in
+  // flight advances one step per ~16K cycles and only the third, fourth ... tile adds time: in item units
+  // cost(group) = 2 * longest + sum of all but the two longest.  Dealing tiles round-robin leaves the group that owns
+  // the longest tile with long companions too; instead the tiles go, longest first, to the group that keeps the maximum
+  // group cost lowest (the longest tile's group then takes the second longest for free and short ones after that).
+  {
+    int order[REC_MAX_TILES];
+    for (int b = 0; b < num_btiles; ++b) order[b] = b;
+    std::stable_sort(order, order + num_btiles, [&](int a, int b) { return p.tile_steps[a] > p.tile_steps[b]; });
+    for (int g = 0; g < REC_GRID_Y; ++g) { p.group_count[g] = 0; for (int i = 0; i < REC_MAX_TILES; ++i) p.group_tile[g][i] = 0; }
+    auto cost = [&](int g, int extra) {          // tiles arrive longest first, so a group's list is sorted
+      long long c = 0;
+      const int n = p.group_count[g] + (extra >= 0 ? 1 : 0);
+      for (int i = 0; i < n; ++i) {
+        const int s = i < p.group_count[g] ? p.tile_steps[p.group_tile[g][i]] : extra;
+        c += (i == 0) ? 2ll * s : (i == 1 ? 0 : s);
+      }
+      return c;
+    };
+    for (int k = 0; k < num_btiles; ++k) {
+      const int b = order[k];
+      int best = 0;
+      if (num_btiles <= grid_y) {
+        best = k;                                  // one tile per group while there are groups to spare
+      } else {
+        long long best_max = -1, best_sum = -1;
+        for (int g = 0; g < grid_y; ++g) {
+          long long mx = 0, sum = 0;
+          for (int j = 0; j < grid_y; ++j) { const long long c = cost(j, j == g ? p.tile_steps[b] : -1); mx = std::max(mx, c); sum += c; }
+          if (best_max < 0 || mx < best_max || (mx == best_max && sum < best_sum)) { best_max = mx; best_sum = sum; best = g; }
+        }
+      }
+      p.group_tile[best][p.group_count[best]++] = b;
+    }
   }
   p.g = G; p.g_blocked = g_blocked; p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;

@@ -99,7 +99,7 @@ struct RecSmem {
   static constexpr int TAB_OFFSET = BIAS_OFFSET + 512;               // whole-function table of the Pade tanh kernel
   static constexpr int TAB_BYTES = (REC_TAB_N * 2 + 15) / 16 * 16;   // 35,328
   static constexpr int BAR_OFFSET = TAB_OFFSET + TAB_BYTES;
-  static constexpr int TOTAL = BAR_OFFSET + 512;          // barriers/counters (the window itself is 1024-byte aligned)
+  static constexpr int TOTAL = BAR_OFFSET + 512;          // barriers/counters + two int[32] tables (the window itself is 1024-byte aligned)
 };
 static_assert(RecSmem::TOTAL <= 232448, "recurrent kernel shared memory");
 
@@ -117,6 +117,8 @@ struct RecParams {
   float rb_scale, in_scale, out_scale;
   int T, N, num_btiles, skip_quant_y;
   int tile_steps[REC_MAX_TILES];   // timesteps to run for each batch tile (<= T); ragged batches sorted by length
+  int group_count[REC_GRID_Y];     // batch tiles of each of the grid's tile groups (blockIdx.y) ...
+  int group_tile[REC_GRID_Y][REC_MAX_TILES];   // ... and their ids
   int debug;               // profiling only (rnnt_debug_set_recurrent_flags): 1 skip MMAs, 2 skip gate math, 4 skip h loads, 8 skip y/c stores,
                            // 16 relaxed publish, 32 no proxy fence, 64 no G, 128 no c prefetch, 256 ignore the h_t flags
   long long* trace;        // optional [T][16] clock64 stamps of CTA (0,0) (profiles/trace_recurrent.py; NULL otherwise)

@@ -58,10 +58,10 @@ __device__ __forceinline__ void sts64(uint32_t addr, uint32_t a, uint32_t b) {
 // Work items of a CTA in issue order: for t, for its tiles, skipping tiles that have finished.  Start with (t=0, i=-1).
 struct ItemCursor {
   int t, i;
-  __device__ __forceinline__ bool next(int T, int my_tiles, int by, int gy, const int* steps) {
+  __device__ __forceinline__ bool next(int T, int my_tiles, const int* tiles, const int* steps) {
     for (;;) {
       if (++i >= my_tiles) { i = 0; if (++t >= T) return false; }
-      if (t < steps[by + i * gy]) return true;
+      if (t < steps[tiles[i]]) return true;
     }
   }
 };
@@ -102,21 +102,27 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   const uint32_t wfull_bar = bar_base + 176;
   const uint32_t tmem_slot = bar_base + 184;
   int* s_steps = reinterpret_cast<int*>(smem_gen + S::BAR_OFFSET + 208);   // [REC_MAX_TILES]
+  int* s_tile = s_steps + REC_MAX_TILES;                                   // [REC_MAX_TILES] tile ids of this group
   float* s_bias = reinterpret_cast<float*>(smem_gen + S::BIAS_OFFSET);     // [gate][unit of the slice]
   static_assert(REC_NS * 8 <= 48, "barrier layout");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x;
   const int num_slices = gridDim.x;
-  const int by = blockIdx.y, gy = gridDim.y;
-  const int my_tiles = (p.num_btiles - by + gy - 1) / gy;
+  // batch tiles of this CTA's tile group, dealt by the host (api.cu: the group that holds the longest tile gets the
+  // shortest ones as company, so that no group is left alone with a long single-tile tail)
+  const int by = blockIdx.y;
+  const int my_tiles = p.group_count[by];
   const uint32_t cta_rank = (CS > 1) ? cluster_ctarank() : 0u;
   long long* const trace = RNNT_TRACE_PTR(p);
   const bool tracer = trace && blockIdx.x == 0 && blockIdx.y == 0;
 
   for (int i = threadIdx.x; i < 1024; i += REC_THREADS) lut[i] = c_rcp_lut[i];
   if (threadIdx.x < 4 * HS) s_bias[threadIdx.x] = p.bias[(threadIdx.x / HS) * REC_H + blockIdx.x * HS + (threadIdx.x % HS)];
-  if (threadIdx.x < REC_MAX_TILES) s_steps[threadIdx.x] = (threadIdx.x < p.num_btiles) ? p.tile_steps[threadIdx.x] : 0;
+  if (threadIdx.x < REC_MAX_TILES) {
+    s_steps[threadIdx.x] = (threadIdx.x < p.num_btiles) ? p.tile_steps[threadIdx.x] : 0;
+    s_tile[threadIdx.x] = p.group_tile[blockIdx.y][threadIdx.x];
+  }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_h0); tma_prefetch_desc(&tmap_h);
   }
@@ -156,9 +162,9 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       bool ok = true;
       uint32_t chunk = 0;
       ItemCursor cur{0, -1};
-      bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
+      bool have = cur.next(p.T, my_tiles, s_tile, s_steps);
       while (have && ok) {
-        const int t = cur.t, bt = by + cur.i * gy;
+        const int t = cur.t, bt = s_tile[cur.i];
         if (t > 0 && !RNNT_DBG(p, 256)) {
           // wait until every slice CTA has published its part of h_t for this batch tile
           const int* flag = p.flags + bt * REC_FLAG_STRIDE;
@@ -196,7 +202,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
             else tma_load_2d_mc(dst, &tmap_h, bar, 0, hrow0 + kc * REC_BM, MC_MASK);
           }
         }
-        have = cur.next(p.T, my_tiles, by, gy, s_steps);
+        have = cur.next(p.T, my_tiles, s_tile, s_steps);
       }
     }
   } else if (warp == 1) {
@@ -206,7 +212,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       bool ok = mbar_wait(wfull_bar, 0, p.status);
       uint32_t chunk = 0; int acc = 0; uint32_t acc_phase = 0;
       ItemCursor cur{0, -1};
-      while (ok && cur.next(p.T, my_tiles, by, gy, s_steps)) {
+      while (ok && cur.next(p.T, my_tiles, s_tile, s_steps)) {
         const bool mtr = tracer && cur.i == 0;
         long long c0 = mtr ? clock64() : 0, w_full = 0;
         if (!mbar_wait(done_bar + 8 * acc, acc_phase ^ 1u, p.status)) break;
@@ -243,8 +249,8 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     int acc = 0; uint32_t acc_phase = 0;
     bool ok = true;
     ItemCursor cur{0, -1};
-    while (ok && cur.next(p.T, my_tiles, by, gy, s_steps)) {
-      const int t = cur.t, bt = by + cur.i * gy;
+    while (ok && cur.next(p.T, my_tiles, s_tile, s_steps)) {
+      const int t = cur.t, bt = s_tile[cur.i];
       const bool last = t + 1 == s_steps[bt];
       const bool tr = tracer && cur.i == 0 && sw == 0 && lane == 0;
       if (!mbar_wait(staged_bar + 8 * acc, acc_phase, p.status)) break;
@@ -365,19 +371,19 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     };
     int acc = 0; uint32_t acc_phase = 0, item = 0;
     ItemCursor cur{0, -1}, nxt{0, -1};
-    bool have = cur.next(p.T, my_tiles, by, gy, s_steps);
-    bool have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);     // nxt runs one item ahead of cur
-    if (have_next) have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);
+    bool have = cur.next(p.T, my_tiles, s_tile, s_steps);
+    bool have_next = nxt.next(p.T, my_tiles, s_tile, s_steps);     // nxt runs one item ahead of cur
+    if (have_next) have_next = nxt.next(p.T, my_tiles, s_tile, s_steps);
     uint4 cn = make_uint4(0u, 0u, 0u, 0u);
-    if (have) load_c(cur.t, by + cur.i * gy, cn);
-    for (; have; have = cur.next(p.T, my_tiles, by, gy, s_steps), ++item) {
-      const int t = cur.t, bt = by + cur.i * gy;
+    if (have) load_c(cur.t, s_tile[cur.i], cn);
+    for (; have; have = cur.next(p.T, my_tiles, s_tile, s_steps), ++item) {
+      const int t = cur.t, bt = s_tile[cur.i];
       const int steps = s_steps[bt];
       const int n = bt * REC_BM + row;
       const bool valid = n < p.N;
       uint32_t cbits[4] = {cn.x, cn.y, cn.z, cn.w};
-      const bool carry = have_next && (by + nxt.i * gy) == bt;       // next item = next step of this very tile
-      if (have_next && !carry) load_c(nxt.t, by + nxt.i * gy, cn);
+      const bool carry = have_next && (s_tile[nxt.i]) == bt;       // next item = next step of this very tile
+      if (have_next && !carry) load_c(nxt.t, s_tile[nxt.i], cn);
       const bool tr = tracer && cur.i == 0 && e == 0 && lane == 0;
       load_g(t, bt);
       const long long f0 = tr ? clock64() : 0;
@@ -453,7 +459,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       __syncwarp();
       if (lane == 0) mbar_arrive(done_bar + 8 * acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
-      if (have_next) have_next = nxt.next(p.T, my_tiles, by, gy, s_steps);
+      if (have_next) have_next = nxt.next(p.T, my_tiles, s_tile, s_steps);
     }
   }
 
