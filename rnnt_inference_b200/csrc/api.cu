@@ -674,6 +674,8 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
       p.group_tile[best][p.group_count[best]++] = b;
     }
   }
+  int used_groups = 0;                              // groups are filled in index order: launch only the non-empty ones
+  while (used_groups < grid_y && p.group_count[used_groups] > 0) ++used_groups;
   p.g = G; p.g_blocked = g_blocked; p.bias = bias; p.h_buf = h_buf; p.hx = hx; p.cx = cx; p.c_ws = c_ws; p.y = y; p.flags = flags; p.status = status;
   p.rb_scale = rb_scale; p.in_scale = in_scale; p.out_scale = out_scale;
   p.T = T; p.N = N; p.num_btiles = num_btiles; p.skip_quant_y = skip_quant_y ? 1 : 0;
@@ -684,7 +686,7 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
   p.trace = nullptr;
   p.debug = 0;
 #endif
-  if (int r = rec_launch(tw, th0, th, p, num_slices, grid_y, rec_cluster_pref(), st)) return r;
+  if (int r = rec_launch(tw, th0, th, p, num_slices, used_groups, rec_cluster_pref(), st)) return r;
   // tiles that ran a single step left their final h in the ping-pong buffer (see lstm_recurrent.cu): move it to hx
   unsigned one_step = 0;
   for (int b = 0; b < num_btiles; ++b) one_step |= (p.tile_steps[b] == 1) ? (1u << b) : 0u;

@@ -59,6 +59,7 @@ __device__ __forceinline__ void sts64(uint32_t addr, uint32_t a, uint32_t b) {
 struct ItemCursor {
   int t, i;
   __device__ __forceinline__ bool next(int T, int my_tiles, const int* tiles, const int* steps) {
+    if (my_tiles <= 0) return false;          // a tile group the host left empty
     for (;;) {
       if (++i >= my_tiles) { i = 0; if (++t >= T) return false; }
       if (t < steps[tiles[i]]) return true;
