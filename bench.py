@@ -198,7 +198,7 @@ def run_step_device(decoder, staged, world=1, n_max=None):
 
 
 # ------------------------------------------------------------------------------------------------ roofline
-NCU_TRAFFIC_RATIO = 1.789 / 2.412
+NCU_TRAFFIC_RATIO = 9.626 / 12.362
 
 
 def recurrent_roofline(events, peaks):
@@ -216,14 +216,15 @@ def recurrent_roofline(events, peaks):
     launches = len(recs)
     achieved = tot_bytes / (tot_ms * 1e-3) / 1e9
     peak = peaks.get("hbm_gbs", 6650.0)
-    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of ONE `ncu --set full` launch (N=1024, T=100, int8 y;
-    # profiles/r01/SUMMARY.md): 1.789e9 bytes against 2.412e9 algorithmic (part of G is still in L2 from the GEMM that
-    # wrote it).  The measured ratio is applied to this run's mean launch so the figure is per launch like `achieved`.
+    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of ONE `ncu --set full` launch (first pre-RNN layer of the bench's
+    # 2048-utterance batch, profiles/r02/ncu_raw_summary.md): 9.031 + 0.596 GB against 12.362 GB algorithmic (524 866 true
+    # frames x 23 552 B; part of G is still in L2 from the GEMM that wrote it).  The measured ratio is applied to this
+    # run's mean launch so the figure is per launch like `achieved`.
     traffic = round(NCU_TRAFFIC_RATIO * tot_bytes / launches)
     roof = {"kernel": "lstm_recurrent_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
             "frac": round(achieved / peak, 4), "traffic": traffic,
             "bytes_basis": "true (frame, utterance) pairs x 23552 B (24576 B for the bf16 last layer); tile padding and rows past an utterance's end are not counted",
-            "traffic_source": "ncu --set full, one launch N=1024 T=100: 1.789 GB dram r+w / 2.412 GB algorithmic = 0.742, scaled to this run's mean launch",
+            "traffic_source": "ncu --set full (profiles/r02/ncu_raw_summary.md), pre-RNN layer 0 of the 2048-utterance batch: 9.626 GB dram r+w / 12.362 GB algorithmic = 0.779, scaled to this run's mean launch",
             "peak_source": peaks.get("_source", "fallback"),
             "launches": launches, "avg_launch_ms": round(tot_ms / launches, 4),
             "algorithmic_bytes_per_launch": round(tot_bytes / launches), "tensor_top_s": round(tot_ops / (tot_ms * 1e-3) / 1e12, 1)}
