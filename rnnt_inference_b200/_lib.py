@@ -49,6 +49,7 @@ _SIGS = {
     "rnnt_lstm_recurrent_i8_gate_blocked_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_tune_recurrent_cluster": (_i, [_i]),
     "rnnt_tune_gemm_cluster": (_i, [_i]),
+    "rnnt_tune_gemm_pair": (_i, [_i]),
     "rnnt_lstm_layer_i8": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_stack_time_i8": (_i, [_vp, _vp, _i, _vp, _i, _i, _i, _vp]),
     "rnnt_linear_bf16_bf16": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),

@@ -314,6 +314,45 @@ static int gemm_cluster_pref() {
   return v;
 }
 
+// CTA-pair variant (gemm_i8_pair.cu, tcgen05 cta_group::2): rnnt_tune_gemm_pair / environment variable RNNT_GEMM_PAIR.
+static int g_gemm_pair = -1;
+static bool gemm_pair_pref() {
+  if (g_gemm_pair < 0) {
+    const char* s = getenv("RNNT_GEMM_PAIR");
+    g_gemm_pair = s ? (atoi(s) != 0) : 0;
+  }
+  return g_gemm_pair != 0;
+}
+
+static int gemm_launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int num_m, int num_n, int num_k,
+                            int* status, const RowSkip& skip, bool gate_blocked, cudaStream_t st, bool* unsupported) {
+  auto kern = gemm_i8_i32_pair_kernel;
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmPairSmem::TOTAL));
+  const int sms = sm_count();
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = GemmPairSmem::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int pairs = std::max(1, (sms > 0 ? sms : 148) / 2);
+  cfg.gridDim = dim3(pairs * 2);
+  int max_active = 0;
+  if (cudaOccupancyMaxActiveClusters(&max_active, kern, &cfg) != cudaSuccess || max_active < 1) {
+    cudaGetLastError();
+    *unsupported = true;
+    return RNNT_OK;
+  }
+  const int num_super = ((num_m + 1) / 2) * num_n;
+  pairs = std::max(1, std::min(std::min(pairs, max_active), num_super));
+  cfg.gridDim = dim3(pairs * 2);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0);
+  if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "gemm_i8_i32 (pair) launch failed: %s", cudaGetErrorString(e));
+  return RNNT_OK;
+}
+
 template <int BN, int CM>
 static int gemm_launch_cm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int num_m, int num_n, int num_k,
                           int* status, const RowSkip& skip, bool gate_blocked, cudaStream_t st, bool* unsupported,
@@ -360,6 +399,7 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
   const int num_m = (int)((M + GEMM_BM - 1) / GEMM_BM), num_n = N / BN, num_k = (K + GEMM_BK - 1) / GEMM_BK;
   // clusters pay off when there are several m tiles per n tile; small problems and BN < 256 run as single CTAs
   int cm = (BN == 256 && num_m >= 8) ? gemm_cluster_pref() : 1;
+  bool pair = BN == 256 && num_m >= 2 && gemm_pair_pref();
   // epilogue: staged in shared memory and written by TMA (default), or registers -> global directly (RNNT_GEMM_EPILOGUE=direct;
   // measured slower on B200: 11.3 vs 10.2 ms per bench step)
   static const bool direct_epilogue = [] { const char* e = getenv("RNNT_GEMM_EPILOGUE"); return e && !strcmp(e, "direct"); }();
@@ -375,7 +415,7 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
     }
     {
       uint64_t dims[2] = {(uint64_t)K, (uint64_t)N}, str[1] = {(uint64_t)K};
-      uint32_t box[2] = {GEMM_BK, (uint32_t)(BN / cm)};
+      uint32_t box[2] = {GEMM_BK, (uint32_t)(pair ? BN / 2 : BN / cm)};
       if (int r = make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, W, dims, str, box)) return r;
     }
     if (!gate_blocked) {
@@ -393,6 +433,13 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
     }
     bool unsupported = false;
     int r;
+    if (pair) {
+      r = gemm_launch_pair(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+      if (r) return r;
+      if (!unsupported) return RNNT_OK;
+      pair = false;                                // no resident CTA pair possible here: the single-CTA kernel
+      continue;
+    }
     if constexpr (BN == 256) {
       if (cm == 4) r = gemm_launch_cm<256, 4>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
       else if (cm == 2) r = gemm_launch_cm<256, 2>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
@@ -561,6 +608,10 @@ extern "C" {
 static int g_rec_debug = 0;
 int rnnt_debug_set_recurrent_flags(int flags) { g_rec_debug = flags; return RNNT_OK; }
 #endif
+int rnnt_tune_gemm_pair(int on) {
+  g_gemm_pair = on ? 1 : 0;
+  return RNNT_OK;
+}
 int rnnt_tune_gemm_cluster(int ctas) {
   if (ctas != 1 && ctas != 2 && ctas != 4) return fail(RNNT_ERR_INVALID, "gemm cluster size must be 1, 2 or 4");
   g_gemm_cluster = ctas;

@@ -49,6 +49,20 @@ __global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, c
                                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
                                    int num_k_blocks, int* __restrict__ status, const RowSkip skip, const int gate_blocked,
                                    int32_t* __restrict__ c_direct, const long long M, const int ldc);
+// gemm_i8_pair.cu: one 256 x 256 tile per CTA pair (cta_group::2); each CTA stages 128 rows of A and 128 rows of W
+struct GemmPairSmem {
+  static constexpr int STAGES = 6;
+  static constexpr int A_BYTES = GEMM_BM * GEMM_BK;           // 16 KB
+  static constexpr int B_BYTES = 128 * GEMM_BK;               // 16 KB: this CTA's half of the 256-row W tile
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int C_WARP_BYTES = 32 * 128;
+  static constexpr int C_BYTES = 4 * 2 * C_WARP_BYTES;        // 32 KB
+  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + C_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;
+};
+__global__ void gemm_i8_i32_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                                        const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,
+                                        int num_k_blocks, int* __restrict__ status, const RowSkip skip, const int gate_blocked);
 __global__ void gemm_i8_i32_simt_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, int32_t* __restrict__ C,
                                         long long M, int N, int K);
 

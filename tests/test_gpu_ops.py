@@ -518,16 +518,20 @@ def test_greedy_decode_tensor_cores_small(ops, n, t2):
     assert (res_idx[f_lens == 0] == -1).all()
 
 
-@pytest.mark.parametrize("cm", [1, 2, 4])
+@pytest.mark.parametrize("cm", [1, 2, 4, "pair"])
 def test_gemm_i8_clusters(ops, cm):
-    """Projection GEMM with CM CTAs per cluster sharing the W operand by TMA multicast: same int32 results as the
-    CUDA-core GEMM for a large problem (several tiles per CTA, edge m tile) and, for a ragged batch whose super tiles
-    straddle timesteps and mix live and dead m tiles, live rows exact and dead rows untouched."""
+    """Projection GEMM with CM CTAs per cluster sharing the W operand by TMA multicast, or on CTA pairs (cta_group::2
+    MMAs, 256 x 256 tiles): same int32 results as the CUDA-core GEMM for a large problem (several tiles per CTA, an odd
+    number of m tiles with an edge tile) and, for a ragged batch whose super tiles straddle timesteps and mix live and
+    dead m tiles, live rows exact and dead rows untouched."""
     import ctypes
     from rnnt_inference_b200 import _lib
-    _lib.check(_lib.lib.rnnt_tune_gemm_cluster(cm))
+    if cm == "pair":
+        _lib.check(_lib.lib.rnnt_tune_gemm_pair(1))
+    else:
+        _lib.check(_lib.lib.rnnt_tune_gemm_cluster(cm))
     try:
-        g = torch.Generator(device="cuda").manual_seed(cm)
+        g = torch.Generator(device="cuda").manual_seed(7 if cm == "pair" else cm)
         m, n, k = 20000 + 77, 4096, 1024
         a = torch.randint(-128, 128, (m, k), dtype=torch.int8, device="cuda", generator=g)
         w = torch.randint(-128, 128, (n, k), dtype=torch.int8, device="cuda", generator=g)
@@ -550,3 +554,4 @@ def test_gemm_i8_clusters(ops, cm):
             assert bool((c[s:, b] == 123456789).all()), f"dead rows of tile {b} were written"
     finally:
         _lib.lib.rnnt_tune_gemm_cluster(1)
+        _lib.lib.rnnt_tune_gemm_pair(0)
