@@ -107,8 +107,8 @@ int rnnt_tune_recurrent_cluster(int ctas);
  * its W operand by TMA multicast.  Measured on B200 (profiles/r02): no gain — the operand traffic does not bound the kernel. */
 int rnnt_tune_gemm_cluster(int ctas);
 /* TUNING (process-wide, results do not depend on it): run the projection GEMM on CTA pairs (tcgen05 cta_group::2, one
- * 256 x 256 tile per pair, each CTA staging half of the W tile) instead of single CTAs.  Default off, or the environment
- * variable RNNT_GEMM_PAIR=1. */
+ * 256 x 256 tile per pair, each CTA staging half of the W tile) instead of single CTAs.  Default on (problems with at
+ * least two m tiles and N % 256 == 0), or the environment variable RNNT_GEMM_PAIR=0 / 1. */
 int rnnt_tune_gemm_pair(int on);
 
 /* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.

@@ -29,11 +29,22 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
                 ts.append(e0.elapsed_time(e1))
             row.append((flags, round(min(ts[1:]), 3)))
         _lib.lib.rnnt_debug_set_gemm_flags(0)
+        _lib.lib.rnnt_tune_gemm_pair(1)           # the CTA-pair kernel (gemm_i8_pair.cu), full pipeline only
+        ts = []
+        for rep in range(4):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.check(_lib.lib.rnnt_gemm_i8_i32_gate_blocked_ragged(_lib.ptr(a), _lib.ptr(w), _lib.ptr(c), m, n, k, 0, None, _lib.stream_ptr()))
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        _lib.lib.rnnt_tune_gemm_pair(0)
+        row.append(("pair", round(min(ts[1:]), 3)))
         _lib.lib.rnnt_check_device_status(None)
         print(f"  K={k}: ms by flags (1 no loads, 2 no MMAs, 4 no stores): {row}; algorithmic: tensor {2.0 * m * n * k / 4.74e15 * 1e3:.3f} ms, "
               f"HBM write {m * n * 4 / 6.5e12 * 1e3:.3f} ms")
 else:
-    for ep in ("direct", "tma"):
+    for ep in ("tma",) if "--tma-only" in sys.argv else ("direct", "tma"):
         print("epilogue", ep, flush=True)
         env = dict(os.environ, RNNT_GEMM_EPILOGUE=ep)
         subprocess.run([sys.executable, os.path.abspath(__file__), "child"], env=env, check=False)

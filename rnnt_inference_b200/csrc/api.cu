@@ -315,22 +315,23 @@ static int gemm_cluster_pref() {
 }
 
 // CTA-pair variant (gemm_i8_pair.cu, tcgen05 cta_group::2): rnnt_tune_gemm_pair / environment variable RNNT_GEMM_PAIR.
+// On by default: 10.0 vs 10.3 ms per bench step on B200 (a third less L2 -> SM operand traffic per tile).
 static int g_gemm_pair = -1;
 static bool gemm_pair_pref() {
   if (g_gemm_pair < 0) {
     const char* s = getenv("RNNT_GEMM_PAIR");
-    g_gemm_pair = s ? (atoi(s) != 0) : 0;
+    g_gemm_pair = s ? (atoi(s) != 0) : 1;
   }
   return g_gemm_pair != 0;
 }
 
 static int gemm_launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int num_m, int num_n, int num_k,
-                            int* status, const RowSkip& skip, bool gate_blocked, cudaStream_t st, bool* unsupported) {
+                            int* status, const RowSkip& skip, int gb_mode, cudaStream_t st, bool* unsupported) {
   auto kern = gemm_i8_i32_pair_kernel;
   CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmPairSmem::TOTAL));
   const int sms = sm_count();
   cudaLaunchConfig_t cfg = {};
-  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.blockDim = dim3(GEMM_I8_THREADS);
   cfg.dynamicSmemBytes = GemmPairSmem::TOTAL;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -348,21 +349,21 @@ static int gemm_launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
   const int num_super = ((num_m + 1) / 2) * num_n;
   pairs = std::max(1, std::min(std::min(pairs, max_active), num_super));
   cfg.gridDim = dim3(pairs * 2);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked ? 1 : 0);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, num_m, num_n, num_k, status, skip, gb_mode);
   if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "gemm_i8_i32 (pair) launch failed: %s", cudaGetErrorString(e));
   return RNNT_OK;
 }
 
 template <int BN, int CM>
 static int gemm_launch_cm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int num_m, int num_n, int num_k,
-                          int* status, const RowSkip& skip, bool gate_blocked, cudaStream_t st, bool* unsupported,
+                          int* status, const RowSkip& skip, int gb_mode, cudaStream_t st, bool* unsupported,
                           int32_t* c_direct, long long M, int ldc) {
   auto kern = gemm_i8_i32_kernel<BN, CM>;
   // the opt-in is per device/context: set on every launch (a cached per-process flag would skip it on a second GPU)
   CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::TOTAL));
   const int sms = sm_count();
   cudaLaunchConfig_t cfg = {};
-  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.blockDim = dim3(GEMM_I8_THREADS);
   cfg.dynamicSmemBytes = GemmSmem<BN>::TOTAL;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -384,7 +385,7 @@ static int gemm_launch_cm(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   const int num_super = ((num_m + CM - 1) / CM) * num_n;
   clusters = std::max(1, std::min(clusters, num_super));
   cfg.gridDim = dim3(clusters * CM);
-  int gb = gate_blocked ? 1 : 0;
+  int gb = gb_mode;
 #ifdef RNNT_DEBUG_HOOKS
   gb |= g_gemm_debug << 8;
 #endif
@@ -408,6 +409,7 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
   for (;;) {
     CUtensorMap ta, tb, tc;
+    int gb_mode = 0;              // 0 row-major result, 1 gate-blocked as 32-byte rows, 2 gate-blocked as 1 KB runs
     {
       uint64_t dims[2] = {(uint64_t)K, (uint64_t)M}, str[1] = {(uint64_t)K};
       uint32_t box[2] = {GEMM_BK, GEMM_BM};
@@ -422,30 +424,38 @@ static int gemm_launch(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, 
       uint64_t dims[2] = {(uint64_t)N, (uint64_t)M}, str[1] = {(uint64_t)N * 4};
       uint32_t box[2] = {32, 32};
       if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 2, C, dims, str, box)) return r;
-    } else {
+    } else if (M % 32 == 0) {
       // gate-blocked projection for the recurrent kernel: C[slice 32][gate 4][unit octet 4][row M][8] int32, column
-      // gate*1024 + slice*32 + octet*8 + u of the row-major result.  A 32-column chunk of the epilogue is one (gate, slice):
-      // box = 8 units x 32 rows x 4 octets.
+      // gate*1024 + slice*32 + octet*8 + u of the row-major result.  A 32-column chunk of the epilogue is one (gate, slice),
+      // and its 32 rows x 8 units of one octet are one contiguous KB: box = 256 int32 x 1 run x 4 octets.
+      uint64_t dims[5] = {256, (uint64_t)M / 32, 4, 4, 32};
+      uint64_t str[4] = {1024, (uint64_t)M * 32, (uint64_t)M * 128, (uint64_t)M * 512};
+      uint32_t box[5] = {256, 1, 4, 1, 1};
+      if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 5, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return r;
+      gb_mode = 2;
+    } else {
+      // the same layout for any M, as rows of 32 bytes: box = 8 units x 32 rows x 4 octets
       uint64_t dims[5] = {8, (uint64_t)M, 4, 4, 32};
       uint64_t str[4] = {32, (uint64_t)M * 32, (uint64_t)M * 128, (uint64_t)M * 512};
       uint32_t box[5] = {8, 32, 4, 1, 1};
       if (int r = make_tmap(&tc, CU_TENSOR_MAP_DATA_TYPE_INT32, 5, C, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return r;
+      gb_mode = 1;
     }
     bool unsupported = false;
     int r;
     if (pair) {
-      r = gemm_launch_pair(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported);
+      r = gemm_launch_pair(ta, tb, tc, num_m, num_n, num_k, status, skip, gb_mode, st, &unsupported);
       if (r) return r;
       if (!unsupported) return RNNT_OK;
       pair = false;                                // no resident CTA pair possible here: the single-CTA kernel
       continue;
     }
     if constexpr (BN == 256) {
-      if (cm == 4) r = gemm_launch_cm<256, 4>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
-      else if (cm == 2) r = gemm_launch_cm<256, 2>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
-      else r = gemm_launch_cm<256, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
+      if (cm == 4) r = gemm_launch_cm<256, 4>(ta, tb, tc, num_m, num_n, num_k, status, skip, gb_mode, st, &unsupported, c_direct, M, N);
+      else if (cm == 2) r = gemm_launch_cm<256, 2>(ta, tb, tc, num_m, num_n, num_k, status, skip, gb_mode, st, &unsupported, c_direct, M, N);
+      else r = gemm_launch_cm<256, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gb_mode, st, &unsupported, c_direct, M, N);
     } else {
-      r = gemm_launch_cm<BN, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gate_blocked, st, &unsupported, c_direct, M, N);
+      r = gemm_launch_cm<BN, 1>(ta, tb, tc, num_m, num_n, num_k, status, skip, gb_mode, st, &unsupported, c_direct, M, N);
     }
     if (r) return r;
     if (!unsupported) return RNNT_OK;

@@ -10,8 +10,9 @@
 //   warp 1   : MMA issuer     — one elected lane issues tcgen05.mma.kind::i8 (M=128, N=BN, K=32) x4 per stage,
 //                               accumulating in TMEM; 2 accumulator stages (2*BN <= 512 columns)
 //   warp 2   : TMEM allocator
-//   warps 4-7: epilogue       — tcgen05.ld 32 lanes x 32 columns -> swizzled smem staging -> TMA store of a
-//                               32-row x 128-byte box per warp (fully coalesced int32 rows in HBM)
+//   warps 4-11: epilogue      — tcgen05.ld 32 lanes x 32 columns -> swizzled smem staging -> TMA store of a
+//                               32-row x 128-byte box per warp (fully coalesced int32 rows in HBM); two warps per TMEM
+//                               lane quarter on alternate chunks (gemm_i8_epilogue.cuh)
 // Clusters (template parameter CM = 1, 2, 4): the kernel is bound by the L2 -> SM operand traffic (ncu round 1: L2 71 %,
 // tensor pipe 45 %, DRAM 45 %): a 128 x 256 tile reads (128 + 256) x K bytes.  CM CTAs of a thread-block cluster work on CM
 // consecutive m tiles of the SAME n tile and share its W operand: each CTA fetches 1/CM of the W box and TMA-multicasts
@@ -20,13 +21,13 @@
 // The int32 result is stored unscaled on purpose: the reference adds the recurrent int32 accumulator BEFORE
 // converting to float (tile_product_tpp.hpp:336-342), and |acc| may exceed 2^24, so pre-scaling to float would
 // break bit-exactness.  Bound: HBM write of C (16 B * 4H... = 4*N bytes per row) vs tensor pipe at large K.
-#include "kernels.cuh"
+#include "gemm_i8_epilogue.cuh"
 
 namespace rnnt {
 
 
 template <int BN, int CM>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_I8_THREADS, 1)
 gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles, int num_k_blocks,
                    int* __restrict__ status, const RowSkip skip, const int gate_blocked_and_debug, int32_t* __restrict__ c_direct,
@@ -51,12 +52,12 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_a = smem_base;
-  const uint32_t smem_b = smem_base + GEMM_STAGES * S::A_BYTES;
-  const uint32_t smem_c = smem_base + GEMM_STAGES * S::STAGE_BYTES;
+  const uint32_t smem_b = smem_base + S::STAGES * S::A_BYTES;
+  const uint32_t smem_c = smem_base + S::STAGES * S::STAGE_BYTES;
   const uint32_t bar_base = smem_base + S::BAR_OFFSET;
   const uint32_t full_bar = bar_base;                 // [STAGES]
-  const uint32_t empty_bar = bar_base + 8 * GEMM_STAGES;
-  const uint32_t tfull_bar = bar_base + 16 * GEMM_STAGES;       // [2]
+  const uint32_t empty_bar = bar_base + 8 * S::STAGES;
+  const uint32_t tfull_bar = bar_base + 16 * S::STAGES;       // [2]
   const uint32_t tempty_bar = tfull_bar + 16;                   // [2]
   const uint32_t tmem_slot = tempty_bar + 16;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -70,8 +71,8 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     tma_prefetch_desc(&tmap_c);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < GEMM_STAGES; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CM); }
-    for (int i = 0; i < 2; ++i) { mbar_init(tfull_bar + 8 * i, 1); mbar_init(tempty_bar + 8 * i, 4); }
+    for (int i = 0; i < S::STAGES; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CM); }
+    for (int i = 0; i < 2; ++i) { mbar_init(tfull_bar + 8 * i, 1); mbar_init(tempty_bar + 8 * i, GEMM_I8_EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<2 * BN>(tmem_slot);
@@ -92,7 +93,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
           if (!mbar_wait(empty_bar + 8 * stage, phase ^ 1, status)) { ok = false; break; }
-          if (dbg & 1) { mbar_arrive(full_bar + 8 * stage); if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; } continue; }
+          if (dbg & 1) { mbar_arrive(full_bar + 8 * stage); if (++stage == S::STAGES) { stage = 0; phase ^= 1; } continue; }
           mbar_expect_tx(full_bar + 8 * stage, (alive ? S::A_BYTES : 0) + S::B_BYTES);
           if (alive) tma_load_2d(smem_a + stage * S::A_BYTES, &tmap_a, full_bar + 8 * stage, kb * GEMM_BK, m_blk * GEMM_BM);
           if (CM == 1) {
@@ -101,7 +102,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             tma_load_2d_mc(smem_b + stage * S::B_BYTES + rank * (BN / CM) * GEMM_BK, &tmap_b, full_bar + 8 * stage, kb * GEMM_BK,
                            n_blk * BN + rank * (BN / CM), MC_MASK);
           }
-          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -132,7 +133,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           // tile still takes part: its peers multicast into its stage too
           if (CM == 1) umma_commit(empty_bar + 8 * stage);
           else umma_commit_mc(empty_bar + 8 * stage, MC_MASK);
-          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
         if (!ok) break;
         if (alive) {
@@ -144,7 +145,8 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   } else if (warp >= 4) {
     // ------------------------------------------------------------ epilogue (TMEM -> smem -> TMA store)
     const int q = warp & 3;                       // TMEM lane quarter this warp may access
-    const uint32_t cbuf0 = smem_c + (uint32_t)(q * 2) * S::C_WARP_BYTES;
+    const int half = (warp - 4) >> 2;             // the two warps of a quarter take alternate 32-column chunks
+    const uint32_t cbuf0 = smem_c + (uint32_t)((warp - 4) * 2) * S::C_WARP_BYTES;
     int acc = 0; uint32_t acc_phase = 0; int buf = 0;
     for (int st = cluster_id; st < num_super; st += num_clusters) {
       if (!alive_at(st, rank)) continue;
@@ -152,17 +154,20 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, status)) break;
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      if (!c_direct) {
+        gemm_i8_store_chunks(t_row, cbuf0, buf, half, GEMM_I8_EPI_WARPS / 4, BN / 32, &tmap_c, gate_blocked,
+                             m_blk * GEMM_BM + q * 32, n_blk * BN, lane, (dbg & 4) != 0);
+      } else {
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t v[32];
-        RNNT_TMEM_LD_X16(t_row + c * 32, v);
-        RNNT_TMEM_LD_X16(t_row + c * 32 + 16, v + 16);
-        tmem_ld_wait();
-        if (dbg & 4) continue;
-        if (c_direct) {
+        for (int c = half; c < BN / 32; c += GEMM_I8_EPI_WARPS / 4) {
+          uint32_t v[32];
+          RNNT_TMEM_LD_X16(t_row + c * 32, v);
+          RNNT_TMEM_LD_X16(t_row + c * 32 + 16, v + 16);
+          tmem_ld_wait();
+          if (dbg & 4) continue;
           // straight from registers to global memory: a thread owns 32 consecutive columns of one row = one full 128-byte
-          // line (row-major) or four 32-byte sectors, each part of a 1 KB run written by the warp (gate-blocked).  No
-          // staging, no TMA-store read latency in the loop (the TMA-store epilogue wrote at 11 B/clk/SM).
+          // line (row-major) or four 32-byte sectors, each part of a 1 KB run written by the warp (gate-blocked).
+          // Measured slower than the staged TMA stores.
           const long long row = (long long)m_blk * GEMM_BM + q * 32 + lane;
           if (row < M) {
             const int col0 = n_blk * BN + c * 32;
@@ -180,40 +185,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
               }
             }
           }
-          continue;
         }
-        // staging buffer `buf` was last read by the TMA store issued two chunks ago
-        if (lane == 0) tma_store_wait_read<1>();
-        __syncwarp();
-        if (!gate_blocked) {
-          const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 128u;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t a = dst + (uint32_t)((j ^ (lane & 7)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
-                         "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
-          }
-        } else {
-          // gate-blocked result (see api.cu): staging = [unit octet 4][row 32][8 units] with the 32-byte TMA swizzle
-          // (16-byte half ^= bit 2 of the row), which spreads the eight lanes of a store phase over all 32 banks
-          const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 32u;
-          const uint32_t hsw = (uint32_t)((lane >> 2) & 1);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t a = dst + (uint32_t)((j >> 1) * 1024) + ((((uint32_t)j & 1u) ^ hsw) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
-                         "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
-          }
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          const int col0 = n_blk * BN + c * 32, row0 = m_blk * GEMM_BM + q * 32;
-          if (!gate_blocked) tma_store_2d(&tmap_c, cbuf0 + (uint32_t)buf * S::C_WARP_BYTES, col0, row0);
-          else tma_store_5d(&tmap_c, cbuf0 + (uint32_t)buf * S::C_WARP_BYTES, 0, row0, 0, col0 >> 10, (col0 & 1023) >> 5);
-          tma_store_commit();
-        }
-        buf ^= 1;
       }
       // all TMEM reads of this accumulator are complete (wait::ld above): hand it back to the MMA warp
       tc_fence_before();

@@ -5,19 +5,19 @@
 // tile every CTA stages 128 + 256 rows of operands and the UMMAs read them back.  Here two CTAs of a cluster (one TPC)
 // compute ONE 256 x 256 tile with M256 x N256 x K32 MMAs issued by the leader CTA: each CTA stages its own 128 rows of A
 // and only HALF of the W tile (128 rows), the tensor cores of both SMs read both halves — 128 + 128 rows per CTA and
-// 128 x 256 outputs, i.e. a third less shared-memory traffic per output, and room for a 6-stage operand ring.
+// 128 x 256 outputs, i.e. a third less shared-memory traffic per output, and room for a 5-stage operand ring beside 64 KB of result staging.
 //   warp 0 (both CTAs): TMA producer — its A box and its half of the W box into its own shared memory
 //                       (cp.async.bulk.tensor .cta_group::2), completion bytes on the LEADER's full barrier
 //   warp 1 (leader)   : one thread issues tcgen05.mma.cta_group::2.kind::i8; tcgen05.commit multicast frees the stage in
 //                       both CTAs and publishes the accumulator to both epilogues
 //   warp 2 (both)     : TMEM allocation (cta_group::2)
-//   warps 4-7 (both)  : epilogue of the CTA's own 128 rows (tcgen05.ld -> swizzled smem -> TMA store), then an arrive
+//   warps 4-11 (both) : epilogue of the CTA's own 128 rows (gemm_i8_epilogue.cuh), then an arrive
 //                       on the leader's accumulator-free barrier (remote for the peer)
-#include "kernels.cuh"
+#include "gemm_i8_epilogue.cuh"
 
 namespace rnnt {
 
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_I8_THREADS, 1)
 gemm_i8_i32_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                         const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles, int num_k_blocks,
                         int* __restrict__ status, const RowSkip skip, const int gate_blocked) {
@@ -53,7 +53,7 @@ gemm_i8_i32_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S::STAGES; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(tfull_bar + 8 * i, 1); mbar_init(tempty_bar + 8 * i, 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(tfull_bar + 8 * i, 1); mbar_init(tempty_bar + 8 * i, 2 * GEMM_I8_EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc_pair<2 * BN>(tmem_slot);
@@ -110,7 +110,8 @@ gemm_i8_i32_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   } else if (warp >= 4) {
     // ------------------------------------------------------------ epilogue of this CTA's 128 rows
     const int q = warp & 3;
-    const uint32_t cbuf0 = smem_c + (uint32_t)(q * 2) * S::C_WARP_BYTES;
+    const int half = (warp - 4) >> 2;             // the two warps of a TMEM lane quarter take alternate 32-column chunks
+    const uint32_t cbuf0 = smem_c + (uint32_t)((warp - 4) * 2) * S::C_WARP_BYTES;
     const uint32_t lead_tempty = map_to_cta(tempty_bar, 0);
     int acc = 0; uint32_t acc_phase = 0; int buf = 0;
     for (int st = pair_id; st < num_super; st += num_pairs) {
@@ -120,44 +121,9 @@ gemm_i8_i32_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, status)) break;
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
-      if (alive) {
-#pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          uint32_t v[32];
-          RNNT_TMEM_LD_X16(t_row + c * 32, v);
-          RNNT_TMEM_LD_X16(t_row + c * 32 + 16, v + 16);
-          tmem_ld_wait();
-          if (lane == 0) tma_store_wait_read<1>();       // staging buffer `buf` was last read by the store issued two chunks ago
-          __syncwarp();
-          if (!gate_blocked) {
-            const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 128u;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const uint32_t a = dst + (uint32_t)((j ^ (lane & 7)) << 4);
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
-                           "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
-            }
-          } else {
-            const uint32_t dst = cbuf0 + (uint32_t)buf * S::C_WARP_BYTES + (uint32_t)lane * 32u;
-            const uint32_t hsw = (uint32_t)((lane >> 2) & 1);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const uint32_t a = dst + (uint32_t)((j >> 1) * 1024) + ((((uint32_t)j & 1u) ^ hsw) << 4);
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[4 * j]), "r"(v[4 * j + 1]),
-                           "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
-            }
-          }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            const int col0 = n_blk * BN + c * 32, row0 = m_blk * GEMM_BM + q * 32;
-            if (!gate_blocked) tma_store_2d(&tmap_c, cbuf0 + (uint32_t)buf * S::C_WARP_BYTES, col0, row0);
-            else tma_store_5d(&tmap_c, cbuf0 + (uint32_t)buf * S::C_WARP_BYTES, 0, row0, 0, col0 >> 10, (col0 & 1023) >> 5);
-            tma_store_commit();
-          }
-          buf ^= 1;
-        }
-      }
+      if (alive)
+        gemm_i8_store_chunks(t_row, cbuf0, buf, half, GEMM_I8_EPI_WARPS / 4, BN / 32, &tmap_c, gate_blocked,
+                             m_blk * GEMM_BM + q * 32, n_blk * BN, lane, false);
       // this warp is done with the accumulator (nothing to read for a dead half): tell the leader's MMA thread
       tc_fence_before();
       __syncwarp();

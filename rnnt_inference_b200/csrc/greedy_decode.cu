@@ -49,7 +49,7 @@ __device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
 }
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+  asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
@@ -348,6 +348,43 @@ __device__ __forceinline__ void lstm_stage_store(uint8_t* act_g, int nc, const L
   }
 }
 
+// The contraction of one chunk of lanes on the tensor cores.  Warp w = (matrix m = w >> 2: x.W_ih or h.W_hh, gate-column
+// tiles 2 (w & 3) and 2 (w & 3) + 1): an A fragment (ldmatrix.x4 of the lanes' activations) serves two n tiles, a B
+// fragment two m tiles.  ldmatrix is a volatile asm (it must stay behind the barrier that publishes the staged rows), so
+// the order below is the order of the SASS: the fragments of k-pair kp + 1 are requested BEFORE the MMAs of k-pair kp are
+// issued (two fragment sets in registers) — issued in program order as load, MMA, MMA, load ... every ldmatrix latency sat
+// on the critical path (4.7 K cycles per chunk for 140 instructions, profiles/r02/dec_trace_tc_runahead.txt).  MT = m16
+// tiles with live lanes; rows of a tile past the chunk's lanes hold stale bytes, their results are never read.
+template <int MT>
+__device__ __forceinline__ void lstm_dot_tc(uint32_t wl_s, uint32_t act_s, int layer, float (&acc)[2][2][2][4]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m = warp >> 2, np = warp & 3;
+  const int brow = (layer * 2 + m) * DEC_COLS + 2 * np * 8 + (lane & 7);
+  const int arow = (lane & 7) + ((lane >> 3) & 1) * 8;
+  uint32_t b[2][2][4], a[2][2][MT][4];
+  auto load = [&](int kp, int buf) {
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) ldsm_x4(swz(wl_s, brow + nt * 8, DEC_P * 2, kp * 4 + (lane >> 3)), b[buf][nt]);
+#pragma unroll
+    for (int k2 = 0; k2 < 2; ++k2)
+#pragma unroll
+      for (int mi = 0; mi < MT; ++mi)
+        ldsm_x4(swz(act_s, mi * 16 + arow, 2 * DEC_P * 2, m * (DEC_P / 8) + (kp * 2 + k2) * 2 + (lane >> 4)), a[buf][k2][mi]);
+  };
+  load(0, 0);
+#pragma unroll
+  for (int kp = 0; kp < DEC_P / 32; ++kp) {
+    const int buf = kp & 1;
+    if (kp + 1 < DEC_P / 32) load(kp + 1, buf ^ 1);
+#pragma unroll
+    for (int k2 = 0; k2 < 2; ++k2)
+#pragma unroll
+      for (int mi = 0; mi < MT; ++mi)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) mma_bf16_16816(acc[nt][mi][k2], a[buf][k2][mi], b[buf][nt][2 * k2], b[buf][nt][2 * k2 + 1]);
+  }
+}
+
 __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int g, int s, const int* alist, int na,
                                               const int4* s_state, uint32_t wl_s, const float* s_bias, uint8_t* act_g,
                                               uint32_t act_s, long long* lt = nullptr) {
@@ -376,36 +413,12 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
       }
     }
     if (lt && tid == 0 && a0 == 0) lt[0] = clock64();
-    // ---- tensor-core contraction.  Warp w = (matrix m = w >> 2: x.W_ih or h.W_hh, gate-column tiles 2 (w & 3) and
-    // 2 (w & 3) + 1): an A fragment (ldmatrix.x4 of the lanes' activations) serves two n tiles, a B fragment two m tiles —
-    // 60 ldmatrix for 80 MMAs per warp; the shared-memory reads (not the tensor pipe) bound this loop.  Accumulators per
-    // (n tile, m tile, k-step parity) are independent MMA chains.
+    // ---- tensor-core contraction (lstm_dot_tc); accumulators per (n tile, m tile, k-step parity) are independent chains
     float acc[2][2][2][4];
 #pragma unroll
     for (int i = 0; i < 32; ++i) (&acc[0][0][0][0])[i] = 0.f;
-    {
-      const int m = warp >> 2, np = warp & 3;
-#pragma unroll
-      for (int kp = 0; kp < DEC_P / 32; ++kp) {
-        uint32_t b[2][4];
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt)
-          ldsm_x4(swz(wl_s, (layer * 2 + m) * DEC_COLS + (2 * np + nt) * 8 + (lane & 7), DEC_P * 2, kp * 4 + (lane >> 3)), b[nt]);
-#pragma unroll
-        for (int k2 = 0; k2 < 2; ++k2) {
-          const int chunk = m * (DEC_P / 8) + (kp * 2 + k2) * 2 + (lane >> 4);
-#pragma unroll
-          for (int mi = 0; mi < 2; ++mi) {
-            if (mi < mt) {
-              uint32_t a[4];
-              ldsm_x4(swz(act_s, mi * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * DEC_P * 2, chunk), a);
-#pragma unroll
-              for (int nt = 0; nt < 2; ++nt) mma_bf16_16816(acc[nt][mi][k2], a, b[nt][2 * k2], b[nt][2 * k2 + 1]);
-            }
-          }
-        }
-      }
-    }
+    if (mt == 2) lstm_dot_tc<2>(wl_s, act_s, layer, acc);
+    else lstm_dot_tc<1>(wl_s, act_s, layer, acc);
     __syncthreads();                       // every warp is done reading act: reuse it for the partial gate sums
     {                                       // part[m][lane][col] fp32
       const int m = warp >> 2, np = warp & 3;
@@ -452,46 +465,59 @@ __device__ __forceinline__ void fc1_phase_tc(const DecParams& p, int g, int s, c
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int lane0 = g * p.LG;
   const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
+  // g = h1 of a chunk's lanes as 16-byte pieces in registers, requested one chunk ahead (their L2 round trip hides behind
+  // the previous chunk's MMAs, as in lstm_phase_tc)
+  constexpr int VPL = DEC_P / 8;          // 40
+  constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;   // 5
+  uint4 v[R]; int dst[R];
+  auto stage_load = [&](int a0, int nc) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int e = tid + r * DEC_THREADS;
+      const int a = e / VPL, q = e % VPL;
+      dst[r] = -1;
+      v[r] = make_uint4(0u, 0u, 0u, 0u);
+      if (a < nc) {
+        const int li = alist[a0 + a];
+        const int cur = s_state[li].x & LS_CUR;
+        dst[r] = a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4);
+        v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li) * DEC_P) + q);
+      }
+    }
+  };
+  if (na > 0) stage_load(0, min(DEC_TC_LANES, na));
   for (int a0 = 0; a0 < na; a0 += DEC_TC_LANES) {
     const int nc = min(DEC_TC_LANES, na - a0);
     const int mt = (nc + 15) >> 4;
-    {
-      constexpr int VPL = DEC_P / 8;          // 40
-      constexpr int R = DEC_TC_LANES * VPL / DEC_THREADS;   // 5
-      uint4 v[R]; int dst[R];
 #pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int e = tid + r * DEC_THREADS;
-        const int a = e / VPL, q = e % VPL;
-        dst[r] = -1;
-        v[r] = make_uint4(0u, 0u, 0u, 0u);
-        if (a < nc) {
-          const int li = alist[a0 + a];
-          const int cur = s_state[li].x & LS_CUR;
-          dst[r] = a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4);
-          v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li) * DEC_P) + q);
-        }
-      }
-#pragma unroll
-      for (int r = 0; r < R; ++r)
-        if (dst[r] >= 0) *reinterpret_cast<uint4*>(act_g + dst[r]) = v[r];
-    }
+    for (int r = 0; r < R; ++r)
+      if (dst[r] >= 0) *reinterpret_cast<uint4*>(act_g + dst[r]) = v[r];
     __syncthreads();
+    if (a0 + DEC_TC_LANES < na) stage_load(a0 + DEC_TC_LANES, min(DEC_TC_LANES, na - a0 - DEC_TC_LANES));
     const int mi = warp >> 2, ni = warp & 3;
     if (mi < mt) {
-      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      // fragments of k-pair kp + 1 requested before the MMAs of k-pair kp (see lstm_dot_tc); one accumulator per k-step
+      // parity, summed at the end
+      float acc2[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
       const int brow = min(ni * 8 + (lane & 7), ncol - 1);
-#pragma unroll 2
-      for (int kp = 0; kp < DEC_P / 32; ++kp) {
-        uint32_t b[4];
-        ldsm_x4(swz(wp_s, brow, DEC_P * 2, kp * 4 + (lane >> 3)), b);
+      const int arow = mi * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+      uint32_t b[2][4], a[2][2][4];
+      auto load = [&](int kp, int buf) {
+        ldsm_x4(swz(wp_s, brow, DEC_P * 2, kp * 4 + (lane >> 3)), b[buf]);
 #pragma unroll
-        for (int k2 = 0; k2 < 2; ++k2) {
-          uint32_t a[4];
-          ldsm_x4(swz(act_s, mi * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, 2 * DEC_P * 2, (kp * 2 + k2) * 2 + (lane >> 4)), a);
-          mma_bf16_16816(acc, a, b[2 * k2], b[2 * k2 + 1]);
-        }
+        for (int k2 = 0; k2 < 2; ++k2) ldsm_x4(swz(act_s, arow, 2 * DEC_P * 2, (kp * 2 + k2) * 2 + (lane >> 4)), a[buf][k2]);
+      };
+      load(0, 0);
+#pragma unroll
+      for (int kp = 0; kp < DEC_P / 32; ++kp) {
+        const int buf = kp & 1;
+        if (kp + 1 < DEC_P / 32) load(kp + 1, buf ^ 1);
+#pragma unroll
+        for (int k2 = 0; k2 < 2; ++k2) mma_bf16_16816(acc2[k2], a[buf][k2], b[buf][2 * k2], b[buf][2 * k2 + 1]);
       }
+      float acc[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i] = acc2[0][i] + acc2[1][i];
       const int r0 = mi * 16 + (lane >> 2), c0 = ni * 8 + 2 * (lane & 3);
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
@@ -832,10 +858,12 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         {
           float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll
-          for (int ks = 0; ks < 16; ++ks) {
-            uint32_t a[4];
-            ldsm_x4(arow + ks * 32, a);
-            mma_bf16_16816(acc[ks & 1], a, w2f[2 * ks], w2f[2 * ks + 1]);
+          for (int k4 = 0; k4 < 4; ++k4) {       // four fragments in flight per batch of MMAs (ldmatrix is a volatile asm)
+            uint32_t a[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ldsm_x4(arow + (k4 * 4 + i) * 32, a[i]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mma_bf16_16816(acc[i & 1], a[i], w2f[2 * (k4 * 4 + i)], w2f[2 * (k4 * 4 + i) + 1]);
           }
           float* out = lg + (warp >> 2) * (16 * DEC_V);
           const int r0 = lane >> 2, c0 = (warp & 3) * 8 + 2 * (lane & 3);

@@ -30,17 +30,20 @@ struct RowSkip {
 // ------------------------------------------------------------------ gemm_i8.cu
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 128;   // bytes of K per stage = one 128-byte swizzle row
-constexpr int GEMM_STAGES = 4;
-constexpr int GEMM_THREADS = 256;
+constexpr int GEMM_STAGES = 4;      // gemm_bf16.cu
+constexpr int GEMM_THREADS = 256;   // gemm_bf16.cu: 4 control + 4 epilogue warps
+constexpr int GEMM_I8_EPI_WARPS = 8;                            // two per TMEM lane quarter (gemm_i8_epilogue.cuh)
+constexpr int GEMM_I8_THREADS = 32 * (4 + GEMM_I8_EPI_WARPS);   // 384
 
 template <int BN>
 struct GemmSmem {
+  static constexpr int STAGES = BN == 256 ? 3 : 4;
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK;           // 16 KB
   static constexpr int B_BYTES = BN * GEMM_BK;                // 32 KB at BN=256
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int C_WARP_BYTES = 32 * 128;               // 32 rows x 32 int32
-  static constexpr int C_BYTES = 4 /*warps*/ * 2 /*buffers*/ * C_WARP_BYTES;  // 32 KB
-  static constexpr int BAR_OFFSET = GEMM_STAGES * STAGE_BYTES + C_BYTES;
+  static constexpr int C_BYTES = GEMM_I8_EPI_WARPS * 2 /*buffers*/ * C_WARP_BYTES;  // 64 KB
+  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + C_BYTES;
   static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;       // barriers + alignment slack
 };
 
@@ -51,14 +54,14 @@ __global__ void gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, c
                                    int32_t* __restrict__ c_direct, const long long M, const int ldc);
 // gemm_i8_pair.cu: one 256 x 256 tile per CTA pair (cta_group::2); each CTA stages 128 rows of A and 128 rows of W
 struct GemmPairSmem {
-  static constexpr int STAGES = 6;
+  static constexpr int STAGES = 5;
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK;           // 16 KB
   static constexpr int B_BYTES = 128 * GEMM_BK;               // 16 KB: this CTA's half of the 256-row W tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int C_WARP_BYTES = 32 * 128;
-  static constexpr int C_BYTES = 4 * 2 * C_WARP_BYTES;        // 32 KB
+  static constexpr int C_BYTES = GEMM_I8_EPI_WARPS * 2 * C_WARP_BYTES;   // 64 KB
   static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + C_BYTES;
-  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;       // 225.25 KB
 };
 __global__ void gemm_i8_i32_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                                         const __grid_constant__ CUtensorMap tmap_c, int num_m_tiles, int num_n_tiles,

@@ -526,9 +526,8 @@ def test_gemm_i8_clusters(ops, cm):
     dead m tiles, live rows exact and dead rows untouched."""
     import ctypes
     from rnnt_inference_b200 import _lib
-    if cm == "pair":
-        _lib.check(_lib.lib.rnnt_tune_gemm_pair(1))
-    else:
+    _lib.check(_lib.lib.rnnt_tune_gemm_pair(1 if cm == "pair" else 0))
+    if cm != "pair":
         _lib.check(_lib.lib.rnnt_tune_gemm_cluster(cm))
     try:
         g = torch.Generator(device="cuda").manual_seed(7 if cm == "pair" else cm)
@@ -554,4 +553,4 @@ def test_gemm_i8_clusters(ops, cm):
             assert bool((c[s:, b] == 123456789).all()), f"dead rows of tile {b} were written"
     finally:
         _lib.lib.rnnt_tune_gemm_cluster(1)
-        _lib.lib.rnnt_tune_gemm_pair(0)
+        _lib.lib.rnnt_tune_gemm_pair(1)
