@@ -136,7 +136,7 @@ __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g,
                                            const int4* s_state, const uint16_t* wl, const float* s_bias, float* act,
                                            float* part, long long* lt = nullptr) {
   const int tid = threadIdx.x;
-  const int lane0 = g * p.LG;
+  const int lane0 = g, lstep = p.NG;      // lane li of group g is lane g + li * NG of the batch
   constexpr int VPL = 2 * DEC_P / 8;      // 16-byte vectors per lane: 40 of x, 40 of h
   for (int a0 = 0; a0 < na; a0 += DEC_CHUNK) {
     const int nc = min(DEC_CHUNK, na - a0);
@@ -145,7 +145,7 @@ __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g,
     float c_old = 0.f; int un = 0, ucur = 0;
     if (ua < nc) {
       const int li = alist[a0 + ua];
-      un = lane0 + li;
+      un = lane0 + li * lstep;
       ucur = s_state[li].x & LS_CUR;
       c_old = p.cg[ucur][layer][(size_t)un * DEC_P + s * DEC_U + uu];
     }
@@ -161,7 +161,7 @@ __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g,
           const int a = e / VPL, q = e % VPL;
           const int li = alist[a0 + a];
           const int4 st = s_state[li];
-          const int n = lane0 + li, cur = st.x & LS_CUR;
+          const int n = lane0 + li * p.NG, cur = st.x & LS_CUR;
           dsti[r] = a * 2 * DEC_P + q * 8;
           if (q < VPL / 2) {
             if (layer == 0) {
@@ -222,7 +222,7 @@ __device__ __forceinline__ void lstm_phase(const DecParams& p, int layer, int g,
 __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, const int* alist, int na, const int4* s_state,
                                           const uint16_t* wp, float* act) {
   const int tid = threadIdx.x;
-  const int lane0 = g * p.LG;
+  const int lane0 = g, lstep = p.NG;      // lane li of group g is lane g + li * NG of the batch
   const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
   constexpr int VPL = DEC_P / 8;     // 40 vectors of 8 bf16 per lane
   for (int a0 = 0; a0 < na; a0 += 2 * DEC_CHUNK) {
@@ -239,7 +239,7 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
           const int li = alist[a0 + a];
           const int cur = s_state[li].x & LS_CUR;
           dsti[r] = a * DEC_P + q * 8;
-          v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li) * DEC_P) + q);
+          v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li * lstep) * DEC_P) + q);
         }
       }
 #pragma unroll
@@ -288,7 +288,7 @@ __device__ __forceinline__ void fc1_phase(const DecParams& p, int g, int s, cons
         }
 #pragma unroll
         for (int i = 0; i < 3; ++i)
-          if (i < nl) p.z[(size_t)(lane0 + alist[a0 + lg + i * nslot]) * DEC_J + col0 + cl] = acc[i];
+          if (i < nl) p.z[(size_t)(lane0 + alist[a0 + lg + i * nslot] * lstep) * DEC_J + col0 + cl] = acc[i];
       }
     }
     __syncthreads();
@@ -320,7 +320,7 @@ __device__ __forceinline__ void lstm_stage_load(const DecParams& p, int layer, i
     if (a < nc) {
       const int li = alist[a0 + a];
       const int4 st = s_state[li];
-      const int n = lane0 + li, cur = st.x & LS_CUR;
+      const int n = lane0 + li * p.NG, cur = st.x & LS_CUR;
       const uint4* hsrc = reinterpret_cast<const uint4*>(p.hg[cur][layer] + (size_t)n * DEC_P);
       const uint4* xsrc = nullptr;
       if (layer == 0) { if (st.z >= 0 && st.z <= 27) xsrc = reinterpret_cast<const uint4*>(p.embed + st.z * DEC_P); }
@@ -389,7 +389,7 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
                                               const int4* s_state, uint32_t wl_s, const float* s_bias, uint8_t* act_g,
                                               uint32_t act_s, long long* lt = nullptr) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int lane0 = g * p.LG;
+  const int lane0 = g, lstep = p.NG;      // lane li of group g is lane g + li * NG of the batch
   float* part = reinterpret_cast<float*>(act_g);          // [ih | hh][32 lanes][64 columns] fp32 partial sums, after the MMAs
   LstmStage sg;
   lstm_stage_load(p, layer, lane0, alist, 0, min(DEC_TC_LANES, na), s_state, sg);
@@ -407,7 +407,7 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
       const int a = ua + 16 * h;
       if (a < nc) {
         const int li = alist[a0 + a];
-        un[h] = lane0 + li;
+        un[h] = lane0 + li * lstep;
         ucur[h] = s_state[li].x & LS_CUR;
         c_old[h] = p.cg[ucur[h]][layer][(size_t)un[h] * DEC_P + s * DEC_U + uu];
       }
@@ -463,7 +463,7 @@ __device__ __forceinline__ void lstm_phase_tc(const DecParams& p, int layer, int
 __device__ __forceinline__ void fc1_phase_tc(const DecParams& p, int g, int s, const int* alist, int na, const int4* s_state,
                                              uint32_t wp_s, uint8_t* act_g, uint32_t act_s) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int lane0 = g * p.LG;
+  const int lane0 = g, lstep = p.NG;      // lane li of group g is lane g + li * NG of the batch
   const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
   // g = h1 of a chunk's lanes as 16-byte pieces in registers, requested one chunk ahead (their L2 round trip hides behind
   // the previous chunk's MMAs, as in lstm_phase_tc)
@@ -481,7 +481,7 @@ __device__ __forceinline__ void fc1_phase_tc(const DecParams& p, int g, int s, c
         const int li = alist[a0 + a];
         const int cur = s_state[li].x & LS_CUR;
         dst[r] = a * (2 * DEC_P * 2) + ((q ^ (a & 7)) << 4);
-        v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li) * DEC_P) + q);
+        v[r] = __ldcg(reinterpret_cast<const uint4*>(p.hg[cur ^ 1][1] + (size_t)(lane0 + li * lstep) * DEC_P) + q);
       }
     }
   };
@@ -523,7 +523,7 @@ __device__ __forceinline__ void fc1_phase_tc(const DecParams& p, int g, int s, c
       for (int h = 0; h < 2; ++h) {
         const int r = r0 + 8 * h;
         if (r < nc) {
-          float* zr = p.z + (size_t)(lane0 + alist[a0 + r]) * DEC_J + col0;
+          float* zr = p.z + (size_t)(lane0 + alist[a0 + r] * lstep) * DEC_J + col0;
           if (c0 < ncol) zr[c0] = acc[2 * h];
           if (c0 + 1 < ncol) zr[c0 + 1] = acc[2 * h + 1];
         }
@@ -666,8 +666,8 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = blockIdx.x / DEC_S, s = blockIdx.x % DEC_S;
-  const int lane0 = g * p.LG;
-  const int nl = max(0, min(p.LG, p.N - lane0));    // lanes of this group
+  const int lane0 = g, lstep = p.NG;      // lane li of group g is lane g + li * NG of the batch
+  const int nl = g < p.N ? (p.N - g + p.NG - 1) / p.NG : 0;    // lanes of this group
   const int col0 = s * DEC_JC, ncol = min(DEC_JC, DEC_J - col0);
 
   // resident weights: wl[layer][m][c][k], c = gate*16 + u  <-  W[(gate*320 + s*16 + u)][k]
@@ -724,7 +724,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   }
   // lane state init (each lane by the CTA that owns it in phase D)
   for (int li = s + tid * DEC_S; li < nl; li += DEC_S * DEC_THREADS)
-    *reinterpret_cast<int4*>(p.lane_state + (size_t)(lane0 + li) * 4) = make_int4(LS_NEED, 0, p.pre_g[lane0 + li], 0);
+    *reinterpret_cast<int4*>(p.lane_state + (size_t)(lane0 + li * lstep) * 4) = make_int4(LS_NEED, 0, p.pre_g[lane0 + li * lstep], 0);
   if (tid == 0) s_fail = 0;
   int epoch = 0; bool ok = true;
   group_barrier(p, g, epoch, ok, &s_fail);
@@ -737,7 +737,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     // network has to be re-evaluated, count the lanes still to finish (phase 1) / still to replay (phase 2)
     if (tid == 0) { s_na = 0; s_unfinished = 0; s_live = 0; s_maxdc = 0; }
     for (int li = tid; li < nl; li += DEC_THREADS)
-      s_state[li] = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li) * 4));
+      s_state[li] = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li * lstep) * 4));
     __syncthreads();
     if (tid < 32) {
       for (int base = 0; base < nl; base += 32) {
@@ -836,7 +836,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
           run[h] = runnable(st2[h], total);
         }
         if (run[h]) {
-          const int n = lane0 + li;
+          const int n = lane0 + li * lstep;
           jr[h] = load_counters(p, n, lane);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -874,7 +874,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           if (run[h]) {
-            const int j = warp + 8 * h, n = lane0 + s + j * DEC_S;
+            const int j = warp + 8 * h, n = lane0 + (s + j * DEC_S) * lstep;
             const float logit = __fadd_rn(__fadd_rn(lg[j * DEC_V + lane], lg[16 * DEC_V + j * DEC_V + lane]), s_b2[lane]);
             const int t_before = st2[h].y;
             run[h] = joint_update(p, n, st2[h], jr[h], logit, lane, total) && budget > 0;
@@ -903,7 +903,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
         int4 st = s_state[li];
         if (!runnable(st, total)) continue;
-        const int n = lane0 + li;
+        const int n = lane0 + li * lstep;
         JointRegs jr = load_counters(p, n, lane);
         float zf[16]; uint4 yv[2];
 #pragma unroll
@@ -936,7 +936,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   // committed h/c back into the caller's arrays (s_state holds the final states: it was refreshed after the last barrier).
   if (ok && total >= 0) {
     for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
-      const int n = lane0 + li;
+      const int n = lane0 + li * lstep;
       const int4 st = s_state[li];
       if (lane == 0 && (st.x & LS_FIXED)) p.time_idx[n] += total - st.w;
       if (st.x & LS_CUR) {
