@@ -44,7 +44,30 @@ for k, v in ev.items():
     print(k, "ms", round(sum(s.elapsed_time(e) for s, e, _ in v), 3))
 iters = int(dec.last_iters.item())
 print("N", n, "T2", (int(lens.max()) + 1) // 2, "iters", iters, "tokens", int(res_len.sum()))
-tr = trace.cpu().numpy()[:min(iters, CAP)].astype(np.float64)
+tr_all = trace.cpu().numpy().astype(np.float64)
+rows = tr_all[tr_all[:, 0] > 0]
+if len(rows):
+    span = rows[-1, 6] - rows[0, 0]
+    ph = [np.sum(rows[:, b] - rows[:, a]) for a, b in ((0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6))]
+    work = rows[rows[:, 7] > 0]
+    idle = rows[rows[:, 7] == 0]
+    print("rounds of CTA 0 (group 0): %d (%d with prediction-network work, %d blank-skipping only); first round start -> last round end: "
+          "%.0f cycles" % (len(rows), len(work), len(idle), span))
+    print("  sum over rounds (cycles): lstm0 %.0f  barrier %.0f  lstm1+barrier %.0f  fc1+barrier %.0f  joint/update %.0f  barrier %.0f; "
+          "between rounds (state refresh, lists) %.0f" % (*ph, span - sum(ph)))
+    gap = np.concatenate([rows[1:, 0] - rows[:-1, 6], [0.0]])       # end of a round -> start of the next one
+    for lo, hi in ((1, 4), (5, 32), (33, 64), (65, 400)):
+        m = (rows[:, 7] >= lo) & (rows[:, 7] <= hi)
+        if m.any():
+            r = rows[m]
+            print("  rounds with %3d..%3d active lanes: %3d; mean cycles: lstm0 %.0f  barrier %.0f  lstm1+barrier %.0f  fc1+barrier %.0f  "
+                  "joint/update %.0f (%.1f decisions of CTA 0)  barrier %.0f  gap to next round %.0f" %
+                  (lo, hi, m.sum(), *[np.mean(r[:, b2] - r[:, a2]) for a2, b2 in ((0, 1), (1, 2), (2, 3), (3, 4), (4, 5))],
+                   np.mean(r[:, 8]), np.mean(r[:, 6] - r[:, 5]), np.mean(gap[m])))
+    if len(idle):
+        print("  blank-skipping rounds: mean joint %.0f  barrier %.0f cycles" %
+              (np.mean(idle[:, 5] - idle[:, 0]), np.mean(idle[:, 6] - idle[:, 5])))
+tr = tr_all[:min(iters, CAP)]
 full = tr[tr[:, 7] > 0]
 d = lambda a, b: np.median(full[:, a] - full[:, b])
 print("iterations with LSTM work:", len(full), "median active lanes in group 0:", np.median(full[:, 7]))

@@ -662,7 +662,8 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   __shared__ int4 s_state[DEC_MAXLG];
   __shared__ int alist[DEC_MAXLG];
   __shared__ float s_bias[2 * DEC_COLS], s_b2[DEC_V];
-  __shared__ int s_na, s_unfinished, s_live, s_maxdc, s_fail;
+  __shared__ int4 s_blk[(DEC_MAXLG + 31) / 32];      // per 32-lane block: need mask, unfinished, live, max decisions
+  __shared__ int s_unfinished, s_fail;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = blockIdx.x / DEC_S, s = blockIdx.x % DEC_S;
@@ -734,43 +735,49 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   bool w2_valid = false;
   for (;;) {
     // ---- snapshot the group's lane states (one 16-byte load per lane), build the list of lanes whose prediction
-    // network has to be re-evaluated, count the lanes still to finish (phase 1) / still to replay (phase 2)
-    if (tid == 0) { s_na = 0; s_unfinished = 0; s_live = 0; s_maxdc = 0; }
-    for (int li = tid; li < nl; li += DEC_THREADS)
-      s_state[li] = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li * lstep) * 4));
-    __syncthreads();
-    if (tid < 32) {
-      for (int base = 0; base < nl; base += 32) {
-        const int li = base + tid;
-        int need = 0, unfin = 0, live = 0, dc = 0;
-        if (li < nl) {
-          const int4 st = s_state[li];
-          const bool replay = total >= 0 && (st.x & LS_FINISHED) && !(st.x & LS_FIXED) && st.w < total;
-          unfin = !(st.x & LS_FINISHED);
-          live = unfin || replay;
-          need = (st.x & LS_NEED) && !(st.x & LS_FIXED) && live;
-          dc = st.w;
-        }
-        const unsigned mneed = __ballot_sync(0xffffffffu, need);
-        const unsigned munf = __ballot_sync(0xffffffffu, unfin);
-        const unsigned mlive = __ballot_sync(0xffffffffu, live);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) dc = max(dc, __shfl_xor_sync(0xffffffffu, dc, off));
-        if (need) alist[s_na + __popc(mneed & ((1u << tid) - 1))] = li;
-        __syncwarp();
-        if (tid == 0) { s_na += __popc(mneed); s_unfinished += __popc(munf); s_live += __popc(mlive); s_maxdc = max(s_maxdc, dc); }
-        __syncwarp();
+    // network has to be re-evaluated, count the lanes still to finish (phase 1) / still to replay (phase 2).  This sits on
+    // the critical path of every round (a lane that emits symbol after symbol is a chain of rounds), so it is two
+    // barriers deep: warp w scans the 32-lane blocks w, w + 8 straight from global memory, the per-block results go
+    // through shared memory, every thread sums the <= 10 of them.
+    const int nblk = (nl + 31) >> 5;
+    bool need_r[2] = {false, false};
+    for (int b = warp, i = 0; b < nblk; b += DEC_WARPS, ++i) {
+      const int li = b * 32 + lane;
+      int need = 0, unfin = 0, live = 0, dc = 0;
+      if (li < nl) {
+        const int4 st = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li * lstep) * 4));
+        s_state[li] = st;
+        const bool replay = total >= 0 && (st.x & LS_FINISHED) && !(st.x & LS_FIXED) && st.w < total;
+        unfin = !(st.x & LS_FINISHED);
+        live = unfin || replay;
+        need = (st.x & LS_NEED) && !(st.x & LS_FIXED) && live;
+        dc = st.w;
       }
+      const unsigned mneed = __ballot_sync(0xffffffffu, need);
+      const unsigned munf = __ballot_sync(0xffffffffu, unfin);
+      const unsigned mlive = __ballot_sync(0xffffffffu, live);
+      dc = __reduce_max_sync(0xffffffffu, dc);
+      need_r[i] = need != 0;
+      if (lane == 0) s_blk[b] = make_int4((int)mneed, __popc(munf), __popc(mlive), dc);
     }
     __syncthreads();
-    const int na = s_na;
+    int na = 0, unfinished = 0, live_lanes = 0, maxdc = 0, before[2] = {0, 0};
+    for (int b = 0; b < nblk; ++b) {
+      const int4 v = s_blk[b];
+      if (b == warp) before[0] = na;
+      if (b == warp + DEC_WARPS) before[1] = na;
+      na += __popc((unsigned)v.x); unfinished += v.y; live_lanes += v.z; maxdc = max(maxdc, v.w);
+    }
+    for (int b = warp, i = 0; b < nblk; b += DEC_WARPS, ++i)
+      if (need_r[i]) alist[before[i] + __popc((unsigned)s_blk[b].x & ((1u << lane) - 1u))] = b * 32 + lane;
+    __syncthreads();
     if (!ok) break;
-    if (total < 0 && s_unfinished == 0) {
+    if (total < 0 && unfinished == 0) {
       // ---- every lane of the group has finished: rendezvous of all groups; the largest decision count any lane needed to
       // finish is the number of iterations of the reference's lock-step loop
       if (tid == 0) {
         if (s == 0) {
-          atomicMax(p.global_sync + 1, s_maxdc);
+          atomicMax(p.global_sync + 1, maxdc);
           __threadfence();
           atomicAdd(p.global_sync + 0, 1);
         }
@@ -792,7 +799,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
       continue;            // rebuild the lists with `total` known: the lanes parked on the cap become live again
     }
-    if (total >= 0 && s_live == 0) break;
+    if (total >= 0 && live_lanes == 0) break;
     ++round;
     long long* const trace = RNNT_TRACE_PTR(p);
     const bool tr = trace && blockIdx.x == 0 && tid == 0 && round <= p.trace_cap;
