@@ -98,6 +98,21 @@ int rnnt_lstm_recurrent_i8_gate_blocked_ragged(const int32_t* G, const int8_t* w
                                                float in_scale, float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y,
                                                int T, int N, int H, const int32_t* tile_steps_host, void* workspace, void* stream);
 
+/* rnnt_lstm_recurrent_i8 for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernel, arguments and results as rnnt_lstm_recurrent_i8, but no `workspace` argument: the scratch (device status
+ * word, per-tile release counters, h ping-pong buffer, c scratch) is a file-scope device array inside the library —
+ * 2,099,968 bytes that every GPU which loads the library holds until the process exits.  LIMIT: N <= 512 rows per call
+ * (T unbounded); a larger N returns RNNT_ERR_INVALID with a message naming the limit.  The call performs no cudaMalloc /
+ * cudaFree / allocating library routine.  The array is shared by all calls and keeps the last call's contents; what must
+ * start at zero (status word, counters) is cleared on `stream` at the start of each call.  Calls that overlap on one
+ * GPU (different streams, parallel graph branches) RACE on it: serialise them.  Device-side failures (watchdog) are
+ * reported through status_out_host (may be NULL; page-locked host int32, written asynchronously on `stream`: 0 = ok)
+ * — this variant does not touch the status word of rnnt_check_device_status / rnnt_peek_device_status. */
+int rnnt_lstm_recurrent_i8_static_scratch(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale,
+                                          float in_scale, float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y,
+                                          int T, int N, int H, int32_t* status_out_host, void* stream);
+
 /* TUNING (process-wide, results do not depend on it): slice-CTAs per thread-block cluster of the recurrent kernel, 1, 2, 4
  * or 8 (default 1, or the environment variable RNNT_REC_CLUSTER); the h tile of a batch tile is TMA-multicast inside a
  * cluster.  Measured on B200: no gain over 1 (profiles/r01/rec_cluster_v5.txt). */

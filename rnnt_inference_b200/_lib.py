@@ -45,6 +45,7 @@ _SIGS = {
     "rnnt_gemm_i8_i32_simt": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "rnnt_lstm_recurrent_workspace_bytes": (_i64, [_i]),
     "rnnt_lstm_recurrent_i8": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "rnnt_lstm_recurrent_i8_static_scratch": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "rnnt_lstm_recurrent_i8_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_lstm_recurrent_i8_gate_blocked_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_tune_recurrent_cluster": (_i, [_i]),

@@ -634,7 +634,7 @@ int rnnt_tune_recurrent_cluster(int ctas) {
 }
 static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
                    float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
-                   const int32_t* tile_steps_host, void* workspace, void* stream);
+                   const int32_t* tile_steps_host, void* workspace, void* stream, int* status_word = nullptr);
 int rnnt_lstm_recurrent_i8_ragged(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
                                   float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
                                   const int32_t* tile_steps_host, void* workspace, void* stream) {
@@ -647,7 +647,7 @@ int rnnt_lstm_recurrent_i8_gate_blocked_ragged(const int32_t* G, const int8_t* w
 }
 static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
                    float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
-                   const int32_t* tile_steps_host, void* workspace, void* stream) {
+                   const int32_t* tile_steps_host, void* workspace, void* stream, int* status_word) {
   if (!G || !w_hh || !bias || !hx || !cx || !y || !workspace) return fail(RNNT_ERR_INVALID, "lstm_recurrent: null pointer");
   if (H != REC_H) return fail(RNNT_ERR_INVALID, "lstm_recurrent: hidden size must be 1024 (got %d)", H);
   if (T < 0 || N <= 0) return fail(RNNT_ERR_INVALID, "lstm_recurrent: need T >= 0, N > 0 (T=%d N=%d)", T, N);
@@ -662,7 +662,7 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
   int* flags = reinterpret_cast<int*>(ws + 1024);
   int8_t* h_buf = reinterpret_cast<int8_t*>(ws + 1024 + rec_flags_bytes(N));
   h_buf = reinterpret_cast<int8_t*>(round_up((int64_t)reinterpret_cast<uintptr_t>(h_buf), 1024));
-  int* status = device_status();
+  int* status = status_word ? status_word : device_status();     // status_word: only the static-scratch entry point passes one
   if (!status) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
 
   RecParams p;
@@ -763,6 +763,59 @@ int rnnt_lstm_recurrent_i8(const int32_t* G, const int8_t* w_hh, const float* bi
                            void* workspace, void* stream) {
   return rnnt_lstm_recurrent_i8_ragged(G, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, hx, cx, y, T, N, H, nullptr,
                                        workspace, stream);
+}
+
+// ---- rnnt_lstm_recurrent_i8_static_scratch: the recurrent kernel for callers that cannot allocate (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  Its scratch — the device status word, the per-tile release
+// counters, the h ping-pong buffer and the blocked c scratch — lives in ONE file-scope device array of fixed size; every
+// GPU that loads the library holds these bytes until the process exits.  All calls share the array: it keeps the last
+// call's contents (the status word and the counters are cleared at the start of every call), and two calls that overlap
+// on one GPU — different streams, or graph branches — race on it.
+constexpr int REC_STATIC_MAX_N = 512;                       // batch rows per call
+constexpr int64_t REC_STATIC_STATUS_BYTES = 256;            // the status word, in front of the workspace proper
+constexpr int64_t REC_STATIC_WS_BYTES =                     // = rnnt_lstm_recurrent_workspace_bytes(REC_STATIC_MAX_N)
+    1024 + (REC_STATIC_MAX_N / REC_BM) * REC_FLAG_STRIDE * 4 + 2ll * REC_STATIC_MAX_N * REC_H + 1024 + 2ll * REC_STATIC_MAX_N * REC_H;
+static_assert(REC_STATIC_MAX_N % REC_BM == 0 && ((REC_STATIC_MAX_N / REC_BM) * REC_FLAG_STRIDE * 4) % 256 == 0, "flag block is a multiple of 256 B");
+static __device__ __align__(256) unsigned char g_rec_static_scratch[REC_STATIC_STATUS_BYTES + REC_STATIC_WS_BYTES];   // 2,099,968 B
+
+// Device address of the array on the current device.  In host code `g_rec_static_scratch` is only a handle for the
+// runtime, not an address a kernel could use: cudaGetSymbolAddress translates it, once per device, with that device current.
+static int rec_static_scratch_ptr(uint8_t** out) {
+  static uint8_t* ptr[64] = {nullptr};
+  static std::mutex mu;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    void* q = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&q, g_rec_static_scratch);
+    if (e != cudaSuccess || !q)
+      return fail(RNNT_ERR_CUDA, "cudaGetSymbolAddress(g_rec_static_scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+    ptr[dev] = reinterpret_cast<uint8_t*>(q);
+  }
+  *out = ptr[dev];
+  return RNNT_OK;
+}
+
+int rnnt_lstm_recurrent_i8_static_scratch(const int32_t* G, const int8_t* w_hh, const float* bias, float rb_scale, float in_scale,
+                                          float out_scale, int skip_quant_y, int8_t* hx, uint16_t* cx, void* y, int T, int N, int H,
+                                          int32_t* status_out_host, void* stream) {
+  if (N > REC_STATIC_MAX_N)
+    return fail(RNNT_ERR_INVALID, "lstm_recurrent_static_scratch: N = %d exceeds the static scratch (N <= %d per call); use "
+                "rnnt_lstm_recurrent_i8 with a caller-owned workspace", N, REC_STATIC_MAX_N);
+  if (N > 0 && rnnt_lstm_recurrent_workspace_bytes(N) > REC_STATIC_WS_BYTES)
+    return fail(RNNT_ERR_INVALID, "lstm_recurrent_static_scratch: workspace for N = %d does not fit the static scratch", N);
+  uint8_t* scratch = nullptr;
+  if (int r = rec_static_scratch_ptr(&scratch)) return r;
+  cudaStream_t st = (cudaStream_t)stream;
+  int* status = reinterpret_cast<int*>(scratch);
+  // must start at zero: the status word (kernels bail out while it is set); rec_run clears the release counters itself
+  CUDA_TRY(cudaMemsetAsync(status, 0, REC_STATIC_STATUS_BYTES, st));
+  if (int r = rec_run(G, 0, w_hh, bias, rb_scale, in_scale, out_scale, skip_quant_y, hx, cx, y, T, N, H, nullptr,
+                      scratch + REC_STATIC_STATUS_BYTES, stream, status))
+    return r;
+  if (status_out_host) CUDA_TRY(cudaMemcpyAsync(status_out_host, status, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  return RNNT_OK;
 }
 
 int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* w_ih, const int8_t* w_hh, const float* bias,
