@@ -553,7 +553,9 @@ def main():
         h2d = reduce_scalar(float(sut.h2d_bytes - h0), dist.ReduceOp.SUM if world > 1 else None)
         d2h = reduce_scalar(float(sut.d2h_bytes - d0), dist.ReduceOp.SUM if world > 1 else None)
         e2e = {"value": round(done_all / sec, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d / k_e2e),
-               "d2h_bytes_per_step": int(d2h / k_e2e), "steps": k_e2e, "api": "PytorchSUT.issue_queries via loadgen_shim.StartTest"}
+               "d2h_bytes_per_step": int(d2h / k_e2e), "steps": k_e2e, "api": "PytorchSUT.issue_queries via loadgen_shim.StartTest",
+               "chunks": f"sorted query cut by sharding.plan_chunks(batch {args.batch}, head_fraction {sut.head_fraction}): the first chunk's "
+                         "compute covers the second chunk's host->device copy"}
 
     micro = encoder_microbench(decoder, device) if (rank == 0 and not args.no_microbench) else None
     cpu = parity = None

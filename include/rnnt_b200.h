@@ -59,9 +59,11 @@ int rnnt_quantize_ragged_f32_i8(const float* packed, const int64_t* offsets, con
  * C[M][N] int32 = A[M][K] int8 . W[N][K]^T int8, exact.  tcgen05 kind::i8, TMEM accumulators, TMA in/out.
  * Requirements: K % 16 == 0, N % 64 == 0, pointers 16-byte aligned. */
 int rnnt_gemm_i8_i32(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, void* stream);
-/* Same GEMM over a ragged time-major batch sorted by length: M = T * rows_per_step rows, rows_per_step % 128 == 0;
- * 128-row tile b of timestep t is computed only if t < tile_steps_host[b] (HOST array, rows_per_step/128 entries);
- * the other rows of C are left untouched (the recurrent kernel never reads them).  tile_steps_host NULL = all rows. */
+/* Same GEMM over a ragged time-major batch sorted by length: M = T * rows_per_step rows (any rows_per_step <= 4096);
+ * batch tile b (rows [128 b, 128 b + 128) of a timestep) is live at timestep t if t < tile_steps_host[b] (HOST array,
+ * ceil(rows_per_step / 128) entries).  A 128-row block of C whose rows are all dead is not computed and left untouched
+ * (the recurrent kernel never reads dead rows); a block that straddles live and dead rows is computed whole.
+ * tile_steps_host NULL = all rows. */
 int rnnt_gemm_i8_i32_ragged(const int8_t* A, const int8_t* W, int32_t* C, int64_t M, int N, int K, int rows_per_step,
                             const int32_t* tile_steps_host, void* stream);
 /* Same product for N = 4096 = 4 gates x 1024 units, stored gate-blocked for rnnt_lstm_recurrent_i8_gate_blocked_ragged:
@@ -149,7 +151,7 @@ int rnnt_linear_bf16_bf16_ragged(const uint16_t* x, const uint16_t* w, uint16_t*
  * the fp32 accumulation inside the tensor core is not the oracle's (nor AMX's): results agree to <= 1 bf16 ulp (pinned
  * against AMX hardware output, tests/test_amx_golden.py).  K % 8 == 0, N % 64 == 0, 16-byte aligned pointers. */
 int rnnt_gemm_bf16_bf16(const uint16_t* A, const uint16_t* W, uint16_t* C, int64_t M, int N, int K, void* stream);
-/* Ragged variant (rows_per_step % 128 == 0, see rnnt_gemm_i8_i32_ragged): dead rows of C are left untouched. */
+/* Ragged variant (see rnnt_gemm_i8_i32_ragged): blocks of dead rows of C are left untouched. */
 int rnnt_gemm_bf16_bf16_ragged(const uint16_t* A, const uint16_t* W, uint16_t* C, int64_t M, int N, int K, int rows_per_step,
                                const int32_t* tile_steps_host, void* stream);
 

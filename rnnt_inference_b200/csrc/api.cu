@@ -93,9 +93,10 @@ inline int64_t round_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 static int make_skip(RowSkip* skip, int64_t M, int rows_per_step, const int32_t* tile_steps_host, int block_rows) {
   memset(skip, 0, sizeof *skip);
   if (!tile_steps_host) return RNNT_OK;
-  if (rows_per_step <= 0 || rows_per_step % block_rows != 0 || M % rows_per_step != 0 || rows_per_step > 32 * 128)
-    return fail(RNNT_ERR_INVALID, "ragged row skipping needs rows_per_step %% %d == 0, <= 4096 and M %% rows_per_step == 0 (M=%lld, rows_per_step=%d)",
-                block_rows, (long long)M, rows_per_step);
+  (void)block_rows;       // any rows_per_step: RowSkip::dead walks a block of rows that straddles tiles or timesteps
+  if (rows_per_step <= 0 || M % rows_per_step != 0 || rows_per_step > 32 * 128)
+    return fail(RNNT_ERR_INVALID, "ragged row skipping needs 0 < rows_per_step <= 4096 and M %% rows_per_step == 0 (M=%lld, rows_per_step=%d)",
+                (long long)M, rows_per_step);
   skip->rows_per_t = rows_per_step;
   for (int b = 0; b < (rows_per_step + 127) / 128; ++b) skip->steps[b] = tile_steps_host[b];
   return RNNT_OK;

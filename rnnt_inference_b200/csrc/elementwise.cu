@@ -158,7 +158,7 @@ linear_bf16_kernel(const uint16_t* __restrict__ x, const uint16_t* __restrict__ 
   __shared__ float ws[LB_TK][LB_TO + 4];
   const long long m0 = (long long)blockIdx.y * LB_TM;
   const int o0 = blockIdx.x * LB_TO;
-  if (skip.dead(m0)) return;
+  if (skip.dead(m0, LB_TM)) return;
   const int tm = (threadIdx.x >> 4) << 2;   // 0..60
   const int to = (threadIdx.x & 15) << 2;   // 0..60
   float acc[4][4];
@@ -246,7 +246,7 @@ linear_bf16_big_kernel(const uint16_t* __restrict__ x, const uint16_t* __restric
   __shared__ __align__(16) float ws[LBB_TK][LBB_T];
   const long long m0 = (long long)blockIdx.y * LBB_T;
   const int o0 = blockIdx.x * LBB_T;
-  if (skip.dead(m0)) return;
+  if (skip.dead(m0, LBB_T)) return;
   const int tm = (threadIdx.x >> 4) << 2;   // 0..60 (and + 64)
   const int to = (threadIdx.x & 15) << 2;   // 0..60 (and + 64)
   const int lrow = threadIdx.x >> 2;        // loader: rows lrow, lrow + 64; k octet lkq

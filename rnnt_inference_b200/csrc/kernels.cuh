@@ -17,13 +17,21 @@ namespace rnnt {
 
 // Ragged batches sorted by length: rows are (t, n) with rows_per_t = N rows per timestep; batch tile b = rows
 // [128 b, 128 b + 128) of every timestep is live for t < steps[b].  rows_per_t == 0 switches the test off.
+// dead(m0, rows): are ALL of the rows [m0, m0 + rows) dead?  Exact for any N: a block of rows that straddles batch
+// tiles or timesteps is walked segment by segment (all rows of a segment share (t, b)); rows past the matrix are dead.
 struct RowSkip {
   int rows_per_t;
   int steps[32];
-  __device__ __forceinline__ bool dead(long long m0) const {
+  __device__ __forceinline__ bool dead(long long m0, int rows = 128) const {
     if (rows_per_t == 0) return false;
-    const int t = (int)(m0 / rows_per_t), b = (int)(m0 % rows_per_t) >> 7;
-    return t >= steps[b];
+    const long long end = m0 + rows;
+    long long m = m0;
+    while (m < end) {
+      const int t = (int)(m / rows_per_t), n = (int)(m % rows_per_t), b = n >> 7;
+      if (t < steps[b]) return false;
+      m += min((b + 1) << 7, rows_per_t) - n;
+    }
+    return true;
   }
 };
 

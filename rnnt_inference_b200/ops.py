@@ -139,7 +139,7 @@ def lstm_layer_i8(x, hx, cx, w_ih, w_hh, bias, rb_scale, in_scale, out_scale, sk
     # that bench.py can time each kernel with CUDA events.  The projection scratch between them is gate-blocked
     # ([32 slices][4 gates][4 unit octets][T*N rows][8] int32): the rows a warp of the recurrent kernel reads are
     # contiguous there, 8 lines per load instead of 32 of the row-major [T*N][4096] result.
-    gemm_ts = ts_ptr if n % 128 == 0 else None     # dead (t, tile) rows of the projection are skipped as well
+    gemm_ts = ts_ptr                               # dead (t, tile) rows of the projection are skipped as well
     telemetry.bracket("gemm_i8", (t * n, k), lambda: L.check(
         L.lib.rnnt_gemm_i8_i32_gate_blocked_ragged(L.ptr(x), L.ptr(w_ih), L.ptr(g_ws), t * n, 4 * H, k, n, gemm_ts, st)))
     # telemetry units of the recurrent kernel: (TRUE (frame, utterance) pairs the layer has to process — tile padding and
@@ -183,7 +183,7 @@ def stack_time(x, lens, factor):
 
 def linear_bf16_bf16(x, w, tile_steps=None):
     """y = bf16(x . w^T) with the oracle's accumulation order (amx_linear.cpp:137-150, i16o16b0).  tile_steps (host int32
-    per 128-row tile of a time-major {T, N, K} input, N % 64 == 0): rows past a tile's last step are not computed."""
+    per 128-row tile of a time-major {T, N, K} input): blocks of rows past a tile's last step are not computed."""
     L.require_cuda(x, w)
     if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
         raise RuntimeError("linear_bf16_bf16 expects bfloat16")
@@ -193,7 +193,7 @@ def linear_bf16_bf16(x, w, tile_steps=None):
     y = torch.empty(x.shape[:-1] + (o,), dtype=torch.bfloat16, device=x.device)
     telemetry.launches += 1
     ts_ptr, rows = None, 0
-    if tile_steps is not None and x.dim() == 3 and x.shape[1] % 64 == 0:
+    if tile_steps is not None and x.dim() == 3:
         ts_ptr, rows = ctypes.c_void_p(tile_steps.ctypes.data), x.shape[1]
     telemetry.bracket("linear_bf16", (m, k, o), lambda: L.check(
         L.lib.rnnt_linear_bf16_bf16_ragged(L.ptr(x), L.ptr(w), L.ptr(y), m, k, o, rows, ts_ptr, L.stream_ptr())))
@@ -203,7 +203,7 @@ def linear_bf16_bf16(x, w, tile_steps=None):
 def gemm_bf16_bf16(x, w, tile_steps=None):
     """y = bf16(x . w^T) on the tensor cores (tcgen05 kind::f16, fp32 accumulation in TMEM): the hoisted transcription
     half of the joint fc1 (amx_linear.cpp:137-150).  Agrees with the order-defined linear_bf16_bf16 to <= 1 bf16 ulp.
-    tile_steps: as in linear_bf16_bf16 (time-major {T, N, K} input, N % 128 == 0)."""
+    tile_steps: as in linear_bf16_bf16 (time-major {T, N, K} input)."""
     L.require_cuda(x, w)
     if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
         raise RuntimeError("gemm_bf16_bf16 expects bfloat16")
@@ -215,7 +215,7 @@ def gemm_bf16_bf16(x, w, tile_steps=None):
     y = torch.empty(x.shape[:-1] + (o,), dtype=torch.bfloat16, device=x.device)
     telemetry.launches += 1
     ts_ptr, rows = None, 0
-    if tile_steps is not None and x.dim() == 3 and x.shape[1] % 128 == 0:
+    if tile_steps is not None and x.dim() == 3:
         ts_ptr, rows = ctypes.c_void_p(tile_steps.ctypes.data), x.shape[1]
     telemetry.bracket("gemm_bf16", (m, k, o), lambda: L.check(
         L.lib.rnnt_gemm_bf16_bf16_ragged(L.ptr(x), L.ptr(w), L.ptr(y), m, o, k, rows, ts_ptr, L.stream_ptr())))

@@ -10,8 +10,9 @@ PytorchSUT(model_path, dataset_dir, batch_size, run_mode, args) with the referen
 What changes underneath on the B200: the batch travels as the UNPADDED concatenation of its utterances (one async
 copy per pinned sample on a copy stream), padding/quantisation happen in one device kernel, and the Offline loop is
 software-pipelined — batch i+1 is staged while batch i computes and batch i-1 is answered, chunks running shortest
-first so that the one exposed copy is the smallest — so the GPU never waits for the host.  Results are identical to
-the synchronous order.
+first so that the one exposed copy is the smallest, and the short end of the query cut by frames so that the first
+chunk's compute covers the next chunk's copy (sharding.plan_chunks; head_fraction=0 restores the reference's plain
+batch_size chunks) — so the GPU never waits for the host.
 """
 import math
 import os
@@ -25,7 +26,7 @@ try:
 except ImportError:   # not installed offline
     from . import loadgen_shim as lg
 
-from . import _lib
+from . import _lib, sharding
 from .decoder import GreedyDecoder
 from .modeling_rnnt import RNNT
 from .rnnt_qsl import RNNTQSL
@@ -68,6 +69,9 @@ class PytorchSUT:
         self.h2d_bytes = 0          # running totals, read by bench.py
         self.d2h_bytes = 0
         self.batches_run = 0
+        # pipelined Offline path: share of the short end's frames that runs first (sharding.plan_chunks); 0 = plain chunks
+        self.head_fraction = float(kwargs.get("head_fraction", os.environ.get("RNNT_SUT_HEAD_FRACTION", 0.15)))
+        self.head_min_frames = int(kwargs.get("head_min_frames", 65536))
         if self.pipelined:
             dev = self.model.device
             self._copy_stream = torch.cuda.Stream(dev)
@@ -81,16 +85,23 @@ class PytorchSUT:
         if self.batch_sort:
             keys = self.qsl._keys
             samples.sort(key=lambda s: keys[s.index])
-        chunks = [samples[i:i + self.batch_size] for i in range(0, len(samples), self.batch_size)]
         if not self.pipelined:
+            chunks = [samples[i:i + self.batch_size] for i in range(0, len(samples), self.batch_size)]
             for chunk in chunks:
                 results, results_idx = self.inference([s.index for s in chunk])
                 self.query_samples_complete(chunk, results, results_idx)
             return
         # Shortest chunk first: its host->device copy (the only one nothing can hide) is the smallest, and every later,
-        # larger copy overlaps the previous chunk's compute.  Chunks are independent and each is answered whole, so the
-        # order in which they run changes no transcript (LoadGen accepts completions in any order).
-        chunks.reverse()
+        # larger copy overlaps the previous chunk's compute; sharding.plan_chunks sizes the first chunk so that its
+        # compute covers the next copy.  Chunks are independent and each is answered whole, so the order in which they
+        # run changes no transcript (LoadGen accepts completions in any order).
+        if self.batch_sort:
+            x_lens = self.qsl.x_lens_host
+            plan = sharding.plan_chunks([x_lens[s.index] for s in samples], self.batch_size, self.head_fraction,
+                                        self.head_min_frames)
+            chunks = [samples[lo:hi] for lo, hi in plan]
+        else:
+            chunks = [samples[i:i + self.batch_size] for i in range(0, len(samples), self.batch_size)][::-1]
         staged = self._stage(chunks[0]) if chunks else None
         in_flight = None
         for i in range(len(chunks)):

@@ -12,6 +12,45 @@ import torch
 import torch.distributed as dist
 
 
+def plan_chunks(lens_desc, batch_size, head_fraction=0.15, min_frames=65536):
+    """Chunks of one pipelined Offline query, as (lo, hi) ranges into the length-sorted (descending) sample list, in the
+    order they RUN (shortest first).
+
+    Plain chunking — the reference's `samples[i:i + batch_size]` (models/pytorch_sut.py:62), run back to front — leaves
+    one host->device copy that nothing hides: the copy of the first full batch behind the compute of the short
+    remainder (2513 utterances at batch 2048: 9 ms of copy behind 4 ms of compute).  Copying a frame costs about a
+    quarter of computing it, so the short end of the query — the remainder plus the last full batch — is cut instead
+    where the head (run first; its own copy is the exposed one) holds `head_fraction` of that region's frames: its
+    compute then covers the copy of the rest of the region, and every later full batch is covered by its predecessor
+    (measured on B200, 2513 utterances: 53.1 K utterances/s end to end with plain chunks, 56.0 K for 0.12 - 0.18, 53.5 K
+    at 0.25 where the smaller batches cost more device time than the copy they hide).
+    Regions with fewer than `min_frames` frames (copy under a millisecond) and head_fraction <= 0 keep the plain chunks.
+    Chunks are independent, so the plan changes no transcript except through the reference's batch-scoped quirk (a lane
+    capped on its last frame emits until its batch's loop ends), exactly as the choice of batch_size does."""
+    n = len(lens_desc)
+    if n == 0:
+        return []
+    plain = [(i, min(i + batch_size, n)) for i in range(0, n, batch_size)][::-1]
+    if head_fraction <= 0 or n < 2:
+        return plain
+    rem = n % batch_size
+    region = rem + batch_size if n > batch_size else n          # the shortest `region` samples: [n - region, n)
+    if rem == 0 and n >= batch_size:
+        region = batch_size
+    lo = n - region
+    frames = np.asarray(lens_desc[lo:], dtype=np.int64)
+    total = int(frames.sum())
+    if total < min_frames:
+        return plain
+    # head = the shortest samples whose frames reach head_fraction of the region; both parts within batch_size
+    tail_cum = np.cumsum(frames[::-1])
+    k = int(np.searchsorted(tail_cum, head_fraction * total)) + 1
+    k = max(k, region - batch_size, 1)
+    k = min(k, batch_size, region - 1)
+    full = [(i, i + batch_size) for i in range(0, lo, batch_size)][::-1]
+    return [(n - k, n), (lo, n - k)] + full
+
+
 def shard_batches(lengths, batch_size, world=1, rank=0):
     """lengths: per-sample feature lengths of the WHOLE query.  Returns this rank's batches, each a list of
     (sample_index, length), in the order they are to be run (longest first)."""

@@ -554,3 +554,36 @@ def test_gemm_i8_clusters(ops, cm):
     finally:
         _lib.lib.rnnt_tune_gemm_cluster(1)
         _lib.lib.rnnt_tune_gemm_pair(1)
+
+
+
+@pytest.mark.parametrize("rows", [1000, 96, 1696])
+def test_gemm_i8_ragged_any_batch_width(ops, rows):
+    """Ragged row skipping when the batch width is not a multiple of the 128-row GEMM tile (m tiles straddle batch tiles
+    and timesteps): every live row exact, and whole blocks of dead rows really are skipped."""
+    import ctypes
+    from rnnt_inference_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(rows)
+    t, n, k = 9, 4096, 256
+    nb = (rows + 127) // 128
+    steps = np.maximum(0, t - np.arange(nb) * 2).astype(np.int32)          # 9, 7, 5, ... sorted like a ragged batch
+    a = torch.randint(-128, 128, (t * rows, k), dtype=torch.int8, device="cuda", generator=g)
+    w = torch.randint(-128, 128, (n, k), dtype=torch.int8, device="cuda", generator=g)
+    c = torch.full((t * rows, n), 123456789, dtype=torch.int32, device="cuda")
+    _lib.check(_lib.lib.rnnt_gemm_i8_i32_ragged(_lib.ptr(a), _lib.ptr(w), _lib.ptr(c), t * rows, n, k, rows,
+                                                ctypes.c_void_p(steps.ctypes.data), _lib.stream_ptr()))
+    ref = ops.gemm_i8_i32(a, w, simt=True)
+    _lib.check_device_status()
+    live = torch.from_numpy((np.arange(t)[:, None] < steps[np.arange(rows) // 128][None, :]).reshape(-1)).cuda()
+    assert torch.equal(c[live], ref[live])
+    untouched = (c == 123456789).all(dim=1)
+    assert not bool((untouched & live).any())
+    if nb > 1:
+        assert int(untouched.sum()) >= 128                               # some all-dead block was skipped
+    # the hoisted joint GEMM (bf16) shares the skip logic
+    x = torch.randn((t * rows, 64), device="cuda", generator=g).to(torch.bfloat16)
+    wb = torch.randn((512, 64), device="cuda", generator=g).to(torch.bfloat16)
+    full = ops.gemm_bf16_bf16(x, wb)
+    part = ops.gemm_bf16_bf16(x.view(t, rows, 64), wb, tile_steps=steps).view(t * rows, 512)
+    _lib.check_device_status()
+    assert torch.equal(part[live], full[live])

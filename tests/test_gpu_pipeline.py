@@ -181,6 +181,34 @@ def test_sut_offline_query_vs_oracle(setup):
             np.testing.assert_array_equal(got[i], o_res[j, :o_len[j]])
 
 
+def test_sut_offline_head_split_vs_oracle(setup):
+    """The pipelined Offline path with the short end of the query cut by frames (sharding.plan_chunks, forced on for this
+    tiny query): every sample answered once, bytes equal to the oracle's in the planner's batches."""
+    from rnnt_inference_b200 import loadgen_shim as lg
+    from rnnt_inference_b200 import sharding
+    from rnnt_inference_b200.pytorch_sut import PytorchSUT
+    sd, _rnnt, params, _ = setup
+    lens = [25, 7, 31, 18, 12, 31, 3, 22, 9, 16, 28, 5, 14]
+    feats = [S.make_features(n, 700 + i) for i, n in enumerate(lens)]
+    data = {"x": feats, "x_lens": [torch.tensor(n) for n in lens]}
+    sut = PytorchSUT(sd, data, 8, "quant", None, enable_bf16=True, scenario="Offline", exact_order=True, head_fraction=0.3,
+                     head_min_frames=0)
+    settings = lg.TestSettings()
+    settings.scenario = lg.TestScenario.Offline
+    settings.mode = lg.TestMode.AccuracyOnly
+    out = lg.StartTest(sut.sut, sut.qsl.qsl, settings)
+    assert out["completed"] == len(lens)
+    got = {e["qsl_idx"]: np.frombuffer(bytes.fromhex(e["data"]), np.int32) for e in out["accuracy_log"]}
+    order = sorted(range(len(lens)), key=lambda i: -lens[i])
+    plan = sharding.plan_chunks([lens[i] for i in order], 8, 0.3, 0)
+    assert len(plan) == 2 and plan != [(8, 13), (0, 8)]                  # the short end really was cut by frames
+    for lo, hi in plan:
+        idx = order[lo:hi]
+        o_res, o_len, _ = _oracle(params, [feats[i] for i in idx], pad_to=32)
+        for j, i in enumerate(idx):
+            np.testing.assert_array_equal(got[i], o_res[j, :o_len[j]])
+
+
 def test_sut_default_path_and_sync_inference(setup):
     """The SUT as a user runs it (tensor-core hoist): the pipelined Offline path and the synchronous
     inference() + query_samples_complete() path of the reference (pytorch_sut.py:67-118) give the same bytes, and

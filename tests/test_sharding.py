@@ -121,3 +121,27 @@ def test_distributed_offline_front_world2(tmp_path):
             ls = [lengths[i] for i in sh]
             assert ls == sorted(ls, reverse=True)                                                   # each share longest first
         assert abs(len(shares[0]) - len(shares[1])) <= 1
+
+
+def test_plan_chunks_covers_the_query_and_respects_the_batch_size():
+    """The pipelined SUT's chunk plan: every sample exactly once, no chunk above batch_size, shortest chunk first, plain
+    chunks when the short end is too small to matter, head of the short end = the requested share of its frames."""
+    rng = np.random.default_rng(5)
+    for n, bs in ((1, 4), (2, 4), (3, 2), (10, 4), (2513, 2048), (4096, 2048), (24576, 2048), (5000, 1024)):
+        lens = np.sort(rng.integers(1, 500, n))[::-1]
+        for hf, mf in ((0.0, 0), (0.2, 0), (0.2, 65536), (0.5, 0)):
+            plan = sharding.plan_chunks(list(lens), bs, hf, mf)
+            seen = np.zeros(n, np.int32)
+            for lo, hi in plan:
+                assert 0 <= lo < hi <= n and hi - lo <= bs
+                seen[lo:hi] += 1
+            assert (seen == 1).all()
+            assert plan[0][1] == n                                   # the shortest samples run first
+            if hf == 0.0:
+                assert plan == [(i, min(i + bs, n)) for i in range(0, n, bs)][::-1]
+    lens = np.sort(rng.integers(50, 500, 2513))[::-1]
+    plan = sharding.plan_chunks(list(lens), 2048, 0.2, 0)
+    assert len(plan) == 2
+    head = lens[plan[0][0]:plan[0][1]].sum() / lens.sum()
+    assert 0.2 <= head < 0.21
+    assert sharding.plan_chunks([30, 20, 10], 4, 0.2, 65536) == [(0, 3)]      # tiny query: plain
