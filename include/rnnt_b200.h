@@ -128,6 +128,28 @@ int rnnt_tune_gemm_cluster(int ctas);
  * least two m tiles and N % 256 == 0), or the environment variable RNNT_GEMM_PAIR=0 / 1. */
 int rnnt_tune_gemm_pair(int on);
 
+/* ---- audio front-end: the step before the hot path, datasets/parts/features.py:186-252.  fp32 throughout.
+ * preemphasis (init.cpp: preemphasis; preemphasis.cpp:10-46): x [N][L], lens [N] (device int32) -> out [N][L + 2 pad]:
+ * y[i] = x[i] - coeff * x[i-1] for i < len, reflect-padded by `pad` on both sides, zeros behind. */
+int rnnt_preemphasis_f32(const float* x, const int32_t* lens, float coeff, int pad, float* out, int N, int L, void* stream);
+/* power_spectrum (power_spectrum.cpp:10-33): x [N][T][F][2] (re, im) -> out [N][T][F] = re^2 + im^2, frames >= lens[n] zero. */
+int rnnt_power_spectrum_f32(const float* x, const int32_t* lens, float* out, int N, int T, int F, void* stream);
+/* frame_splicing (frame_splicing.cpp:12-45): x [N][C][T] -> out [N][C * factor][ceil(T / factor)],
+ * out[n][k*C + c][j] = x[n][c][factor*j + k] if that frame is < lens[n], else 0. */
+int rnnt_frame_splicing_f32(const float* x, const int32_t* lens, float* out, int N, int C, int T, int factor, void* stream);
+/* i_layernorm_pad (normalization.cpp:10-64; i_layernorm_tpp.cpp:10-76): per (sample, feature) over the lens[n] valid frames:
+ * var = E[x^2] - mean^2 + eps (times len/(len-1) if unbiased), y = (x - mean) / sqrt(var) * w + b; weight / bias [C][T] or
+ * NULL (1 / 0).  out [n_pad][c_out][t_out]; everything the reference leaves unwritten (padding samples, features >= C,
+ * frames >= len) is zero here. */
+int rnnt_layernorm_pad_f32(const float* x, const int32_t* lens, const float* weight, const float* bias, float* out, int N, int C,
+                           int T, int n_pad, int c_out, int t_out, float eps, int unbiased, void* stream);
+/* torch.stft(n_fft 512, hop, window win_len centred in n_fft, center=False) + power_spectrum + dither^2 + mel filterbank +
+ * log of features.py:201-227 in one kernel (the reference calls torch.stft, a library FFT, between its operators).
+ * y [N][Lp] pre-emphasised, padded waveforms; frame_lens [N] (frames, device int32); window [win_len]; fb [n_mels][257];
+ * out [N][n_mels][T] = log(fb . (|STFT|^2 masked past frame_lens + dither2) + log_bias).  n_fft must be 512, n_mels <= 96. */
+int rnnt_logmel_f32(const float* y, const int32_t* frame_lens, const float* window, const float* fb, float* out, int N, int Lp,
+                    int T, int n_fft, int hop, int win_len, int n_mels, float dither2, float log_bias, void* stream);
+
 /* lstm_layer_amx_int8 (lstm_amx.cpp:59-158; schema init.cpp:129-131) = projection GEMM + recurrent kernel.
  * x [T][N][K] int8 (K % 16 == 0).  g_ws: T*N*4H int32 scratch for the projection. */
 int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* w_ih, const int8_t* w_hh,

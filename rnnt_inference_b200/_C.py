@@ -151,3 +151,41 @@ def lstm(x: Tensor, hx: List[Tensor], cx: List[Tensor], all_weights: List[List[T
     return x, hy, cy
 quantize_ragged = ops.quantize_ragged
 tile_steps_for = ops.tile_steps_for
+
+
+# ------------------------------------------------------------------------------------------------ audio front-end operators
+def preemphasis(input: Tensor, length: Tensor, coeff=0.97, pad_size=0) -> Tensor:
+    """intel_mlperf::preemphasis (preemphasis.cpp:10-46)."""
+    return ops.preemphasis(input, length, coeff, pad_size)
+
+
+def power_spectrum(input: Tensor, length: Tensor) -> Tensor:
+    """intel_mlperf::power_spectrum (power_spectrum.cpp:10-33)."""
+    return ops.power_spectrum(input, length)
+
+
+def frame_splicing(input: Tensor, length: Tensor, factor) -> Tensor:
+    """intel_mlperf::frame_splicing (frame_splicing.cpp:12-45); like the reference, factor 3 only."""
+    if int(factor) != 3:
+        raise RuntimeError("Unsupported frame splicing factor.")
+    return ops.frame_splicing(input, length, 3)
+
+
+def i_layernorm_pad(input: Tensor, weight, bias, length: Tensor, eps=1e-12, unbiased=False, output_shape=None):
+    """intel_mlperf::i_layernorm_pad (normalization.cpp:10-64): returns (output [padded_batch, out_feat, max(length)], length
+    padded with zeros to padded_batch).  weight / bias [1, C, T'] or None."""
+    n, c, _t = input.shape
+    n_pad, c_out = n, c
+    out_len = length
+    if output_shape is not None:
+        n_pad, c_out = int(output_shape[0]), int(output_shape[1])
+        if n_pad == 1:
+            n_pad = n
+        else:
+            out_len = torch.nn.functional.pad(length, (0, n_pad - n), "constant", 0)
+    w = b = None
+    if weight is not None and not bool((weight == 1).all()):
+        w = weight[0, :c, :input.shape[2]].to(input.device).contiguous()
+    if bias is not None and not bool((bias == 0).all()):
+        b = bias[0, :c, :input.shape[2]].to(input.device).contiguous()
+    return ops.layernorm_pad(input, length, eps, unbiased, n_pad, c_out, None, w, b), out_len

@@ -49,6 +49,11 @@ _SIGS = {
     "rnnt_lstm_recurrent_i8_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_lstm_recurrent_i8_gate_blocked_ragged": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "rnnt_tune_recurrent_cluster": (_i, [_i]),
+    "rnnt_preemphasis_f32": (_i, [_vp, _vp, _f, _i, _vp, _i, _i, _vp]),
+    "rnnt_power_spectrum_f32": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "rnnt_frame_splicing_f32": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "rnnt_layernorm_pad_f32": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "rnnt_logmel_f32": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp]),
     "rnnt_tune_gemm_cluster": (_i, [_i]),
     "rnnt_tune_gemm_pair": (_i, [_i]),
     "rnnt_lstm_layer_i8": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),

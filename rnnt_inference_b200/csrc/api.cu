@@ -13,6 +13,7 @@
 #include "../../include/rnnt_b200_debug.h"
 #endif
 #include "kernels.cuh"
+#include "api_internal.h"
 
 using namespace rnnt;
 
@@ -88,6 +89,16 @@ inline bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_
 inline int64_t round_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
 }  // namespace
+
+namespace rnnt {
+int api_fail(int code, const char* fmt, ...) {      // api_internal.h: for frontend.cu
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+}  // namespace rnnt
 
 // RowSkip for a ragged batch: rows_per_step rows per timestep, tile_steps_host[b] live steps of 128-row tile b (NULL = all live)
 static int make_skip(RowSkip* skip, int64_t M, int rows_per_step, const int32_t* tile_steps_host, int block_rows) {

@@ -350,3 +350,72 @@ def greedy_decode_update(symbols, symbols_added, res, res_idx, f, f_lens, time_i
                                             L.ptr(pre_hg[1]), L.ptr(pre_cg[0]), L.ptr(pre_cg[1]), L.ptr(hg[0]), L.ptr(hg[1]),
                                             L.ptr(cg[0]), L.ptr(cg[1]), n, l, c, p, L.ptr(flag), L.stream_ptr()))
     return int(flag[:4].view(torch.int32).item()) == 0
+
+
+# ------------------------------------------------------------------------------------------------ audio front-end
+def _i32(lens, device):
+    return lens.to(device=device, dtype=torch.int32).contiguous()
+
+
+def preemphasis(x, lens, coeff=0.97, pad_size=0):
+    """preemphasis.cpp:10-46: x fp32 [N, L] -> [N, L + 2 pad] (y = x[i] - coeff x[i-1], reflect padding, zeros behind)."""
+    L.require_cuda(x)
+    x = x.contiguous()
+    n, l = x.shape
+    out = torch.empty((n, l + 2 * int(pad_size)), dtype=torch.float32, device=x.device)
+    L.check(L.lib.rnnt_preemphasis_f32(L.ptr(x), L.ptr(_i32(lens, x.device)), float(coeff), int(pad_size), L.ptr(out), n, l,
+                                       L.stream_ptr()))
+    return out
+
+
+def power_spectrum(x, lens):
+    """power_spectrum.cpp:10-33: x fp32 [N, T, F, 2] -> [N, T, F]."""
+    L.require_cuda(x)
+    x = x.contiguous()
+    n, t, f, _ = x.shape
+    out = torch.empty((n, t, f), dtype=torch.float32, device=x.device)
+    L.check(L.lib.rnnt_power_spectrum_f32(L.ptr(x), L.ptr(_i32(lens, x.device)), L.ptr(out), n, t, f, L.stream_ptr()))
+    return out
+
+
+def frame_splicing(x, lens, factor):
+    """frame_splicing.cpp:12-45: x fp32 [N, C, T] -> [N, C * factor, ceil(T / factor)]."""
+    L.require_cuda(x)
+    x = x.contiguous()
+    n, c, t = x.shape
+    factor = int(factor)
+    out = torch.empty((n, c * factor, (t + factor - 1) // factor), dtype=torch.float32, device=x.device)
+    L.check(L.lib.rnnt_frame_splicing_f32(L.ptr(x), L.ptr(_i32(lens, x.device)), L.ptr(out), n, c, t, factor, L.stream_ptr()))
+    return out
+
+
+def layernorm_pad(x, lens, eps=1e-12, unbiased=True, n_pad=None, c_out=None, t_out=None, weight=None, bias=None):
+    """normalization.cpp:10-64 on fp32 [N, C, T]: out [n_pad, c_out, t_out] (t_out defaults to max(lens))."""
+    L.require_cuda(x)
+    x = x.contiguous()
+    n, c, t = x.shape
+    lens = _i32(lens, x.device)
+    n_pad = n if n_pad is None else int(n_pad)
+    c_out = c if c_out is None else int(c_out)
+    t_out = int(lens.max().item()) if t_out is None else int(t_out)
+    out = torch.empty((n_pad, c_out, max(t_out, 1)), dtype=torch.float32, device=x.device)
+    L.check(L.lib.rnnt_layernorm_pad_f32(L.ptr(x), L.ptr(lens), L.ptr(weight) if weight is not None else None,
+                                         L.ptr(bias) if bias is not None else None, L.ptr(out), n, c, t, n_pad, c_out, max(t_out, 1),
+                                         float(eps), int(bool(unbiased)), L.stream_ptr()))
+    return out
+
+
+def logmel(y, frame_lens, window, fb, n_fft, hop, dither2, log_bias):
+    """STFT + power spectrum + dither^2 + mel + log of features.py:201-227 in one kernel.  y fp32 [N, Lp] (pre-emphasised and
+    padded), frame_lens [N], window [win_length], fb [n_mels, n_fft / 2 + 1] -> [N, n_mels, T], T = 1 + (Lp - n_fft) // hop."""
+    L.require_cuda(y, window, fb)
+    y = y.contiguous()
+    n, lp = y.shape
+    t = 1 + (lp - n_fft) // hop
+    n_mels = fb.shape[0]
+    out = torch.empty((n, n_mels, t), dtype=torch.float32, device=y.device)
+    L.check(L.lib.rnnt_logmel_f32(L.ptr(y), L.ptr(_i32(frame_lens, y.device)), L.ptr(window.contiguous()), L.ptr(fb.contiguous()),
+                                  L.ptr(out), n, lp, t, int(n_fft), int(hop), int(window.numel()), int(n_mels), float(dither2),
+                                  float(log_bias), L.stream_ptr()))
+    telemetry.launches += 1
+    return out

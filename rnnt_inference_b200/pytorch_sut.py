@@ -49,11 +49,18 @@ class PytorchSUT:
             merged.update({k: v for k, v in vars(args).items()})
         merged.update(kwargs)
         args = SimpleNamespace(**merged)
-        if args.enable_process:
-            raise RuntimeError("the audio front-end (--enable_process) is outside this package's scope: feed pre-extracted "
-                               "240-dim stacked filterbank features, as launch_sut.sh does without --processor")
         self.processor = None
-        self.enable_process = False
+        if args.enable_process:
+            # pytorch_sut.py:24-35: the featurizer in front of the model, configured by [input_eval] of the toml file (the
+            # MLPerf RNN-T values when no file is given); the samples of the QSL are then 1-D waveforms
+            from .features import AudioProcessing, MLPERF_INPUT_EVAL
+            cfg = dict(MLPERF_INPUT_EVAL)
+            if args.toml_path and os.path.exists(args.toml_path):
+                import tomllib
+                with open(args.toml_path, "rb") as fh:
+                    cfg = tomllib.load(fh)["input_eval"]
+            self.processor = AudioProcessing(run_mode, pad_batch_size=True, **cfg).eval()
+        self.enable_process = self.processor is not None
         self.batch_size = batch_size
         self.run_mode = run_mode
         self.device = kwargs.get("device")
@@ -62,7 +69,7 @@ class PytorchSUT:
                                    exact_order=args.exact_order)
         self.scenario = args.scenario if run_mode != "calib" else None
         self.batch_sort = self.scenario == "Offline"
-        self.pipelined = run_mode == "quant" and args.split_len == -1
+        self.pipelined = run_mode == "quant" and args.split_len == -1 and not self.enable_process
         self.qsl = RNNTQSL(dataset_dir, preload=kwargs.get("preload", True))
         self.sut = lg.ConstructSUT(self.issue_queries, self.flush_queries)
         self.response_hook = None   # callable(samples, tokens, counts) replacing lg.QuerySamplesComplete
@@ -241,6 +248,8 @@ class PytorchSUT:
         """pytorch_sut.py:67-105: returns (res {N_padded, L}, res_len {N_padded}) for the given sample indices."""
         batch_idx = list(batch_idx)
         self.actual_batch_size = len(batch_idx)
+        if self.enable_process:
+            return self._inference_from_waveforms(batch_idx)
         with torch.no_grad():
             feas = torch.nn.utils.rnn.pad_sequence([self.qsl[i][0] for i in batch_idx])          # {T, N, 240}
             fea_lens = torch.tensor([int(self.qsl[i][1]) for i in batch_idx], dtype=torch.int64)
@@ -251,6 +260,23 @@ class PytorchSUT:
             self.h2d_bytes += feas.numel() * 4 + fea_lens.numel() * 8
             results = self.model(feas, fea_lens)
             _lib.check_device_status()          # synchronises; raises instead of returning garbage transcripts
+        self.batches_run += 1
+        return results
+
+    def _inference_from_waveforms(self, batch_idx):
+        """pytorch_sut.py:70-82: waveforms -> features on the GPU (features.AudioProcessing) -> {T, N, C} -> decoder."""
+        dev = self.model.device
+        if next(self.processor.buffers()).device != dev:
+            self.processor.to(dev)
+        with torch.no_grad():
+            wavs = torch.nn.utils.rnn.pad_sequence([self.qsl[i][0] for i in batch_idx], batch_first=True)
+            wav_lens = torch.tensor([int(self.qsl[i][1]) for i in batch_idx])
+            self.h2d_bytes += wavs.numel() * 4 + wav_lens.numel() * 8
+            feas, fea_lens = self.processor(wavs.to(dev, non_blocking=True), wav_lens.to(torch.int32),
+                                            pad_batch_size=(self.scenario == "Offline"))
+            feas = feas.permute(2, 0, 1).contiguous()                                             # {N, C, T} -> {T, N, C}
+            results = self.model(feas, fea_lens)
+            _lib.check_device_status()
         self.batches_run += 1
         return results
 

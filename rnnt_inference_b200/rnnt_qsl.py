@@ -58,8 +58,9 @@ class RNNTQSL:
         outside LoadGen's timed region (LoadSamplesToRam)."""
         ids = sorted(self.sample_id_to_sample, key=self._keys.__getitem__)
         rows = [self.rows[i] for i in ids]
-        width = int(self.dataset[0][ids[0]].shape[1])
-        arena = torch.empty((sum(rows), width), dtype=torch.float32, pin_memory=True)
+        first = self.dataset[0][ids[0]]
+        shape = (sum(rows),) if first.dim() == 1 else (sum(rows), int(first.shape[1]))     # 1-D: waveforms (--enable_process)
+        arena = torch.empty(shape, dtype=torch.float32, pin_memory=True)
         off = 0
         for i, n in zip(ids, rows):
             arena[off:off + n].copy_(self.dataset[0][i][:n])
