@@ -10,8 +10,8 @@
 //   frame_splicing_kernel   [N, C, T] -> [N, 3C, ceil(T/3)] (frame_splicing.cpp:12-45)
 //   layernorm_pad_kernel    per-(sample, feature) normalisation over time with unbiased variance, output padded in batch
 //                           and features (normalization.cpp:10-64, i_layernorm_tpp.cpp:10-76)
-// All of it is HBM-bound byte shuffling except the FFT + mel product (about 25 K FMA per frame on CUDA cores; fp32 like the
-// reference).  Floating point: tolerances are stated in tests/test_frontend.py.
+// All of it is HBM-bound byte shuffling except the FFT (about 12 K flop per frame on CUDA cores; fp32 like the reference); the
+// mel product only visits the non-zero span of each triangular filter (~520 FMA per frame instead of 80 x 257).  Floating point: tolerances are stated in tests/test_frontend.py.
 #include <algorithm>
 
 #include "kernels.cuh"
@@ -95,36 +95,57 @@ __global__ void layernorm_pad_kernel(const float* __restrict__ x, const int32_t*
 // ---------------------------------------------------------------------------------------------- STFT + power + mel + log
 constexpr int FE_NFFT = 512, FE_BINS = 257, FE_WARPS = 8, FE_TF = 8;     // frames per warp task (one 32-byte sector per output row)
 constexpr int FE_MAX_MELS = 96;
+constexpr int FE_MAXW = 64;                                              // widest filter (bins) kept in shared memory
 
 struct LogmelSmem {
-  static constexpr int FB_PITCH = FE_MAX_MELS;                           // fb transposed: [bin][mel], lanes read consecutive mels
-  static constexpr int FB_BYTES = FE_BINS * FB_PITCH * 4;                // 98,688
+  static constexpr int FB_PITCH = FE_MAXW + 1;                           // [mel][bin - first bin of the mel], odd pitch: no conflicts
+  static constexpr int FB_BYTES = FE_MAX_MELS * FB_PITCH * 4;            // 24,960
+  static constexpr int RANGE_BYTES = FE_MAX_MELS * 8;                    // (first bin, bins) per mel
+  static constexpr int CONST_BYTES = FE_MAX_MELS * 4;                    // log-mel of a frame past the utterance (power = 0)
   static constexpr int TW_BYTES = FE_BINS * 8;                           // exp(-2 pi i k / 512), k = 0..256
   static constexpr int WIN_BYTES = FE_NFFT * 4;                          // window zero-padded to n_fft
+  static constexpr int SHARED_BYTES = FB_BYTES + RANGE_BYTES + CONST_BYTES + TW_BYTES + WIN_BYTES;
   static constexpr int WARP_BYTES = (256 * 2 + FE_BINS + 3) * 4 + FE_MAX_MELS * FE_TF * 4;   // z re | z im | power | staged output
-  static constexpr int TOTAL = FB_BYTES + TW_BYTES + WIN_BYTES + FE_WARPS * WARP_BYTES + 64;
+  static constexpr int TOTAL = SHARED_BYTES + FE_WARPS * WARP_BYTES + 64;                    // 79,584: two blocks per SM
 };
+static_assert(LogmelSmem::SHARED_BYTES % 8 == 0 && LogmelSmem::FB_BYTES % 8 == 0, "float2 tables are 8-byte aligned");
 
 __device__ __forceinline__ int bitrev8(int v) { return (int)(__brev((unsigned)v) >> 24); }
 
-__global__ void __launch_bounds__(FE_WARPS * 32)
+// mel m of one frame: sum over the filter's bins in ascending order (= the dense product without its exact zeros)
+__device__ __forceinline__ float mel_dot(const float* w, const float* pw, int first, int bins) {
+  float acc = 0.f;
+  for (int i = 0; i < bins; ++i) acc = fmaf(w[i], pw[first + i], acc);
+  return acc;
+}
+
+__global__ void __launch_bounds__(FE_WARPS * 32, 2)
 logmel_kernel(const float* __restrict__ y, const int32_t* __restrict__ frame_lens, const float* __restrict__ window,
               const float* __restrict__ fb, float* __restrict__ out, int N, int Lp, int T, int hop, int win_len, int n_mels,
               float dither2, float log_bias) {
   extern __shared__ __align__(16) uint8_t fe_smem[];
-  float* fbt = reinterpret_cast<float*>(fe_smem);
-  float2* tw = reinterpret_cast<float2*>(fe_smem + LogmelSmem::FB_BYTES);
-  float* win = reinterpret_cast<float*>(fe_smem + LogmelSmem::FB_BYTES + LogmelSmem::TW_BYTES);
+  float* fbs = reinterpret_cast<float*>(fe_smem);
+  int2* range = reinterpret_cast<int2*>(fe_smem + LogmelSmem::FB_BYTES);
+  float* cst = reinterpret_cast<float*>(fe_smem + LogmelSmem::FB_BYTES + LogmelSmem::RANGE_BYTES);
+  float2* tw = reinterpret_cast<float2*>(fe_smem + LogmelSmem::FB_BYTES + LogmelSmem::RANGE_BYTES + LogmelSmem::CONST_BYTES);
+  float* win = reinterpret_cast<float*>(fe_smem + LogmelSmem::SHARED_BYTES - LogmelSmem::WIN_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* zr = reinterpret_cast<float*>(fe_smem + LogmelSmem::FB_BYTES + LogmelSmem::TW_BYTES + LogmelSmem::WIN_BYTES +
-                                       warp * LogmelSmem::WARP_BYTES);
+  float* zr = reinterpret_cast<float*>(fe_smem + LogmelSmem::SHARED_BYTES + warp * LogmelSmem::WARP_BYTES);
   float* zi = zr + 256;
   float* pw = zi + 256;
   float* stage = pw + FE_BINS + 3;
 
-  for (int e = threadIdx.x; e < FE_BINS * LogmelSmem::FB_PITCH; e += blockDim.x) {
-    const int k = e / LogmelSmem::FB_PITCH, m = e % LogmelSmem::FB_PITCH;
-    fbt[e] = m < n_mels ? fb[(size_t)m * FE_BINS + k] : 0.f;
+  // ---- per block: the non-zero span of every mel filter (triangles: 2 .. ~20 bins), its weights, twiddles, window
+  for (int m = threadIdx.x; m < FE_MAX_MELS; m += blockDim.x) {
+    int first = 0, last = -1;
+    if (m < n_mels) {
+      const float* row = fb + (size_t)m * FE_BINS;
+      first = FE_BINS;
+      for (int k = 0; k < FE_BINS; ++k)
+        if (row[k] != 0.f) { if (first == FE_BINS) first = k; last = k; }
+      if (last < 0) first = 0;
+    }
+    range[m] = make_int2(first, last - first + 1);
   }
   for (int k = threadIdx.x; k < FE_BINS; k += blockDim.x) {
     float s, c;
@@ -133,6 +154,19 @@ logmel_kernel(const float* __restrict__ y, const int32_t* __restrict__ frame_len
   }
   const int left = (FE_NFFT - win_len) / 2;                   // torch.stft centres a short window inside n_fft
   for (int j = threadIdx.x; j < FE_NFFT; j += blockDim.x) win[j] = (j >= left && j < left + win_len) ? window[j - left] : 0.f;
+  __syncthreads();
+  for (int e = threadIdx.x; e < FE_MAX_MELS * FE_MAXW; e += blockDim.x) {
+    const int m = e / FE_MAXW, i = e % FE_MAXW;
+    const int2 r = range[m];
+    fbs[m * LogmelSmem::FB_PITCH + i] = (m < n_mels && i < r.y && r.y <= FE_MAXW) ? fb[(size_t)m * FE_BINS + r.x + i] : 0.f;
+  }
+  __syncthreads();
+  // a filter wider than FE_MAXW bins (not a mel triangle at these sizes) is read from global memory instead
+  auto weights = [&](int m, int2 r) { return r.y <= FE_MAXW ? fbs + m * LogmelSmem::FB_PITCH : fb + (size_t)m * FE_BINS + r.x; };
+  for (int k = lane; k < FE_BINS; k += 32) pw[k] = dither2;    // a frame past the utterance: power_spectrum zeroed it, + dither^2
+  __syncwarp();
+  if (warp == 0)
+    for (int m = lane; m < n_mels; m += 32) { const int2 r = range[m]; cst[m] = logf(mel_dot(weights(m, r), pw, r.x, r.y) + log_bias); }
   __syncthreads();
 
   const int groups = (T + FE_TF - 1) / FE_TF;
@@ -144,65 +178,61 @@ logmel_kernel(const float* __restrict__ y, const int32_t* __restrict__ frame_len
     for (int ft = 0; ft < FE_TF; ++ft) {
       const int t = t0 + ft;
       if (t >= T) break;
-      if (t < flen) {
-        // ---- windowed frame as 256 complex points z[m] = s[2m] + i s[2m+1], stored bit-reversed
-        const float* fr = yr + (size_t)t * hop;
-        for (int m = lane; m < 256; m += 32) {
-          const int j = 2 * m;
-          float a = 0.f, b = 0.f;
-          if (j + 1 >= left && j < left + win_len) {
-            const float2 wv = *reinterpret_cast<const float2*>(win + j);
-            a = fr[j] * wv.x; b = fr[j + 1] * wv.y;
-          }
-          const int r = bitrev8(m);
-          zr[r] = a; zi[r] = b;
+      if (t >= flen) {
+        for (int m = lane; m < n_mels; m += 32) stage[m * FE_TF + ft] = cst[m];
+        continue;
+      }
+      // ---- windowed frame as 256 complex points z[m] = s[2m] + i s[2m+1], stored bit-reversed
+      const float* fr = yr + (size_t)t * hop;
+      for (int m = lane; m < 256; m += 32) {
+        const int j = 2 * m;
+        float a = 0.f, b = 0.f;
+        if (j + 1 >= left && j < left + win_len) {
+          const float2 wv = *reinterpret_cast<const float2*>(win + j);
+          a = fr[j] * wv.x; b = fr[j + 1] * wv.y;
+        }
+        const int r = bitrev8(m);
+        zr[r] = a; zi[r] = b;
+      }
+      __syncwarp();
+      // ---- 256-point radix-2 FFT (decimation in time), 128 butterflies per stage
+#pragma unroll 1
+      for (int half = 1; half < 256; half <<= 1) {
+        const int tstep = 256 / half;                         // twiddle exp(-2 pi i pos / (2 half)) = tw[pos * 256 / half]
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int b = lane + 32 * q;
+          const int pos = b & (half - 1);
+          const int i0 = ((b - pos) << 1) + pos, i1 = i0 + half;
+          const float2 w = tw[pos * tstep];
+          const float xr = zr[i1], xi = zi[i1];
+          const float tr = w.x * xr - w.y * xi, ti = w.x * xi + w.y * xr;
+          const float ar = zr[i0], ai = zi[i0];
+          zr[i1] = ar - tr; zi[i1] = ai - ti;
+          zr[i0] = ar + tr; zi[i0] = ai + ti;
         }
         __syncwarp();
-        // ---- 256-point radix-2 FFT (decimation in time), 128 butterflies per stage
-#pragma unroll 1
-        for (int half = 1; half < 256; half <<= 1) {
-          const int tstep = 256 / half;                         // twiddle exp(-2 pi i pos / (2 half)) = tw[pos * 256 / half]
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int b = lane + 32 * q;
-            const int pos = b & (half - 1);
-            const int i0 = ((b - pos) << 1) + pos, i1 = i0 + half;
-            const float2 w = tw[pos * tstep];
-            const float xr = zr[i1], xi = zi[i1];
-            const float tr = w.x * xr - w.y * xi, ti = w.x * xi + w.y * xr;
-            const float ar = zr[i0], ai = zi[i0];
-            zr[i1] = ar - tr; zi[i1] = ai - ti;
-            zr[i0] = ar + tr; zi[i0] = ai + ti;
-          }
-          __syncwarp();
-        }
-        // ---- split into the 257 bins of the real transform, power
-        for (int k = lane; k < FE_BINS; k += 32) {
-          const int ka = k & 255, kb = (256 - k) & 255;
-          const float ar = zr[ka], ai = zi[ka], br = zr[kb], bi = -zi[kb];          // Z[k], conj(Z[256 - k])
-          const float er = 0.5f * (ar + br), ei = 0.5f * (ai + bi);                 // even part
-          const float dr = 0.5f * (ar - br), di = 0.5f * (ai - bi);                 // (Z - conj Z') / 2; odd part = -i * that
-          const float orr = di, oi = -dr;
-          const float2 w = tw[k];
-          const float xr = er + (w.x * orr - w.y * oi), xi = ei + (w.x * oi + w.y * orr);
-          pw[k] = xr * xr + xi * xi + dither2;
-        }
-      } else {
-        for (int k = lane; k < FE_BINS; k += 32) pw[k] = dither2;                   // power_spectrum zeroes frames past the length
+      }
+      // ---- split into the 257 bins of the real transform, power
+      for (int k = lane; k < FE_BINS; k += 32) {
+        const int ka = k & 255, kb = (256 - k) & 255;
+        const float ar = zr[ka], ai = zi[ka], br = zr[kb], bi = -zi[kb];          // Z[k], conj(Z[256 - k])
+        const float er = 0.5f * (ar + br), ei = 0.5f * (ai + bi);                 // even part
+        const float dr = 0.5f * (ar - br), di = 0.5f * (ai - bi);                 // (Z - conj Z') / 2; odd part = -i * that
+        const float orr = di, oi = -dr;
+        const float2 w = tw[k];
+        const float xr = er + (w.x * orr - w.y * oi), xi = ei + (w.x * oi + w.y * orr);
+        pw[k] = xr * xr + xi * xi + dither2;
       }
       __syncwarp();
       // ---- mel filterbank + log: lane = mel m, m + 32, m + 64
-      float acc[3] = {0.f, 0.f, 0.f};
-#pragma unroll 4
-      for (int k = 0; k < FE_BINS; ++k) {
-        const float p = pw[k];
-        const float* f = fbt + k * LogmelSmem::FB_PITCH + lane;
-        acc[0] = fmaf(f[0], p, acc[0]); acc[1] = fmaf(f[32], p, acc[1]); acc[2] = fmaf(f[64], p, acc[2]);
+      for (int m = lane; m < n_mels; m += 32) {
+        const int2 r = range[m];
+        stage[m * FE_TF + ft] = logf(mel_dot(weights(m, r), pw, r.x, r.y) + log_bias);
       }
-#pragma unroll
-      for (int q = 0; q < 3; ++q) stage[(lane + 32 * q) * FE_TF + ft] = logf(acc[q] + log_bias);
       __syncwarp();
     }
+    __syncwarp();
     // ---- write the staged [mel][FE_TF] block: eight consecutive frames of a mel row are one 32-byte sector
     const int nt = min(FE_TF, T - t0);
     for (int e = lane; e < n_mels * FE_TF; e += 32) {
@@ -275,7 +305,7 @@ int rnnt_logmel_f32(const float* y, const int32_t* frame_lens, const float* wind
   cudaError_t e = cudaFuncSetAttribute(logmel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LogmelSmem::TOTAL);
   if (e != cudaSuccess) return api_fail(RNNT_ERR_CUDA, "logmel: shared-memory opt-in failed: %s", cudaGetErrorString(e));
   const long long tasks = (long long)N * ((T + FE_TF - 1) / FE_TF);
-  const int blocks = (int)std::min<long long>((tasks + FE_WARPS - 1) / FE_WARPS, 148);
+  const int blocks = (int)std::min<long long>((tasks + FE_WARPS - 1) / FE_WARPS, 2 * 148);
   logmel_kernel<<<blocks, FE_WARPS * 32, LogmelSmem::TOTAL, (cudaStream_t)stream>>>(y, frame_lens, window, fb, out, N, Lp, T, hop,
                                                                                     win_len, n_mels, dither2, log_bias);
   if (cudaGetLastError() != cudaSuccess) return api_fail(RNNT_ERR_CUDA, "logmel launch failed");
