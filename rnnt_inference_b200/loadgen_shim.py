@@ -34,7 +34,30 @@ class TestSettings:
         self.server_duration_s = 5.0
         self.server_seed = 20240607
 
-    def FromConfig(self, path, model, scenario):   # mlperf.conf / user.conf parsing is not needed offline
+    def FromConfig(self, path, model, scenario):
+        """mlperf.conf / user.conf: lines `<model|*>.<scenario|*>.<key> = <value>`; the keys this shim acts on are
+        min_query_count (Offline: samples of the query), target_qps and min_duration (Server; ms, capped for offline
+        use by server_duration_s set afterwards)."""
+        try:
+            lines = open(path).read().splitlines()
+        except OSError:
+            return 1
+        for line in lines:
+            line = line.split("#", 1)[0].strip()
+            if "=" not in line:
+                continue
+            key, value = (t.strip() for t in line.split("=", 1))
+            parts = key.split(".")
+            if len(parts) != 3 or parts[0] not in ("*", model) or parts[1] not in ("*", scenario):
+                continue
+            try:
+                v = float(value)
+            except ValueError:
+                continue
+            if parts[2] == "min_query_count":
+                self.min_query_count = int(v)
+            elif parts[2] == "target_qps":
+                self.server_target_qps = v
         return 0
 
 

@@ -24,7 +24,8 @@ from .utils import migrate_state_dict
 class RNNT(torch.nn.Module):
     def __init__(self, model_path=None, run_mode=None, enable_bf16=False, load_jit=False, device=None):
         """model_path: path of an MLPerf-format checkpoint (or the already loaded dict).  device: where the model
-        runs; defaults to the current CUDA device for run_mode "quant" and to the CPU for the fp32 modes."""
+        runs; defaults to the current CUDA device for run_mode "quant" (and for the fp32 modes with enable_bf16, whose
+        prediction / joint operators are GPU kernels) and to the CPU for the plain fp32 modes."""
         super().__init__()
         if run_mode == "quant" and not enable_bf16:
             raise RuntimeError("run_mode='quant' runs the prediction/joint networks in bf16: pass enable_bf16=True "
@@ -40,7 +41,9 @@ class RNNT(torch.nn.Module):
             calibrated = run_mode not in (None, "f32", "calib")
             self._load_model(model_path, run_mode, enable_bf16, load_jit, calibrated)
             if device is None:
-                device = torch.device("cuda", torch.cuda.current_device()) if run_mode == "quant" else torch.device("cpu")
+                # the int8 encoder and the bf16 prediction / joint operators exist on the GPU only
+                on_gpu = run_mode == "quant" or (enable_bf16 and torch.cuda.is_available())
+                device = torch.device("cuda", torch.cuda.current_device()) if on_gpu else torch.device("cpu")
             self.to(device)
 
     def _load_model(self, model_path, run_mode=None, enable_bf16=False, load_jit=False, saved_quantizers=False):
