@@ -469,6 +469,10 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    numa = None
+    if world > 1 and os.environ.get("RNNT_NUMA_BIND", "1") != "0":
+        from rnnt_inference_b200 import sharding as _sh
+        numa = _sh.bind_to_gpu_numa_node(local)       # before any pinned allocation of this rank
     import torch.distributed as dist
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
@@ -577,7 +581,8 @@ def main():
                        "batches_per_step": len(batches), "tokens_per_step_rank0": tokens_per_step,
                        "tokens_per_stacked_frame": round(tokens_per_step / max(1, sum((n + 1) // 2 for b in batches for _, n in b)), 4),
                        "l2": "inputs and per-layer int32 projections (up to 2 GB) exceed the 126 MB L2; no explicit flush",
-                       "parallelism": f"dp{world}: length-sorted utterances dealt round-robin to ranks, transcripts gathered with one NCCL all_gather per query"},
+                       "parallelism": f"dp{world}: length-sorted utterances dealt round-robin to ranks, transcripts gathered with one NCCL all_gather per query",
+                       "numa_binding_rank0": (f"node {numa[0]}, {numa[1]} cores" if numa else None)},
             "lstm_step_us": round(step_us, 3) if step_us else None,
             "lstm_step_us_note": "recurrent kernel, mean per (layer, timestep, 128-row batch tile) item of this workload",
             "lstm_step_us_c2": micro["lstm_step_us"] if micro else None,

@@ -12,6 +12,31 @@ import torch
 import torch.distributed as dist
 
 
+def bind_to_gpu_numa_node(device_index):
+    """One process per GPU: run this process on the CPU cores of the NUMA node its GPU hangs off, BEFORE it allocates its
+    page-locked feature arena, so that the arena lands in that node's memory (first touch) and the per-batch host->device
+    copies of the 8 ranks do not all cross the socket interconnect.  Returns (node, number of cores) or None when the
+    topology cannot be read (then nothing changes)."""
+    import os
+    try:
+        props = torch.cuda.get_device_properties(device_index)
+        bdf = f"{props.pci_domain_id:04x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node, len(cpus)
+    except (OSError, ValueError, AttributeError, RuntimeError):
+        return None
+
+
 def plan_chunks(lens_desc, batch_size, head_fraction=0.15, min_frames=65536):
     """Chunks of one pipelined Offline query, as (lo, hi) ranges into the length-sorted (descending) sample list, in the
     order they RUN (shortest first).
