@@ -403,15 +403,15 @@ def e2e_strong(sd, args, device, world, rank, barrier, reduce_scalar):
         collected.clear()
         sut.issue_queries(list(samples))
         n = sum(len(c[0]) for c in collected)
-        ids = torch.tensor([i for c in collected for i in c[0]], dtype=torch.int64)
-        cnt = torch.tensor([v for c in collected for v in c[2]], dtype=torch.int32)
-        tok = torch.full((n, QUERY_TOKEN_CAP), -1, dtype=torch.int32)
+        ids = torch.from_numpy(np.concatenate([np.asarray(c[0], dtype=np.int64) for c in collected]))
+        cnt = torch.from_numpy(np.concatenate([np.asarray(c[2], dtype=np.int32) for c in collected]))
+        tok = np.full((n, QUERY_TOKEN_CAP), -1, dtype=np.int32)
         r = 0
         for _ids, t, _c in collected:
             w = min(t.shape[1], QUERY_TOKEN_CAP)
-            tok[r:r + t.shape[0], :w] = torch.from_numpy(t[:, :w])
+            tok[r:r + t.shape[0], :w] = t[:, :w]
             r += t.shape[0]
-        return ids.to(device), cnt.to(device), tok.to(device)
+        return ids.to(device), cnt.to(device), torch.from_numpy(tok).to(device)
 
     front = sharding.DistributedOfflineSUT(run_shard, ulen, device, l_max=QUERY_TOKEN_CAP, complete=lg.QuerySamplesComplete,
                                            make_sample=lg.QuerySample, make_response=lg.QuerySampleResponse)
