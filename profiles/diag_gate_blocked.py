@@ -1,3 +1,5 @@
+"""Gate-blocked projection layout check: rnnt_gemm_i8_i32_gate_blocked_ragged against the CUDA-core GEMM, element by
+element, with the mismatch pattern by slice / gate / octet / row / unit.  Usage: python profiles/diag_gate_blocked.py"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

@@ -1,3 +1,5 @@
+"""Per-operator CUDA-event timing of the audio front-end on the bench's 2048-utterance batch as waveforms
+(profiles/r02/frontend_bench.md).  Usage: python profiles/frontend_breakdown.py"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
