@@ -18,6 +18,8 @@ int rnnt_debug_set_recurrent_flags(int flags);
 int rnnt_debug_set_gemm_flags(int flags);
 /* Device buffer of max_iters*16 int64 receiving clock64 stamps of CTA 0 per decode iteration. NULL = off. */
 int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);
+/* which CTA writes the decode trace (default 0; CTA 20 g + s is CTA s of lane group g) */
+int rnnt_debug_set_decode_trace_block(int block);
 #ifdef __cplusplus
 }
 #endif

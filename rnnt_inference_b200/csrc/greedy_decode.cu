@@ -802,7 +802,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     if (total >= 0 && live_lanes == 0) break;
     ++round;
     long long* const trace = RNNT_TRACE_PTR(p);
-    const bool tr = trace && blockIdx.x == 0 && tid == 0 && round <= p.trace_cap;
+    const bool tr = trace && (int)blockIdx.x == p.trace_block && tid == 0 && round <= p.trace_cap;
     long long* trow = trace + (size_t)(round - 1) * 16;
     if (tr) { trow[0] = clock64(); trow[7] = na; }
 
@@ -856,12 +856,15 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       }
       const uint32_t arow = act_s + (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * DecSmemTC::JY_PITCH) +
                             (uint32_t)((warp >> 2) * DEC_J) + (uint32_t)((lane >> 4) << 4);
+      bool first_it = true;
       while (__syncthreads_or(run[0] || run[1])) {
         --budget;
+        if (tr && first_it) trow[9] = clock64();
 #pragma unroll
         for (int h = 0; h < 2; ++h)
           if (run[h]) joint_y(zf[h], yv[h], b1r, reinterpret_cast<uint16_t*>(jy_g + (warp + 8 * h) * DecSmemTC::JY_PITCH), lane);
         __syncthreads();
+        if (tr && first_it) trow[10] = clock64();
         {
           float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll
@@ -878,6 +881,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
           *reinterpret_cast<float2*>(out + (r0 + 8) * DEC_V + c0) = make_float2(acc[0][2] + acc[1][2], acc[0][3] + acc[1][3]);
         }
         __syncthreads();
+        if (tr && first_it) trow[11] = clock64();
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           if (run[h]) {
@@ -893,7 +897,10 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
             if (!run[h]) store_lane(p, n, st2[h], jr[h], lane);
           }
         }
+        if (tr && first_it) trow[14] = clock64();
+        first_it = false;
       }
+      if (tr) trow[15] = clock64();
     } else {
       // ---- phase D, exact variant: lanes li = s, s + S, ...; one warp per lane, decision after decision.  The LSTM / fc1
       // phases overwrite the overlay, so the fc2 weights are staged again whenever they ran.

@@ -236,6 +236,7 @@ struct DecParams {
   int max_run;          // decisions a lane may take per round without a group barrier (run-ahead through blank frames)
   long long* trace;     // optional [iters][8] clock64 stamps of CTA 0 (profiles/trace_decode.py; NULL otherwise)
   int trace_cap;
+  int trace_block;      // the CTA whose thread 0 writes the trace (debug build)
 };
 
 // tensor-core variant: bf16 weights / activations as XOR-swizzled 16-byte chunks (conflict-free ldmatrix), no row padding
