@@ -209,6 +209,36 @@ def test_sut_offline_head_split_vs_oracle(setup):
             np.testing.assert_array_equal(got[i], o_res[j, :o_len[j]])
 
 
+def test_sut_offline_multi_tile_query_vs_oracle(setup):
+    """A query of 420 utterances at batch 160 through the pipelined path: three chunks (the short end cut by frames, one full
+    batch), each with two 128-row encoder tiles of different lengths and a batch width that is not a multiple of 128 (ragged
+    row skipping inside straddling GEMM tiles); bytes equal to the oracle's in the planner's batches."""
+    from rnnt_inference_b200 import loadgen_shim as lg
+    from rnnt_inference_b200 import sharding
+    from rnnt_inference_b200.pytorch_sut import PytorchSUT
+    sd, _rnnt, params, _ = setup
+    rng = np.random.default_rng(21)
+    lens = [int(v) for v in rng.integers(6, 64, 420)]
+    feats = [S.make_features(n, 2000 + i) for i, n in enumerate(lens)]
+    data = {"x": feats, "x_lens": [torch.tensor(n) for n in lens]}
+    sut = PytorchSUT(sd, data, 160, "quant", None, enable_bf16=True, scenario="Offline", exact_order=True, head_fraction=0.3,
+                     head_min_frames=0)
+    settings = lg.TestSettings()
+    settings.scenario = lg.TestScenario.Offline
+    settings.mode = lg.TestMode.AccuracyOnly
+    out = lg.StartTest(sut.sut, sut.qsl.qsl, settings)
+    assert out["completed"] == len(lens)
+    got = {e["qsl_idx"]: np.frombuffer(bytes.fromhex(e["data"]), np.int32) for e in out["accuracy_log"]}
+    order = sorted(range(len(lens)), key=lambda i: (-lens[i], i))
+    plan = sharding.plan_chunks([lens[i] for i in order], 160, 0.3, 0)
+    assert len(plan) == 3 and plan[-1] == (0, 160) and plan != sharding.plan_chunks([lens[i] for i in order], 160, 0.0, 0)
+    for lo, hi in plan:
+        idx = order[lo:hi]
+        o_res, o_len, _ = _oracle(params, [feats[i] for i in idx], pad_to=32)
+        for j, i in enumerate(idx):
+            np.testing.assert_array_equal(got[i], o_res[j, :o_len[j]])
+
+
 def test_sut_default_path_and_sync_inference(setup):
     """The SUT as a user runs it (tensor-core hoist): the pipelined Offline path and the synchronous
     inference() + query_samples_complete() path of the reference (pytorch_sut.py:67-118) give the same bytes, and
