@@ -14,7 +14,8 @@ int rnnt_debug_set_recurrent_trace(void* device_buffer);
  * stores, 4 relaxed publish, 5 no proxy fence, 6 no G, 7 no c prefetch, 8 ignore the h_t flags; 0 = normal operation. */
 int rnnt_debug_set_recurrent_flags(int flags);
 /* PROFILING ONLY (results become garbage): projection GEMM with bit 0 no operand loads, bit 1 no MMAs, bit 2 no result
- * stores — attributes the kernel time to its three pipelines (profiles/gemm_attrib.py). */
+ * stores, bit 3 every CTA stores all its tiles onto one tile of its own (the result stays in L2: no HBM write-back) — attributes the kernel time
+ * to its pipelines (profiles/gemm_attrib.py). */
 int rnnt_debug_set_gemm_flags(int flags);
 /* Device buffer of max_iters*16 int64 receiving clock64 stamps of CTA 0 per decode iteration. NULL = off. */
 int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);

@@ -12,12 +12,13 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
     from rnnt_inference_b200 import _lib
     torch.cuda.set_device(0)
     m, n = 102400, 4096
+    _lib.lib.rnnt_tune_gemm_pair(0)            # the switch-off flags exist in the single-CTA kernel
     for k in (256, 1024, 2048):
         a = torch.randint(-128, 128, (m, k), dtype=torch.int8, device="cuda")
         w = torch.randint(-128, 128, (n, k), dtype=torch.int8, device="cuda")
         c = torch.empty((m, n), dtype=torch.int32, device="cuda")
         row = []
-        for flags in (0, 1, 2, 4, 5, 3, 6):
+        for flags in (0, 1, 2, 4, 5, 3, 6, 8, 9, 11):
             _lib.lib.rnnt_debug_set_gemm_flags(flags)
             ts = []
             for rep in range(4):
@@ -41,7 +42,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
         _lib.lib.rnnt_tune_gemm_pair(0)
         row.append(("pair", round(min(ts[1:]), 3)))
         _lib.lib.rnnt_check_device_status(None)
-        print(f"  K={k}: ms by flags (1 no loads, 2 no MMAs, 4 no stores): {row}; algorithmic: tensor {2.0 * m * n * k / 4.74e15 * 1e3:.3f} ms, "
+        print(f"  K={k}: ms by flags (1 no loads, 2 no MMAs, 4 no stores, 8 every CTA stores onto one L2-resident tile of its own): {row}; algorithmic: tensor {2.0 * m * n * k / 4.74e15 * 1e3:.3f} ms, "
               f"HBM write {m * n * 4 / 6.5e12 * 1e3:.3f} ms")
 else:
     for ep in ("tma",) if "--tma-only" in sys.argv else ("direct", "tma"):

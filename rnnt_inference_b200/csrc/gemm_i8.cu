@@ -34,7 +34,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                    const long long M, const int ldc) {
   using S = GemmSmem<BN>;
 #ifdef RNNT_DEBUG_HOOKS
-  const int dbg = gate_blocked_and_debug >> 8;        // profiling only: 1 no operand loads, 2 no MMAs, 4 no result stores
+  const int dbg = gate_blocked_and_debug >> 8;        // profiling only: 1 no operand loads, 2 no MMAs, 4 no result stores, 8 every CTA stores all its tiles onto one tile of its own (L2-resident)
 #else
   constexpr int dbg = 0;
 #endif
@@ -156,7 +156,7 @@ gemm_i8_i32_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
       if (!c_direct) {
         gemm_i8_store_chunks(t_row, cbuf0, buf, half, GEMM_I8_EPI_WARPS / 4, BN / 32, &tmap_c, gate_blocked,
-                             m_blk * GEMM_BM + q * 32, n_blk * BN, lane, (dbg & 4) != 0);
+                             (dbg & 8) ? (int)blockIdx.x * GEMM_BM + q * 32 : m_blk * GEMM_BM + q * 32, (dbg & 8) ? 0 : n_blk * BN, lane, (dbg & 4) != 0);
       } else {
 #pragma unroll 1
         for (int c = half; c < BN / 32; c += GEMM_I8_EPI_WARPS / 4) {
