@@ -71,17 +71,57 @@ def dist_env():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md recipe).  NVML in a thread of this
+    process, one sample every 10 ms (a `nvidia-smi -lms` child takes longer to start on an 8-GPU box than five steps take);
+    the nvidia-smi child is the fallback when the NVML binding is missing."""
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
+    NVML_REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"),
+                    (0x4, "sw_power_cap"))
 
     def __init__(self, gpu_index):
         self.gpu_index = gpu_index
         self.proc = None
         self.path = None
+        self.thread = None
+        self.stop_flag = threading.Event()
+        self.sm, self.reason_bits, self.smax = [], 0, None
+        self.nvml = self.handle = None
+        try:                                    # handle looked up before the timed region starts
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(gpu_index).uuid)
+                uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+                try:
+                    self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+                except TypeError:
+                    self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = self.handle = None
+
+    def _sample_nvml(self):
+        n = self.nvml
+        reasons = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        while True:
+            try:
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+                self.reason_bits |= int(reasons(self.handle))
+            except Exception:
+                pass
+            if self.stop_flag.wait(0.010):
+                return
 
     def start(self):
+        if self.nvml is not None:
+            self.thread = threading.Thread(target=self._sample_nvml, daemon=True)
+            self.thread.start()
+            return
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
@@ -93,6 +133,13 @@ class ClockSampler:
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.thread is not None:
+            self.stop_flag.set()
+            self.thread.join(timeout=5)
+            if self.sm:
+                out.update(sm_mhz=float(np.median(self.sm)), sm_max_mhz=self.smax, samples=len(self.sm), source="nvml",
+                           reasons=sorted(name for bit, name in self.NVML_REASONS if self.reason_bits & bit))
+            return out
         if self.proc is None:
             return out
         self.proc.terminate()
@@ -119,7 +166,8 @@ class ClockSampler:
         except Exception:
             pass
         if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=smax, reasons=sorted(reasons), samples=len(sm))
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=smax, reasons=sorted(reasons), samples=len(sm),
+                       source="nvidia-smi")
         return out
 
 
