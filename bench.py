@@ -56,6 +56,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--utts", type=int, default=UTTS_PER_GPU, help="utterances per GPU and step")
     ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--streams", type=int, default=2, help="compute streams the batches of a step alternate between (PytorchSUT: RNNT_SUT_COMPUTE_STREAMS)")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -221,28 +222,41 @@ def stage_on_device(batches, feats, device):
     return staged
 
 
-def run_step_device(decoder, staged, world=1, n_max=None):
+_batches_run = [0]
+
+
+def run_step_device(decoder, staged, world=1, n_max=None, streams=None):
     """One step = one pass over this rank's query, inputs already in HBM; with N > 1 the step ends with the ONE
     all_gather of (sample id, length, tokens) from all ranks (the path's only collective; n_max = rows per rank and the
-    token width are known from the query, so no shape exchange).  Returns (emitted-token count tensor, outputs)."""
+    token width are known from the query, so no shape exchange).  With `streams`, consecutive batches rotate over them like
+    the chunks of PytorchSUT.issue_queries (the caller forks / joins them around the timed region; with N > 1 they are
+    joined before the gather).  Returns the emitted-token count as a list of device scalars, one per batch."""
     from rnnt_inference_b200 import sharding
-    total, outs = None, []
+    totals, outs = [], []
     cap = max((m + 1) // 2 for _p, _o, _l, m, _n, _h, _i in staged) if staged else 1
+    main = torch.cuda.current_stream()
     for packed, offsets, lens, max_len, n_actual, lens_host, ids in staged:
-        res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len, lens_host)
-        s = res_len[:n_actual].sum()
-        total = s if total is None else total + s
-        if world > 1:
-            tok = torch.full((n_actual, cap), -1, dtype=torch.int32, device=res.device)
-            w = min(cap, res.shape[1])
-            tok[:, :w] = res[:n_actual, :w]
-            outs.append((ids, res_len[:n_actual].to(torch.int32), tok))
+        _batches_run[0] += 1
+        with torch.cuda.stream(streams[_batches_run[0] % len(streams)] if streams else main):
+            res, res_len = decoder.forward_ragged(packed, offsets, lens, max_len, lens_host)
+            totals.append(res_len[:n_actual].sum())
+            if world > 1:
+                tok = torch.full((n_actual, cap), -1, dtype=torch.int32, device=res.device)
+                w = min(cap, res.shape[1])
+                tok[:, :w] = res[:n_actual, :w]
+                outs.append((ids, res_len[:n_actual].to(torch.int32), tok))
+    if world > 1 and streams:
+        for st in streams:
+            main.wait_stream(st)
     if world > 1:
         dev = staged[0][0].device if staged else torch.device("cuda", torch.cuda.current_device())
         cat = lambda k, dt, shape: torch.cat([o[k] for o in outs], 0) if outs else torch.empty(shape, dtype=dt, device=dev)
         sharding.gather_transcripts(cat(0, torch.int64, (0,)), cat(1, torch.int32, (0,)), cat(2, torch.int32, (0, cap)), world,
                                     n_max=n_max, l_max=QUERY_TOKEN_CAP)
-    return total
+        if streams:                      # the next step's batches reuse the gathered buffers' streams
+            for st in streams:
+                st.wait_stream(main)
+    return totals
 
 
 # ------------------------------------------------------------------------------------------------ roofline
@@ -549,9 +563,22 @@ def main():
     my_frames = sum(n for b in batches for _, n in b)
 
     # ---- device-resident leg: W warm-up steps, then exactly K timed steps (no per-kernel instrumentation inside)
+    streams = [torch.cuda.Stream(device) for _ in range(args.streams)] if args.streams > 1 else None
+    main_stream = torch.cuda.current_stream()
+
+    def fork():
+        for st in streams or []:
+            st.wait_stream(main_stream)
+
+    def join():
+        for st in streams or []:
+            main_stream.wait_stream(st)
+
     with torch.no_grad():
+        fork()
         for _ in range(args.warmup):
-            run_step_device(decoder, staged, world, n_max)
+            run_step_device(decoder, staged, world, n_max, streams)
+        join()
         ops.telemetry.events = None
         launches0 = ops.telemetry.launches
         sampler = ClockSampler(local)
@@ -559,9 +586,11 @@ def main():
         sampler.start()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
+        fork()
         tokens = None
         for _ in range(args.steps):
-            tokens = run_step_device(decoder, staged, world, n_max)
+            tokens = run_step_device(decoder, staged, world, n_max, streams)
+        join()
         ev1.record()
         barrier()
         clocks = sampler.stop()
@@ -580,7 +609,7 @@ def main():
     value = utts_total * args.steps / (ms_total * 1e-3)
     roof, step_us = recurrent_roofline(events, load_peaks())
     shares = kernel_shares(events)
-    tokens_per_step = int(tokens.item()) if tokens is not None else 0
+    tokens_per_step = int(sum(int(t.item()) for t in tokens)) if tokens else 0
 
     # ---- e2e leg: PytorchSUT + LoadGen shim, host features
     e2e = None
@@ -626,7 +655,7 @@ def main():
             "dtype": "int8", "data": "synthetic",
             "config": {"workload": workload + f", sorted, batch {args.batch}, full int8 RNN-T greedy decode",
                        "utterances_per_gpu_per_step": my_utts, "frames_per_gpu_per_step": my_frames, "batch": args.batch,
-                       "batches_per_step": len(batches), "tokens_per_step_rank0": tokens_per_step,
+                       "batches_per_step": len(batches), "compute_streams": args.streams, "tokens_per_step_rank0": tokens_per_step,
                        "tokens_per_stacked_frame": round(tokens_per_step / max(1, sum((n + 1) // 2 for b in batches for _, n in b)), 4),
                        "l2": "inputs and per-layer int32 projections (up to 2 GB) exceed the 126 MB L2; no explicit flush",
                        "parallelism": f"dp{world}: length-sorted utterances dealt round-robin to ranks, transcripts gathered with one NCCL all_gather per query",

@@ -899,6 +899,8 @@ static int decode_run(bool tensor_cores, const uint16_t* y1, const int32_t* f_le
   p.iters_out = iters_out; p.status = status; p.NG = NG; p.LG = LG;
   static const int max_run = [] { const char* e = getenv("RNNT_DEC_MAX_RUN"); const int v = e ? atoi(e) : 4; return v > 0 ? v : 4; }();   // measured: 2048-lane batch 11.3 / 11.6 / 12.5 / 15.0 ms for 4 / 8 / 16 / 64
   p.max_run = max_run;      // tuning knob (results do not depend on it)
+  const char* ee = getenv("RNNT_DEC_EARLY_EXIT");      // read per call: tests run both settings in one process
+  p.early_exit = ee ? (atoi(ee) != 0) : 1;
 #ifdef RNNT_DEBUG_HOOKS
   p.trace = g_dec_trace; p.trace_cap = g_dec_trace_cap; p.trace_block = g_dec_trace_block;
 #else

@@ -39,7 +39,7 @@ _DEFAULT_ARGS = dict(enable_bf16=False, split_len=-1, scenario="Offline", load_j
 class _Batch:
     """One staged / in-flight batch of the pipelined Offline loop."""
     __slots__ = ("samples", "n_actual", "n_padded", "max_len", "packed", "meta", "ready", "done", "res", "res_len", "tok_host",
-                 "len_host", "cap", "h2d_bytes", "keep", "lens_host", "status_host")
+                 "len_host", "cap", "h2d_bytes", "keep", "lens_host", "status_host", "stream")
 
 
 class PytorchSUT:
@@ -82,7 +82,12 @@ class PytorchSUT:
         if self.pipelined:
             dev = self.model.device
             self._copy_stream = torch.cuda.Stream(dev)
-            self._compute_stream = torch.cuda.Stream(dev)
+            # Chunks alternate between two compute streams (each with its own scratch, ops.Workspace): the next chunk's
+            # GEMMs run on the SMs the recurrent kernel leaves idle (128 of 148 CTAs) and on those the decode kernel
+            # frees when all but the replaying lane groups have left (greedy_decode.cu, rendezvous).
+            n_streams = max(1, int(kwargs.get("compute_streams", os.environ.get("RNNT_SUT_COMPUTE_STREAMS", 2))))
+            self._compute_streams = [torch.cuda.Stream(dev) for _ in range(n_streams)]
+            self._launched = 0
             self._packed = [None, None]         # double-buffered device staging of the ragged batch
             self._slot = 0
             self._prev_done = [None, None]
@@ -181,8 +186,10 @@ class PytorchSUT:
 
     def _launch(self, b):
         """Encoder + fused decode of a staged batch on the compute stream, then the (small) result copy back."""
-        with torch.cuda.stream(self._compute_stream), torch.no_grad():
-            self._compute_stream.wait_event(b.ready)
+        b.stream = self._compute_streams[self._launched % len(self._compute_streams)]
+        self._launched += 1
+        with torch.cuda.stream(b.stream), torch.no_grad():
+            b.stream.wait_event(b.ready)
             offsets = b.meta[0]
             lens = b.meta[1].to(torch.int32)
             b.res, b.res_len = self.model.forward_ragged(b.packed, offsets, lens, b.max_len, b.lens_host)
@@ -196,7 +203,7 @@ class PytorchSUT:
             b.status_host = torch.zeros(1, dtype=torch.int32).pin_memory()
             _lib.check(_lib.lib.rnnt_peek_device_status(_lib.ptr(b.status_host), _lib.stream_ptr()))
             b.done = torch.cuda.Event()
-            b.done.record(self._compute_stream)
+            b.done.record(b.stream)
         self._prev_done[b.keep[1]] = b.done
 
     def _finish(self, b):
@@ -212,7 +219,7 @@ class PytorchSUT:
             # a few rows (a frame that ran into the 30-symbol cap) hold more tokens than the prefix copied back: fetch just
             # those rows, at the width they need, and widen the host array
             rows = np.nonzero(lens[:b.n_actual] > b.cap)[0]
-            with torch.cuda.stream(self._compute_stream):
+            with torch.cuda.stream(b.stream):
                 sel = torch.from_numpy(rows).to(b.res.device)
                 extra = b.res.index_select(0, sel)[:, :longest].cpu().numpy()
             wide = np.full((b.n_actual, longest), -1, dtype=np.int32)
