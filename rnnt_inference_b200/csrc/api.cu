@@ -79,6 +79,37 @@ int* device_status() {
   return ptr[dev];
 }
 
+// Cooperative kernels of this library (recurrent, greedy decode) wait on flags written by their own CTAs, which is safe
+// only while all of a grid's CTAs become resident.  Two such grids from DIFFERENT streams, handed to an idle GPU at the same
+// time, can each be given part of the SMs and then wait for ever (observed on an 8-GPU box with two compute streams per
+// rank: watchdog code 102 on 3 of 8 ranks).  They are therefore ordered per device, whatever stream they come from: each
+// waits for the completion of the one launched before it.  Kernels without inter-CTA waits (GEMMs, byte kernels) are not
+// ordered and still overlap with them.  On one stream the wait is already implied and costs nothing on the device.
+struct CoopOrder {
+  std::unique_lock<std::mutex> lock;
+  cudaEvent_t ev = nullptr;
+  cudaStream_t st = nullptr;
+  int begin(cudaStream_t stream) {
+    static std::mutex mu;
+    static cudaEvent_t evs[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
+    lock = std::unique_lock<std::mutex>(mu);
+    if (!evs[dev] && cudaEventCreateWithFlags(&evs[dev], cudaEventDisableTiming) != cudaSuccess)
+      return fail(RNNT_ERR_CUDA, "cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
+    ev = evs[dev]; st = stream;
+    cudaError_t e = cudaStreamWaitEvent(st, ev, 0);      // an event never recorded is complete
+    if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "cudaStreamWaitEvent failed: %s", cudaGetErrorString(e));
+    return RNNT_OK;
+  }
+  int end() {
+    cudaError_t e = cudaEventRecord(ev, st);
+    lock.unlock();
+    if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "cudaEventRecord failed: %s", cudaGetErrorString(e));
+    return RNNT_OK;
+  }
+};
+
 int sm_count() {
   int dev = 0, n = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return -1;
@@ -145,12 +176,14 @@ int rnnt_check_device_status(void* stream) {
   int* st = device_status();
   if (!st) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
   cudaStream_t s = (cudaStream_t)stream;
-  int h = 0;
-  CUDA_TRY(cudaMemcpyAsync(&h, st, sizeof(int), cudaMemcpyDeviceToHost, s));
+  int h[8] = {0};       // [0] code, then what the wait that fired left behind: site, CTA, epoch / step
+  CUDA_TRY(cudaMemcpyAsync(h, st, sizeof(h), cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaStreamSynchronize(s));
-  if (h != 0) {
-    cudaMemsetAsync(st, 0, sizeof(int), s);
-    return fail(RNNT_ERR_DEVICE, "device-side watchdog/protocol error %d (101 mbarrier timeout, 102 flag timeout)", h);
+  if (h[0] != 0) {
+    cudaMemsetAsync(st, 0, sizeof(h), s);
+    return fail(RNNT_ERR_DEVICE, "device-side watchdog/protocol error %d (101 mbarrier timeout, 102 flag timeout); site %d "
+                "(1 decode group barrier, 2 decode rendezvous, 3 recurrent h flags; 0 = an mbarrier) CTA %d epoch/step %d",
+                h[0], h[1], h[2], h[3]);
   }
   return RNNT_OK;
 }
@@ -166,7 +199,7 @@ int rnnt_peek_device_status(int32_t* host_dst, void* stream) {
 int rnnt_clear_device_status(void* stream) {
   int* st = device_status();
   if (!st) return fail(RNNT_ERR_CUDA, "no usable CUDA device");
-  CUDA_TRY(cudaMemsetAsync(st, 0, sizeof(int), (cudaStream_t)stream));
+  CUDA_TRY(cudaMemsetAsync(st, 0, 8 * sizeof(int), (cudaStream_t)stream));
   return RNNT_OK;
 }
 
@@ -759,7 +792,16 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
   p.trace = nullptr;
   p.debug = 0;
 #endif
-  if (int r = rec_launch(tw, th0, th, p, num_slices, used_groups, rec_cluster_pref(), st)) return r;
+  if (status_word) {      // static-scratch entry point: no library state is created; overlapping calls race by contract
+    if (int r = rec_launch(tw, th0, th, p, num_slices, used_groups, rec_cluster_pref(), st)) return r;
+  } else {
+    CoopOrder order;
+    if (int r = order.begin(st)) return r;
+    const int r = rec_launch(tw, th0, th, p, num_slices, used_groups, rec_cluster_pref(), st);
+    const int r2 = order.end();
+    if (r) return r;
+    if (r2) return r2;
+  }
   // tiles that ran a single step left their final h in the ping-pong buffer (see lstm_recurrent.cu): move it to hx
   unsigned one_step = 0;
   for (int b = 0; b < num_btiles; ++b) one_step |= (p.tile_steps[b] == 1) ? (1u << b) : 0u;
@@ -899,8 +941,6 @@ static int decode_run(bool tensor_cores, const uint16_t* y1, const int32_t* f_le
   p.iters_out = iters_out; p.status = status; p.NG = NG; p.LG = LG;
   static const int max_run = [] { const char* e = getenv("RNNT_DEC_MAX_RUN"); const int v = e ? atoi(e) : 4; return v > 0 ? v : 4; }();   // measured: 2048-lane batch 11.3 / 11.6 / 12.5 / 15.0 ms for 4 / 8 / 16 / 64
   p.max_run = max_run;      // tuning knob (results do not depend on it)
-  const char* ee = getenv("RNNT_DEC_EARLY_EXIT");      // read per call: tests run both settings in one process
-  p.early_exit = ee ? (atoi(ee) != 0) : 1;
 #ifdef RNNT_DEBUG_HOOKS
   p.trace = g_dec_trace; p.trace_cap = g_dec_trace_cap; p.trace_block = g_dec_trace_block;
 #else
@@ -911,7 +951,12 @@ static int decode_run(bool tensor_cores, const uint16_t* y1, const int32_t* f_le
   const int smem_bytes = tensor_cores ? DecSmemTC::TOTAL : DecSmem::TOTAL;
   CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));   // per device
   void* args[1] = {(void*)&p};
-  CUDA_TRY(cudaLaunchCooperativeKernel(kern, dim3(NG * DEC_S), dim3(DEC_THREADS), args, smem_bytes, st));
+  CoopOrder order;
+  if (int r = order.begin(st)) return r;
+  const cudaError_t le = cudaLaunchCooperativeKernel(kern, dim3(NG * DEC_S), dim3(DEC_THREADS), args, smem_bytes, st);
+  const int r2 = order.end();
+  if (le != cudaSuccess) return fail(RNNT_ERR_CUDA, "greedy_decode launch failed: %s", cudaGetErrorString(le));
+  if (r2) return r2;
   return RNNT_OK;
 }
 

@@ -12,6 +12,12 @@ namespace rnnt {
 
 // device-side error codes written to the per-launch status word
 enum : int { DEV_OK = 0, DEV_TIMEOUT_MBAR = 101, DEV_TIMEOUT_FLAG = 102, DEV_ABORTED = 103, DEV_BAD_SMEM = 104 };
+// the wait whose watchdog fired first leaves its whereabouts behind the status word (read by rnnt_check_device_status)
+static __device__ __noinline__ void watchdog_fired(int* status, int code, int site, int epoch) {
+  if (atomicCAS(status, DEV_OK, code) == DEV_OK) {
+    status[1] = site; status[2] = (int)(blockIdx.x + gridDim.x * blockIdx.y); status[3] = epoch;
+  }
+}
 
 constexpr long long kWatchdogCycles = 4000000000ll;  // ~2 s at 2 GHz
 

@@ -73,7 +73,7 @@ __device__ __forceinline__ void group_barrier(const DecParams& p, int g, int& ep
       if (v >= target) break;
       if ((++spins & 63u) == 0) {
         if (*(volatile int*)p.status != DEV_OK) { *s_fail = 1; break; }
-        if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_FLAG); *s_fail = 1; break; }
+        if (clock64() - t0 > kWatchdogCycles) { watchdog_fired(p.status, DEV_TIMEOUT_FLAG, 1, epoch); *s_fail = 1; break; }
       }
     }
     asm volatile("fence.acquire.gpu;" ::: "memory");
@@ -645,53 +645,6 @@ __device__ __forceinline__ float fc2_chain(const uint8_t* w2s, const uint16_t* y
   return acc;
 }
 
-// Rendezvous of the lane groups once every lane of group g has finished (see the call site).  Out of line: it runs
-// once per launch and must not cost the round loop registers.
-__device__ __noinline__ void rendezvous(int32_t* global_sync, int* status, const int32_t* lane_state, int32_t* time_idx,
-                                        int32_t* iters_out, int N, int NG, int g, int s, bool leave, int maxdc, int* s_total,
-                                        int* s_last) {
-  const int tid = threadIdx.x;
-  if (tid == 0) {
-    bool last = false;
-    if (s == 0) {
-      if (leave) global_sync[2 + g] = 1;
-      atomicMax(global_sync + 1, maxdc);
-      __threadfence();
-      last = atomicAdd(global_sync + 0, 1) == NG - 1;
-      __threadfence();
-    }
-    if (!leave) {
-      long long t0 = clock64(); uint32_t spins = 0;
-      for (;;) {
-        int v;
-        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(global_sync) : "memory");
-        if (v >= NG) break;
-        if ((++spins & 63u) == 0) {
-          if (*(volatile int*)status != DEV_OK) break;
-          if (clock64() - t0 > kWatchdogCycles) { atomicCAS(status, DEV_OK, DEV_TIMEOUT_FLAG); break; }
-        }
-      }
-    }
-    *s_total = (!leave || last) ? *(volatile int*)(global_sync + 1) : -1;
-    *s_last = last;
-  }
-  __syncthreads();
-  if (*s_last) {
-    // all groups have arrived: the count is final and the leavers' lane states are (their stores precede their arrival)
-    const int tot = *s_total;
-    for (int gg = 0; gg < NG; ++gg) {
-      if (__ldcg(global_sync + 2 + gg) == 0) continue;
-      const int nlg = (N - gg + NG - 1) / NG;
-      for (int li = tid; li < nlg; li += DEC_THREADS) {
-        const int n = gg + li * NG;
-        const int4 st = __ldcg(reinterpret_cast<const int4*>(lane_state + (size_t)n * 4));
-        if (st.x & LS_FIXED) time_idx[n] = __ldcg(time_idx + n) + tot - st.w;      // written by another SM: read from L2
-      }
-    }
-    if (tid == 0 && iters_out) *iters_out = tot;
-  }
-}
-
 template <bool TC>
 __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const DecParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -710,7 +663,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   __shared__ int alist[DEC_MAXLG];
   __shared__ float s_bias[2 * DEC_COLS], s_b2[DEC_V];
   __shared__ int4 s_blk[(DEC_MAXLG + 31) / 32];      // per 32-lane block: need mask, unfinished, live, max decisions
-  __shared__ int s_unfinished, s_fail, s_last;
+  __shared__ int s_unfinished, s_fail;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = blockIdx.x / DEC_S, s = blockIdx.x % DEC_S;
@@ -780,7 +733,6 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   int round = 0;
   int total = -1;         // batch-lockstep iteration count of the reference loop; unknown during phase 1
   bool w2_valid = false;
-  bool left = false;      // this group left at the rendezvous (no lane to replay)
   for (;;) {
     // ---- snapshot the group's lane states (one 16-byte load per lane), build the list of lanes whose prediction
     // network has to be re-evaluated, count the lanes still to finish (phase 1) / still to replay (phase 2).  This sits on
@@ -791,13 +743,12 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     bool need_r[2] = {false, false};
     for (int b = warp, i = 0; b < nblk; b += DEC_WARPS, ++i) {
       const int li = b * 32 + lane;
-      int need = 0, unfin = 0, live = 0, dc = 0, park = 0;
+      int need = 0, unfin = 0, live = 0, dc = 0;
       if (li < nl) {
         const int4 st = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li * lstep) * 4));
         s_state[li] = st;
         const bool replay = total >= 0 && (st.x & LS_FINISHED) && !(st.x & LS_FIXED) && st.w < total;
         unfin = !(st.x & LS_FINISHED);
-        park = (st.x & LS_FINISHED) && !(st.x & LS_FIXED);      // capped on its last frame: may have to replay
         live = unfin || replay;
         need = (st.x & LS_NEED) && !(st.x & LS_FIXED) && live;
         dc = st.w;
@@ -805,18 +756,17 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       const unsigned mneed = __ballot_sync(0xffffffffu, need);
       const unsigned munf = __ballot_sync(0xffffffffu, unfin);
       const unsigned mlive = __ballot_sync(0xffffffffu, live);
-      const unsigned mpark = __ballot_sync(0xffffffffu, park);
       dc = __reduce_max_sync(0xffffffffu, dc);
       need_r[i] = need != 0;
-      if (lane == 0) s_blk[b] = make_int4((int)mneed, __popc(munf) | (__popc(mpark) << 8), __popc(mlive), dc);
+      if (lane == 0) s_blk[b] = make_int4((int)mneed, __popc(munf), __popc(mlive), dc);
     }
     __syncthreads();
-    int na = 0, unfinished = 0, parked = 0, live_lanes = 0, maxdc = 0, before[2] = {0, 0};
+    int na = 0, unfinished = 0, live_lanes = 0, maxdc = 0, before[2] = {0, 0};
     for (int b = 0; b < nblk; ++b) {
       const int4 v = s_blk[b];
       if (b == warp) before[0] = na;
       if (b == warp + DEC_WARPS) before[1] = na;
-      na += __popc((unsigned)v.x); unfinished += v.y & 255; parked += v.y >> 8; live_lanes += v.z; maxdc = max(maxdc, v.w);
+      na += __popc((unsigned)v.x); unfinished += v.y; live_lanes += v.z; maxdc = max(maxdc, v.w);
     }
     for (int b = warp, i = 0; b < nblk; b += DEC_WARPS, ++i)
       if (need_r[i]) alist[before[i] + __popc((unsigned)s_blk[b].x & ((1u << lane) - 1u))] = b * 32 + lane;
@@ -824,14 +774,26 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     if (!ok) break;
     if (total < 0 && unfinished == 0) {
       // ---- every lane of the group has finished: rendezvous of all groups; the largest decision count any lane needed to
-      // finish is the number of iterations of the reference's lock-step loop.  Only a group that holds a lane parked on
-      // the cap needs that number to go on (replay phase); a group without one LEAVES here — its SMs are free for
-      // whatever the other streams have queued while the replay chain of one or two lanes runs in another group — and
-      // the last group to arrive applies the one thing that depends on the count to the leavers' lanes (time_idx of the
-      // lanes at their fixed point), and writes iters_out.
-      const bool leave = p.early_exit && parked == 0;
-      rendezvous(p.global_sync, p.status, p.lane_state, p.time_idx, p.iters_out, p.N, p.NG, g, s, leave, maxdc, &s_unfinished, &s_last);
-      if (leave) { left = true; break; }
+      // finish is the number of iterations of the reference's lock-step loop
+      if (tid == 0) {
+        if (s == 0) {
+          atomicMax(p.global_sync + 1, maxdc);
+          __threadfence();
+          atomicAdd(p.global_sync + 0, 1);
+        }
+        long long t0 = clock64(); uint32_t spins = 0;
+        for (;;) {
+          int v;
+          asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.global_sync) : "memory");
+          if (v >= p.NG) break;
+          if ((++spins & 63u) == 0) {
+            if (*(volatile int*)p.status != DEV_OK) break;
+            if (clock64() - t0 > kWatchdogCycles) { watchdog_fired(p.status, DEV_TIMEOUT_FLAG, 2, g); break; }
+          }
+        }
+        s_unfinished = *(volatile int*)(p.global_sync + 1);
+      }
+      __syncthreads();
       total = s_unfinished;
       __syncthreads();
       if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
@@ -986,11 +948,11 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
 
   // ---- epilogue: reference-visible state of lanes that sat at their fixed point while the lock-step loop went on,
   // committed h/c back into the caller's arrays (s_state holds the final states: it was refreshed after the last barrier).
-  if (ok && (total >= 0 || left)) {
+  if (ok && total >= 0) {
     for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
       const int n = lane0 + li * lstep;
       const int4 st = s_state[li];
-      if (!left && lane == 0 && (st.x & LS_FIXED)) p.time_idx[n] += total - st.w;      // leavers: done by the last group to arrive
+      if (lane == 0 && (st.x & LS_FIXED)) p.time_idx[n] += total - st.w;
       if (st.x & LS_CUR) {
         for (int k = lane; k < DEC_P; k += 32) {
           p.hg[0][0][(size_t)n * DEC_P + k] = __ldcg(p.hg[1][0] + (size_t)n * DEC_P + k);
@@ -1000,6 +962,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         }
       }
     }
+    if (blockIdx.x == 0 && tid == 0 && p.iters_out) *p.iters_out = total;
   }
 }
 

@@ -230,11 +230,10 @@ struct DecParams {
   float* z;             // [N][J] fp32 : g.W_pred of the current candidate
   int32_t* lane_state;  // [N][4]: flags (1 cur, 2 need_lstm, 4 finished, 8 fixed), cur_t, pre_g, fix_iter
   int32_t* group_cnt;   // [NG][32] barrier arrival counters
-  int32_t* global_sync; // [0] groups done, [1] max iterations, [2 + g] group g left at the rendezvous
+  int32_t* global_sync; // [0] groups done, [1] max iterations
   int32_t* iters_out; int* status;
   int NG, LG;           // groups, lanes per group
   int max_run;          // decisions a lane may take per round without a group barrier (run-ahead through blank frames)
-  int early_exit;       // groups without a lane to replay leave at the rendezvous (results do not depend on it)
   long long* trace;     // optional [iters][8] clock64 stamps of CTA 0 (profiles/trace_decode.py; NULL otherwise)
   int trace_cap;
   int trace_block;      // the CTA whose thread 0 writes the trace (debug build)

@@ -178,7 +178,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
             if (v >= target) break;
             if ((++spins & 63u) == 0) {
               if (*(volatile int*)p.status != DEV_OK) { ok = false; break; }
-              if (clock64() - t0 > kWatchdogCycles) { atomicCAS(p.status, DEV_OK, DEV_TIMEOUT_FLAG); ok = false; break; }
+              if (clock64() - t0 > kWatchdogCycles) { watchdog_fired(p.status, DEV_TIMEOUT_FLAG, 3, t); ok = false; break; }
             }
           }
           if (!ok) break;

@@ -82,9 +82,10 @@ class PytorchSUT:
         if self.pipelined:
             dev = self.model.device
             self._copy_stream = torch.cuda.Stream(dev)
-            # Chunks alternate between two compute streams (each with its own scratch, ops.Workspace): the next chunk's
-            # GEMMs run on the SMs the recurrent kernel leaves idle (128 of 148 CTAs) and on those the decode kernel
-            # frees when all but the replaying lane groups have left (greedy_decode.cu, rendezvous).
+            # Consecutive chunks alternate between two compute streams (each with its own scratch, ops.Workspace): the
+            # GEMMs and byte kernels of one chunk run on the SMs the other chunk's recurrent kernel leaves idle (128 of 148
+            # CTAs).  The library orders the COOPERATIVE kernels (recurrent, decode) of one device whatever stream they come
+            # from (api.cu, CoopOrder), so two of them are never resident together.
             n_streams = max(1, int(kwargs.get("compute_streams", os.environ.get("RNNT_SUT_COMPUTE_STREAMS", 2))))
             self._compute_streams = [torch.cuda.Stream(dev) for _ in range(n_streams)]
             self._launched = 0

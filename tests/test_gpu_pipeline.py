@@ -181,9 +181,11 @@ def test_sut_offline_query_vs_oracle(setup):
             np.testing.assert_array_equal(got[i], o_res[j, :o_len[j]])
 
 
-def test_sut_offline_head_split_vs_oracle(setup):
+@pytest.mark.parametrize("compute_streams", [1, 2])
+def test_sut_offline_head_split_vs_oracle(setup, compute_streams):
     """The pipelined Offline path with the short end of the query cut by frames (sharding.plan_chunks, forced on for this
-    tiny query): every sample answered once, bytes equal to the oracle's in the planner's batches."""
+    tiny query): every sample answered once, bytes equal to the oracle's in the planner's batches.  compute_streams=2:
+    consecutive chunks on alternating streams (their cooperative kernels are ordered by the library)."""
     from rnnt_inference_b200 import loadgen_shim as lg
     from rnnt_inference_b200 import sharding
     from rnnt_inference_b200.pytorch_sut import PytorchSUT
@@ -192,7 +194,7 @@ def test_sut_offline_head_split_vs_oracle(setup):
     feats = [S.make_features(n, 700 + i) for i, n in enumerate(lens)]
     data = {"x": feats, "x_lens": [torch.tensor(n) for n in lens]}
     sut = PytorchSUT(sd, data, 8, "quant", None, enable_bf16=True, scenario="Offline", exact_order=True, head_fraction=0.3,
-                     head_min_frames=0)
+                     head_min_frames=0, compute_streams=compute_streams)
     settings = lg.TestSettings()
     settings.scenario = lg.TestScenario.Offline
     settings.mode = lg.TestMode.AccuracyOnly
