@@ -608,10 +608,11 @@ __device__ __forceinline__ JointRegs load_counters(const DecParams& p, int n, in
   r.ti = __shfl_sync(0xffffffffu, r.ti, 0); r.flen = __shfl_sync(0xffffffffu, r.flen, 0);
   return r;
 }
-__device__ __forceinline__ void store_lane(const DecParams& p, int n, int4 st, JointRegs r, int lane) {
+// `next` = the lane-state copy the NEXT round's scan reads (see the round loop: the states are double-buffered)
+__device__ __forceinline__ void store_lane(const DecParams& p, int32_t* next, int n, int4 st, JointRegs r, int lane) {
   if (lane == 0) {
     p.symbols_added[n] = r.sa; p.res_idx[n] = r.ri; p.time_idx[n] = r.ti; p.pre_g[n] = st.z;
-    *reinterpret_cast<int4*>(p.lane_state + (size_t)n * 4) = st;
+    *reinterpret_cast<int4*>(next + (size_t)n * 4) = st;
   }
 }
 // may this lane take decisions in this round?  phase 1 (total < 0): every unfinished lane; replay phase: the lanes that
@@ -731,6 +732,13 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
   group_barrier(p, g, epoch, ok, &s_fail);
 
   int round = 0;
+  // Lane states are double-buffered by round parity: the scan of a round reads copy `par`, the decisions of the round write
+  // copy `par ^ 1` (every CTA carries the states of its lanes that took no decision forward).  A round without prediction
+  // work has no group barrier between the scan and the decisions, so with a single copy a CTA that is a few microseconds
+  // late in its scan could read a state another CTA has already advanced, build a different work list and fall out of
+  // step with its group; with two copies the scan of round r never sees a store of round r (and a CTA cannot be two rounds
+  // ahead: one barrier per round).
+  int par = 0;
   int total = -1;         // batch-lockstep iteration count of the reference loop; unknown during phase 1
   bool w2_valid = false;
   for (;;) {
@@ -745,7 +753,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       const int li = b * 32 + lane;
       int need = 0, unfin = 0, live = 0, dc = 0;
       if (li < nl) {
-        const int4 st = __ldcg(reinterpret_cast<const int4*>(p.lane_state + (size_t)(lane0 + li * lstep) * 4));
+        const int4 st = __ldcg(reinterpret_cast<const int4*>(p.lane_state + ((size_t)par * p.N + lane0 + li * lstep) * 4));
         s_state[li] = st;
         const bool replay = total >= 0 && (st.x & LS_FINISHED) && !(st.x & LS_FIXED) && st.w < total;
         unfin = !(st.x & LS_FINISHED);
@@ -822,6 +830,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       if (tr) trow[4] = clock64();
     }
     int decisions = 0;
+    int32_t* const ls_next = p.lane_state + (size_t)(par ^ 1) * p.N * 4;
     if constexpr (TC) {
       // ---- phase D on the tensor cores: this CTA's lanes li = s + 20 j (j < 16) form ONE m16 tile; warp w drives the
       // lanes j = w and w + 8.  Sub-iteration: every running lane stages y of its current frame as a row of a [16][512]
@@ -841,6 +850,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
         if (li < nl) {
           st2[h] = s_state[li];
           run[h] = runnable(st2[h], total);
+          if (!run[h] && lane == 0) *reinterpret_cast<int4*>(ls_next + (size_t)(lane0 + li * lstep) * 4) = st2[h];      // carried forward
         }
         if (run[h]) {
           const int n = lane0 + li * lstep;
@@ -894,7 +904,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
               yv[h][0] = yn[h][0]; yv[h][1] = yn[h][1];
               load_y1(p, n, min(st2[h].y + 1, p.T2 - 1), yn[h], lane);
             }
-            if (!run[h]) store_lane(p, n, st2[h], jr[h], lane);
+            if (!run[h]) store_lane(p, ls_next, n, st2[h], jr[h], lane);
           }
         }
         if (tr && first_it) trow[14] = clock64();
@@ -916,8 +926,11 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
       uint16_t* ybuf = jy + warp * DEC_J;
       for (int li = s + warp * DEC_S; li < nl; li += DEC_S * DEC_WARPS) {
         int4 st = s_state[li];
-        if (!runnable(st, total)) continue;
         const int n = lane0 + li * lstep;
+        if (!runnable(st, total)) {
+          if (lane == 0) *reinterpret_cast<int4*>(ls_next + (size_t)n * 4) = st;      // carried forward
+          continue;
+        }
         JointRegs jr = load_counters(p, n, lane);
         float zf[16]; uint4 yv[2];
 #pragma unroll
@@ -938,11 +951,12 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
           if (go && st.y != t_before) load_y1(p, n, st.y, yv, lane);
           __syncwarp();
         }
-        store_lane(p, n, st, jr, lane);
+        store_lane(p, ls_next, n, st, jr, lane);
       }
     }
     if (tr) { trow[5] = clock64(); trow[8] = decisions; }
     group_barrier(p, g, epoch, ok, &s_fail);
+    par ^= 1;
     if (tr) trow[6] = clock64();
   }
 

@@ -228,7 +228,7 @@ struct DecParams {
   float* cg[2][2];
   // workspace
   float* z;             // [N][J] fp32 : g.W_pred of the current candidate
-  int32_t* lane_state;  // [N][4]: flags (1 cur, 2 need_lstm, 4 finished, 8 fixed), cur_t, pre_g, fix_iter
+  int32_t* lane_state;  // [2][N][4]: flags (1 cur, 2 need_lstm, 4 finished, 8 fixed), cur_t, pre_g, fix_iter; double-buffered by round parity
   int32_t* group_cnt;   // [NG][32] barrier arrival counters
   int32_t* global_sync; // [0] groups done, [1] max iterations
   int32_t* iters_out; int* status;
