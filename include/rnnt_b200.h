@@ -34,8 +34,13 @@ const char* rnnt_last_error(void);
 int rnnt_abi_version(void);
 int rnnt_device_sm_count(void);
 /* Kernels run asynchronously on `stream`; their device-side watchdogs (a protocol error ends the kernel
- * instead of hanging the GPU) record a code in a 4-byte status word owned by the library.  This call
- * synchronises `stream`, returns RNNT_ERR_DEVICE if a code was recorded, and clears it. */
+ * instead of hanging the GPU) record a code in a status block owned by the library (first word; the wait that fired
+ * first also leaves its site, CTA and epoch, which the error message reports).  This call synchronises `stream`, returns
+ * RNNT_ERR_DEVICE if a code was recorded, and clears it.
+ * Streams: every entry point may be called on any stream.  The two cooperative kernels (rnnt_lstm_recurrent_i8*,
+ * rnnt_greedy_decode*) are ordered per device by the library itself — each waits (cudaStreamWaitEvent) for the one
+ * launched before it, whatever stream that was on — because two grids that wait on flags of their own CTAs must never be
+ * resident half each; every other kernel overlaps freely. */
 int rnnt_check_device_status(void* stream);
 /* Non-synchronising pair for pipelined callers (the SUT): enqueue a copy of the status word into *host_dst (pinned host
  * int32) on `stream`, look at it after the caller's own synchronisation point; non-zero = a watchdog fired and every
