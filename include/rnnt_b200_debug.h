@@ -21,6 +21,10 @@ int rnnt_debug_set_gemm_flags(int flags);
 int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters);
 /* which CTA writes the decode trace (default 0; CTA 20 g + s is CTA s of lane group g) */
 int rnnt_debug_set_decode_trace_block(int block);
+/* TEST ONLY: CTA 1 of every decode lane group idles `cycles` before each scan of the lane states, i.e. scans while the
+ * other CTAs of its group may already be taking the round's decisions.  Results must not change (the lane states are
+ * double-buffered by round parity); 0 = off. */
+int rnnt_debug_set_decode_skew(int cycles);
 #ifdef __cplusplus
 }
 #endif

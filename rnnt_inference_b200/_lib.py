@@ -80,6 +80,7 @@ _DEBUG_SIGS = {
     "rnnt_debug_set_recurrent_flags": (_i, [_i]),
     "rnnt_debug_set_decode_trace": (_i, [_vp, _i]),
     "rnnt_debug_set_decode_trace_block": (_i, [_i]),
+    "rnnt_debug_set_decode_skew": (_i, [_i]),
     "rnnt_debug_set_gemm_flags": (_i, [_i]),
 }
 for _name, (_res, _args) in _SIGS.items():

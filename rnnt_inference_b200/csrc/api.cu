@@ -887,8 +887,9 @@ int rnnt_lstm_layer_i8(const int8_t* x, int8_t* hx, uint16_t* cx, const int8_t* 
 //                            hg1 [2][N][320] bf16 | cg1 [2][N][320] f32
 #ifdef RNNT_DEBUG_HOOKS
 static long long* g_dec_trace = nullptr;
-static int g_dec_trace_cap = 0, g_dec_trace_block = 0;
+static int g_dec_trace_cap = 0, g_dec_trace_block = 0, g_dec_skew = 0;
 int rnnt_debug_set_decode_trace_block(int block) { g_dec_trace_block = block; return RNNT_OK; }
+int rnnt_debug_set_decode_skew(int cycles) { g_dec_skew = cycles; return RNNT_OK; }
 int rnnt_debug_set_decode_trace(void* device_buffer, int max_iters) {
   g_dec_trace = reinterpret_cast<long long*>(device_buffer); g_dec_trace_cap = max_iters; return RNNT_OK;
 }
@@ -942,9 +943,9 @@ static int decode_run(bool tensor_cores, const uint16_t* y1, const int32_t* f_le
   static const int max_run = [] { const char* e = getenv("RNNT_DEC_MAX_RUN"); const int v = e ? atoi(e) : 4; return v > 0 ? v : 4; }();   // measured: 2048-lane batch 11.3 / 11.6 / 12.5 / 15.0 ms for 4 / 8 / 16 / 64
   p.max_run = max_run;      // tuning knob (results do not depend on it)
 #ifdef RNNT_DEBUG_HOOKS
-  p.trace = g_dec_trace; p.trace_cap = g_dec_trace_cap; p.trace_block = g_dec_trace_block;
+  p.trace = g_dec_trace; p.trace_cap = g_dec_trace_cap; p.trace_block = g_dec_trace_block; p.skew = g_dec_skew;
 #else
-  p.trace = nullptr; p.trace_cap = 0; p.trace_block = 0;
+  p.trace = nullptr; p.trace_cap = 0; p.trace_block = 0; p.skew = 0;
 #endif
   CUDA_TRY(cudaMemsetAsync(ws, 0, 256 + 1024, st));
   const void* kern = tensor_cores ? (const void*)greedy_decode_kernel<true> : (const void*)greedy_decode_kernel<false>;

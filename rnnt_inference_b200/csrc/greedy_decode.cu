@@ -747,6 +747,12 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) greedy_decode_kernel(const Dec
     // the critical path of every round (a lane that emits symbol after symbol is a chain of rounds), so it is two
     // barriers deep: warp w scans the 32-lane blocks w, w + 8 straight from global memory, the per-block results go
     // through shared memory, every thread sums the <= 10 of them.
+#ifdef RNNT_DEBUG_HOOKS
+    if (p.skew > 0 && s == 1) {       // one CTA of the group scans late: the other CTAs' decisions of this round are under way
+      const long long t0 = clock64();
+      while (clock64() - t0 < p.skew) {}
+    }
+#endif
     const int nblk = (nl + 31) >> 5;
     bool need_r[2] = {false, false};
     for (int b = warp, i = 0; b < nblk; b += DEC_WARPS, ++i) {

@@ -237,6 +237,7 @@ struct DecParams {
   long long* trace;     // optional [iters][8] clock64 stamps of CTA 0 (profiles/trace_decode.py; NULL otherwise)
   int trace_cap;
   int trace_block;      // the CTA whose thread 0 writes the trace (debug build)
+  int skew;             // debug build: CTA 1 of every lane group idles this many cycles before each scan (tests/test_gpu_decode_skew.py)
 };
 
 // tensor-core variant: bf16 weights / activations as XOR-swizzled 16-byte chunks (conflict-free ldmatrix), no row padding
