@@ -615,16 +615,16 @@ int64_t rnnt_lstm_recurrent_workspace_bytes(int N) {
 // Launch with `cs` slice-CTAs per thread-block cluster (h tiles are TMA-multicast inside a cluster).  Cooperative so that
 // all CTAs are co-resident (they exchange h through per-tile counters).  Returns cudaErrorCooperativeLaunchTooLarge /
 // cluster errors to the caller, which falls back to a smaller cluster.
-template <int CS>
+template <int CS, int HS>
 static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th,
                                  const RecParams& p, int num_slices, int grid_y, cudaStream_t st) {
-  auto kern = lstm_recurrent_kernel<CS>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, RecSmem::TOTAL);   // per device
+  auto kern = lstm_recurrent_kernel<CS, HS>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, RecSmemT<HS>::TOTAL);   // per device
   if (e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(num_slices, grid_y);
   cfg.blockDim = dim3(REC_THREADS);
-  cfg.dynamicSmemBytes = RecSmem::TOTAL;
+  cfg.dynamicSmemBytes = RecSmemT<HS>::TOTAL;
   cfg.stream = st;
   cudaLaunchAttribute attrs[2];
   int na = 0;
@@ -636,15 +636,21 @@ static cudaError_t rec_launch_cs(const CUtensorMap& tw, const CUtensorMap& th0, 
   cfg.attrs = attrs; cfg.numAttrs = na;
   return cudaLaunchKernelEx(&cfg, kern, tw, th0, th, p);
 }
-static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th,
-                      const RecParams& p, int num_slices, int grid_y, int cs_max, cudaStream_t st) {
+template <int HS>
+static int rec_launch_hs(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th,
+                         const RecParams& p, int num_slices, int grid_y, int cs_max, cudaStream_t st) {
   cudaError_t e = cudaErrorUnknown;
-  if (cs_max >= 8) { e = rec_launch_cs<8>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
-  if (cs_max >= 4) { e = rec_launch_cs<4>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
-  if (cs_max >= 2) { e = rec_launch_cs<2>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
-  e = rec_launch_cs<1>(tw, th0, th, p, num_slices, grid_y, st);
+  if (cs_max >= 8) { e = rec_launch_cs<8, HS>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  if (cs_max >= 4) { e = rec_launch_cs<4, HS>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  if (cs_max >= 2) { e = rec_launch_cs<2, HS>(tw, th0, th, p, num_slices, grid_y, st); if (e == cudaSuccess) return RNNT_OK; cudaGetLastError(); }
+  e = rec_launch_cs<1, HS>(tw, th0, th, p, num_slices, grid_y, st);
   if (e != cudaSuccess) return fail(RNNT_ERR_CUDA, "lstm_recurrent launch failed: %s", cudaGetErrorString(e));
   return RNNT_OK;
+}
+static int rec_launch(const CUtensorMap& tw, const CUtensorMap& th0, const CUtensorMap& th,
+                      const RecParams& p, int hs, int grid_y, int cs_max, cudaStream_t st) {
+  return hs == 16 ? rec_launch_hs<16>(tw, th0, th, p, REC_H / 16, grid_y, cs_max, st)
+                  : rec_launch_hs<32>(tw, th0, th, p, REC_H / 32, grid_y, cs_max, st);
 }
 
 static int g_rec_cluster = -1;
@@ -726,12 +732,16 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
   CUDA_TRY(cudaMemsetAsync(flags, 0, rec_flags_bytes(N), st));
   uint16_t* c_ws = reinterpret_cast<uint16_t*>(h_buf + 2 * n_pad * REC_H);
 
-  const int num_slices = REC_H / REC_HS;
-  const int grid_y = num_btiles < REC_GRID_Y ? num_btiles : REC_GRID_Y;
+  // Batches of <= 4 tiles run ONE dependency chain per tile group and timestep: there the kernel with 16-unit slices
+  // (64 slice CTAs x 2 tile groups, 7 ring slots, 4 units per epilogue thread) has the shorter chain (kernels.cuh).
+  static const bool hs16_ok = [] { const char* e = getenv("RNNT_REC_HS16"); return e ? atoi(e) != 0 : true; }();
+  const int hs = (!status_word && hs16_ok && num_btiles <= 4) ? 16 : REC_HS;
+  const int max_groups = hs == 16 ? 2 : REC_GRID_Y;
+  const int grid_y = num_btiles < max_groups ? num_btiles : max_groups;
   CUtensorMap tw, th0, th;
   {   // W_hh [4 gates][1024 units][1024 k]: box = 128 B of k x 32 units x 4 gates
     uint64_t dims[3] = {REC_H, REC_H, 4}, str[2] = {REC_H, (uint64_t)REC_H * REC_H};
-    uint32_t box[3] = {128, (uint32_t)REC_HS, 4};
+    uint32_t box[3] = {128, (uint32_t)hs, 4};
     if (int r = make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, w_hh, dims, str, box)) return r;
   }
   {   // h_0 = the caller's hx [N][1024] (rows >= N read as zero)
@@ -793,11 +803,11 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
   p.debug = 0;
 #endif
   if (status_word) {      // static-scratch entry point: no library state is created; overlapping calls race by contract
-    if (int r = rec_launch(tw, th0, th, p, num_slices, used_groups, rec_cluster_pref(), st)) return r;
+    if (int r = rec_launch(tw, th0, th, p, hs, used_groups, rec_cluster_pref(), st)) return r;
   } else {
     CoopOrder order;
     if (int r = order.begin(st)) return r;
-    const int r = rec_launch(tw, th0, th, p, num_slices, used_groups, rec_cluster_pref(), st);
+    const int r = rec_launch(tw, th0, th, p, hs, used_groups, rec_cluster_pref(), st);
     const int r2 = order.end();
     if (r) return r;
     if (r2) return r2;

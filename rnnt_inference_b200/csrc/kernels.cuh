@@ -99,7 +99,6 @@ constexpr int REC_H = 1024;
 constexpr int REC_BM = 128;          // batch rows per tile (UMMA M)
 constexpr int REC_HS = 32;           // hidden units per slice CTA (all four gates: UMMA N = 128)
 constexpr int REC_KC = 8;            // K chunks of 128 bytes per tile
-constexpr int REC_NS = 3;            // stages of the h operand ring (16 KB each; measured: depth 3..8 makes no difference)
 constexpr int REC_TAB_N = 0x44FA;    // entries of the fp16 activation table: |x| bit patterns 0 .. 0x44F9 (4.97 = 0x44F8)
 constexpr int REC_CTRL_WARPS = 4;    // 0: TMA producer, 1: MMA issuer, 2: TMEM alloc, 3: publisher
 constexpr int REC_EPI_WARPS = 16;
@@ -109,23 +108,32 @@ constexpr int REC_FLAG_STRIDE = 32;  // ints between per-tile counters (128 B)
 constexpr int REC_MAX_TILES = 32;    // batch tiles per launch (N <= 4096)
 constexpr int REC_GRID_Y = 4;        // batch-tile groups: 32 slices x 4 = 128 CTAs
 
-struct RecSmem {
-  static constexpr int UMMA_N = 4 * REC_HS;               // 128
-  static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice (16 KB)
-  static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 128 KB
+// HS = hidden units per slice CTA.  32 (UMMA N = 128; 32 slices x 4 tile groups) is the throughput configuration.  16 (UMMA
+// N = 64; 64 slices x 2 tile groups) serves batches of <= 4 tiles, where every tile group runs ONE dependency chain per
+// timestep: half the W slice leaves room for 7 ring slots instead of 3 (the h ingest is bound by bytes in flight,
+// profiles/r02/rec_trace_chain_mode.txt), and a thread's gate math covers 4 units instead of 8.
+template <int HS>
+struct RecSmemT {
+  static constexpr int NS = HS == 32 ? 3 : 7;             // stages of the h operand ring (16 KB each)
+  static constexpr int UMMA_N = 4 * HS;                   // 128 | 64
+  static constexpr int UPT = HS / 4;                      // hidden units per epilogue thread: 8 | 4
+  static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice (16 | 8 KB)
+  static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 128 | 64 KB
   static constexpr int H_CHUNK = REC_BM * 128;            // 16 KB
-  static constexpr int H_BYTES = REC_NS * H_CHUNK;        // 48 KB
+  static constexpr int H_BYTES = NS * H_CHUNK;            // 48 | 112 KB
   static constexpr int OUT_OFFSET = W_BYTES + H_BYTES;    // staging of h (int8) and y (int8 | bf16) rows, one item deep;
   static constexpr int OUT_H = 8 * REC_BM * 4;            // [unit quad][row] 4 B  = 4 KB     (the rcp LUT lives here during set-up)
   static constexpr int OUT_Y = 8 * REC_BM * 8;            // [unit quad][row] 8 B  = 8 KB
   static constexpr int OUT_STAGE = OUT_H + OUT_Y;
   static constexpr int LUT_OFFSET = OUT_OFFSET;
-  static constexpr int BIAS_OFFSET = OUT_OFFSET + OUT_STAGE;         // [4 gates][32 units] fp32
+  static constexpr int BIAS_OFFSET = OUT_OFFSET + OUT_STAGE;         // [4 gates][HS units] fp32
   static constexpr int TAB_OFFSET = BIAS_OFFSET + 512;               // whole-function table of the Pade tanh kernel
   static constexpr int TAB_BYTES = (REC_TAB_N * 2 + 15) / 16 * 16;   // 35,328
   static constexpr int BAR_OFFSET = TAB_OFFSET + TAB_BYTES;
   static constexpr int TOTAL = BAR_OFFSET + 512;          // barriers/counters + two int[32] tables (the window itself is 1024-byte aligned)
 };
+using RecSmem = RecSmemT<REC_HS>;
+static_assert(RecSmemT<16>::TOTAL <= 232448, "recurrent kernel shared memory (HS = 16)");
 static_assert(RecSmem::TOTAL <= 232448, "recurrent kernel shared memory");
 
 struct RecParams {
@@ -149,7 +157,7 @@ struct RecParams {
   long long* trace;        // optional [T][16] clock64 stamps of CTA (0,0) (profiles/trace_recurrent.py; NULL otherwise)
 };
 
-template <int CS>
+template <int CS, int HS = REC_HS>
 __global__ void lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h0,
                                       const __grid_constant__ CUtensorMap tmap_h, const RecParams p);
 

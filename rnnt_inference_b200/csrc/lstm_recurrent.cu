@@ -67,17 +67,23 @@ struct ItemCursor {
   }
 };
 
-__device__ __forceinline__ void ldg256_stream(const int32_t* ptr, int (&v)[8]) {
+__device__ __forceinline__ void ldg_units_stream(const int32_t* ptr, int (&v)[8]) {
   asm volatile("ld.global.nc.L1::no_allocate.v8.s32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "l"(ptr));
 }
+__device__ __forceinline__ void ldg_units_stream(const int32_t* ptr, int (&v)[4]) {
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "l"(ptr));
+}
 
-template <int CS>
+template <int CS, int HS>
 __global__ void __launch_bounds__(REC_THREADS, 1)
 lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h0,
                       const __grid_constant__ CUtensorMap tmap_h, const RecParams p) {
-  using S = RecSmem;
-  constexpr int HS = REC_HS;
+  using S = RecSmemT<HS>;
+  constexpr int NS = S::NS;
+  constexpr int UPT = S::UPT;              // hidden units per epilogue thread (8 | 4), processed as pairs
+  constexpr int SPC = 128 / HS;            // slices per 128-byte K chunk of the h tile (4 | 8)
   constexpr uint16_t MC_MASK = (uint16_t)((1u << CS) - 1u);
   // 1024-byte alignment is declared (the dynamic window starts on such a boundary) rather than fixed up at run time, so
   // every shared-memory address below is base-constant + offset and folds into the instructions' immediate fields.
@@ -94,18 +100,18 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   uint16_t* lut = reinterpret_cast<uint16_t*>(smem_gen + S::LUT_OFFSET);
   const uint32_t tab = smem_base + S::TAB_OFFSET;
   const uint32_t bar_base = smem_base + S::BAR_OFFSET;
-  const uint32_t full_bar = bar_base;                  // [REC_NS] h chunk landed (TMA complete_tx)
-  const uint32_t empty_bar = bar_base + 48;            // [REC_NS] h chunk consumed by the MMAs of all CS CTAs
-  const uint32_t outfree_bar = bar_base + 96;          // staging buffer read by the storing warps (one item deep)
-  const uint32_t tfull_bar = bar_base + 128;           // [2] accumulator complete
-  const uint32_t done_bar = bar_base + 144;            // [2] item finished by all epilogue warps (frees the accumulator)
-  const uint32_t staged_bar = bar_base + 160;          // [2] h / y rows of the item staged in shared memory
-  const uint32_t wfull_bar = bar_base + 176;
-  const uint32_t tmem_slot = bar_base + 184;
+  const uint32_t full_bar = bar_base;                  // [NS] h chunk landed (TMA complete_tx)
+  const uint32_t empty_bar = bar_base + 64;            // [NS] h chunk consumed by the MMAs of all CS CTAs
+  const uint32_t outfree_bar = bar_base + 128;         // staging buffer read by the storing warps (one item deep)
+  const uint32_t tfull_bar = bar_base + 144;           // [2] accumulator complete
+  const uint32_t done_bar = bar_base + 160;            // [2] item finished by all epilogue warps (frees the accumulator)
+  const uint32_t staged_bar = bar_base + 176;          // [2] h / y rows of the item staged in shared memory
+  const uint32_t wfull_bar = bar_base + 192;
+  const uint32_t tmem_slot = bar_base + 200;
   int* s_steps = reinterpret_cast<int*>(smem_gen + S::BAR_OFFSET + 208);   // [REC_MAX_TILES]
   int* s_tile = s_steps + REC_MAX_TILES;                                   // [REC_MAX_TILES] tile ids of this group
   float* s_bias = reinterpret_cast<float*>(smem_gen + S::BIAS_OFFSET);     // [gate][unit of the slice]
-  static_assert(REC_NS * 8 <= 48, "barrier layout");
+  static_assert(NS * 8 <= 64 && 208 + 2 * REC_MAX_TILES * 4 <= 512, "barrier layout");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x;
@@ -128,7 +134,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_h0); tma_prefetch_desc(&tmap_h);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < REC_NS; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CS); }
+    for (int i = 0; i < NS; ++i) { mbar_init(full_bar + 8 * i, 1); mbar_init(empty_bar + 8 * i, CS); }
     mbar_init(outfree_bar, 2);
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull_bar + 8 * i, 1);
@@ -188,7 +194,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (tracer && cur.i == 0) trace[t * 16 + 0] = clock64();
         const int hrow0 = (((t & 1) * p.num_btiles + bt) * REC_KC) * REC_BM;   // row of chunk 0 in the chunk-major h buffer
         for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
-          const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
+          const uint32_t st = chunk % NS, ph = (chunk / NS) & 1u;
           // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
           if (!mbar_wait(empty_bar + 8 * st, ph ^ 1u, p.status)) { ok = false; break; }
           if (RNNT_DBG(p, 4)) { mbar_arrive(full_bar + 8 * st); continue; }
@@ -221,7 +227,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * S::UMMA_N;
         for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
-          const uint32_t st = chunk % REC_NS, ph = (chunk / REC_NS) & 1u;
+          const uint32_t st = chunk % NS, ph = (chunk / NS) & 1u;
           if (mtr) c0 = clock64();
           if (!mbar_wait(full_bar + 8 * st, ph, p.status)) { ok = false; break; }
           if (mtr) w_full += clock64() - c0;
@@ -256,18 +262,19 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       const bool tr = tracer && cur.i == 0 && sw == 0 && lane == 0;
       if (!mbar_wait(staged_bar + 8 * acc, acc_phase, p.status)) break;
       const uint32_t out_h = smem_out, out_y = out_h + S::OUT_H;
-      uint32_t hw[2][8], yw[2][16];
+      constexpr int QUADS = HS / 4;          // unit quads of the slice = 32-bit words of int8 h per row (8 | 4)
+      uint32_t hw[2][QUADS], yw[2][2 * QUADS];
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
         const int row = sw * 64 + r * 32 + lane;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) hw[r][i] = lds32(out_h + (uint32_t)(i * REC_BM + row) * 4u);
+        for (int i = 0; i < QUADS; ++i) hw[r][i] = lds32(out_h + (uint32_t)(i * REC_BM + row) * 4u);
         if (p.skip_quant_y) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) { const uint2 v = lds64(out_y + (uint32_t)(i * REC_BM + row) * 8u); yw[r][2 * i] = v.x; yw[r][2 * i + 1] = v.y; }
+          for (int i = 0; i < QUADS; ++i) { const uint2 v = lds64(out_y + (uint32_t)(i * REC_BM + row) * 8u); yw[r][2 * i] = v.x; yw[r][2 * i + 1] = v.y; }
         } else {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) yw[r][i] = lds32(out_y + (uint32_t)(i * REC_BM + row) * 4u);
+          for (int i = 0; i < QUADS; ++i) yw[r][i] = lds32(out_y + (uint32_t)(i * REC_BM + row) * 4u);
         }
       }
       __syncwarp();
@@ -280,14 +287,14 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         // A tile that runs a single step keeps its final h in the ping-pong buffer too: other slice CTAs may still be
         // reading h_0 from hx (nothing orders t = 0 across CTAs); rec_copy_h1_kernel moves it to hx after the launch.
         if (!last || t == 0) {
-          uint4* hn = reinterpret_cast<uint4*>(p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + (slice >> 2)) * REC_BM + row) * 128 +
-                                               (slice & 3) * HS);
-          hn[0] = make_uint4(hw[r][0], hw[r][1], hw[r][2], hw[r][3]);
-          hn[1] = make_uint4(hw[r][4], hw[r][5], hw[r][6], hw[r][7]);
+          uint4* hn = reinterpret_cast<uint4*>(p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + slice / SPC) * REC_BM + row) * 128 +
+                                               (slice % SPC) * HS);
+#pragma unroll
+          for (int i = 0; i < QUADS / 4; ++i) hn[i] = make_uint4(hw[r][4 * i], hw[r][4 * i + 1], hw[r][4 * i + 2], hw[r][4 * i + 3]);
         } else if (n < p.N) {   // last step of this tile: hand the state back to the caller's hx
           uint4* hp = reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS);
-          hp[0] = make_uint4(hw[r][0], hw[r][1], hw[r][2], hw[r][3]);
-          hp[1] = make_uint4(hw[r][4], hw[r][5], hw[r][6], hw[r][7]);
+#pragma unroll
+          for (int i = 0; i < QUADS / 4; ++i) hp[i] = make_uint4(hw[r][4 * i], hw[r][4 * i + 1], hw[r][4 * i + 2], hw[r][4 * i + 3]);
         }
       }
       if (tr) trace[t * 16 + 5] = clock64();
@@ -311,11 +318,11 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
           if (p.skip_quant_y) {
             uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.y) + yoff);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) yp[i] = make_uint4(yw[r][4 * i], yw[r][4 * i + 1], yw[r][4 * i + 2], yw[r][4 * i + 3]);
+            for (int i = 0; i < QUADS / 2; ++i) yp[i] = make_uint4(yw[r][4 * i], yw[r][4 * i + 1], yw[r][4 * i + 2], yw[r][4 * i + 3]);
           } else {
             uint4* yp = reinterpret_cast<uint4*>(reinterpret_cast<int8_t*>(p.y) + yoff);
-            yp[0] = make_uint4(yw[r][0], yw[r][1], yw[r][2], yw[r][3]);
-            yp[1] = make_uint4(yw[r][4], yw[r][5], yw[r][6], yw[r][7]);
+#pragma unroll
+            for (int i = 0; i < QUADS / 4; ++i) yp[i] = make_uint4(yw[r][4 * i], yw[r][4 * i + 1], yw[r][4 * i + 2], yw[r][4 * i + 3]);
           }
         }
       }
@@ -325,49 +332,62 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     // ---------------------------------------------------------------- epilogue: gates, cell update, outputs
     const int e = warp - REC_CTRL_WARPS;
     const int q = warp & 3;                 // TMEM lane quarter accessible to this warp (warp id % 4)
-    const int ug = e >> 2;                  // unit group within the slice (8 units each, processed as two quads)
+    const int ug = e >> 2;                  // unit group within the slice (UPT = 8 | 4 units each, processed as quads)
     const int row = q * 32 + lane;          // batch row within the tile
-    const int j0 = slice * HS + ug * 8;     // first hidden unit of this thread
+    const int j0 = slice * HS + ug * UPT;   // first hidden unit of this thread
     const HalfConsts k = make_half_consts();
     const __half2 in_s = __float2half2_rn(p.in_scale), out_s = __float2half2_rn(p.out_scale);
     const bool same_scale = h2_bits(in_s) == h2_bits(out_s);
-    const uint32_t bias_s = smem_base + S::BIAS_OFFSET + (uint32_t)(ug * 8) * 4u;
+    const uint32_t bias_s = smem_base + S::BIAS_OFFSET + (uint32_t)(ug * UPT) * 4u;
 
     // c of an item: t == 0 from the caller's cx, else from the blocked scratch this same thread wrote one step earlier.
     // It is fetched one item ahead (cn) so that its L2 latency hides behind the previous item's gate math; when the next
     // item is the same tile (a CTA with one live tile) the freshly computed value is carried in registers instead.
+    struct CVec { uint32_t w[UPT / 2]; };      // UPT binary16 values: one 16- or 8-byte access
     auto c_scratch = [&](int bt_) {
-      return p.c_ws + ((((size_t)bt_ * (REC_H / HS) + slice) * 4 + ug) * REC_BM + row) * 8;
+      return p.c_ws + ((((size_t)bt_ * (REC_H / HS) + slice) * 4 + ug) * REC_BM + row) * UPT;
     };
-    auto load_c = [&](int t_, int bt_, uint4& c) {
+    auto ld_c = [&](const uint16_t* src, CVec& c) {
+      if constexpr (UPT == 8) { const uint4 v = *reinterpret_cast<const uint4*>(src); c.w[0] = v.x; c.w[1] = v.y; c.w[2] = v.z; c.w[3] = v.w; }
+      else { const uint2 v = *reinterpret_cast<const uint2*>(src); c.w[0] = v.x; c.w[1] = v.y; }
+    };
+    auto st_c = [&](uint16_t* dst, const CVec& c) {
+      if constexpr (UPT == 8) *reinterpret_cast<uint4*>(dst) = make_uint4(c.w[0], c.w[1], c.w[2], c.w[3]);
+      else *reinterpret_cast<uint2*>(dst) = make_uint2(c.w[0], c.w[1]);
+    };
+    auto load_c = [&](int t_, int bt_, CVec& c) {
       if (t_ == 0) {
         const int n_ = bt_ * REC_BM + row;
-        c = (n_ < p.N) ? *reinterpret_cast<const uint4*>(p.cx + (size_t)n_ * REC_H + j0) : make_uint4(0u, 0u, 0u, 0u);
+        if (n_ < p.N) ld_c(p.cx + (size_t)n_ * REC_H + j0, c);
+        else {
+#pragma unroll
+          for (int i = 0; i < UPT / 2; ++i) c.w[i] = 0u;
+        }
       } else {
-        c = *reinterpret_cast<const uint4*>(c_scratch(bt_));
+        ld_c(c_scratch(bt_), c);
       }
     };
     // G of an item (this row's input projection, one full sector per gate) does not depend on the recurrent product: it
     // is requested before the wait for the accumulator.  (Fetching it a whole item ahead was measured slower.)
-    int gi[4][8];
+    int gi[4][UPT];
     auto load_g = [&](int t_, int bt_) {
       const int n_ = bt_ * REC_BM + row;
       if (n_ < p.N && !RNNT_DBG(p, 64)) {
-        if (p.g_blocked) {      // a warp's 32 rows are 1 KB contiguous: 8 lines per load instead of 32
+        if (p.g_blocked) {      // [32-unit slice][gate][unit octet][row][8]: a warp's 32 rows are 1 KB contiguous per octet
           const size_t rows = (size_t)p.T * p.N;
-          const int32_t* gp = p.g + (((size_t)slice * 16 + ug) * rows + (size_t)t_ * p.N + n_) * 8;
+          const int32_t* gp = p.g + (((size_t)(j0 >> 5) * 16 + ((j0 & 31) >> 3)) * rows + (size_t)t_ * p.N + n_) * 8 + (j0 & 7);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) ldg256_stream(gp + (size_t)g * 4 * rows * 8, gi[g]);
+          for (int g = 0; g < 4; ++g) ldg_units_stream(gp + (size_t)g * 4 * rows * 8, gi[g]);
         } else {
           const int32_t* gp = p.g + ((size_t)t_ * p.N + n_) * (4 * REC_H) + j0;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) ldg256_stream(gp + g * REC_H, gi[g]);
+          for (int g = 0; g < 4; ++g) ldg_units_stream(gp + g * REC_H, gi[g]);
         }
       } else {
 #pragma unroll
         for (int g = 0; g < 4; ++g)
 #pragma unroll
-          for (int u = 0; u < 8; ++u) gi[g][u] = 0;
+          for (int u = 0; u < UPT; ++u) gi[g][u] = 0;
       }
     };
     int acc = 0; uint32_t acc_phase = 0, item = 0;
@@ -375,14 +395,18 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
     bool have = cur.next(p.T, my_tiles, s_tile, s_steps);
     bool have_next = nxt.next(p.T, my_tiles, s_tile, s_steps);     // nxt runs one item ahead of cur
     if (have_next) have_next = nxt.next(p.T, my_tiles, s_tile, s_steps);
-    uint4 cn = make_uint4(0u, 0u, 0u, 0u);
+    CVec cn;
+#pragma unroll
+    for (int i = 0; i < UPT / 2; ++i) cn.w[i] = 0u;
     if (have) load_c(cur.t, s_tile[cur.i], cn);
     for (; have; have = cur.next(p.T, my_tiles, s_tile, s_steps), ++item) {
       const int t = cur.t, bt = s_tile[cur.i];
       const int steps = s_steps[bt];
       const int n = bt * REC_BM + row;
       const bool valid = n < p.N;
-      uint32_t cbits[4] = {cn.x, cn.y, cn.z, cn.w};
+      uint32_t cbits[UPT / 2];
+#pragma unroll
+      for (int i = 0; i < UPT / 2; ++i) cbits[i] = cn.w[i];
       const bool carry = have_next && (s_tile[nxt.i]) == bt;       // next item = next step of this very tile
       if (have_next && !carry) load_c(nxt.t, s_tile[nxt.i], cn);
       const bool tr = tracer && cur.i == 0 && e == 0 && lane == 0;
@@ -391,20 +415,26 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       if (!mbar_wait(tfull_bar + 8 * acc, acc_phase, p.status)) break;
       if (tr) { trace[t * 16 + 3] = clock64(); trace[t * 16 + 11] = clock64() - f0; }
       tc_fence_after();
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * 8);
-      uint32_t hq_pack[2] = {0u, 0u}, yq_pack[2] = {0u, 0u};
-      uint32_t ybf[4];
-      // all eight units of the thread at once: four independent (pair) chains keep the table-lookup latency covered
-      __half2 gate[4][4];
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * S::UMMA_N + ug * UPT);
+      uint32_t hq_pack[UPT / 4], yq_pack[UPT / 4];
+#pragma unroll
+      for (int i = 0; i < UPT / 4; ++i) { hq_pack[i] = 0u; yq_pack[i] = 0u; }
+      uint32_t ybf[UPT / 2];
+      // all units of the thread at once: independent (pair) chains keep the table-lookup latency covered
+      __half2 gate[4][UPT / 2];
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
-        uint32_t a[8];
-        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                     : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7])
-                     : "r"(t_row + g * HS) : "memory");
+        uint32_t a[UPT];
+        if constexpr (UPT == 8)
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                       : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7])
+                       : "r"(t_row + g * HS) : "memory");
+        else
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]) : "r"(t_row + g * HS) : "memory");
         tmem_ld_wait();
 #pragma unroll
-        for (int pr = 0; pr < 4; ++pr) {
+        for (int pr = 0; pr < UPT / 2; ++pr) {
           const uint2 bb = lds64(bias_s + (uint32_t)(g * HS + 2 * pr) * 4u);
           gate[g][pr] = __floats2half2_rn(dequant_gate((int)a[2 * pr], gi[g][2 * pr], __uint_as_float(bb.x), p.rb_scale),
                                           dequant_gate((int)a[2 * pr + 1], gi[g][2 * pr + 1], __uint_as_float(bb.y), p.rb_scale));
@@ -413,7 +443,7 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       tc_fence_before();
       if (tr) trace[t * 16 + 4] = clock64();
 #pragma unroll
-      for (int pr = 0; pr < 4; ++pr) {
+      for (int pr = 0; pr < UPT / 2; ++pr) {
         const int half = pr >> 1, u = (pr & 1) * 2;
         const __half2 it_ = sigmoid_tab2(gate[0][pr], k, tab);
         const __half2 ft_ = sigmoid_tab2(gate[1][pr], k, tab);
@@ -434,21 +464,23 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
       }
       // ---- c: final value to the caller's array, otherwise to the CTA-private blocked scratch (coalesced 512 B per warp)
       const bool last = t + 1 == steps;
-      const uint4 cv = make_uint4(cbits[0], cbits[1], cbits[2], cbits[3]);
+      CVec cv;
+#pragma unroll
+      for (int i = 0; i < UPT / 2; ++i) cv.w[i] = cbits[i];
       if (last) {
-        if (valid) *reinterpret_cast<uint4*>(p.cx + (size_t)n * REC_H + j0) = cv;
+        if (valid) st_c(p.cx + (size_t)n * REC_H + j0, cv);
       } else if (carry) {
         cn = cv;
       } else {
-        *reinterpret_cast<uint4*>(c_scratch(bt)) = cv;
+        st_c(c_scratch(bt), cv);
       }
       // ---- stage h_{t+1} and y[t] as [unit quad][row] so that four warps can write whole 32 / 64-byte row segments.
       // The staging buffer is one item deep: wait until the storing warps have read the previous item out of it.
       if (!mbar_wait(outfree_bar, (item & 1u) ^ 1u, p.status)) break;
       const uint32_t out_h = smem_out, out_y = out_h + S::OUT_H;
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const uint32_t slot = (uint32_t)((ug * 2 + half) * REC_BM + row);
+      for (int half = 0; half < UPT / 4; ++half) {
+        const uint32_t slot = (uint32_t)((ug * (UPT / 4) + half) * REC_BM + row);
         sts32(out_h + slot * 4u, hq_pack[half]);
         if (p.skip_quant_y) sts64(out_y + slot * 8u, ybf[half * 2], ybf[half * 2 + 1]);
         else sts32(out_y + slot * 4u, yq_pack[half]);
@@ -470,9 +502,10 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
   if (warp == 2) { tc_fence_after(); tmem_dealloc<2 * S::UMMA_N>(tmem_base); }
 }
 
-#define RNNT_REC_INST(CS)                                                                                            \
-  template __global__ void lstm_recurrent_kernel<CS>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
-                                                     const __grid_constant__ CUtensorMap, const RecParams);
-RNNT_REC_INST(1) RNNT_REC_INST(2) RNNT_REC_INST(4) RNNT_REC_INST(8)
+#define RNNT_REC_INST(CS, HS)                                                                                            \
+  template __global__ void lstm_recurrent_kernel<CS, HS>(const __grid_constant__ CUtensorMap, const __grid_constant__ CUtensorMap, \
+                                                         const __grid_constant__ CUtensorMap, const RecParams);
+RNNT_REC_INST(1, 32) RNNT_REC_INST(2, 32) RNNT_REC_INST(4, 32) RNNT_REC_INST(8, 32)
+RNNT_REC_INST(1, 16) RNNT_REC_INST(2, 16) RNNT_REC_INST(4, 16) RNNT_REC_INST(8, 16)
 
 }  // namespace rnnt
