@@ -749,10 +749,11 @@ static int rec_run(const int32_t* G, int g_blocked, const int8_t* w_hh, const fl
     uint32_t box[2] = {128, REC_BM};
     if (int r = make_tmap(&th0, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, hx, dims, str, box)) return r;
   }
-  {   // h ping-pong, K-chunk-major: rows of 128 B, one 128-row chunk = 16 KB contiguous
+  {   // h ping-pong, K-chunk-major: rows of 128 B, one 128-row chunk = 16 KB contiguous, stored 128-byte-swizzled by the
+      // kernel itself (read back with one bulk copy per chunk; this map, without swizzle, serves the multicast variants)
     uint64_t dims[2] = {128, (uint64_t)(2 * n_pad * REC_KC)}, str[1] = {128};
     uint32_t box[2] = {128, REC_BM};
-    if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, h_buf, dims, str, box)) return r;
+    if (int r = make_tmap(&th, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, h_buf, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return r;
   }
   // ---- deal the batch tiles to the grid's tile groups.  Cost model from the traces (profiles/r02): a work item costs a CTA
   // ~8K cycles of throughput, but one (tile, step) dependency chain is ~16K cycles long, so a group with 1 or 2 tiles in

@@ -56,7 +56,7 @@ __global__ void rec_copy_h1_kernel(const int8_t* __restrict__ h_buf, int8_t* __r
   for (int i = threadIdx.x; i < REC_KC * REC_BM * 8; i += blockDim.x) {      // 16-byte pieces: [chunk 8][row 128][8]
     const int kc = i / (REC_BM * 8), row = (i / 8) % REC_BM, part = i % 8;
     const int n = b * REC_BM + row;
-    if (n < N) reinterpret_cast<uint4*>(hx + (size_t)n * REC_H + kc * 128)[part] = src[i];
+    if (n < N) reinterpret_cast<uint4*>(hx + (size_t)n * REC_H + kc * 128)[part] = src[(i & ~7) | (part ^ (row & 7))];   // chunks are stored 128-byte-swizzled
   }
 }
 

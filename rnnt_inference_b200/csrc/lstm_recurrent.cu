@@ -205,7 +205,10 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
             if (CS == 1) tma_load_2d(dst, &tmap_h0, bar, kc * 128, bt * REC_BM);
             else tma_load_2d_mc(dst, &tmap_h0, bar, kc * 128, bt * REC_BM, MC_MASK);
           } else {
-            if (CS == 1) tma_load_2d(dst, &tmap_h, bar, 0, hrow0 + kc * REC_BM);
+            // the ping-pong buffer holds every 16 KB chunk in the 128-byte-swizzled order the UMMA descriptor expects (the
+            // storing warps write it that way), so a chunk is ONE contiguous bulk copy; clusters multicast it through a
+            // tensor map without swizzle
+            if (CS == 1) bulk_load_1d(dst, p.h_buf + (size_t)(hrow0 + kc * REC_BM) * 128, S::H_CHUNK, bar);
             else tma_load_2d_mc(dst, &tmap_h, bar, 0, hrow0 + kc * REC_BM, MC_MASK);
           }
         }
@@ -287,10 +290,11 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         // A tile that runs a single step keeps its final h in the ping-pong buffer too: other slice CTAs may still be
         // reading h_0 from hx (nothing orders t = 0 across CTAs); rec_copy_h1_kernel moves it to hx after the launch.
         if (!last || t == 0) {
-          uint4* hn = reinterpret_cast<uint4*>(p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + slice / SPC) * REC_BM + row) * 128 +
-                                               (slice % SPC) * HS);
+          // 16-byte unit u of a row goes to position u ^ (row & 7): the shared-memory image of SWIZZLE_128B
+          uint4* hn = reinterpret_cast<uint4*>(p.h_buf + ((((size_t)((t + 1) & 1) * p.num_btiles + bt) * REC_KC + slice / SPC) * REC_BM + row) * 128);
+          const int u0 = (slice % SPC) * (HS / 16);
 #pragma unroll
-          for (int i = 0; i < QUADS / 4; ++i) hn[i] = make_uint4(hw[r][4 * i], hw[r][4 * i + 1], hw[r][4 * i + 2], hw[r][4 * i + 3]);
+          for (int i = 0; i < QUADS / 4; ++i) hn[(u0 + i) ^ (row & 7)] = make_uint4(hw[r][4 * i], hw[r][4 * i + 1], hw[r][4 * i + 2], hw[r][4 * i + 3]);
         } else if (n < p.N) {   // last step of this tile: hand the state back to the caller's hx
           uint4* hp = reinterpret_cast<uint4*>(p.hx + (size_t)n * REC_H + slice * HS);
 #pragma unroll
