@@ -110,17 +110,19 @@ constexpr int REC_GRID_Y = 4;        // batch-tile groups: 32 slices x 4 = 128 C
 
 // HS = hidden units per slice CTA.  32 (UMMA N = 128; 32 slices x 4 tile groups) is the throughput configuration.  16 (UMMA
 // N = 64; 64 slices x 2 tile groups) serves batches of <= 4 tiles, where every tile group runs ONE dependency chain per
-// timestep: half the W slice leaves room for 7 ring slots instead of 3 (the h ingest is bound by bytes in flight,
-// profiles/r02/rec_trace_chain_mode.txt), and a thread's gate math covers 4 units instead of 8.
+// timestep: a thread's gate math covers 4 units instead of 8, and half the W slice leaves room for 32 KB ring slots, i.e.
+// half as many wait / commit hand-shakes of the MMA warp per item (profiles/r02/rec_trace_chain_mode.txt).
 template <int HS>
 struct RecSmemT {
-  static constexpr int NS = HS == 32 ? 3 : 7;             // stages of the h operand ring (16 KB each)
+  static constexpr int CPS = HS == 32 ? 1 : 2;            // 16 KB K-chunks per ring slot: one wait / commit hand-shake of the MMA warp per slot
+  static constexpr int NS = 3;                            // slots of the h operand ring (16 | 32 KB each)
   static constexpr int UMMA_N = 4 * HS;                   // 128 | 64
   static constexpr int UPT = HS / 4;                      // hidden units per epilogue thread: 8 | 4
   static constexpr int W_CHUNK = UMMA_N * 128;            // bytes per K-chunk of the weight slice (16 | 8 KB)
   static constexpr int W_BYTES = REC_KC * W_CHUNK;        // 128 | 64 KB
   static constexpr int H_CHUNK = REC_BM * 128;            // 16 KB
-  static constexpr int H_BYTES = NS * H_CHUNK;            // 48 | 112 KB
+  static constexpr int SLOT = CPS * H_CHUNK;              // 16 | 32 KB
+  static constexpr int H_BYTES = NS * SLOT;               // 48 | 96 KB
   static constexpr int OUT_OFFSET = W_BYTES + H_BYTES;    // staging of h (int8) and y (int8 | bf16) rows, one item deep;
   static constexpr int OUT_H = 8 * REC_BM * 4;            // [unit quad][row] 4 B  = 4 KB     (the rcp LUT lives here during set-up)
   static constexpr int OUT_Y = 8 * REC_BM * 8;            // [unit quad][row] 8 B  = 8 KB

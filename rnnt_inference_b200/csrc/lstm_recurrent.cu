@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(REC_THREADS, 1)
 lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_h0,
                       const __grid_constant__ CUtensorMap tmap_h, const RecParams p) {
   using S = RecSmemT<HS>;
-  constexpr int NS = S::NS;
+  constexpr int NS = S::NS, CPS = S::CPS;
   constexpr int UPT = S::UPT;              // hidden units per epilogue thread (8 | 4), processed as pairs
   constexpr int SPC = 128 / HS;            // slices per 128-byte K chunk of the h tile (4 | 8)
   constexpr uint16_t MC_MASK = (uint16_t)((1u << CS) - 1u);
@@ -193,23 +193,30 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         }
         if (tracer && cur.i == 0) trace[t * 16 + 0] = clock64();
         const int hrow0 = (((t & 1) * p.num_btiles + bt) * REC_KC) * REC_BM;   // row of chunk 0 in the chunk-major h buffer
-        for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
+        for (int kd = 0; kd < REC_KC / CPS; ++kd, ++chunk) {          // `chunk` counts ring slots (CPS K-chunks each)
           const uint32_t st = chunk % NS, ph = (chunk / NS) & 1u;
-          // the stage is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
+          // the slot is free in EVERY CTA of the cluster once this barrier flips (multicast commits)
           if (!mbar_wait(empty_bar + 8 * st, ph ^ 1u, p.status)) { ok = false; break; }
           if (RNNT_DBG(p, 4)) { mbar_arrive(full_bar + 8 * st); continue; }
-          mbar_expect_tx(full_bar + 8 * st, S::H_CHUNK);
-          if (CS > 1 && (uint32_t)(kc % CS) != cta_rank) continue;
-          const uint32_t dst = smem_h + st * S::H_CHUNK, bar = full_bar + 8 * st;
-          if (t == 0) {              // h_0 straight from the caller's [N][1024] array (rows >= N read as zero)
-            if (CS == 1) tma_load_2d(dst, &tmap_h0, bar, kc * 128, bt * REC_BM);
-            else tma_load_2d_mc(dst, &tmap_h0, bar, kc * 128, bt * REC_BM, MC_MASK);
-          } else {
+          mbar_expect_tx(full_bar + 8 * st, S::SLOT);
+          const uint32_t dst = smem_h + st * S::SLOT, bar = full_bar + 8 * st;
+          if (t > 0 && CS == 1) {
             // the ping-pong buffer holds every 16 KB chunk in the 128-byte-swizzled order the UMMA descriptor expects (the
-            // storing warps write it that way), so a chunk is ONE contiguous bulk copy; clusters multicast it through a
-            // tensor map without swizzle
-            if (CS == 1) bulk_load_1d(dst, p.h_buf + (size_t)(hrow0 + kc * REC_BM) * 128, S::H_CHUNK, bar);
-            else tma_load_2d_mc(dst, &tmap_h, bar, 0, hrow0 + kc * REC_BM, MC_MASK);
+            // storing warps write it that way) and the chunks of a tile follow each other, so a slot is ONE contiguous bulk
+            // copy; clusters multicast chunk by chunk through a tensor map without swizzle
+            bulk_load_1d(dst, p.h_buf + (size_t)(hrow0 + kd * CPS * REC_BM) * 128, S::SLOT, bar);
+            continue;
+          }
+#pragma unroll
+          for (int c = 0; c < CPS; ++c) {
+            const int kc = kd * CPS + c;
+            if (CS > 1 && (uint32_t)(kc % CS) != cta_rank) continue;
+            if (t == 0) {            // h_0 straight from the caller's [N][1024] array (rows >= N read as zero)
+              if (CS == 1) tma_load_2d(dst + c * S::H_CHUNK, &tmap_h0, bar, kc * 128, bt * REC_BM);
+              else tma_load_2d_mc(dst + c * S::H_CHUNK, &tmap_h0, bar, kc * 128, bt * REC_BM, MC_MASK);
+            } else {
+              tma_load_2d_mc(dst + c * S::H_CHUNK, &tmap_h, bar, 0, hrow0 + kc * REC_BM, MC_MASK);
+            }
           }
         }
         have = cur.next(p.T, my_tiles, s_tile, s_steps);
@@ -229,18 +236,22 @@ lstm_recurrent_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_c
         if (mtr) trace[cur.t * 16 + 8] = clock64() - c0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * S::UMMA_N;
-        for (int kc = 0; kc < REC_KC; ++kc, ++chunk) {
+        for (int kd = 0; kd < REC_KC / CPS; ++kd, ++chunk) {
           const uint32_t st = chunk % NS, ph = (chunk / NS) & 1u;
           if (mtr) c0 = clock64();
           if (!mbar_wait(full_bar + 8 * st, ph, p.status)) { ok = false; break; }
           if (mtr) w_full += clock64() - c0;
-          if (kc == 0 && tracer && cur.i == 0) trace[cur.t * 16 + 1] = clock64();
+          if (kd == 0 && tracer && cur.i == 0) trace[cur.t * 16 + 1] = clock64();
           tc_fence_after();
-          const uint64_t adesc = umma_desc_sw128(smem_h + st * S::H_CHUNK);
-          const uint64_t bdesc = umma_desc_sw128(smem_w + kc * S::W_CHUNK);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (!RNNT_DBG(p, 1)) umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) != 0);
+          for (int c = 0; c < CPS; ++c) {
+            const int kc = kd * CPS + c;
+            const uint64_t adesc = umma_desc_sw128(smem_h + st * S::SLOT + c * S::H_CHUNK);
+            const uint64_t bdesc = umma_desc_sw128(smem_w + kc * S::W_CHUNK);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (!RNNT_DBG(p, 1)) umma_i8(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kc | k) != 0);
+          }
           if (CS == 1) umma_commit(empty_bar + 8 * st);
           else umma_commit_mc(empty_bar + 8 * st, MC_MASK);
         }
